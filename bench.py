@@ -1,0 +1,285 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of b200reduce (driver contract: see the task statement).
+
+Metric  : reduction throughput in decimal GB/s, the number the reference prints as
+          "Reduction, Throughput = %.4f GB/s" (cuda/C/src/reduction/reduction.cpp:744-745) and plots as the CUDA lines
+          of its figures (mpi/makePlots.gp:17-19): int32 SUM over 2^24 elements per GPU (reduction.cpp:665 default).
+Step    : ONE full reduction to a scalar.
+          N = 1 : one launch of the sm_100a kernel family on one of several rotating inputs (total > 4x L2, so every
+                  step streams from HBM, never from the 126 MB L2).
+          N > 1 : weak scaling — every GPU owns 2^24 elements; one fused kernel per GPU reduces the local shard and
+                  combines the P partials at root over NVLink (b2r_reduce_scalar_sharded; the vendored simpleMultiGPU
+                  does this with a host loop, simpleMultiGPU.cpp:264-293). value = N * bytes * K / max-over-ranks time.
+e2e     : the same metric through the public Python API on HOST data: every step copies its 64 MiB input from pinned
+          host memory (chunked, copy engine overlapped with the reduction kernels) and reads the scalar back.
+Reference arm (--impl reference): the UNMODIFIED reference sample built from baseline/_ref (see baseline/README.md),
+          run through its own CLI; its stock code path times 100 iterations on ONE L2-resident buffer.
+
+Prints exactly one JSON line on rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import re
+import subprocess
+import sys
+import time
+
+REPO = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, REPO)
+
+N_ELEMS = 1 << 24  # the SDK sample's default workload (reduction.cpp:665)
+BASELINE_GBS = 90.8413  # CUDA reduction, int, SUM (mpi/CUdata.txt:6)
+METRIC = "reduction_throughput_int32_sum_2p24"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=2000)
+    ap.add_argument("--warmup", type=int, default=50)
+    ap.add_argument("--impl", default="b2r", choices=["b2r", "reference"])
+    ap.add_argument("--e2e-steps", type=int, default=0, help="steps of the end-to-end arm (default min(steps, 40))")
+    ap.add_argument("--dtype", default="int32", choices=["int32", "float32", "float64", "bfloat16"])
+    ap.add_argument("--op", default="sum", choices=["sum", "min", "max"])
+    ap.add_argument("--n", type=int, default=N_ELEMS)
+    return ap.parse_args()
+
+
+def dist_env():
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", str(rank)))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    return rank, local_rank, world
+
+
+# --------------------------------------------------------------------------------------------- reference arm
+def run_reference(args) -> None:
+    rank, local_rank, world = dist_env()
+    exe = os.path.join(REPO, "baseline", "_ref", "bin", "reduction")
+    out = {"impl": "reference"}
+    if not os.path.exists(exe):
+        build = os.path.join(REPO, "baseline", "build_reference.sh")
+        if os.path.exists(build) and os.path.isdir(os.path.join(REPO, "baseline", "_ref", "src")):
+            subprocess.run(["bash", build], capture_output=True)
+    if not os.path.exists(exe):
+        if rank == 0:
+            out["unavailable"] = "baseline/_ref/bin/reduction missing (reference sample not installed; see DESIGN.md)"
+            print(json.dumps(out), flush=True)
+        return
+    import torch
+
+    if world > 1:
+        import torch.distributed as dist
+
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    typ = {"int32": "int", "float32": "float", "float64": "double"}.get(args.dtype)
+    if typ is None:
+        if rank == 0:
+            print(json.dumps({"impl": "reference", "unavailable": "the reference has no bf16 path"}), flush=True)
+        return
+    # The reference's stock path: fixed 100 timed iterations after one warm-up (reduction.cpp:729-738); --steps/--warmup
+    # cannot be passed to it, they are reported as what it actually ran. --n is a power of two by its own rule.
+    cmd = [exe, f"--method={args.op.upper()}", f"--type={typ}", f"--n={args.n}", f"--device={local_rank}", "--noprompt"]
+    if world > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    res = subprocess.run(cmd, capture_output=True, text=True, cwd=os.path.dirname(exe))
+    wall = time.perf_counter() - t0
+    m = re.search(r"Throughput = ([0-9.]+) GB/s, Time = ([0-9.]+) s", res.stdout)
+    passed = "PASSED" in res.stdout
+    gbs = float(m.group(1)) if m else 0.0
+    sec = float(m.group(2)) if m else 0.0
+    if world > 1:
+        # the reference has no multi-GPU reduction; N ranks each run the unmodified sample on their own shard and the
+        # job-level rate is N * bytes / slowest rank (the cross-GPU combine, a host loop in simpleMultiGPU.cpp:287-291,
+        # is not part of its timed region either).
+        t = torch.tensor([sec], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ok = torch.tensor([1 if passed else 0], device="cuda")
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        sec = t.item()
+        passed = bool(ok.item())
+        esz = {"int32": 4, "float32": 4, "float64": 8}[args.dtype]
+        gbs = world * args.n * esz / sec * 1e-9 if sec > 0 else 0.0
+    if rank == 0:
+        out.update({
+            "metric": METRIC, "value": gbs, "unit": "GB/s", "n_gpus": world, "steps": 100, "warmup": 1,
+            "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": gbs / BASELINE_GBS if gbs else None, "dtype": args.dtype, "data": "synthetic (rand()&0xFF, the sample's own generator)",
+            "config": {"model": "SDK reduction sample (reference, unmodified) recompiled for sm_100", "elements_per_gpu": args.n,
+                       "op": args.op, "parallelism": f"dp{world}" if world > 1 else "single-gpu",
+                       "timing": "reference's own host stopwatch around sync+2 launches+sync; one L2-resident buffer (stock path)"},
+            "self_check": "PASSED" if passed else "FAILED", "wall_s": wall,
+        })
+        if not m:
+            out["unavailable"] = "reference binary produced no throughput line: " + (res.stdout[-200:] + res.stderr[-200:]).replace("\n", " ")
+        print(json.dumps(out), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+# --------------------------------------------------------------------------------------------- our arm
+def run_b2r(args) -> None:
+    import torch
+
+    import cuda_mpi_reductions_b200 as b2r
+    from cuda_mpi_reductions_b200.utils import ClockSampler, rotating_copies
+
+    rank, local_rank, world = dist_env()
+    if args.gpus != world and world > 1 and rank == 0:
+        print(f"warning: --gpus {args.gpus} but WORLD_SIZE={world}; using WORLD_SIZE", file=sys.stderr)
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (run it through gpurun)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    dtype = getattr(torch, args.dtype)
+    esz = torch.empty((), dtype=dtype).element_size()
+    nbytes = args.n * esz
+    steps, warmup = args.steps, max(args.warmup, 3)
+
+    comm = None
+    if world > 1:
+        import torch.distributed as dist
+
+        from cuda_mpi_reductions_b200.parallel import Communicator
+
+        dist.init_process_group("nccl", device_id=dev)
+        comm = Communicator.from_torch_distributed()
+
+    copies = rotating_copies(nbytes)
+    big = torch.empty(copies * args.n, dtype=dtype, device=dev)
+    inputs = [big[c * args.n:(c + 1) * args.n] for c in range(copies)]
+    for c, t in enumerate(inputs):
+        b2r.fill_device(args.n, dtype, seed=1000 * rank + c, mode="sdk", out=t)
+    out = torch.empty((), dtype=dtype, device=dev)
+    ws = b2r.Workspace(dev)
+
+    if comm is None:
+        def step(i):
+            b2r.reduce(inputs[i % copies], args.op, out=out, workspace=ws)
+    else:
+        def step(i):
+            comm.reduce_scalar_sharded(inputs[i % copies], args.op, root=0, out=out)
+
+    # correctness of what is being timed (cheap: one step per distinct input, against the CPU oracle)
+    step(0)
+    torch.cuda.synchronize()
+    if comm is None:
+        want = b2r.reduce_oracle(inputs[0].cpu(), args.op)
+        assert out.cpu().item() == want.item(), f"self-check failed: got {out.item()} want {want.item()}"
+    else:
+        import torch.distributed as dist
+
+        local = b2r.reduce_oracle(inputs[0].cpu(), args.op).to(dev).to(torch.int64 if dtype == torch.int32 else dtype)
+        dist.all_reduce(local, op={"sum": dist.ReduceOp.SUM, "min": dist.ReduceOp.MIN, "max": dist.ReduceOp.MAX}[args.op])
+        if rank == 0:
+            w = local.item()
+            if dtype == torch.int32:
+                w = (w + 2**31) % 2**32 - 2**31
+                assert out.item() == w, f"self-check failed: got {out.item()} want {w}"
+            else:
+                assert abs(out.item() - w) <= 1e-5 * abs(w) + 1e-6, f"self-check failed: got {out.item()} want {w}"
+
+    sampler = ClockSampler(local_rank).start() if rank == 0 else None
+    for i in range(warmup):
+        step(i)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t_start = time.perf_counter()
+    ev0.record()
+    for i in range(steps):
+        step(i)
+    ev1.record()
+    torch.cuda.synchronize()
+    t_end = time.perf_counter()
+    if world > 1:
+        dist.barrier()
+    ms = ev0.elapsed_time(ev1)
+    if world > 1:
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = t.item()
+    clocks = sampler.summary(t_start, t_end) if sampler else None
+
+    # ---- end-to-end arm: host (pinned) -> device copy of every step's input + scalar back on the host
+    e2e_steps = args.e2e_steps or max(3, min(steps, 40))
+    host_copies = 2
+    host_in = [b2r.fill_host(args.n, dtype, seed=77 + 1000 * rank + c, mode="sdk", pin_memory=True) for c in range(host_copies)]
+    if comm is None:
+        def e2e_step(i):
+            return b2r.reduce_from_host(host_in[i % host_copies], args.op, device=dev, workspace=ws)
+    else:
+        def e2e_step(i):
+            return comm.reduce_scalar_sharded_from_host(host_in[i % host_copies], args.op, root=0)
+    want_e2e = b2r.reduce_oracle(host_in[0], args.op)
+    for i in range(3):
+        r = e2e_step(i)
+    if comm is None:
+        assert e2e_step(0).item() == want_e2e.item(), "e2e self-check failed"
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for i in range(e2e_steps):
+        r = e2e_step(i)  # synchronous: returns the scalar on the host
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([e2e_s], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = t.item()
+    chunk_bytes = int(os.environ.get("B2R_H2D_CHUNK_MB", "8")) << 20
+    nchunks = -(-nbytes // chunk_bytes)
+    acc_sz = 8 if dtype == torch.float64 else 4
+
+    if sampler:
+        sampler.stop()
+    if rank == 0:
+        total_bytes = world * nbytes
+        value = total_bytes * steps / (ms * 1e-3) * 1e-9
+        e2e_value = total_bytes * e2e_steps / e2e_s * 1e-9
+        peaks = {}
+        try:
+            with open(os.path.join(REPO, "MEASURED_PEAKS.json")) as f:
+                peaks = json.load(f)
+        except Exception:
+            pass
+        hbm = peaks.get("hbm_gbs", 6650.0)
+        line = {
+            "metric": METRIC, "value": value, "unit": "GB/s", "n_gpus": world, "steps": steps, "warmup": warmup,
+            "ms_per_step": ms / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": value / BASELINE_GBS,
+            "dtype": args.dtype, "data": "synthetic (counter-based generator, SDK-style values 0..255)",
+            "config": {"model": "SDK reduction sample workload (single-pass scalar reduction)", "elements_per_gpu": args.n, "op": args.op,
+                       "global_elements": world * args.n, "parallelism": f"dp{world} (sharded scalar reduce to root over NVLink)" if world > 1 else "single-gpu",
+                       "cache_control": f"{copies} rotating inputs of {nbytes >> 20} MiB (total {copies * nbytes >> 20} MiB > 4x L2)",
+                       "geometry": b2r.plan(args.n, dtype, args.op, device=local_rank)},
+            "clocks": clocks,
+            "e2e": {"value": e2e_value, "unit": "GB/s", "h2d_bytes_per_step": nbytes, "d2h_bytes_per_step": nchunks * acc_sz,
+                    "steps": e2e_steps, "ms_per_step": e2e_s * 1e3 / e2e_steps,
+                    "api": "cuda_mpi_reductions_b200.reduce_from_host(pinned_tensor)" if comm is None else "Communicator.reduce_scalar_sharded_from_host(pinned_tensor)"},
+            "gpu_launches": steps,
+            "hbm_fraction_of_measured": value / world / hbm,
+            "impl": "b2r",
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        comm.close()
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b2r(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,266 @@
+// reduce_kernels.cuh — the single-GPU kernel family (one launch, arbitrary 64-bit n, deterministic).
+//
+// Pipeline of one launch (replaces sumreduce6/minreduce6/maxreduce6 + the second in-place pass,
+// reduction_kernel.cu:74-253 and reduction.cpp:344-357, and generalises the vendored single-pass
+// threadFenceReduction, threadFenceReduction_kernel.cu:116-171):
+//   stream   : every CTA owns one contiguous, 128-byte-aligned slice of the body and streams it either with
+//              unrolled 128/256-bit LDGs (reduce_ldg_kernel) or with a cp.async.bulk ring fed by one producer
+//              lane (reduce_tma_kernel); head/tail elements that do not fill a vector are folded in by CTA 0.
+//   warp     : redux.sync (int32, fp32 min/max) or shfl.sync butterflies.
+//   block    : one shared-memory hop, warp 0 finishes.
+//   cluster  : (optional) non-leader CTAs store their partial into the leader's shared memory (DSMEM),
+//              barrier.cluster, leader combines in rank order.
+//   grid     : leader stores the partial, takes a ticket with atom.acq_rel.gpu; the last arriver re-reduces all
+//              partials in index order, writes the scalar and re-arms the ticket.
+#pragma once
+#include <cooperative_groups.h>
+
+#include "primitives.cuh"
+
+namespace b2r {
+
+namespace cg = cooperative_groups;
+
+// TMA variant: every consumer thread owns this many 16-byte vectors of a tile (tile = consumers x 4 x 16 bytes).
+constexpr int kTmaVecsPerThread = 4;
+
+struct LocalParams {
+  const void* in;             // element-aligned base pointer
+  void* out;                  // one element of the input dtype
+  uint64_t n;                 // elements
+  uint64_t head;              // scalar elements before the first aligned vector
+  uint64_t nvec;              // vectors (16 or 32 bytes) in the body
+  uint64_t tail;              // scalar elements after the body
+  void* partials;             // acc_t[gridDim.x / cluster]
+  unsigned* ticket;           // zero between launches
+  unsigned long long* trace;  // nullable: 4 stamps per CTA
+  void* mailbox;              // nullable: see scalar-sharded collective (unused here)
+  int stages;                 // TMA ring depth
+  int tile_vecs;              // TMA tile size in 16-byte vectors
+  int out_as_acc;             // store the scalar as acc_t (fp32 for bf16) instead of the input dtype
+};
+
+// CTA c of G gets vectors [split(c), split(c+1)); boundaries are multiples of `align` vectors (128 bytes).
+__device__ __forceinline__ uint64_t split_point(uint64_t nvec, unsigned G, unsigned c, unsigned align) {
+  if (c >= G) return nvec;
+  // nvec < 2^60 / 16 and c < 2^16: the product fits comfortably in 64 bits for any addressable buffer
+  uint64_t s = (nvec / G) * c + ((nvec % G) * c) / G;
+  return s - (s % align);
+}
+
+template <class R>
+__device__ __forceinline__ void store_result(const LocalParams& p, typename R::acc_t v) {
+  if (p.out_as_acc) *(typename R::acc_t*)p.out = v;
+  else R::store(p.out, v);
+}
+
+// Everything after the streaming loop. `tv` is the per-thread value.
+template <class R, bool CLUSTER>
+__device__ __forceinline__ void finish_block(typename R::acc_t tv, const LocalParams& p) {
+  using acc_t = typename R::acc_t;
+  using F = typename R::F;
+  __shared__ acc_t s_scratch[32];
+  __shared__ acc_t s_cluster[8];
+  __shared__ int s_is_last;
+
+  acc_t v = block_reduce<R>(tv, s_scratch);
+  if (p.trace && threadIdx.x == 0) p.trace[4 * blockIdx.x + 2] = globaltimer_ns();
+
+  unsigned nparts = gridDim.x, part = blockIdx.x;
+  if (CLUSTER) {
+    cg::cluster_group cluster = cg::this_cluster();
+    const unsigned cr = cluster.block_rank(), cs = cluster.num_blocks();
+    if (threadIdx.x == 0) {
+      acc_t* leader = cluster.map_shared_rank(s_cluster, 0);  // DSMEM address in the leader CTA
+      leader[cr] = v;
+    }
+    cluster.sync();  // barrier.cluster.arrive.release + wait.acquire
+    if (cr != 0) return;
+    if (threadIdx.x == 0) {
+      v = s_cluster[0];
+      for (unsigned i = 1; i < cs; ++i) v = F::apply(v, s_cluster[i]);
+    }
+    nparts = gridDim.x / cs;
+    part = blockIdx.x / cs;
+  }
+
+  if (nparts == 1) {
+    if (threadIdx.x == 0) {
+      store_result<R>(p, v);
+      if (p.trace) p.trace[4 * blockIdx.x + 3] = globaltimer_ns();
+    }
+    return;
+  }
+
+  acc_t* partials = (acc_t*)p.partials;
+  if (threadIdx.x == 0) {
+    partials[part] = v;
+    // release our partial, acquire everybody else's if we turn out to be last
+    unsigned t = atom_add_acq_rel_gpu(p.ticket, 1u);
+    s_is_last = (t == nparts - 1);
+  }
+  __syncthreads();
+  if (!s_is_last) {
+    if (p.trace && threadIdx.x == 0) p.trace[4 * blockIdx.x + 3] = globaltimer_ns();
+    return;
+  }
+  acc_t a = F::identity();
+  for (unsigned i = threadIdx.x; i < nparts; i += blockDim.x) a = F::apply(a, ld_cg(partials + i));
+  a = block_reduce<R>(a, s_scratch);
+  if (threadIdx.x == 0) {
+    store_result<R>(p, a);
+    *p.ticket = 0;  // re-arm for the next (stream-ordered) launch
+    if (p.trace) p.trace[4 * blockIdx.x + 3] = globaltimer_ns();
+  }
+}
+
+// Head/tail scalars (fewer than one vector each) are folded in by CTA 0.
+template <class R>
+__device__ __forceinline__ void add_edges(typename R::Thread& acc, const LocalParams& p, uint64_t body_elems) {
+  if (blockIdx.x != 0) return;
+  const uint64_t edge = p.head + p.tail;
+  for (uint64_t i = threadIdx.x; i < edge; i += blockDim.x) {
+    const uint64_t idx = i < p.head ? i : p.head + body_elems + (i - p.head);
+    acc.add_elem(p.in, idx);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ LDG variant
+template <int D, int O, int VECW, int UNROLL, bool CLUSTER>
+__global__ void __launch_bounds__(512) reduce_ldg_kernel(const __grid_constant__ LocalParams p) {
+  using R = Reducer<D, O>;
+  using Vec = typename std::conditional<VECW == 8, V32, V16>::type;
+  constexpr unsigned kAlign = 128 / sizeof(Vec);
+
+  if (p.trace && threadIdx.x == 0) p.trace[4 * blockIdx.x + 0] = globaltimer_ns();
+
+  typename R::Thread acc;
+  acc.init();
+
+  const Vec* __restrict__ vp = (const Vec*)((const char*)p.in + p.head * R::kElemBytes);
+  const uint64_t lo = split_point(p.nvec, gridDim.x, blockIdx.x, kAlign);
+  const uint64_t hi = split_point(p.nvec, gridDim.x, blockIdx.x + 1, kAlign);
+  const unsigned nt = blockDim.x;
+
+  uint64_t i = lo + threadIdx.x;
+  // UNROLL independent vector loads are issued back to back, then consumed: UNROLL*sizeof(Vec) bytes in
+  // flight per thread.
+  for (; i + (uint64_t)(UNROLL - 1) * nt < hi; i += (uint64_t)UNROLL * nt) {
+    Vec v[UNROLL];
+#pragma unroll
+    for (int u = 0; u < UNROLL; ++u) v[u] = ldg_stream(vp + i + (uint64_t)u * nt);
+#pragma unroll
+    for (int u = 0; u < UNROLL; ++u) {
+      acc.add16(v[u].w);
+      if (VECW == 8) acc.add16(v[u].w + 4);
+    }
+  }
+  for (; i < hi; i += nt) {
+    Vec v = ldg_stream(vp + i);
+    acc.add16(v.w);
+    if (VECW == 8) acc.add16(v.w + 4);
+  }
+  add_edges<R>(acc, p, p.nvec * (sizeof(Vec) / R::kElemBytes));
+  if (p.trace && threadIdx.x == 0) p.trace[4 * blockIdx.x + 1] = globaltimer_ns();
+
+  finish_block<R, CLUSTER>(acc.collapse(), p);
+}
+
+// ------------------------------------------------------------------------------------------------ TMA (bulk-copy) variant
+// Warp 0 is the producer: one elected lane keeps `stages` cp.async.bulk transfers in flight into a shared-memory
+// ring (full/empty mbarriers). Warps 1.. are consumers: conflict-free LDS.128 + register accumulate. No register
+// is tied up by data in flight, so few resident threads suffice to cover the HBM latency-bandwidth product.
+template <int D, int O, bool CLUSTER>
+__global__ void __launch_bounds__(512) reduce_tma_kernel(const __grid_constant__ LocalParams p) {
+  using R = Reducer<D, O>;
+  extern __shared__ __align__(128) unsigned char smem[];
+
+  if (p.trace && threadIdx.x == 0) p.trace[4 * blockIdx.x + 0] = globaltimer_ns();
+
+  const int stages = p.stages;
+  const uint32_t tile_vecs = (uint32_t)p.tile_vecs;
+  const uint32_t tile_bytes = tile_vecs * 16u;
+  const uint32_t ring = smem_u32(smem);
+  const uint32_t bars = ring + (uint32_t)stages * tile_bytes;  // full[stages], empty[stages]
+  const unsigned warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const unsigned ncw = (blockDim.x >> 5) - 1;  // consumer warps
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < stages; ++s) {
+      mbar_init(bars + 8u * s, 1u);               // producer's arrive.expect_tx
+      mbar_init(bars + 8u * (stages + s), ncw);   // one arrive per consumer warp
+    }
+    mbar_fence_init();
+  }
+  __syncthreads();
+
+  typename R::Thread acc;
+  acc.init();
+
+  const V16* __restrict__ vp = (const V16*)((const char*)p.in + p.head * R::kElemBytes);
+  const uint64_t lo = split_point(p.nvec, gridDim.x, blockIdx.x, 8);
+  const uint64_t hi = split_point(p.nvec, gridDim.x, blockIdx.x + 1, 8);
+  const uint64_t nv = hi - lo;
+  const uint64_t ntiles = (nv + tile_vecs - 1) / tile_vecs;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int s = 0;
+      uint32_t k = 0;  // how many times the ring has wrapped
+      for (uint64_t t = 0; t < ntiles; ++t) {
+        mbar_wait(bars + 8u * (stages + s), (k & 1u) ^ 1u);  // slot free (passes immediately on first use)
+        const uint64_t off = t * tile_vecs;
+        const uint32_t vecs = (uint32_t)min((uint64_t)tile_vecs, nv - off);
+        mbar_arrive_expect_tx(bars + 8u * s, vecs * 16u);
+        bulk_g2s(ring + (uint32_t)s * tile_bytes, vp + lo + off, vecs * 16u, bars + 8u * s);
+        if (++s == stages) { s = 0; ++k; }
+      }
+    }
+    __syncwarp();
+  } else {
+    const unsigned ct = threadIdx.x - 32, nct = blockDim.x - 32;
+    int s = 0;
+    uint32_t k = 0;
+    for (uint64_t t = 0; t < ntiles; ++t) {
+      mbar_wait(bars + 8u * s, k & 1u);  // bytes have landed
+      const uint64_t off = t * tile_vecs;
+      const uint32_t vecs = (uint32_t)min((uint64_t)tile_vecs, nv - off);
+      const uint32_t base = ring + (uint32_t)s * tile_bytes;
+      if (vecs == tile_vecs) {
+        // full tile: kTmaVecsPerThread conflict-free LDS.128 issued back to back, then consumed
+        V16 v[kTmaVecsPerThread];
+#pragma unroll
+        for (int u = 0; u < kTmaVecsPerThread; ++u) v[u] = lds128(base + (ct + (uint32_t)u * nct) * 16u);
+#pragma unroll
+        for (int u = 0; u < kTmaVecsPerThread; ++u) acc.add16(v[u].w);
+      } else {
+        for (uint32_t j = ct; j < vecs; j += nct) {
+          V16 v = lds128(base + j * 16u);
+          acc.add16(v.w);
+        }
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bars + 8u * (stages + s));  // slot may be refilled
+      if (++s == stages) { s = 0; ++k; }
+    }
+  }
+  add_edges<R>(acc, p, p.nvec * (16 / R::kElemBytes));
+  if (p.trace && threadIdx.x == 0) p.trace[4 * blockIdx.x + 1] = globaltimer_ns();
+
+  finish_block<R, CLUSTER>(acc.collapse(), p);
+}
+
+// ------------------------------------------------------------------------------------------------ host-side launcher (per dtype TU)
+struct LaunchGeom {
+  int variant;   // b2r_variant_t (resolved, never AUTO)
+  int threads;
+  int ctas;
+  int cluster;   // >= 1
+  int unroll;    // 4 or 8
+  int smem_bytes;
+};
+
+template <int D>
+b2r_status_t launch_local(int op, const LaunchGeom& g, const LocalParams& p, cudaStream_t stream);
+
+}  // namespace b2r

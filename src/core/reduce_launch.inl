@@ -1,0 +1,76 @@
+// reduce_launch.inl — included by one translation unit per dtype (parallel builds); instantiates the kernel
+// matrix {op} x {LDG128, LDG256} x {unroll 4, 8} x {cluster, no cluster} + {TMA} x {cluster, no cluster} and the
+// switch that picks one. This is the counterpart of the reference's switch(threads) template dispatch
+// (reduction_kernel.cu:263-346), keyed on what matters on sm_100a instead of on a power-of-two block size.
+#include <mutex>
+#include <set>
+
+#include "../util/check.h"
+#include "reduce_kernels.cuh"
+
+namespace b2r {
+namespace {
+
+using KernelFn = void (*)(const LocalParams);
+
+template <int D, int O, bool CL>
+KernelFn pick_kernel(const LaunchGeom& g) {
+  switch (g.variant) {
+    case B2R_VARIANT_LDG128:
+      return g.unroll == 8 ? (KernelFn)reduce_ldg_kernel<D, O, 4, 8, CL> : (KernelFn)reduce_ldg_kernel<D, O, 4, 4, CL>;
+    case B2R_VARIANT_LDG256:
+      // (8 x 256-bit loads per thread makes ptxas serialise load->use; 4 in flight = 128 B/thread is the useful maximum)
+      return (KernelFn)reduce_ldg_kernel<D, O, 8, 4, CL>;
+    case B2R_VARIANT_TMA:
+      return (KernelFn)reduce_tma_kernel<D, O, CL>;
+  }
+  return nullptr;
+}
+
+template <int D, int O>
+b2r_status_t launch_op(const LaunchGeom& g, const LocalParams& p, cudaStream_t stream) {
+  KernelFn k = g.cluster > 1 ? pick_kernel<D, O, true>(g) : pick_kernel<D, O, false>(g);
+  if (!k) return fail(B2R_ERR_INVALID, "launch_local: bad variant %d", g.variant);
+  if (g.smem_bytes > 48 * 1024) {
+    // opt in to large dynamic shared memory once per (kernel, device)
+    static std::mutex mu;
+    static std::set<std::pair<const void*, int>> done;
+    int dev = 0;
+    B2R_CUDA_CHECK(cudaGetDevice(&dev));
+    std::lock_guard<std::mutex> lk(mu);
+    if (!done.count({(const void*)k, dev})) {
+      B2R_CUDA_CHECK(cudaFuncSetAttribute((const void*)k, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+      done.insert({(const void*)k, dev});
+    }
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)g.ctas);
+  cfg.blockDim = dim3((unsigned)g.threads);
+  cfg.dynamicSmemBytes = (size_t)g.smem_bytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  if (g.cluster > 1) {
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = (unsigned)g.cluster;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+  }
+  B2R_CUDA_CHECK(cudaLaunchKernelEx(&cfg, k, p));
+  return B2R_OK;
+}
+
+}  // namespace
+
+template <>
+b2r_status_t launch_local<B2R_LAUNCH_DTYPE>(int op, const LaunchGeom& g, const LocalParams& p, cudaStream_t stream) {
+  switch (op) {
+    case B2R_SUM: return launch_op<B2R_LAUNCH_DTYPE, B2R_SUM>(g, p, stream);
+    case B2R_MIN: return launch_op<B2R_LAUNCH_DTYPE, B2R_MIN>(g, p, stream);
+    case B2R_MAX: return launch_op<B2R_LAUNCH_DTYPE, B2R_MAX>(g, p, stream);
+  }
+  return fail(B2R_ERR_INVALID, "launch_local: bad op %d", op);
+}
+
+}  // namespace b2r

@@ -1,0 +1,357 @@
+// reduce_local.cu — host side of the single-GPU reduction: workspace, launch planning, public entry points.
+// Counterpart of the reference's host wrappers sumreduce/minreduce/maxreduce (reduction_kernel.cu:263-524) and of
+// getNumBlocksAndThreads (reduction.cpp:272-291). Differences by design: no power-of-two restriction, 64-bit
+// counts, one launch instead of a multi-pass loop, geometry sized to the machine (k CTAs per SM, persistent).
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+#include "../util/check.h"
+#include "b2r.h"
+#include "reduce_kernels.cuh"
+#include "workspace.h"
+
+namespace b2r {
+
+namespace {
+
+int env_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  if (!v || !*v) return dflt;
+  return atoi(v);
+}
+
+struct Tuned {
+  int variant, threads, ctas_per_sm, cluster, unroll, stages, tile_bytes;
+};
+
+// Defaults measured on B200 (see profiles/local_sweep.md); every field can be overridden per call through
+// b2r_launch_cfg_t or globally through B2R_VARIANT / B2R_THREADS / B2R_CTAS_PER_SM / B2R_CLUSTER / B2R_UNROLL /
+// B2R_STAGES / B2R_TILE_BYTES.
+Tuned tuned_defaults(b2r_dtype_t dtype, b2r_op_t op) {
+  (void)op;
+  Tuned t;
+  t.variant = B2R_VARIANT_LDG128;
+  t.threads = 512;
+  t.ctas_per_sm = 4;  // for the TMA variant threads includes the producer warp
+  t.cluster = 1;
+  t.unroll = 4;
+  t.stages = 4;
+  t.tile_bytes = 16384;
+  if (dtype == B2R_FLOAT64) t.unroll = 4;
+  return t;
+}
+
+}  // namespace
+
+b2r_status_t plan_local(uint64_t count, b2r_dtype_t dtype, b2r_op_t op, int sm_count, const b2r_launch_cfg_t* hint,
+                        LaunchGeom* g, int* stages, int* tile_vecs) {
+  const uint64_t bytes = count * b2r_dtype_size(dtype);
+  Tuned t = tuned_defaults(dtype, op);
+  t.variant = env_int("B2R_VARIANT", t.variant);
+  t.threads = env_int("B2R_THREADS", t.threads);
+  t.ctas_per_sm = env_int("B2R_CTAS_PER_SM", t.ctas_per_sm);
+  t.cluster = env_int("B2R_CLUSTER", t.cluster);
+  t.unroll = env_int("B2R_UNROLL", t.unroll);
+  t.stages = env_int("B2R_STAGES", t.stages);
+  t.tile_bytes = env_int("B2R_TILE_BYTES", t.tile_bytes);
+
+  int variant = t.variant, threads = t.threads, cluster = t.cluster, unroll = t.unroll;
+  int st = t.stages, tile_bytes = t.tile_bytes;
+  int ctas = 0;
+  if (hint) {
+    if (hint->variant) variant = hint->variant;
+    if (hint->threads) threads = hint->threads;
+    if (hint->cluster) cluster = hint->cluster;
+    if (hint->unroll) unroll = hint->unroll;
+    if (hint->stages) st = hint->stages;
+    if (hint->tile_bytes) tile_bytes = hint->tile_bytes;
+    ctas = hint->ctas;
+  }
+  B2R_REQUIRE(variant >= B2R_VARIANT_LDG128 && variant <= B2R_VARIANT_TMA, "plan: bad variant %d", variant);
+  B2R_REQUIRE(threads >= 32 && threads <= 512 && threads % 32 == 0, "plan: threads=%d must be a multiple of 32 in [32,512]", threads);
+  B2R_REQUIRE(cluster == 1 || cluster == 2 || cluster == 4 || cluster == 8, "plan: cluster=%d must be 1,2,4 or 8", cluster);
+  B2R_REQUIRE(unroll == 4 || unroll == 8, "plan: unroll=%d must be 4 or 8", unroll);
+  if (variant == B2R_VARIANT_LDG256) unroll = 4;
+  if (variant == B2R_VARIANT_TMA) {
+    B2R_REQUIRE(threads >= 64, "plan: the TMA variant needs a producer warp and at least one consumer warp");
+    B2R_REQUIRE(st >= 1 && st <= 32, "plan: stages=%d out of range", st);
+    tile_bytes = (threads - 32) * 16 * kTmaVecsPerThread;  // derived: every consumer thread owns 4 vectors of a tile
+    B2R_REQUIRE((uint64_t)st * tile_bytes + 16ull * st <= 220 * 1024, "plan: ring of %d x %d bytes exceeds shared memory", st, tile_bytes);
+  }
+
+  const bool explicit_ctas = ctas > 0;
+  if (!explicit_ctas) {
+    // Small inputs: one CTA per ~32 KiB so that the ticket stage does not dominate; a single CTA (no ticket, no
+    // partials) below 64 KiB. Large inputs: persistent grid, ctas_per_sm CTAs on every SM.
+    const uint64_t min_bytes_per_cta = 32 * 1024;
+    uint64_t want = (bytes + min_bytes_per_cta - 1) / min_bytes_per_cta;
+    if (bytes <= 64 * 1024) want = 1;
+    uint64_t cap = (uint64_t)sm_count * (uint64_t)std::max(1, t.ctas_per_sm);
+    ctas = (int)std::max<uint64_t>(1, std::min<uint64_t>(want, cap));
+    if (ctas == 1) {
+      cluster = 1;
+      if (bytes <= 8 * 1024) threads = std::min(threads, 128);
+      else threads = std::min(threads, 256);
+      if (variant == B2R_VARIANT_TMA) threads = std::max(threads, 64);
+    }
+  }
+  B2R_REQUIRE(ctas >= 1 && ctas <= kMaxCtas, "plan: ctas=%d out of range [1,%d]", ctas, kMaxCtas);
+  if (cluster > 1) {
+    if (ctas < cluster) cluster = 1;
+    else ctas -= ctas % cluster;
+  }
+  g->variant = variant;
+  g->threads = threads;
+  g->ctas = ctas;
+  g->cluster = cluster;
+  g->unroll = unroll;
+  g->smem_bytes = variant == B2R_VARIANT_TMA ? st * tile_bytes + 16 * st : 0;
+  *stages = st;
+  *tile_vecs = tile_bytes / 16;
+  return B2R_OK;
+}
+
+template <int D>
+b2r_status_t launch_local(int op, const LaunchGeom& g, const LocalParams& p, cudaStream_t stream);
+
+b2r_status_t launch_any(b2r_dtype_t dtype, int op, const LaunchGeom& g, const LocalParams& p, cudaStream_t stream) {
+  switch (dtype) {
+    case B2R_INT32: return launch_local<B2R_INT32>(op, g, p, stream);
+    case B2R_FLOAT32: return launch_local<B2R_FLOAT32>(op, g, p, stream);
+    case B2R_FLOAT64: return launch_local<B2R_FLOAT64>(op, g, p, stream);
+    case B2R_BFLOAT16: return launch_local<B2R_BFLOAT16>(op, g, p, stream);
+  }
+  return fail(B2R_ERR_INVALID, "bad dtype %d", (int)dtype);
+}
+
+// Fills head/nvec/tail for a given vector width.
+void split_edges(const void* in, uint64_t count, size_t esz, unsigned vec_bytes, LocalParams* p) {
+  const uintptr_t addr = (uintptr_t)in;
+  uint64_t head = ((vec_bytes - (addr % vec_bytes)) % vec_bytes) / esz;
+  if (head > count) head = count;
+  const uint64_t body_bytes = (count - head) * esz;
+  p->head = head;
+  p->nvec = body_bytes / vec_bytes;
+  p->tail = count - head - p->nvec * (vec_bytes / esz);
+}
+
+b2r_status_t reduce_local_impl(const void* in, void* out, uint64_t count, b2r_dtype_t dtype, b2r_op_t op,
+                               b2r_workspace* ws, cudaStream_t stream, const b2r_launch_cfg_t* cfg, int out_as_acc) {
+  B2R_REQUIRE(ws != nullptr, "b2r_reduce_local: workspace is NULL");
+  B2R_REQUIRE(out != nullptr, "b2r_reduce_local: out is NULL");
+  B2R_REQUIRE(in != nullptr || count == 0, "b2r_reduce_local: in is NULL");
+  B2R_REQUIRE(dtype >= B2R_INT32 && dtype <= B2R_BFLOAT16, "b2r_reduce_local: bad dtype %d", (int)dtype);
+  B2R_REQUIRE(op >= B2R_SUM && op <= B2R_MAX, "b2r_reduce_local: bad op %d", (int)op);
+  const size_t esz = b2r_dtype_size(dtype);
+  B2R_REQUIRE(((uintptr_t)in % esz) == 0, "b2r_reduce_local: input pointer %p is not aligned to the element size %zu", in, esz);
+
+  LaunchGeom g;
+  LocalParams p;
+  memset(&p, 0, sizeof(p));
+  int stages = 0, tile_vecs = 0;
+  B2R_CHECK(plan_local(count, dtype, op, ws->sm_count, cfg, &g, &stages, &tile_vecs));
+  p.in = in;
+  p.out = out;
+  p.n = count;
+  split_edges(in, count, esz, g.variant == B2R_VARIANT_LDG256 ? 32u : 16u, &p);
+  p.partials = ws->d_partials;
+  p.ticket = ws->d_ticket;
+  p.trace = ws->trace_enabled ? ws->d_trace : nullptr;
+  p.stages = stages;
+  p.tile_vecs = tile_vecs;
+  p.out_as_acc = out_as_acc;
+  ws->last_ctas = g.ctas;
+  ws->last_geom[0] = g.variant;
+  ws->last_geom[1] = g.threads;
+  ws->last_geom[2] = g.ctas;
+  ws->last_geom[3] = g.cluster;
+  return launch_any(dtype, (int)op, g, p, stream);
+}
+
+}  // namespace b2r
+
+using namespace b2r;
+
+extern "C" {
+
+b2r_status_t b2r_workspace_create(b2r_workspace_t* out, int device) {
+  B2R_REQUIRE(out != nullptr, "b2r_workspace_create: out is NULL");
+  int prev = 0;
+  B2R_CUDA_CHECK(cudaGetDevice(&prev));
+  B2R_CUDA_CHECK(cudaSetDevice(device));
+  b2r_workspace* ws = new b2r_workspace();
+  ws->device = device;
+  cudaError_t e = cudaDeviceGetAttribute(&ws->sm_count, cudaDevAttrMultiProcessorCount, device);
+  if (e == cudaSuccess) e = cudaMalloc(&ws->d_partials, (size_t)kMaxCtas * 8);
+  if (e == cudaSuccess) e = cudaMalloc((void**)&ws->d_ticket, 256);
+  if (e == cudaSuccess) e = cudaMemset(ws->d_ticket, 0, 256);
+  if (e == cudaSuccess) e = cudaMalloc((void**)&ws->d_trace, (size_t)kMaxCtas * 4 * sizeof(unsigned long long));
+  if (e == cudaSuccess) e = cudaMemset(ws->d_trace, 0, (size_t)kMaxCtas * 4 * sizeof(unsigned long long));
+  if (e == cudaSuccess) e = cudaDeviceSynchronize();
+  cudaSetDevice(prev);
+  if (e != cudaSuccess) {
+    b2r_workspace_destroy(ws);
+    return fail(B2R_ERR_CUDA, "b2r_workspace_create(device %d): %s", device, cudaGetErrorString(e));
+  }
+  *out = ws;
+  return B2R_OK;
+}
+
+b2r_status_t b2r_workspace_destroy(b2r_workspace_t ws) {
+  if (!ws) return B2R_OK;
+  int prev = 0;
+  cudaGetDevice(&prev);
+  cudaSetDevice(ws->device);
+  if (ws->d_partials) cudaFree(ws->d_partials);
+  if (ws->d_ticket) cudaFree(ws->d_ticket);
+  if (ws->d_trace) cudaFree(ws->d_trace);
+  for (int i = 0; i < kStageBufs; ++i) {
+    if (ws->d_stage[i]) cudaFree(ws->d_stage[i]);
+    if (ws->ev_copied[i]) cudaEventDestroy(ws->ev_copied[i]);
+    if (ws->ev_consumed[i]) cudaEventDestroy(ws->ev_consumed[i]);
+  }
+  if (ws->d_chunk_out) cudaFree(ws->d_chunk_out);
+  if (ws->h_chunk_out) cudaFreeHost(ws->h_chunk_out);
+  if (ws->copy_stream) cudaStreamDestroy(ws->copy_stream);
+  cudaSetDevice(prev);
+  delete ws;
+  return B2R_OK;
+}
+
+b2r_status_t b2r_reduce_local(const void* in, void* out, uint64_t count, b2r_dtype_t dtype, b2r_op_t op,
+                              b2r_workspace_t ws, void* stream) {
+  return reduce_local_impl(in, out, count, dtype, op, ws, (cudaStream_t)stream, nullptr, 0);
+}
+
+b2r_status_t b2r_reduce_local_ex(const void* in, void* out, uint64_t count, b2r_dtype_t dtype, b2r_op_t op,
+                                 b2r_workspace_t ws, void* stream, const b2r_launch_cfg_t* cfg) {
+  return reduce_local_impl(in, out, count, dtype, op, ws, (cudaStream_t)stream, cfg, 0);
+}
+
+b2r_status_t b2r_plan_local(uint64_t count, b2r_dtype_t dtype, b2r_op_t op, int device, const b2r_launch_cfg_t* hint,
+                            b2r_launch_cfg_t* chosen) {
+  B2R_REQUIRE(chosen != nullptr, "b2r_plan_local: chosen is NULL");
+  B2R_REQUIRE(dtype >= B2R_INT32 && dtype <= B2R_BFLOAT16, "b2r_plan_local: bad dtype %d", (int)dtype);
+  int sm = 148;  // B200; used when no device is present (planning is a pure function of the SM count)
+  if (device >= 0) {
+    int v = 0;
+    if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, device) == cudaSuccess && v > 0) sm = v;
+    else cudaGetLastError();
+  }
+  LaunchGeom g;
+  int stages = 0, tile_vecs = 0;
+  B2R_CHECK(plan_local(count, dtype, op, sm, hint, &g, &stages, &tile_vecs));
+  memset(chosen, 0, sizeof(*chosen));
+  chosen->variant = g.variant;
+  chosen->threads = g.threads;
+  chosen->ctas = g.ctas;
+  chosen->cluster = g.cluster;
+  chosen->unroll = g.unroll;
+  chosen->stages = stages;
+  chosen->tile_bytes = tile_vecs * 16;
+  return B2R_OK;
+}
+
+b2r_status_t b2r_workspace_trace_enable(b2r_workspace_t ws, int enable) {
+  B2R_REQUIRE(ws != nullptr, "workspace is NULL");
+  ws->trace_enabled = enable != 0;
+  return B2R_OK;
+}
+
+b2r_status_t b2r_workspace_trace_read(b2r_workspace_t ws, uint64_t* stamps, int max_ctas, int* n_ctas) {
+  B2R_REQUIRE(ws != nullptr && stamps != nullptr && n_ctas != nullptr, "b2r_workspace_trace_read: NULL argument");
+  int n = std::min(ws->last_ctas, max_ctas);
+  int prev = 0;
+  B2R_CUDA_CHECK(cudaGetDevice(&prev));
+  B2R_CUDA_CHECK(cudaSetDevice(ws->device));
+  cudaError_t e = cudaMemcpy(stamps, ws->d_trace, (size_t)n * 4 * sizeof(uint64_t), cudaMemcpyDeviceToHost);
+  cudaSetDevice(prev);
+  if (e != cudaSuccess) return fail(B2R_ERR_CUDA, "trace_read: %s", cudaGetErrorString(e));
+  *n_ctas = n;
+  return B2R_OK;
+}
+
+// Pipelined host -> device + reduce. The host array is cut into chunks; chunk i is copied by the copy engine on a
+// private stream while chunk i-1 is being reduced on `stream`; per-chunk scalars (in accumulator precision) are
+// combined on the host in chunk order, so bf16 is still rounded only once.
+b2r_status_t b2r_reduce_from_host(const void* host_in, void* out_host, uint64_t count, b2r_dtype_t dtype, b2r_op_t op,
+                                  b2r_workspace_t ws, void* stream_) {
+  B2R_REQUIRE(ws != nullptr && out_host != nullptr, "b2r_reduce_from_host: NULL argument");
+  B2R_REQUIRE(host_in != nullptr || count == 0, "b2r_reduce_from_host: host_in is NULL");
+  B2R_REQUIRE(dtype >= B2R_INT32 && dtype <= B2R_BFLOAT16, "bad dtype %d", (int)dtype);
+  B2R_REQUIRE(op >= B2R_SUM && op <= B2R_MAX, "bad op %d", (int)op);
+  cudaStream_t stream = (cudaStream_t)stream_;
+  const size_t esz = b2r_dtype_size(dtype);
+  const size_t acc_sz = dtype == B2R_FLOAT64 ? 8 : 4;
+  const b2r_dtype_t acc_dtype = dtype == B2R_BFLOAT16 ? B2R_FLOAT32 : dtype;
+  int prev = 0;
+  B2R_CUDA_CHECK(cudaGetDevice(&prev));
+  B2R_CUDA_CHECK(cudaSetDevice(ws->device));
+  struct Restore { int d; ~Restore() { cudaSetDevice(d); } } restore{prev};
+
+  const uint64_t chunk_bytes = (uint64_t)std::max(1, env_int("B2R_H2D_CHUNK_MB", 8)) << 20;
+  const uint64_t chunk_elems = chunk_bytes / esz;
+  const uint64_t nchunks = count == 0 ? 0 : (count + chunk_elems - 1) / chunk_elems;
+  B2R_REQUIRE(nchunks <= kMaxChunks, "b2r_reduce_from_host: %llu chunks > %d; raise B2R_H2D_CHUNK_MB",
+              (unsigned long long)nchunks, kMaxChunks);
+
+  if (!ws->copy_stream) {
+    B2R_CUDA_CHECK(cudaStreamCreateWithFlags(&ws->copy_stream, cudaStreamNonBlocking));
+    B2R_CUDA_CHECK(cudaMalloc(&ws->d_chunk_out, (size_t)kMaxChunks * 8));
+    B2R_CUDA_CHECK(cudaMallocHost(&ws->h_chunk_out, (size_t)kMaxChunks * 8));
+    for (int i = 0; i < kStageBufs; ++i) {
+      B2R_CUDA_CHECK(cudaEventCreateWithFlags(&ws->ev_copied[i], cudaEventDisableTiming));
+      B2R_CUDA_CHECK(cudaEventCreateWithFlags(&ws->ev_consumed[i], cudaEventDisableTiming));
+    }
+  }
+  if (ws->stage_bytes < chunk_bytes) {
+    for (int i = 0; i < kStageBufs; ++i) {
+      if (ws->d_stage[i]) B2R_CUDA_CHECK(cudaFree(ws->d_stage[i]));
+      ws->d_stage[i] = nullptr;
+      B2R_CUDA_CHECK(cudaMalloc(&ws->d_stage[i], chunk_bytes));
+    }
+    ws->stage_bytes = chunk_bytes;
+  }
+
+  // the copy stream must not run ahead of work already queued on `stream` that may still use the staging buffers
+  B2R_CUDA_CHECK(cudaEventRecord(ws->ev_consumed[0], stream));
+  B2R_CUDA_CHECK(cudaStreamWaitEvent(ws->copy_stream, ws->ev_consumed[0], 0));
+  for (uint64_t c = 0; c < nchunks; ++c) {
+    const int b = (int)(c % kStageBufs);
+    const uint64_t first = c * chunk_elems;
+    const uint64_t n = std::min(chunk_elems, count - first);
+    if (c >= (uint64_t)kStageBufs) B2R_CUDA_CHECK(cudaStreamWaitEvent(ws->copy_stream, ws->ev_consumed[b], 0));
+    B2R_CUDA_CHECK(cudaMemcpyAsync(ws->d_stage[b], (const char*)host_in + first * esz, n * esz, cudaMemcpyHostToDevice,
+                                   ws->copy_stream));
+    B2R_CUDA_CHECK(cudaEventRecord(ws->ev_copied[b], ws->copy_stream));
+    B2R_CUDA_CHECK(cudaStreamWaitEvent(stream, ws->ev_copied[b], 0));
+    B2R_CHECK(reduce_local_impl(ws->d_stage[b], (char*)ws->d_chunk_out + c * acc_sz, n, dtype, op, ws, stream, nullptr, 1));
+    B2R_CUDA_CHECK(cudaEventRecord(ws->ev_consumed[b], stream));
+  }
+  if (nchunks) {
+    B2R_CUDA_CHECK(cudaMemcpyAsync(ws->h_chunk_out, ws->d_chunk_out, nchunks * acc_sz, cudaMemcpyDeviceToHost, stream));
+  }
+  B2R_CUDA_CHECK(cudaStreamSynchronize(stream));
+  // combine chunk scalars in chunk order (accumulator precision), then round once
+  unsigned char acc[8];
+  b2r_reduce_host(ws->h_chunk_out, acc, nchunks, acc_dtype, op);
+  if (dtype == B2R_BFLOAT16) {
+    float f;
+    memcpy(&f, acc, 4);
+    uint32_t u;
+    memcpy(&u, &f, 4);
+    uint16_t b;
+    if ((u & 0x7fffffffu) > 0x7f800000u) b = (uint16_t)((u >> 16) | 0x40u);
+    else b = (uint16_t)((u + 0x7fffu + ((u >> 16) & 1u)) >> 16);
+    memcpy(out_host, &b, 2);
+  } else {
+    memcpy(out_host, acc, esz);
+  }
+  return B2R_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,192 @@
+"""GPU: the single-GPU kernel family against the fp32/fp64 CPU oracle (W3/W4 of SURVEY §8).
+
+Matrix: dtype x op x n (incl. 0, 1, 2^k±1, non-vector-multiple), misaligned base pointers, NaN/inf,
+every kernel variant x cluster size, determinism, 64-bit sizes. Tolerances follow the reference's self-check
+(reduction.cpp:750-780: int exact, float 1e-8*n, double 1e-12) but relative to the magnitude of the data.
+"""
+import math
+
+import pytest
+import torch
+
+import cuda_mpi_reductions_b200 as b2r
+
+pytestmark = pytest.mark.gpu
+
+DTYPES = [torch.int32, torch.float32, torch.float64, torch.bfloat16]
+OPS = ["sum", "min", "max"]
+SIZES = [0, 1, 2, 3, 31, 32, 33, 255, 256, 257, 1023, 4099, 65536, 65537, (1 << 20) - 1, (1 << 20) + 7, 1 << 24]
+VARIANTS = ["ldg128", "ldg256", "tma"]
+
+
+def check(got: torch.Tensor, x_cpu: torch.Tensor, op: str):
+    want = b2r.reduce_oracle(x_cpu, op)
+    g = got.cpu()
+    n = x_cpu.numel()
+    if x_cpu.dtype == torch.int32 or op != "sum":
+        if want.is_floating_point() and math.isnan(want.item()):
+            assert math.isnan(g.item())
+        else:
+            assert g.item() == want.item(), f"{x_cpu.dtype} {op} n={n}: got {g.item()} want {want.item()}"
+        return
+    mag = x_cpu.double().abs().sum().item() if n else 0.0
+    if x_cpu.dtype == torch.float64:
+        tol = 1e-15 * max(mag, 1e-300) * max(1.0, math.log2(max(n, 2)))
+    elif x_cpu.dtype == torch.float32:
+        tol = 6e-8 * max(mag, 1e-30) * max(1.0, math.log2(max(n, 2)))
+    else:  # bf16: fp32 accumulate, ONE rounding to bf16 at the end
+        exact = x_cpu.double().sum().item()
+        tol = abs(exact) * 2.0**-8 + 6e-8 * mag * max(1.0, math.log2(max(n, 2)))
+    assert abs(g.double().item() - want.double().item()) <= tol, (
+        f"{x_cpu.dtype} {op} n={n}: got {g.item()} want {want.item()} tol {tol}")
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
+@pytest.mark.parametrize("op", OPS)
+def test_matrix_default_dispatch(dtype, op):
+    for n in SIZES:
+        x = b2r.fill_host(n, dtype, seed=n, mode="signed")
+        got = b2r.reduce(x.cuda(), op)
+        check(got, x, op)
+
+
+@pytest.mark.parametrize("variant", VARIANTS)
+@pytest.mark.parametrize("cluster", [1, 2, 8])
+@pytest.mark.parametrize("dtype", DTYPES)
+def test_variants_and_clusters(variant, cluster, dtype):
+    for n in [1, 4097, (1 << 18) + 3, (1 << 22) + 1]:
+        x = b2r.fill_host(n, dtype, seed=11 * n, mode="signed")
+        xd = x.cuda()
+        for op in OPS:
+            for threads in (128, 512):
+                got = b2r.reduce(xd, op, cfg={"variant": variant, "cluster": cluster, "threads": threads, "ctas": 64})
+                check(got, x, op)
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
+@pytest.mark.parametrize("variant", VARIANTS)
+def test_misaligned_base_pointers(dtype, variant):
+    base = b2r.fill_host((1 << 16) + 64, dtype, seed=5, mode="signed")
+    bd = base.cuda()
+    for off in [1, 2, 3, 5, 7, 9, 15]:
+        for n in [1, 17, 1000, (1 << 16)]:
+            x = base[off:off + n]
+            got = b2r.reduce(bd[off:off + n], "sum", cfg={"variant": variant})
+            check(got, x, "sum")
+            got = b2r.reduce(bd[off:off + n], "max", cfg={"variant": variant})
+            check(got, x, "max")
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float64, torch.bfloat16])
+def test_nan_inf_negzero(dtype):
+    n = (1 << 16) + 3
+    x = b2r.fill_host(n, dtype, seed=9, mode="signed")
+    for pos in [0, 1, n // 2, n - 1]:
+        y = x.clone()
+        y[pos] = float("nan")
+        for op in OPS:
+            assert math.isnan(b2r.reduce(y.cuda(), op).item()), (op, pos)
+        z = x.clone()
+        z[pos] = float("-inf")
+        assert b2r.reduce(z.cuda(), "min").item() == -math.inf
+        assert b2r.reduce(z.cuda(), "sum").item() == -math.inf
+        z[pos] = float("inf")
+        assert b2r.reduce(z.cuda(), "max").item() == math.inf
+    w = torch.zeros(1000, dtype=dtype)
+    w[3] = -0.0
+    assert b2r.reduce(w.cuda(), "sum").item() == 0.0
+
+
+def test_int_extremes_and_wrap():
+    x = torch.full(((1 << 20) + 1,), 2**31 - 1, dtype=torch.int32)
+    got = b2r.reduce(x.cuda(), "sum")
+    check(got, x, "sum")
+    x[12345] = -(2**31)
+    assert b2r.reduce(x.cuda(), "min").item() == -(2**31)
+    assert b2r.reduce(x.cuda(), "max").item() == 2**31 - 1
+    full = b2r.fill_host(1 << 22, torch.int32, seed=3, mode="full")
+    check(b2r.reduce(full.cuda(), "sum"), full, "sum")
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float64, torch.bfloat16])
+@pytest.mark.parametrize("variant", VARIANTS)
+def test_deterministic_bitwise(dtype, variant):
+    x = b2r.fill_device((1 << 24) + 13, dtype, seed=1, mode="signed")
+    first = b2r.reduce(x, "sum", cfg={"variant": variant}).clone()
+    for _ in range(20):
+        again = b2r.reduce(x, "sum", cfg={"variant": variant})
+        assert torch.equal(first.view(torch.uint8).cpu(), again.view(torch.uint8).cpu())
+
+
+def test_back_to_back_launches_reuse_ticket():
+    # the ticket is re-armed by the last CTA; 200 stream-ordered launches with different sizes must all be right
+    xs = [b2r.fill_device(n, torch.int32, seed=n, mode="full") for n in (1 << 20, (1 << 21) + 5, 77777, 1 << 22)]
+    want = [b2r.reduce_oracle(x.cpu(), "sum").item() for x in xs]
+    outs = []
+    for i in range(200):
+        outs.append(b2r.reduce(xs[i % 4], "sum"))
+    torch.cuda.synchronize()
+    for i, o in enumerate(outs):
+        assert o.item() == want[i % 4]
+
+
+def test_fill_device_matches_host():
+    for dtype in DTYPES:
+        for mode in ("sdk", "full", "signed"):
+            d = b2r.fill_device(100003, dtype, seed=42, first_index=17, mode=mode)
+            h = b2r.fill_host(100003, dtype, seed=42, first_index=17, mode=mode)
+            assert torch.equal(d.cpu().view(torch.uint8), h.view(torch.uint8)), (dtype, mode)
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
+def test_dot(dtype):
+    n = (1 << 20) + 3
+    a = b2r.fill_host(n, dtype, seed=1, mode="signed")
+    c = b2r.fill_host(n, dtype, seed=2, mode="signed")
+    got = b2r.dot(a.cuda(), c.cuda()).cpu()
+    if dtype == torch.int32:
+        want = (a.long() * c.long()).sum().item()
+        want = (want + 2**31) % 2**32 - 2**31
+        assert got.item() == want
+    else:
+        want = (a.double() * c.double()).sum().item()
+        mag = (a.double() * c.double()).abs().sum().item()
+        rel = {torch.float32: 1e-6, torch.float64: 1e-14, torch.bfloat16: 2.0**-7}[dtype]
+        assert abs(got.double().item() - want) <= rel * max(mag if dtype != torch.bfloat16 else abs(want) + 1e-2 * mag, 1e-30)
+
+
+def test_reduce_from_host_pipeline():
+    for dtype in DTYPES:
+        n = (3 << 21) + 11  # > 1 chunk for every dtype with the default 8 MiB chunk
+        x = b2r.fill_host(n, dtype, seed=8, mode="signed", pin_memory=True)
+        for op in OPS:
+            got = b2r.reduce_from_host(x, op)
+            check(got, x, op)
+
+
+def test_trace_stamps():
+    ws = b2r.Workspace()
+    ws.trace(True)
+    x = b2r.fill_device(1 << 24, torch.float32, seed=1)
+    b2r.reduce(x, "sum", workspace=ws)
+    torch.cuda.synchronize()
+    t = b2r.trace_last(ws)
+    assert t.shape[1] == 4 and t.shape[0] >= 148
+    assert (t[:, 1] >= t[:, 0]).all() and (t[:, 2] >= t[:, 1]).all() and (t[:, 3] >= t[:, 2]).all()
+
+
+@pytest.mark.slow
+def test_two_pow_30_elements_and_beyond_int32_indexing():
+    # 2^31 + 5 bf16 elements = 4 GiB: exceeds the reference's int indexing
+    n = (1 << 31) + 5
+    x = torch.ones(n, dtype=torch.bfloat16, device="cuda")
+    x[-1] = 3.0
+    assert b2r.reduce(x, "max").item() == 3.0
+    assert b2r.reduce(x, "min").item() == 1.0
+    s = b2r.reduce(x, "sum").item()
+    assert abs(s - (n + 2)) <= (n + 2) * 2.0**-8
+    del x
+    y = b2r.fill_device(1 << 30, torch.int32, seed=2, mode="sdk")
+    got = b2r.reduce(y, "sum").item()
+    want = int(y.view(-1, 1 << 20).sum(dim=1, dtype=torch.int64).sum().item())
+    assert got == (want + 2**31) % 2**32 - 2**31
