@@ -158,8 +158,14 @@ def run_b2r(args) -> None:
     out = torch.empty((), dtype=dtype, device=dev)
     ws = b2r.Workspace(dev)
 
+    # pdl=1: programmatic dependent launch — step i+1 may begin streaming its (ready, independent) input while step i is
+    # draining; every step still reads its whole input from HBM and finishes its own scalar.
+    cfg = {"pdl": 1}
     if comm is None:
         def step(i):
+            b2r.reduce(inputs[i % copies], args.op, out=out, workspace=ws, cfg=cfg)
+
+        def step_plain(i):
             b2r.reduce(inputs[i % copies], args.op, out=out, workspace=ws)
     else:
         def step(i):
@@ -206,6 +212,11 @@ def run_b2r(args) -> None:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = t.item()
     clocks = sampler.summary(t_start, t_end) if sampler else None
+    ms_plain = None
+    if comm is None:  # same loop in plain stream order (no overlap between consecutive steps), for the record
+        from cuda_mpi_reductions_b200.utils import time_steps
+
+        ms_plain = time_steps(step_plain, steps, warmup)
 
     # ---- end-to-end arm: host (pinned) -> device copy of every step's input + scalar back on the host
     e2e_steps = args.e2e_steps or max(3, min(steps, 40))
@@ -258,7 +269,8 @@ def run_b2r(args) -> None:
             "config": {"model": "SDK reduction sample workload (single-pass scalar reduction)", "elements_per_gpu": args.n, "op": args.op,
                        "global_elements": world * args.n, "parallelism": f"dp{world} (sharded scalar reduce to root over NVLink)" if world > 1 else "single-gpu",
                        "cache_control": f"{copies} rotating inputs of {nbytes >> 20} MiB (total {copies * nbytes >> 20} MiB > 4x L2)",
-                       "geometry": b2r.plan(args.n, dtype, args.op, device=local_rank)},
+                       "geometry": b2r.plan(args.n, dtype, args.op, device=local_rank, cfg=cfg),
+                       "launch": "programmatic dependent launch between consecutive steps (cfg pdl=1)"},
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": "GB/s", "h2d_bytes_per_step": nbytes, "d2h_bytes_per_step": nchunks * acc_sz,
                     "steps": e2e_steps, "ms_per_step": e2e_s * 1e3 / e2e_steps,
@@ -267,6 +279,8 @@ def run_b2r(args) -> None:
             "hbm_fraction_of_measured": value / world / hbm,
             "impl": "b2r",
         }
+        if ms_plain is not None:
+            line["value_plain_stream_order"] = total_bytes * steps / (ms_plain * 1e-3) * 1e-9
         print(json.dumps(line), flush=True)
     if world > 1:
         comm.close()

@@ -27,13 +27,14 @@ int main(int argc, char** argv) {
   const uint64_t n = (uint64_t)f.i64("n", 1 << 24);
   const int iters = (int)f.i64("iters", 50);
   const bool quick = f.has("quick");
+  const int pdl = f.has("pdl") ? 1 : 0;
   const size_t bytes = n * b2r_dtype_size(dt);
   const int copies = rotating_copies(bytes, (size_t)1 << 30);
 
   BENCH_CUDA(cudaSetDevice((int)f.i64("device", 0)));
   cudaDeviceProp prop;
   BENCH_CUDA(cudaGetDeviceProperties(&prop, 0));
-  printf("# device %s, %d SMs; %s %s n=%llu (%.1f MiB) x %d rotating copies, %d iters\n", prop.name, prop.multiProcessorCount,
+  printf("# device %s, %d SMs; pdl=%d; %s %s n=%llu (%.1f MiB) x %d rotating copies, %d iters\n", prop.name, prop.multiProcessorCount, pdl,
          b2r_dtype_name(dt), b2r_op_name(op), (unsigned long long)n, bytes / 1048576.0, copies, iters);
 
   char* d_in = nullptr;
@@ -56,6 +57,7 @@ int main(int argc, char** argv) {
     cfg.unroll = unroll;
     cfg.stages = stages;
     cfg.cluster = cluster;
+    cfg.pdl = pdl;
     for (int i = 0; i < 3; ++i) {
       if (b2r_reduce_local_ex(d_in + (i % copies) * bytes, d_out, n, dt, op, ws, nullptr, &cfg) != B2R_OK) return;
     }

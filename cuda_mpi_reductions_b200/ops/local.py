@@ -138,7 +138,7 @@ def plan(n: int, dtype: torch.dtype, op="sum", device: int = -1, cfg=None) -> di
     _lib.check(st, "b2r_plan_local")
     names = {v: k for k, v in _lib.VARIANTS.items()}
     return {"variant": names[chosen.variant], "threads": chosen.threads, "ctas": chosen.ctas, "cluster": chosen.cluster,
-            "unroll": chosen.unroll, "stages": chosen.stages, "tile_bytes": chosen.tile_bytes}
+            "unroll": chosen.unroll, "stages": chosen.stages, "tile_bytes": chosen.tile_bytes, "pdl": chosen.pdl}
 
 
 def trace_last(workspace: Workspace, max_ctas: int = 4096) -> torch.Tensor:

@@ -66,7 +66,10 @@ typedef struct {
   int stages;      /* TMA ring depth; 0 = auto */
   int tile_bytes;  /* TMA tile bytes (multiple of 16*32*consumer warps); 0 = auto */
   int unroll;      /* LDG loads in flight per thread: 4 or 8; 0 = auto */
-  int reserved;
+  int pdl;         /* 1 = programmatic dependent launch: this launch may start streaming its input while the previous
+                      kernel in the stream is still finishing (it waits before touching the workspace / out). Only safe
+                      when the input is NOT produced by a kernel that signals programmatic completion early; back-to-back
+                      reductions of ready inputs are the intended use. 0 = plain stream order (default). */
 } b2r_launch_cfg_t;
 
 size_t b2r_dtype_size(b2r_dtype_t dtype);

@@ -38,6 +38,7 @@ struct LocalParams {
   int stages;                 // TMA ring depth
   int tile_vecs;              // TMA tile size in 16-byte vectors
   int out_as_acc;             // store the scalar as acc_t (fp32 for bf16) instead of the input dtype
+  int pdl;                    // launched with programmatic stream serialization (see b2r_launch_cfg_t.pdl)
 };
 
 // CTA c of G gets vectors [split(c), split(c+1)); boundaries are multiples of `align` vectors (128 bytes).
@@ -46,6 +47,16 @@ __device__ __forceinline__ uint64_t split_point(uint64_t nvec, unsigned G, unsig
   // nvec < 2^60 / 16 and c < 2^16: the product fits comfortably in 64 bits for any addressable buffer
   uint64_t s = (nvec / G) * c + ((nvec % G) * c) / G;
   return s - (s % align);
+}
+
+// Programmatic dependent launch: let the next kernel of the stream start while we are still running ...
+__device__ __forceinline__ void pdl_launch_dependents(const LocalParams& p) {
+  if (p.pdl) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+// ... and, as the dependent, wait for the previous kernel (and the visibility of its writes) before touching
+// anything it may still be using: the shared workspace (partials, ticket) and `out`.
+__device__ __forceinline__ void pdl_wait_prior(const LocalParams& p) {
+  if (p.pdl) asm volatile("griddepcontrol.wait;" ::: "memory");
 }
 
 template <class R>
@@ -64,6 +75,7 @@ __device__ __forceinline__ void finish_block(typename R::acc_t tv, const LocalPa
   __shared__ int s_is_last;
 
   acc_t v = block_reduce<R>(tv, s_scratch);
+  pdl_wait_prior(p);
   if (p.trace && threadIdx.x == 0) p.trace[4 * blockIdx.x + 2] = globaltimer_ns();
 
   unsigned nparts = gridDim.x, part = blockIdx.x;
@@ -132,6 +144,7 @@ __global__ void __launch_bounds__(512) reduce_ldg_kernel(const __grid_constant__
   using Vec = typename std::conditional<VECW == 8, V32, V16>::type;
   constexpr unsigned kAlign = 128 / sizeof(Vec);
 
+  pdl_launch_dependents(p);
   if (p.trace && threadIdx.x == 0) p.trace[4 * blockIdx.x + 0] = globaltimer_ns();
 
   typename R::Thread acc;
@@ -175,6 +188,7 @@ __global__ void __launch_bounds__(512) reduce_tma_kernel(const __grid_constant__
   using R = Reducer<D, O>;
   extern __shared__ __align__(128) unsigned char smem[];
 
+  pdl_launch_dependents(p);
   if (p.trace && threadIdx.x == 0) p.trace[4 * blockIdx.x + 0] = globaltimer_ns();
 
   const int stages = p.stages;
@@ -258,6 +272,7 @@ struct LaunchGeom {
   int cluster;   // >= 1
   int unroll;    // 4 or 8
   int smem_bytes;
+  int pdl;
 };
 
 template <int D>

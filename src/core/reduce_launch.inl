@@ -12,6 +12,8 @@ namespace b2r {
 namespace {
 
 using KernelFn = void (*)(const LocalParams);
+// 227 KiB is the per-CTA opt-in limit on sm_100; the kernels also use <1 KiB of static shared memory.
+constexpr int kMaxDynSmem = 226 * 1024;
 
 template <int D, int O, bool CL>
 KernelFn pick_kernel(const LaunchGeom& g) {
@@ -39,7 +41,7 @@ b2r_status_t launch_op(const LaunchGeom& g, const LocalParams& p, cudaStream_t s
     B2R_CUDA_CHECK(cudaGetDevice(&dev));
     std::lock_guard<std::mutex> lk(mu);
     if (!done.count({(const void*)k, dev})) {
-      B2R_CUDA_CHECK(cudaFuncSetAttribute((const void*)k, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+      B2R_CUDA_CHECK(cudaFuncSetAttribute((const void*)k, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem));
       done.insert({(const void*)k, dev});
     }
   }
@@ -48,15 +50,22 @@ b2r_status_t launch_op(const LaunchGeom& g, const LocalParams& p, cudaStream_t s
   cfg.blockDim = dim3((unsigned)g.threads);
   cfg.dynamicSmemBytes = (size_t)g.smem_bytes;
   cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
+  unsigned na = 0;
   if (g.cluster > 1) {
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = (unsigned)g.cluster;
-    attr[0].val.clusterDim.y = 1;
-    attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = 1;
+    attr[na].id = cudaLaunchAttributeClusterDimension;
+    attr[na].val.clusterDim.x = (unsigned)g.cluster;
+    attr[na].val.clusterDim.y = 1;
+    attr[na].val.clusterDim.z = 1;
+    ++na;
   }
+  if (g.pdl) {
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  cfg.attrs = na ? attr : nullptr;
+  cfg.numAttrs = na;
   B2R_CUDA_CHECK(cudaLaunchKernelEx(&cfg, k, p));
   return B2R_OK;
 }

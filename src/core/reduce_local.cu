@@ -28,20 +28,37 @@ struct Tuned {
   int variant, threads, ctas_per_sm, cluster, unroll, stages, tile_bytes;
 };
 
-// Defaults measured on B200 (see profiles/local_sweep.md); every field can be overridden per call through
+// Defaults measured on B200 (profiles/local_sweep.md); every field can be overridden per call through
 // b2r_launch_cfg_t or globally through B2R_VARIANT / B2R_THREADS / B2R_CTAS_PER_SM / B2R_CLUSTER / B2R_UNROLL /
-// B2R_STAGES / B2R_TILE_BYTES.
-Tuned tuned_defaults(b2r_dtype_t dtype, b2r_op_t op) {
+// B2R_STAGES / B2R_PDL.
+//  * >= 256 MiB: the bulk-copy (TMA) ring wins by ~4% (7.0 vs 6.76 TB/s at 1 GiB): 4 consumer warps, 3 CTAs/SM,
+//    4 stages of 8 KiB -> 96 KiB in flight per SM without spending registers on it.
+//  * smaller inputs are dominated by launch/ramp/tail (~7 us fixed): plain stream order likes many resident
+//    threads (512 x 4 per SM); with programmatic dependent launch ONE CTA per SM is best, because the next
+//    kernel's CTAs can become resident while this one drains (9.25 us vs 16.4 us per 64 MiB launch).
+Tuned tuned_defaults(b2r_dtype_t dtype, b2r_op_t op, uint64_t bytes, int pdl) {
   (void)op;
+  (void)dtype;
   Tuned t;
-  t.variant = B2R_VARIANT_LDG128;
-  t.threads = 512;
-  t.ctas_per_sm = 4;  // for the TMA variant threads includes the producer warp
   t.cluster = 1;
   t.unroll = 4;
-  t.stages = 4;
-  t.tile_bytes = 16384;
-  if (dtype == B2R_FLOAT64) t.unroll = 4;
+  t.tile_bytes = 0;
+  if (bytes >= (256ull << 20)) {
+    t.variant = B2R_VARIANT_TMA;
+    t.threads = 160;
+    t.ctas_per_sm = 3;
+    t.stages = 4;
+  } else if (pdl) {
+    t.variant = B2R_VARIANT_TMA;
+    t.threads = 288;
+    t.ctas_per_sm = 1;
+    t.stages = 4;
+  } else {
+    t.variant = B2R_VARIANT_LDG128;
+    t.threads = 512;
+    t.ctas_per_sm = 4;
+    t.stages = 4;
+  }
   return t;
 }
 
@@ -50,14 +67,20 @@ Tuned tuned_defaults(b2r_dtype_t dtype, b2r_op_t op) {
 b2r_status_t plan_local(uint64_t count, b2r_dtype_t dtype, b2r_op_t op, int sm_count, const b2r_launch_cfg_t* hint,
                         LaunchGeom* g, int* stages, int* tile_vecs) {
   const uint64_t bytes = count * b2r_dtype_size(dtype);
-  Tuned t = tuned_defaults(dtype, op);
+  int pdl = env_int("B2R_PDL", 0);
+  if (hint && hint->pdl) pdl = hint->pdl > 0;
+  Tuned t = tuned_defaults(dtype, op, bytes, pdl);
+  if (hint && hint->variant && hint->variant != t.variant) {
+    // a forced variant keeps its own sensible geometry
+    if (hint->variant == B2R_VARIANT_TMA) { t.threads = pdl ? 288 : 160; t.ctas_per_sm = pdl ? 1 : 3; t.stages = 4; }
+    else { t.threads = 512; t.ctas_per_sm = pdl ? 1 : 4; }
+  }
   t.variant = env_int("B2R_VARIANT", t.variant);
   t.threads = env_int("B2R_THREADS", t.threads);
   t.ctas_per_sm = env_int("B2R_CTAS_PER_SM", t.ctas_per_sm);
   t.cluster = env_int("B2R_CLUSTER", t.cluster);
   t.unroll = env_int("B2R_UNROLL", t.unroll);
   t.stages = env_int("B2R_STAGES", t.stages);
-  t.tile_bytes = env_int("B2R_TILE_BYTES", t.tile_bytes);
 
   int variant = t.variant, threads = t.threads, cluster = t.cluster, unroll = t.unroll;
   int st = t.stages, tile_bytes = t.tile_bytes;
@@ -90,7 +113,10 @@ b2r_status_t plan_local(uint64_t count, b2r_dtype_t dtype, b2r_op_t op, int sm_c
     const uint64_t min_bytes_per_cta = 32 * 1024;
     uint64_t want = (bytes + min_bytes_per_cta - 1) / min_bytes_per_cta;
     if (bytes <= 64 * 1024) want = 1;
-    uint64_t cap = (uint64_t)sm_count * (uint64_t)std::max(1, t.ctas_per_sm);
+    int cps = std::max(1, t.ctas_per_sm);
+    if (variant == B2R_VARIANT_TMA) cps = std::max(1, std::min(cps, (220 * 1024) / (st * tile_bytes + 16 * st + 1024)));
+    cps = std::max(1, std::min(cps, 2048 / threads));
+    uint64_t cap = (uint64_t)sm_count * (uint64_t)cps;
     ctas = (int)std::max<uint64_t>(1, std::min<uint64_t>(want, cap));
     if (ctas == 1) {
       cluster = 1;
@@ -109,6 +135,7 @@ b2r_status_t plan_local(uint64_t count, b2r_dtype_t dtype, b2r_op_t op, int sm_c
   g->ctas = ctas;
   g->cluster = cluster;
   g->unroll = unroll;
+  g->pdl = pdl ? 1 : 0;
   g->smem_bytes = variant == B2R_VARIANT_TMA ? st * tile_bytes + 16 * st : 0;
   *stages = st;
   *tile_vecs = tile_bytes / 16;
@@ -164,6 +191,15 @@ b2r_status_t reduce_local_impl(const void* in, void* out, uint64_t count, b2r_dt
   p.stages = stages;
   p.tile_vecs = tile_vecs;
   p.out_as_acc = out_as_acc;
+  // never overlap with the previous launch if this input could be that launch's output scalar
+  if (g.pdl && ws->last_out) {
+    const char* lo = (const char*)in;
+    const char* hi = lo + count * esz;
+    const char* o = (const char*)ws->last_out;
+    if (o + 8 > lo && o < hi) g.pdl = 0;
+  }
+  p.pdl = g.pdl;
+  ws->last_out = out;
   ws->last_ctas = g.ctas;
   ws->last_geom[0] = g.variant;
   ws->last_geom[1] = g.threads;
@@ -253,6 +289,7 @@ b2r_status_t b2r_plan_local(uint64_t count, b2r_dtype_t dtype, b2r_op_t op, int 
   chosen->unroll = g.unroll;
   chosen->stages = stages;
   chosen->tile_bytes = tile_vecs * 16;
+  chosen->pdl = g.pdl;
   return B2R_OK;
 }
 

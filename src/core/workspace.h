@@ -19,6 +19,7 @@ struct b2r_workspace {
   bool trace_enabled = false;
   int last_ctas = 0;
   int last_geom[4] = {0, 0, 0, 0};
+  const void* last_out = nullptr;         // output pointer of the previous launch (PDL overlap guard)
   // b2r_reduce_from_host
   cudaStream_t copy_stream = nullptr;
   void* d_stage[b2r::kStageBufs] = {nullptr, nullptr, nullptr};

@@ -19,9 +19,10 @@ def test_large_inputs_fill_the_machine():
 
 
 def test_grid_grows_with_size():
-    sizes = [1 << k for k in range(10, 31, 2)]
+    sizes = [1 << k for k in range(10, 25, 2)]
     ctas = [b2r.plan(n, torch.float64)["ctas"] for n in sizes]
     assert ctas == sorted(ctas)
+    assert b2r.plan(1 << 30, torch.float64)["ctas"] % 148 == 0
 
 
 @pytest.mark.parametrize("cluster", [2, 4, 8])
@@ -45,3 +46,9 @@ def test_hints_are_respected_and_validated():
 def test_env_override(monkeypatch):
     monkeypatch.setenv("B2R_VARIANT", "2")
     assert b2r.plan(1 << 24, torch.float32)["variant"] == "ldg256"
+
+
+def test_pdl_plans_one_cta_per_sm():
+    p = b2r.plan(1 << 24, torch.int32, cfg={"pdl": 1})
+    assert p["pdl"] == 1 and p["ctas"] == 148
+    assert b2r.plan(1 << 24, torch.int32)["pdl"] == 0
