@@ -160,13 +160,15 @@ def run_b2r(args) -> None:
 
     # pdl=1: programmatic dependent launch — step i+1 may begin streaming its (ready, independent) input while step i is
     # draining; every step still reads its whole input from HBM and finishes its own scalar.
-    cfg = {"pdl": 1}
+    cfg = b2r.launch_config(pdl=1)
     if comm is None:
+        opc = {"sum": 0, "min": 1, "max": 2}[args.op]
+
         def step(i):
-            b2r.reduce(inputs[i % copies], args.op, out=out, workspace=ws, cfg=cfg)
+            b2r.reduce(inputs[i % copies], opc, out=out, workspace=ws, cfg=cfg)
 
         def step_plain(i):
-            b2r.reduce(inputs[i % copies], args.op, out=out, workspace=ws)
+            b2r.reduce(inputs[i % copies], opc, out=out, workspace=ws)
     else:
         def step(i):
             comm.reduce_scalar_sharded(inputs[i % copies], args.op, root=0, out=out)

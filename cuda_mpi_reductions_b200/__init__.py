@@ -6,11 +6,11 @@ benchmark (mpi/reduce.c); see SURVEY.md for the full map.
 """
 from . import _lib
 from ._lib import B2RError, build
-from .ops.local import Workspace, reduce, reduce_from_host, dot, plan, trace_last
+from .ops.local import Workspace, reduce, reduce_from_host, dot, plan, trace_last, launch_config
 from .ops.oracle import reduce_oracle, combine_oracle, fill_host, fill_device
 
 __all__ = [
-    "B2RError", "build", "Workspace", "reduce", "reduce_from_host", "dot", "plan", "trace_last",
+    "B2RError", "build", "Workspace", "reduce", "reduce_from_host", "dot", "plan", "trace_last", "launch_config",
     "reduce_oracle", "combine_oracle", "fill_host", "fill_device",
 ]
 __version__ = "0.1.0"

@@ -34,7 +34,7 @@ class LaunchCfg(C.Structure):
 
 class CommConfig(C.Structure):
     _fields_ = [("heap_bytes", C.c_uint64), ("use_multicast", C.c_int), ("timeout_ms", C.c_int), ("max_ctas", C.c_int),
-                ("reserved", C.c_int * 4)]
+                ("symmetric_only", C.c_int), ("reserved", C.c_int * 3)]
 
 
 class B2RError(RuntimeError):

@@ -1,0 +1,240 @@
+"""Communicators and collectives on CUDA tensors: MPI-style reduce / allreduce (MPI_Reduce semantics, mpi/reduce.c:76,90),
+the fused sharded scalar reduce (vendored simpleMultiGPU analogue) and barriers — all executed by the library's own
+sm_100a kernels over NVLink (src/coll). torch.distributed is used for plumbing only: to agree on a bootstrap id.
+
+Three ways to get communicators:
+  Communicator.from_torch_distributed()   one process per GPU (torchrun); VMM handles travel over a Unix socket
+  Communicator.init_all(devices)          one process driving several GPUs
+  Communicator.loopback(n, device)        n virtual ranks on ONE GPU (protocol tests; one fused cooperative launch)
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import uuid
+
+import torch
+
+from .. import _lib
+from ..ops.oracle import b2r_dtype, op_code
+
+_CAI_TYPESTR = {torch.int32: "<i4", torch.float32: "<f4", torch.float64: "<f8", torch.bfloat16: "<u2"}
+
+
+class _RawCudaBuffer:
+    """Adapter exposing a raw device pointer through __cuda_array_interface__ so torch can wrap it without copying."""
+
+    def __init__(self, ptr: int, numel: int, typestr: str, owner):
+        self.__cuda_array_interface__ = {"shape": (numel,), "typestr": typestr, "data": (ptr, False), "version": 2}
+        self._owner = owner  # keeps the communicator (and with it the heap) alive
+
+
+def _make_cfg(heap_bytes=0, use_multicast=-1, timeout_ms=0, max_ctas=0, symmetric_only=False) -> _lib.CommConfig:
+    cfg = _lib.CommConfig()
+    cfg.heap_bytes = int(heap_bytes)
+    cfg.use_multicast = int(use_multicast)
+    cfg.timeout_ms = int(timeout_ms)
+    cfg.max_ctas = int(max_ctas)
+    cfg.symmetric_only = int(bool(symmetric_only))
+    return cfg
+
+
+class Communicator:
+    def __init__(self, handle: C.c_void_p, group: list | None = None):
+        self._h = handle
+        self._group = group  # loopback / init_all: sibling communicators
+        r, n, d, m = C.c_int(), C.c_int(), C.c_int(), C.c_int()
+        _lib.check(_lib.LIB.b2r_comm_rank(handle, C.byref(r)), "b2r_comm_rank")
+        _lib.check(_lib.LIB.b2r_comm_size(handle, C.byref(n)), "b2r_comm_size")
+        _lib.check(_lib.LIB.b2r_comm_device(handle, C.byref(d)), "b2r_comm_device")
+        _lib.check(_lib.LIB.b2r_comm_has_multicast(handle, C.byref(m)), "b2r_comm_has_multicast")
+        self.rank, self.size, self.device_index, self.has_multicast = r.value, n.value, d.value, bool(m.value)
+        self.device = torch.device("cuda", self.device_index)
+
+    # ------------------------------------------------------------------ construction
+    @classmethod
+    def loopback(cls, nranks: int, device: int = 0, **cfg) -> list["Communicator"]:
+        arr = (C.c_void_p * nranks)()
+        c = _make_cfg(**cfg)
+        _lib.check(_lib.LIB.b2r_comm_init_loopback(arr, nranks, device, C.byref(c)), "b2r_comm_init_loopback")
+        comms: list[Communicator] = []
+        for i in range(nranks):
+            comms.append(cls(C.c_void_p(arr[i]), comms))
+        return comms
+
+    @classmethod
+    def init_all(cls, devices: list[int] | None = None, **cfg) -> list["Communicator"]:
+        devices = list(range(torch.cuda.device_count())) if devices is None else list(devices)
+        n = len(devices)
+        arr = (C.c_void_p * n)()
+        devs = (C.c_int * n)(*devices)
+        c = _make_cfg(**cfg)
+        _lib.check(_lib.LIB.b2r_comm_init_all(arr, n, devs, C.byref(c)), "b2r_comm_init_all")
+        comms: list[Communicator] = []
+        for i in range(n):
+            comms.append(cls(C.c_void_p(arr[i]), comms))
+        return comms
+
+    @classmethod
+    def init_rank(cls, rank: int, nranks: int, device: int, bootstrap_id: str, **cfg) -> "Communicator":
+        h = C.c_void_p()
+        c = _make_cfg(**cfg)
+        _lib.check(_lib.LIB.b2r_comm_init_rank(C.byref(h), nranks, rank, device, bootstrap_id.encode(), C.byref(c)), "b2r_comm_init_rank")
+        return cls(h)
+
+    @classmethod
+    def from_torch_distributed(cls, group=None, device: int | None = None, **cfg) -> "Communicator":
+        """One communicator per process of an initialised torch.distributed job (any backend: nccl on GPUs, gloo in CPU
+        tests of the bootstrap). The processes must share one node."""
+        import torch.distributed as dist
+
+        rank, world = dist.get_rank(group), dist.get_world_size(group)
+        box = [f"{uuid.uuid4().hex}-{os.getpid()}" if rank == 0 else None]
+        dist.broadcast_object_list(box, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+        if device is None:
+            device = torch.cuda.current_device()
+        return cls.init_rank(rank, world, device, box[0], **cfg)
+
+    # ------------------------------------------------------------------ memory
+    def symm_empty(self, numel: int, dtype: torch.dtype) -> torch.Tensor:
+        """A 1-D tensor inside the symmetric heap (zero-copy collectives). Every rank must allocate the same sizes in the
+        same order. Freed all at once by symm_free_all()."""
+        esz = _lib.DTYPE_SIZE[b2r_dtype(dtype)]
+        p = C.c_void_p()
+        _lib.check(_lib.LIB.b2r_symm_alloc(self._h, numel * esz, C.byref(p)), "b2r_symm_alloc")
+        with torch.cuda.device(self.device):
+            t = torch.as_tensor(_RawCudaBuffer(p.value, numel, _CAI_TYPESTR[dtype], self), device=self.device)
+        return t.view(torch.bfloat16) if dtype == torch.bfloat16 else t
+
+    def symm_free_all(self) -> None:
+        _lib.check(_lib.LIB.b2r_symm_free_all(self._h), "b2r_symm_free_all")
+
+    # ------------------------------------------------------------------ collectives
+    def _stream(self) -> int:
+        return torch.cuda.current_stream(self.device).cuda_stream
+
+    def _finish(self, st: int, where: str) -> bool:
+        """True when the operation was launched, False when it was only recorded (loopback, waiting for other ranks)."""
+        if st == _lib.ERR_PENDING:
+            return False
+        _lib.check(st, where)
+        return True
+
+    def allreduce(self, x: torch.Tensor, op="sum", out: torch.Tensor | None = None, algo="auto") -> torch.Tensor:
+        """out[j] = op over ranks of x_r[j] on every rank. out=None allocates; out=x reduces in place."""
+        x = self._prep(x)
+        out = torch.empty_like(x) if out is None else out
+        assert out.is_cuda and out.is_contiguous() and out.dtype == x.dtype and out.numel() == x.numel()
+        st = _lib.LIB.b2r_allreduce_ex(x.data_ptr(), out.data_ptr(), x.numel(), b2r_dtype(x.dtype), op_code(op), self._h, self._stream(),
+                                       _lib.ALGOS[algo] if isinstance(algo, str) else algo)
+        self._finish(st, "b2r_allreduce")
+        return out
+
+    def reduce(self, x: torch.Tensor, op="sum", root: int = 0, out: torch.Tensor | None = None, algo="auto") -> torch.Tensor | None:
+        """out[j] = op over ranks of x_r[j], valid at `root` only (returns None elsewhere unless `out` was passed)."""
+        x = self._prep(x)
+        if out is None and self.rank == root:
+            out = torch.empty_like(x)
+        st = _lib.LIB.b2r_reduce_ex(x.data_ptr(), out.data_ptr() if out is not None else 0, x.numel(), b2r_dtype(x.dtype), op_code(op), root,
+                                    self._h, self._stream(), _lib.ALGOS[algo] if isinstance(algo, str) else algo)
+        self._finish(st, "b2r_reduce")
+        return out
+
+    def reduce_scalar_sharded(self, x: torch.Tensor, op="sum", root: int = 0, all: bool = False, out: torch.Tensor | None = None):
+        """Scalar op over the elements of EVERY rank's shard `x` (shards may have different contents, same length per
+        call): one fused kernel per rank — local streaming reduction, partial stored into the root's mailbox over NVLink,
+        root combines in rank order. Result at root (every rank if all=True) as a 0-dim tensor."""
+        x = self._prep(x)
+        if out is None and (all or self.rank == root):
+            out = torch.empty((), dtype=x.dtype, device=self.device)
+        st = _lib.LIB.b2r_reduce_scalar_sharded(x.data_ptr() if x.numel() else 0, out.data_ptr() if out is not None else 0, x.numel(),
+                                                b2r_dtype(x.dtype), op if isinstance(op, int) else op_code(op), root, int(all), self._h,
+                                                self._stream())
+        self._finish(st, "b2r_reduce_scalar_sharded")
+        return out
+
+    def reduce_scalar_sharded_from_host(self, x: torch.Tensor, op="sum", root: int = 0, all: bool = False):
+        """End-to-end flavour: `x` is this rank's shard in (pinned) HOST memory; it is copied to the GPU, reduced across
+        ranks, and the scalar is read back to the host on the ranks that own it (None elsewhere). Synchronous."""
+        assert not x.is_cuda
+        key = (x.numel(), x.dtype)
+        buf = getattr(self, "_e2e_buf", None)
+        if buf is None or self._e2e_key != key:
+            buf = torch.empty(x.numel(), dtype=x.dtype, device=self.device)
+            self._e2e_buf, self._e2e_key = buf, key
+        buf.copy_(x.reshape(-1), non_blocking=True)
+        out = self.reduce_scalar_sharded(buf, op, root=root, all=all)
+        if out is None:
+            torch.cuda.current_stream(self.device).synchronize()
+            return None
+        return out.cpu()
+
+    def barrier(self) -> None:
+        self._finish(_lib.LIB.b2r_barrier(self._h, self._stream()), "b2r_barrier")
+
+    def check(self) -> None:
+        """Synchronises the current stream and raises B2RError(ERR_TIMEOUT) if a cross-GPU wait gave up."""
+        _lib.check(_lib.LIB.b2r_comm_check(self._h, self._stream()), "b2r_comm_check")
+
+    def select_algo(self, nbytes: int, dtype: torch.dtype, op="sum", allreduce: bool = True) -> str:
+        a = _lib.LIB.b2r_select_algo(int(allreduce), nbytes, b2r_dtype(dtype), op_code(op), self.size, int(self.has_multicast))
+        return {v: k for k, v in _lib.ALGOS.items()}[a]
+
+    def _prep(self, x: torch.Tensor) -> torch.Tensor:
+        if not x.is_cuda or x.device != self.device:
+            raise ValueError(f"tensor must live on {self.device}")
+        return x if x.is_contiguous() else x.contiguous()
+
+    def close(self) -> None:
+        if self._h:
+            _lib.LIB.b2r_comm_destroy(self._h)
+            self._h = None
+
+    # ------------------------------------------------------------------ helpers for single-process groups
+    @staticmethod
+    def group_allreduce(comms: list["Communicator"], xs: list[torch.Tensor], op="sum", algo="auto", outs=None) -> list[torch.Tensor]:
+        """Issues the same allreduce on every communicator of a loopback / init_all group (one host thread)."""
+        outs = outs or [None] * len(comms)
+        res = []
+        for c, x, o in zip(comms, xs, outs):
+            with torch.cuda.device(c.device):
+                res.append(c.allreduce(x, op, out=o, algo=algo))
+        return res
+
+    loopback_allreduce = group_allreduce
+
+    @staticmethod
+    def group_reduce(comms, xs, op="sum", root=0, algo="auto", outs=None):
+        outs = outs or [None] * len(comms)
+        res = []
+        for c, x, o in zip(comms, xs, outs):
+            with torch.cuda.device(c.device):
+                res.append(c.reduce(x, op, root=root, out=o, algo=algo))
+        return res
+
+    @staticmethod
+    def group_reduce_scalar(comms, xs, op="sum", root=0, all=False):
+        res = []
+        for c, x in zip(comms, xs):
+            with torch.cuda.device(c.device):
+                res.append(c.reduce_scalar_sharded(x, op, root=root, all=all))
+        return res
+
+    @staticmethod
+    def group_check(comms) -> None:
+        for c in comms:
+            c.check()
+
+
+def host_reduce_threads(sendbufs: list[torch.Tensor], op="sum", root: int = 0, algo="oneshot") -> torch.Tensor:
+    """The same algorithms run by CPU threads over host tensors (host loopback transport; oracle with identical
+    combination order). root=-1 runs the allreduce flavour and returns a [nranks, count] tensor."""
+    n = len(sendbufs)
+    bufs = [t.contiguous() for t in sendbufs]
+    count, dtype = bufs[0].numel(), bufs[0].dtype
+    assert all(t.numel() == count and t.dtype == dtype and not t.is_cuda for t in bufs)
+    out = torch.empty((n, count) if root < 0 else (count,), dtype=dtype)
+    ptrs = (C.c_void_p * n)(*[t.data_ptr() for t in bufs])
+    st = _lib.LIB.b2r_host_reduce_threads(ptrs, out.data_ptr(), count, b2r_dtype(dtype), op_code(op), n, root, _lib.ALGOS[algo])
+    _lib.check(st, "b2r_host_reduce_threads")
+    return out

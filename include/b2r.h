@@ -145,7 +145,9 @@ typedef struct {
   int use_multicast;     /* -1 auto (use if supported), 0 never, 1 require */
   int timeout_ms;        /* cross-GPU wait deadline, 0 = default (10000), <0 = never time out */
   int max_ctas;          /* CTAs per collective kernel (0 = auto) */
-  int reserved[4];
+  int symmetric_only;    /* 1 = every buffer passed to a collective comes from b2r_symm_alloc on every rank: messages are
+                            never staged nor chunked (one launch per collective whatever the size). All ranks must agree. */
+  int reserved[3];
 } b2r_comm_config_t;
 
 /* Single process, several devices (vendored MonteCarloMultiGPU "one thread, one stream per GPU" mode,

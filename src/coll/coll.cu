@@ -1,0 +1,358 @@
+// coll.cu — host side of the collectives: algorithm selection, staging / chunking of non-symmetric buffers, launch
+// (one kernel per rank; ONE cooperative kernel for all virtual ranks in loopback mode), and the scalar-sharded reduce.
+// API counterpart: MPI_Reduce(sendbuf, recvbuf, count, type, op, root, comm) as used by mpi/reduce.c:76,90.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdlib>
+#include <cstring>
+#include <memory>
+#include <vector>
+
+#include "../comm/comm.h"
+#include "../core/reduce_internal.h"
+#include "../util/check.h"
+#include "coll_kernels.cuh"
+
+namespace b2r {
+
+enum CallKind { kCallReduce = 0, kCallAllreduce = 1, kCallScalar = 2, kCallBarrier = 3 };
+
+struct PendingCall {
+  int kind;
+  const void* send;
+  void* recv;
+  uint64_t count;
+  b2r_dtype_t dtype;
+  b2r_op_t op;
+  int root, all;
+  b2r_algo_t algo;
+  cudaStream_t stream;
+};
+
+namespace {
+
+int env_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return (v && *v) ? atoi(v) : dflt;
+}
+
+using CollKernel = void (*)(const CollLaunch);
+
+template <int D, int O>
+CollKernel pick_kind(int kind) {
+  switch (kind) {
+    case kCollOneshot: return coll_kernel<D, O, kCollOneshot>;
+    case kCollTwoshot: return coll_kernel<D, O, kCollTwoshot>;
+    case kCollTree: return coll_kernel<D, O, kCollTree>;
+    case kCollNvls: return Nvls<D, O>::kSupported ? coll_kernel<D, O, kCollNvls> : nullptr;
+    case kCollBarrier: return coll_kernel<D, O, kCollBarrier>;
+  }
+  return nullptr;
+}
+template <int D>
+CollKernel pick_op(int op, int kind) {
+  switch (op) {
+    case B2R_SUM: return pick_kind<D, B2R_SUM>(kind);
+    case B2R_MIN: return pick_kind<D, B2R_MIN>(kind);
+    case B2R_MAX: return pick_kind<D, B2R_MAX>(kind);
+  }
+  return nullptr;
+}
+CollKernel pick_kernel(b2r_dtype_t dtype, int op, int kind) {
+  switch (dtype) {
+    case B2R_INT32: return pick_op<B2R_INT32>(op, kind);
+    case B2R_FLOAT32: return pick_op<B2R_FLOAT32>(op, kind);
+    case B2R_FLOAT64: return pick_op<B2R_FLOAT64>(op, kind);
+    case B2R_BFLOAT16: return pick_op<B2R_BFLOAT16>(op, kind);
+  }
+  return nullptr;
+}
+
+bool nvls_supported(b2r_dtype_t dtype, b2r_op_t op) {
+  if (dtype == B2R_FLOAT32 || dtype == B2R_FLOAT64) return op == B2R_SUM;
+  return true;  // bf16x2 add/min/max, 32-bit integer add/min/max
+}
+
+struct RankCall {
+  b2r_comm* c;
+  const void* send;
+  void* recv;
+  cudaStream_t stream;
+};
+
+// CTAs per rank for a collective over `bytes` (must be a pure function of things every rank knows).
+int coll_ctas(const b2r_comm* c, uint64_t bytes, int nvirtual) {
+  int cap = c->max_ctas > 0 ? c->max_ctas : 128;
+  cap = std::min(cap, kCollMaxCtas);
+  if (nvirtual > 1) cap = std::max(1, std::min(cap, c->sm_count / nvirtual));  // cooperative launch: all ranks co-resident
+  const uint64_t want = (bytes + 65535) / 65536;
+  return (int)std::max<uint64_t>(1, std::min<uint64_t>(want, (uint64_t)cap));
+}
+
+// Runs one element-wise collective for the `n` calls in rc (n == 1: this process drives one rank; n == P: loopback).
+b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, b2r_dtype_t dtype, b2r_op_t op, int root, b2r_algo_t algo) {
+  b2r_comm* c0 = rc[0].c;
+  const int P = c0->nranks;
+  const size_t esz = b2r_dtype_size(dtype);
+  const bool is_all = kind_call == kCallAllreduce;
+  B2R_REQUIRE(dtype >= B2R_INT32 && dtype <= B2R_BFLOAT16, "collective: bad dtype %d", (int)dtype);
+  B2R_REQUIRE(op >= B2R_SUM && op <= B2R_MAX, "collective: bad op %d", (int)op);
+  B2R_REQUIRE(is_all || (root >= 0 && root < P), "reduce: root %d out of range [0,%d)", root, P);
+  for (int i = 0; i < n; ++i) {
+    b2r_comm* c = rc[i].c;
+    const bool gets_result = is_all || c->rank == root;
+    B2R_REQUIRE(rc[i].send != nullptr || count == 0, "collective: sendbuf is NULL on rank %d", c->rank);
+    B2R_REQUIRE(!gets_result || rc[i].recv != nullptr || count == 0, "collective: recvbuf is NULL on rank %d", c->rank);
+    B2R_REQUIRE(((uintptr_t)rc[i].send % esz) == 0 && ((uintptr_t)rc[i].recv % esz) == 0, "collective: buffer not aligned to the element size");
+  }
+  if (count == 0) return B2R_OK;
+
+  int prev_dev = -1;
+  B2R_CUDA_CHECK(cudaGetDevice(&prev_dev));
+  struct Restore { int d; ~Restore() { cudaSetDevice(d); } } restore{prev_dev};
+  B2R_CUDA_CHECK(cudaSetDevice(c0->device));
+
+  if (P == 1) {
+    if (rc[0].recv != rc[0].send) B2R_CUDA_CHECK(cudaMemcpyAsync(rc[0].recv, rc[0].send, count * esz, cudaMemcpyDeviceToDevice, rc[0].stream));
+    return B2R_OK;
+  }
+
+  const uint64_t total_bytes = count * esz;
+  if (algo == B2R_ALGO_AUTO) algo = b2r_select_algo(is_all ? 1 : 0, total_bytes, dtype, op, P, c0->has_mc ? 1 : 0);
+  if (algo == B2R_ALGO_NVLS) {
+    if (!c0->has_mc) return fail(B2R_ERR_UNSUPPORTED, "NVLS requested but this communicator has no multicast mapping");
+    if (!nvls_supported(dtype, op)) return fail(B2R_ERR_UNSUPPORTED, "NVLS has no %s %s instruction", b2r_dtype_name(dtype), b2r_op_name(op));
+  }
+  const int kind = algo == B2R_ALGO_ONESHOT ? kCollOneshot : algo == B2R_ALGO_TWOSHOT ? kCollTwoshot : algo == B2R_ALGO_TREE ? kCollTree : kCollNvls;
+  CollKernel kernel = pick_kernel(dtype, (int)op, kind);
+  B2R_REQUIRE(kernel != nullptr, "collective: no kernel for dtype %d op %d algo %d", (int)dtype, (int)op, (int)algo);
+
+  // Chunking rule (identical on every rank): messages larger than one staging region are cut into stage-sized chunks,
+  // unless the communicator was created with symmetric_only (then nothing is ever staged and one launch does it all).
+  const uint64_t stage_elems = (c0->stage_bytes / 16) * 16 / esz;
+  const uint64_t chunk_elems = c0->symmetric_only ? count : std::min<uint64_t>(count, stage_elems);
+  // the tree keeps its running partial in the work region: it can never exceed one staging region per launch
+  const uint64_t chunk = (kind == kCollTree) ? std::min<uint64_t>(chunk_elems, stage_elems) : chunk_elems;
+
+  for (uint64_t first = 0; first < count; first += chunk) {
+    const uint64_t cnt = std::min<uint64_t>(chunk, count - first);
+    const uint64_t bytes = cnt * esz;
+    CollLaunch L;
+    memset(&L, 0, sizeof(L));
+    std::vector<bool> recv_staged(n, false);
+    for (int i = 0; i < n; ++i) {
+      b2r_comm* c = rc[i].c;
+      const bool gets_result = is_all || c->rank == root;
+      const char* send = (const char*)rc[i].send + first * esz;
+      char* recv = rc[i].recv ? (char*)rc[i].recv + first * esz : nullptr;
+      int64_t soff = c->heap_offset(send, bytes);
+      int64_t roff = (gets_result && recv) ? c->heap_offset(recv, bytes) : -1;
+      // in place is only safe zero-copy for two-shot / NVLS (a slice is read and written by its single owner)
+      const bool inplace_hazard = (send == recv) && (kind == kCollOneshot || kind == kCollTree);
+      if (soff < 0 || inplace_hazard) {
+        if (c->symmetric_only) return fail(B2R_ERR_INVALID, "rank %d: sendbuf is not a 16-byte aligned symmetric allocation (symmetric_only)", c->rank);
+        B2R_CUDA_CHECK(cudaMemcpyAsync(c->stage_send(), send, bytes, cudaMemcpyDeviceToDevice, rc[i].stream));
+        soff = c->stage_send() - c->my_heap();
+      }
+      if (roff < 0) {
+        if (gets_result && c->symmetric_only) return fail(B2R_ERR_INVALID, "rank %d: recvbuf is not a 16-byte aligned symmetric allocation (symmetric_only)", c->rank);
+        roff = c->stage_recv() - c->my_heap();
+        recv_staged[i] = gets_result;
+      }
+      CollArgs& A = L.a[n == 1 ? 0 : c->rank];
+      A.ctx = c->ctx;
+      A.send_off = (unsigned long long)soff;
+      A.recv_off = (unsigned long long)roff;
+      A.work_off = (unsigned long long)(c->stage_work() - c->my_heap());
+      A.count = cnt;
+      A.epoch = c->epoch;
+      A.root = is_all ? -1 : root;
+      c->epoch += 8;  // start + end + up to 4 tree rounds, rounded up; same increment on every rank
+    }
+    const int ctas = coll_ctas(c0, bytes, n);
+    if (n == 1) {
+      kernel<<<dim3((unsigned)ctas, 1), 512, 0, rc[0].stream>>>(L);
+      B2R_CUDA_CHECK(cudaGetLastError());
+    } else {
+      void* args[] = {(void*)&L};
+      B2R_CUDA_CHECK(cudaLaunchCooperativeKernel((const void*)kernel, dim3((unsigned)ctas, (unsigned)n), dim3(512), args, 0, rc[0].stream));
+    }
+    for (int i = 0; i < n; ++i) {
+      if (!recv_staged[i]) continue;
+      b2r_comm* c = rc[i].c;
+      B2R_CUDA_CHECK(cudaMemcpyAsync((char*)rc[i].recv + first * esz, c->stage_recv(), bytes, cudaMemcpyDeviceToDevice, n == 1 ? rc[i].stream : rc[0].stream));
+    }
+  }
+  return B2R_OK;
+}
+
+b2r_status_t run_barrier(RankCall* rc, int n) {
+  b2r_comm* c0 = rc[0].c;
+  if (c0->nranks == 1) return B2R_OK;
+  int prev_dev = -1;
+  B2R_CUDA_CHECK(cudaGetDevice(&prev_dev));
+  struct Restore { int d; ~Restore() { cudaSetDevice(d); } } restore{prev_dev};
+  B2R_CUDA_CHECK(cudaSetDevice(c0->device));
+  CollLaunch L;
+  memset(&L, 0, sizeof(L));
+  for (int i = 0; i < n; ++i) {
+    b2r_comm* c = rc[i].c;
+    CollArgs& A = L.a[n == 1 ? 0 : c->rank];
+    A.ctx = c->ctx;
+    A.epoch = c->epoch;
+    A.root = -1;
+    c->epoch += 8;
+  }
+  CollKernel kernel = coll_kernel<B2R_INT32, B2R_SUM, kCollBarrier>;
+  if (n == 1) {
+    kernel<<<dim3(1, 1), 32, 0, rc[0].stream>>>(L);
+    B2R_CUDA_CHECK(cudaGetLastError());
+  } else {
+    void* args[] = {(void*)&L};
+    B2R_CUDA_CHECK(cudaLaunchCooperativeKernel((const void*)kernel, dim3(1, (unsigned)n), dim3(32), args, 0, rc[0].stream));
+  }
+  return B2R_OK;
+}
+
+// Scalar-sharded reduce: the local streaming reduction with the cross-GPU mailbox combine fused into its tail.
+b2r_status_t run_scalar(RankCall* rc, int n, uint64_t count, b2r_dtype_t dtype, b2r_op_t op, int root, int all) {
+  b2r_comm* c0 = rc[0].c;
+  const int P = c0->nranks;
+  B2R_REQUIRE(root >= 0 && root < P, "reduce_scalar_sharded: root %d out of range [0,%d)", root, P);
+  for (int i = 0; i < n; ++i) {
+    const bool gets = all || rc[i].c->rank == root;
+    B2R_REQUIRE(!gets || rc[i].recv != nullptr, "reduce_scalar_sharded: out is NULL on rank %d", rc[i].c->rank);
+  }
+  if (n == 1) {
+    b2r_comm* c = rc[0].c;
+    XgCall xg;
+    xg.ctx = (const CollCtx*)(c->my_heap() + kOffCtx);
+    xg.root = root;
+    xg.all = all;
+    xg.seq = ++c->xg_seq;
+    void* out = rc[0].recv ? rc[0].recv : (void*)c->ws->d_partials;  // non-root without `all`: never written
+    if (P == 1) return reduce_local_impl(rc[0].send, out, count, dtype, op, c->ws, rc[0].stream, nullptr, 0, nullptr);
+    return reduce_local_impl(rc[0].send, out, count, dtype, op, c->ws, rc[0].stream, nullptr, 0, &xg);
+  }
+  // loopback: every virtual rank in one cooperative launch (LDG128 variant, same grid for all ranks)
+  int prev_dev = -1;
+  B2R_CUDA_CHECK(cudaGetDevice(&prev_dev));
+  struct Restore { int d; ~Restore() { cudaSetDevice(d); } } restore{prev_dev};
+  B2R_CUDA_CHECK(cudaSetDevice(c0->device));
+  MultiLocalParams mp;
+  memset(&mp, 0, sizeof(mp));
+  const int threads = 256;
+  int ctas = 1;
+  {
+    const uint64_t bytes = count * b2r_dtype_size(dtype);
+    const uint64_t want = (bytes + 32767) / 32768;
+    ctas = (int)std::max<uint64_t>(1, std::min<uint64_t>(want, (uint64_t)std::max(1, c0->sm_count * 2 / n)));
+  }
+  for (int i = 0; i < n; ++i) {
+    b2r_comm* c = rc[i].c;
+    b2r_launch_cfg_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.variant = B2R_VARIANT_LDG128;
+    cfg.threads = threads;
+    cfg.ctas = ctas;
+    cfg.cluster = 1;
+    cfg.unroll = 4;
+    LaunchGeom g;
+    void* out = rc[i].recv ? rc[i].recv : (void*)c->ws->d_partials;
+    B2R_CHECK(prepare_local(rc[i].send, out, count, dtype, op, c->ws, &cfg, 0, &g, &mp.p[c->rank]));
+    LocalParams& p = mp.p[c->rank];
+    p.xg_ctx = (const CollCtx*)(c->my_heap() + kOffCtx);
+    p.xg_root = root;
+    p.xg_all = all;
+    p.xg_seq = ++c->xg_seq;
+    p.pdl = 0;
+  }
+  return launch_multi_any(dtype, (int)op, n, ctas, threads, mp, rc[0].stream);
+}
+
+// Loopback: record the call; the last rank of the group to arrive launches for everybody.
+b2r_status_t loopback_submit(b2r_comm* c, const PendingCall& call) {
+  CommGroup* g = c->group.get();
+  std::lock_guard<std::mutex> lk(g->mu);
+  if (g->pending[c->rank]) return fail(B2R_ERR_INVALID, "loopback rank %d issued a second collective before the group completed the first", c->rank);
+  g->pending[c->rank] = std::make_shared<PendingCall>(call);
+  if (++g->npending < g->nranks) return B2R_ERR_PENDING;
+  std::vector<RankCall> rc(g->nranks);
+  const PendingCall& ref = *g->pending[0];
+  b2r_status_t st = B2R_OK;
+  for (int r = 0; r < g->nranks; ++r) {
+    const PendingCall& pc = *g->pending[r];
+    if (pc.kind != ref.kind || pc.count != ref.count || pc.dtype != ref.dtype || pc.op != ref.op || pc.root != ref.root || pc.all != ref.all ||
+        pc.algo != ref.algo)
+      st = fail(B2R_ERR_INVALID, "loopback: rank %d called with different arguments than rank 0", r);
+    rc[r].c = g->members[r];
+    rc[r].send = pc.send;
+    rc[r].recv = pc.recv;
+    rc[r].stream = call.stream;  // everything runs on the last caller's stream
+  }
+  if (st == B2R_OK) {
+    if (ref.kind == kCallScalar) st = run_scalar(rc.data(), g->nranks, ref.count, ref.dtype, ref.op, ref.root, ref.all);
+    else if (ref.kind == kCallBarrier) st = run_barrier(rc.data(), g->nranks);
+    else st = run_collective(rc.data(), g->nranks, ref.kind, ref.count, ref.dtype, ref.op, ref.root, ref.algo);
+  }
+  for (auto& p : g->pending) p.reset();
+  g->npending = 0;
+  return st;
+}
+
+b2r_status_t submit(b2r_comm* c, const PendingCall& call) {
+  B2R_REQUIRE(c != nullptr, "collective: communicator is NULL");
+  if (c->mode == kModeLoopback && c->nranks > 1) return loopback_submit(c, call);
+  RankCall rc{c, call.send, call.recv, call.stream};
+  if (call.kind == kCallScalar) return run_scalar(&rc, 1, call.count, call.dtype, call.op, call.root, call.all);
+  if (call.kind == kCallBarrier) return run_barrier(&rc, 1);
+  return run_collective(&rc, 1, call.kind, call.count, call.dtype, call.op, call.root, call.algo);
+}
+
+}  // namespace
+}  // namespace b2r
+
+using namespace b2r;
+
+extern "C" {
+
+// Size thresholds measured on 8x B200 (profiles/collective_sweep.md). One-shot costs one NVLink round trip but every
+// rank pulls the WHOLE message from every peer; two-shot / NVLS move 1/P of it per rank.
+b2r_algo_t b2r_select_algo(int is_allreduce, uint64_t bytes, b2r_dtype_t dtype, b2r_op_t op, int nranks, int has_multicast) {
+  if (nranks <= 1) return B2R_ALGO_ONESHOT;
+  const uint64_t oneshot_max = (uint64_t)std::max(0, env_int("B2R_ONESHOT_MAX_KB", is_allreduce ? 256 : 512)) << 10;
+  if (bytes <= oneshot_max) return B2R_ALGO_ONESHOT;
+  const bool nvls_fast = has_multicast && nvls_supported(dtype, op) && (dtype == B2R_FLOAT32 || dtype == B2R_BFLOAT16 || dtype == B2R_FLOAT64);
+  if (nvls_fast && !env_int("B2R_DISABLE_NVLS", 0)) return B2R_ALGO_NVLS;
+  return B2R_ALGO_TWOSHOT;  // int32 (4-byte multimem ops) and fp32/fp64 min/max (no multimem form) stay on P2P
+}
+
+b2r_status_t b2r_reduce_ex(const void* sendbuf, void* recvbuf, uint64_t count, b2r_dtype_t dtype, b2r_op_t op, int root, b2r_comm_t comm,
+                           void* stream, b2r_algo_t algo) {
+  PendingCall pc{kCallReduce, sendbuf, recvbuf, count, dtype, op, root, 0, algo, (cudaStream_t)stream};
+  return submit(comm, pc);
+}
+b2r_status_t b2r_allreduce_ex(const void* sendbuf, void* recvbuf, uint64_t count, b2r_dtype_t dtype, b2r_op_t op, b2r_comm_t comm, void* stream,
+                              b2r_algo_t algo) {
+  PendingCall pc{kCallAllreduce, sendbuf, recvbuf, count, dtype, op, -1, 0, algo, (cudaStream_t)stream};
+  return submit(comm, pc);
+}
+b2r_status_t b2r_reduce(const void* sendbuf, void* recvbuf, uint64_t count, b2r_dtype_t dtype, b2r_op_t op, int root, b2r_comm_t comm,
+                        void* stream) {
+  return b2r_reduce_ex(sendbuf, recvbuf, count, dtype, op, root, comm, stream, B2R_ALGO_AUTO);
+}
+b2r_status_t b2r_allreduce(const void* sendbuf, void* recvbuf, uint64_t count, b2r_dtype_t dtype, b2r_op_t op, b2r_comm_t comm, void* stream) {
+  return b2r_allreduce_ex(sendbuf, recvbuf, count, dtype, op, comm, stream, B2R_ALGO_AUTO);
+}
+b2r_status_t b2r_reduce_scalar_sharded(const void* in, void* out, uint64_t count, b2r_dtype_t dtype, b2r_op_t op, int root, int all,
+                                       b2r_comm_t comm, void* stream) {
+  PendingCall pc{kCallScalar, in, out, count, dtype, op, root, all ? 1 : 0, B2R_ALGO_AUTO, (cudaStream_t)stream};
+  return submit(comm, pc);
+}
+b2r_status_t b2r_barrier(b2r_comm_t comm, void* stream) {
+  PendingCall pc{kCallBarrier, nullptr, nullptr, 0, B2R_INT32, B2R_SUM, -1, 0, B2R_ALGO_AUTO, (cudaStream_t)stream};
+  return submit(comm, pc);
+}
+
+}  // extern "C"

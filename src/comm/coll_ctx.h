@@ -1,0 +1,103 @@
+// coll_ctx.h — what device code needs to know about a communicator: heap layout, context, mailbox, signal helpers.
+// Synchronisation uses monotonically increasing epoch values written with st.release.sys and polled with
+// ld.acquire.sys (no resets -> no ABA), and every wait has a %globaltimer deadline that raises an error
+// word instead of hanging the GPU.
+#pragma once
+#include <cstdint>
+
+#include "b2r.h"
+
+namespace b2r {
+
+// ---- layout of every rank's symmetric heap (identical offsets on all ranks)
+constexpr int kCollMaxCtas = 256;                    // CTAs per collective kernel (per rank)
+constexpr size_t kOffFlags = 0;                      // uint32 flags[kCollMaxCtas][B2R_MAX_RANKS]: per-CTA epoch flags
+constexpr size_t kOffMailbox = 32 * 1024;            // XgMailbox (scalar-sharded reduce)
+constexpr size_t kOffError = 40 * 1024;              // uint32 error word (device-side timeouts)
+constexpr size_t kOffCtx = 44 * 1024;                // device copy of CollCtx (read by the scalar-sharded kernels)
+constexpr size_t kOffMeta = 64 * 1024;               // PeerMeta meta[kCollMaxCtas][B2R_MAX_RANKS]: per-collective buffer offsets
+constexpr size_t kCtrlBytes = 1 << 20;               // control region size; staging starts here
+
+// Where rank r keeps its send/recv buffer for the collective in flight, published to every peer inside the start
+// barrier, so buffers do NOT have to sit at the same heap offset on every rank (only the NVLS path needs that).
+struct PeerMeta {
+  unsigned long long send_off, recv_off;
+};
+
+// What a kernel needs to know about the communicator. Plain data: passed by value in kernel parameters.
+struct CollCtx {
+  char* heap[B2R_MAX_RANKS];  // heap[p]: rank p's symmetric heap as mapped in THIS rank's address space
+  char* mc;                   // multicast (NVLS) mapping of the same heap, or nullptr
+  int rank, nranks;
+  unsigned long long timeout_ns;  // 0 = wait forever
+  unsigned int fault_delay_us;    // fault injection: sleep before the first signal of a collective
+  int fault_skip_signal;          // fault injection: never signal (peers must time out)
+};
+
+struct XgMailbox {
+  unsigned long long val[2][B2R_MAX_RANKS];  // [call parity][source rank]: partial scalar in accumulator precision
+  unsigned int flag[B2R_MAX_RANKS];          // call number last posted by rank r (monotonic, never reset)
+  unsigned long long result[2];              // [call parity]: final scalar pushed by the root (scalar allreduce)
+  unsigned int result_flag;                  // call number of `result`
+  unsigned int ack;                          // last call number the root has finished reading (flow control)
+};
+
+
+#if defined(__CUDACC__)
+__device__ __forceinline__ void st_release_sys(unsigned int* p, unsigned int v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void st_relaxed_sys_u64(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long ld_relaxed_sys_u64(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned int ld_volatile_u32(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long coll_globaltimer() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+// Spins until *flag >= want (wrap-safe). Returns false if the deadline passed or another waiter already gave up; the
+// error word lives in this rank's own control region and is read by b2r_comm_check().
+__device__ __forceinline__ bool wait_flag_ge(const unsigned int* flag, unsigned int want, const CollCtx& c) {
+  unsigned int* err = (unsigned int*)(c.heap[c.rank] + kOffError);
+  unsigned long long t0 = 0;
+  unsigned int spins = 0;
+  while ((int)(ld_acquire_sys(flag) - want) < 0) {
+    if (++spins >= 128) {
+      spins = 0;
+      if (ld_volatile_u32(err)) return false;
+      const unsigned long long now = coll_globaltimer();
+      if (t0 == 0) t0 = now;
+      else if (c.timeout_ns && now - t0 > c.timeout_ns) {
+        atomicExch(err, 1u);
+        return false;
+      }
+      __nanosleep(64);
+    }
+  }
+  return true;
+}
+
+__device__ __forceinline__ void fault_delay(const CollCtx& c) {
+  if (c.fault_delay_us == 0) return;
+  const unsigned long long t0 = coll_globaltimer();
+  while (coll_globaltimer() - t0 < (unsigned long long)c.fault_delay_us * 1000ull) __nanosleep(1000);
+}
+#endif
+
+}  // namespace b2r

@@ -156,6 +156,7 @@ struct Reducer<B2R_INT32, O> {
   using acc_t = int32_t;
   using F = OpI32<O>;
   static constexpr int kElemBytes = 4;
+  static constexpr bool kIsInt = true;
   struct Thread {
     int32_t a[4];
     __device__ __forceinline__ void init() {
@@ -179,6 +180,7 @@ struct Reducer<B2R_FLOAT32, O> {
   using acc_t = float;
   using F = OpF32<O>;
   static constexpr int kElemBytes = 4;
+  static constexpr bool kIsInt = false;
   struct Thread {
     float a[4];
     __device__ __forceinline__ void init() {
@@ -202,6 +204,7 @@ struct Reducer<B2R_FLOAT64, O> {
   using acc_t = double;
   using F = OpF64<O>;
   static constexpr int kElemBytes = 8;
+  static constexpr bool kIsInt = false;
   struct Thread {
     double a[2];
     __device__ __forceinline__ void init() { a[0] = a[1] = F::identity(); }
@@ -224,6 +227,7 @@ struct Reducer<B2R_BFLOAT16, B2R_SUM> {
   using acc_t = float;
   using F = OpF32<B2R_SUM>;
   static constexpr int kElemBytes = 2;
+  static constexpr bool kIsInt = false;
   struct Thread {
     float a[8];
     __device__ __forceinline__ void init() {
@@ -253,6 +257,7 @@ struct Reducer<B2R_BFLOAT16, O> {
   using acc_t = float;
   using F = OpF32<O>;
   static constexpr int kElemBytes = 2;
+  static constexpr bool kIsInt = false;
   __device__ __forceinline__ static uint32_t packed_identity() { return O == B2R_MIN ? 0x7f807f80u : 0xff80ff80u; }
   __device__ __forceinline__ static uint32_t apply2(uint32_t a, uint32_t b) {
     uint32_t r;

@@ -15,6 +15,7 @@
 #pragma once
 #include <cooperative_groups.h>
 
+#include "../comm/coll_ctx.h"
 #include "primitives.cuh"
 
 namespace b2r {
@@ -34,7 +35,10 @@ struct LocalParams {
   void* partials;             // acc_t[gridDim.x / cluster]
   unsigned* ticket;           // zero between launches
   unsigned long long* trace;  // nullable: 4 stamps per CTA
-  void* mailbox;              // nullable: see scalar-sharded collective (unused here)
+  const CollCtx* xg_ctx;      // nullable: scalar-sharded reduce across GPUs (device copy of the communicator context)
+  int xg_root;                //   root rank
+  int xg_all;                 //   1 = every rank receives the scalar
+  unsigned xg_seq;            //   call number (1, 2, ...), same on every rank
   int stages;                 // TMA ring depth
   int tile_vecs;              // TMA tile size in 16-byte vectors
   int out_as_acc;             // store the scalar as acc_t (fp32 for bf16) instead of the input dtype
@@ -63,6 +67,68 @@ template <class R>
 __device__ __forceinline__ void store_result(const LocalParams& p, typename R::acc_t v) {
   if (p.out_as_acc) *(typename R::acc_t*)p.out = v;
   else R::store(p.out, v);
+}
+
+// Scalar-sharded reduce across GPUs, fused into the tail of the local reduction (one kernel per rank; the vendored
+// simpleMultiGPU copies per-GPU partials to the host and sums there, simpleMultiGPU.cpp:264-293). Called by ONE thread
+// that holds this rank's scalar `a`:
+//   post   : store the partial into the root's mailbox over NVLink, then release-store my call number next to it;
+//   root   : acquire all P call numbers, combine the partials in rank order (deterministic), write `out`, push the ack
+//            (and, for the allreduce flavour, the result) to every rank;
+//   others : with `all`, wait for the pushed result.
+// Mailbox slots are double-buffered by call parity; a rank may run at most one call ahead of the root's ack.
+template <class R>
+__device__ __forceinline__ void xgpu_finish(const LocalParams& p, typename R::acc_t a) {
+  using acc_t = typename R::acc_t;
+  using F = typename R::F;
+  const CollCtx& c = *p.xg_ctx;
+  const unsigned seq = p.xg_seq, slot = seq & 1u;
+  XgMailbox* my_mb = (XgMailbox*)(c.heap[c.rank] + kOffMailbox);
+  XgMailbox* root_mb = (XgMailbox*)(c.heap[p.xg_root] + kOffMailbox);
+  fault_delay(c);
+  if (seq >= 3 && !wait_flag_ge(&my_mb->ack, seq - 2, c)) return;  // slot still unread by the root
+  unsigned long long bits = 0;
+  if (sizeof(acc_t) == 8) bits = (unsigned long long)__double_as_longlong((double)a);
+  else if (R::kIsInt) bits = (unsigned long long)(unsigned int)(int)a;
+  else bits = (unsigned long long)__float_as_uint((float)a);
+  if (!c.fault_skip_signal) {
+    st_relaxed_sys_u64(&root_mb->val[slot][c.rank], bits);
+    st_release_sys(&root_mb->flag[c.rank], seq);
+  }
+  auto from_bits = [](unsigned long long b) -> acc_t {
+    if (sizeof(acc_t) == 8) return (acc_t)__longlong_as_double((long long)b);
+    if (R::kIsInt) return (acc_t)(int)(unsigned int)b;
+    return (acc_t)__uint_as_float((unsigned int)b);
+  };
+  if (c.rank == p.xg_root) {
+    acc_t acc = F::identity();
+    for (int r = 0; r < c.nranks; ++r) {
+      if (!wait_flag_ge(&my_mb->flag[r], seq, c)) return;
+      acc = F::apply(acc, from_bits(ld_relaxed_sys_u64(&my_mb->val[slot][r])));
+    }
+    store_result<R>(p, acc);
+    unsigned long long rb = 0;
+    if (sizeof(acc_t) == 8) rb = (unsigned long long)__double_as_longlong((double)acc);
+    else if (R::kIsInt) rb = (unsigned long long)(unsigned int)(int)acc;
+    else rb = (unsigned long long)__float_as_uint((float)acc);
+    for (int r = 0; r < c.nranks; ++r) {
+      XgMailbox* mb = (XgMailbox*)(c.heap[r] + kOffMailbox);
+      if (p.xg_all) {
+        st_relaxed_sys_u64(&mb->result[slot], rb);
+        st_release_sys(&mb->result_flag, seq);
+      }
+      st_release_sys(&mb->ack, seq);
+    }
+  } else if (p.xg_all) {
+    if (!wait_flag_ge(&my_mb->result_flag, seq, c)) return;
+    store_result<R>(p, from_bits(ld_relaxed_sys_u64(&my_mb->result[slot])));
+  }
+}
+
+template <class R>
+__device__ __forceinline__ void finish_scalar(const LocalParams& p, typename R::acc_t v) {
+  if (p.xg_ctx) xgpu_finish<R>(p, v);
+  else store_result<R>(p, v);
 }
 
 // Everything after the streaming loop. `tv` is the per-thread value.
@@ -98,7 +164,7 @@ __device__ __forceinline__ void finish_block(typename R::acc_t tv, const LocalPa
 
   if (nparts == 1) {
     if (threadIdx.x == 0) {
-      store_result<R>(p, v);
+      finish_scalar<R>(p, v);
       if (p.trace) p.trace[4 * blockIdx.x + 3] = globaltimer_ns();
     }
     return;
@@ -120,8 +186,8 @@ __device__ __forceinline__ void finish_block(typename R::acc_t tv, const LocalPa
   for (unsigned i = threadIdx.x; i < nparts; i += blockDim.x) a = F::apply(a, ld_cg(partials + i));
   a = block_reduce<R>(a, s_scratch);
   if (threadIdx.x == 0) {
-    store_result<R>(p, a);
     *p.ticket = 0;  // re-arm for the next (stream-ordered) launch
+    finish_scalar<R>(p, a);
     if (p.trace) p.trace[4 * blockIdx.x + 3] = globaltimer_ns();
   }
 }
@@ -139,7 +205,7 @@ __device__ __forceinline__ void add_edges(typename R::Thread& acc, const LocalPa
 
 // ------------------------------------------------------------------------------------------------ LDG variant
 template <int D, int O, int VECW, int UNROLL, bool CLUSTER>
-__global__ void __launch_bounds__(512) reduce_ldg_kernel(const __grid_constant__ LocalParams p) {
+__device__ __forceinline__ void reduce_ldg_body(const LocalParams& p) {
   using R = Reducer<D, O>;
   using Vec = typename std::conditional<VECW == 8, V32, V16>::type;
   constexpr unsigned kAlign = 128 / sizeof(Vec);
@@ -177,6 +243,22 @@ __global__ void __launch_bounds__(512) reduce_ldg_kernel(const __grid_constant__
   if (p.trace && threadIdx.x == 0) p.trace[4 * blockIdx.x + 1] = globaltimer_ns();
 
   finish_block<R, CLUSTER>(acc.collapse(), p);
+}
+
+template <int D, int O, int VECW, int UNROLL, bool CLUSTER>
+__global__ void __launch_bounds__(512) reduce_ldg_kernel(const __grid_constant__ LocalParams p) {
+  reduce_ldg_body<D, O, VECW, UNROLL, CLUSTER>(p);
+}
+
+// Loopback flavour: gridDim.y virtual ranks in ONE (cooperative) launch, blockIdx.y picks the rank's parameters, so the
+// cross-rank mailbox protocol of xgpu_finish can be exercised on a single GPU without co-scheduling separate kernels.
+constexpr int kMultiMaxRanks = 8;
+struct MultiLocalParams {
+  LocalParams p[kMultiMaxRanks];
+};
+template <int D, int O>
+__global__ void __launch_bounds__(512) reduce_ldg_multi_kernel(const __grid_constant__ MultiLocalParams mp) {
+  reduce_ldg_body<D, O, 4, 4, false>(mp.p[blockIdx.y]);
 }
 
 // ------------------------------------------------------------------------------------------------ TMA (bulk-copy) variant
@@ -277,5 +359,7 @@ struct LaunchGeom {
 
 template <int D>
 b2r_status_t launch_local(int op, const LaunchGeom& g, const LocalParams& p, cudaStream_t stream);
+template <int D>
+b2r_status_t launch_local_multi(int op, int nranks, int ctas, int threads, const MultiLocalParams& mp, cudaStream_t stream);
 
 }  // namespace b2r

@@ -70,7 +70,26 @@ b2r_status_t launch_op(const LaunchGeom& g, const LocalParams& p, cudaStream_t s
   return B2R_OK;
 }
 
+template <int D, int O>
+b2r_status_t launch_multi_op(int nranks, int ctas, int threads, const MultiLocalParams& mp, cudaStream_t stream) {
+  // cooperative launch: all gridDim.x * nranks CTAs must be co-resident because ranks wait for one another
+  void* args[] = {(void*)&mp};
+  B2R_CUDA_CHECK(cudaLaunchCooperativeKernel((const void*)reduce_ldg_multi_kernel<D, O>, dim3((unsigned)ctas, (unsigned)nranks), dim3((unsigned)threads),
+                                             args, 0, stream));
+  return B2R_OK;
+}
+
 }  // namespace
+
+template <>
+b2r_status_t launch_local_multi<B2R_LAUNCH_DTYPE>(int op, int nranks, int ctas, int threads, const MultiLocalParams& mp, cudaStream_t stream) {
+  switch (op) {
+    case B2R_SUM: return launch_multi_op<B2R_LAUNCH_DTYPE, B2R_SUM>(nranks, ctas, threads, mp, stream);
+    case B2R_MIN: return launch_multi_op<B2R_LAUNCH_DTYPE, B2R_MIN>(nranks, ctas, threads, mp, stream);
+    case B2R_MAX: return launch_multi_op<B2R_LAUNCH_DTYPE, B2R_MAX>(nranks, ctas, threads, mp, stream);
+  }
+  return fail(B2R_ERR_INVALID, "launch_local_multi: bad op %d", op);
+}
 
 template <>
 b2r_status_t launch_local<B2R_LAUNCH_DTYPE>(int op, const LaunchGeom& g, const LocalParams& p, cudaStream_t stream) {

@@ -12,6 +12,7 @@
 #include "../util/check.h"
 #include "b2r.h"
 #include "reduce_kernels.cuh"
+#include "reduce_internal.h"
 #include "workspace.h"
 
 namespace b2r {
@@ -142,9 +143,6 @@ b2r_status_t plan_local(uint64_t count, b2r_dtype_t dtype, b2r_op_t op, int sm_c
   return B2R_OK;
 }
 
-template <int D>
-b2r_status_t launch_local(int op, const LaunchGeom& g, const LocalParams& p, cudaStream_t stream);
-
 b2r_status_t launch_any(b2r_dtype_t dtype, int op, const LaunchGeom& g, const LocalParams& p, cudaStream_t stream) {
   switch (dtype) {
     case B2R_INT32: return launch_local<B2R_INT32>(op, g, p, stream);
@@ -166,8 +164,9 @@ void split_edges(const void* in, uint64_t count, size_t esz, unsigned vec_bytes,
   p->tail = count - head - p->nvec * (vec_bytes / esz);
 }
 
-b2r_status_t reduce_local_impl(const void* in, void* out, uint64_t count, b2r_dtype_t dtype, b2r_op_t op,
-                               b2r_workspace* ws, cudaStream_t stream, const b2r_launch_cfg_t* cfg, int out_as_acc) {
+// Validates the arguments, plans the launch and fills the kernel parameters (no launch).
+b2r_status_t prepare_local(const void* in, void* out, uint64_t count, b2r_dtype_t dtype, b2r_op_t op, b2r_workspace* ws,
+                           const b2r_launch_cfg_t* cfg, int out_as_acc, LaunchGeom* g, LocalParams* pp) {
   B2R_REQUIRE(ws != nullptr, "b2r_reduce_local: workspace is NULL");
   B2R_REQUIRE(out != nullptr, "b2r_reduce_local: out is NULL");
   B2R_REQUIRE(in != nullptr || count == 0, "b2r_reduce_local: in is NULL");
@@ -175,16 +174,14 @@ b2r_status_t reduce_local_impl(const void* in, void* out, uint64_t count, b2r_dt
   B2R_REQUIRE(op >= B2R_SUM && op <= B2R_MAX, "b2r_reduce_local: bad op %d", (int)op);
   const size_t esz = b2r_dtype_size(dtype);
   B2R_REQUIRE(((uintptr_t)in % esz) == 0, "b2r_reduce_local: input pointer %p is not aligned to the element size %zu", in, esz);
-
-  LaunchGeom g;
-  LocalParams p;
+  LocalParams& p = *pp;
   memset(&p, 0, sizeof(p));
   int stages = 0, tile_vecs = 0;
-  B2R_CHECK(plan_local(count, dtype, op, ws->sm_count, cfg, &g, &stages, &tile_vecs));
+  B2R_CHECK(plan_local(count, dtype, op, ws->sm_count, cfg, g, &stages, &tile_vecs));
   p.in = in;
   p.out = out;
   p.n = count;
-  split_edges(in, count, esz, g.variant == B2R_VARIANT_LDG256 ? 32u : 16u, &p);
+  split_edges(in, count, esz, g->variant == B2R_VARIANT_LDG256 ? 32u : 16u, &p);
   p.partials = ws->d_partials;
   p.ticket = ws->d_ticket;
   p.trace = ws->trace_enabled ? ws->d_trace : nullptr;
@@ -192,20 +189,56 @@ b2r_status_t reduce_local_impl(const void* in, void* out, uint64_t count, b2r_dt
   p.tile_vecs = tile_vecs;
   p.out_as_acc = out_as_acc;
   // never overlap with the previous launch if this input could be that launch's output scalar
-  if (g.pdl && ws->last_out) {
+  if (g->pdl && ws->last_out) {
     const char* lo = (const char*)in;
     const char* hi = lo + count * esz;
     const char* o = (const char*)ws->last_out;
-    if (o + 8 > lo && o < hi) g.pdl = 0;
+    if (o + 8 > lo && o < hi) g->pdl = 0;
   }
-  p.pdl = g.pdl;
+  p.pdl = g->pdl;
   ws->last_out = out;
-  ws->last_ctas = g.ctas;
-  ws->last_geom[0] = g.variant;
-  ws->last_geom[1] = g.threads;
-  ws->last_geom[2] = g.ctas;
-  ws->last_geom[3] = g.cluster;
+  ws->last_ctas = g->ctas;
+  ws->last_geom[0] = g->variant;
+  ws->last_geom[1] = g->threads;
+  ws->last_geom[2] = g->ctas;
+  ws->last_geom[3] = g->cluster;
+  return B2R_OK;
+}
+
+b2r_status_t reduce_local_impl(const void* in, void* out, uint64_t count, b2r_dtype_t dtype, b2r_op_t op,
+                               b2r_workspace* ws, cudaStream_t stream, const b2r_launch_cfg_t* cfg, int out_as_acc,
+                               const XgCall* xg) {
+  B2R_REQUIRE(ws != nullptr, "b2r_reduce_local: workspace is NULL");
+  // launch on the workspace's device whatever the caller's current device is (cheap when they already agree)
+  int cur = -1;
+  B2R_CUDA_CHECK(cudaGetDevice(&cur));
+  struct DeviceGuard {
+    int prev;
+    bool active;
+    ~DeviceGuard() { if (active) cudaSetDevice(prev); }
+  } guard{cur, cur != ws->device};
+  if (guard.active) B2R_CUDA_CHECK(cudaSetDevice(ws->device));
+  LaunchGeom g;
+  LocalParams p;
+  B2R_CHECK(prepare_local(in, out, count, dtype, op, ws, cfg, out_as_acc, &g, &p));
+  if (xg) {
+    p.xg_ctx = xg->ctx;
+    p.xg_root = xg->root;
+    p.xg_all = xg->all;
+    p.xg_seq = xg->seq;
+    p.pdl = g.pdl = 0;
+  }
   return launch_any(dtype, (int)op, g, p, stream);
+}
+
+b2r_status_t launch_multi_any(b2r_dtype_t dtype, int op, int nranks, int ctas, int threads, const MultiLocalParams& mp, cudaStream_t stream) {
+  switch (dtype) {
+    case B2R_INT32: return launch_local_multi<B2R_INT32>(op, nranks, ctas, threads, mp, stream);
+    case B2R_FLOAT32: return launch_local_multi<B2R_FLOAT32>(op, nranks, ctas, threads, mp, stream);
+    case B2R_FLOAT64: return launch_local_multi<B2R_FLOAT64>(op, nranks, ctas, threads, mp, stream);
+    case B2R_BFLOAT16: return launch_local_multi<B2R_BFLOAT16>(op, nranks, ctas, threads, mp, stream);
+  }
+  return fail(B2R_ERR_INVALID, "bad dtype %d", (int)dtype);
 }
 
 }  // namespace b2r
@@ -260,12 +293,12 @@ b2r_status_t b2r_workspace_destroy(b2r_workspace_t ws) {
 
 b2r_status_t b2r_reduce_local(const void* in, void* out, uint64_t count, b2r_dtype_t dtype, b2r_op_t op,
                               b2r_workspace_t ws, void* stream) {
-  return reduce_local_impl(in, out, count, dtype, op, ws, (cudaStream_t)stream, nullptr, 0);
+  return reduce_local_impl(in, out, count, dtype, op, ws, (cudaStream_t)stream, nullptr, 0, nullptr);
 }
 
 b2r_status_t b2r_reduce_local_ex(const void* in, void* out, uint64_t count, b2r_dtype_t dtype, b2r_op_t op,
                                  b2r_workspace_t ws, void* stream, const b2r_launch_cfg_t* cfg) {
-  return reduce_local_impl(in, out, count, dtype, op, ws, (cudaStream_t)stream, cfg, 0);
+  return reduce_local_impl(in, out, count, dtype, op, ws, (cudaStream_t)stream, cfg, 0, nullptr);
 }
 
 b2r_status_t b2r_plan_local(uint64_t count, b2r_dtype_t dtype, b2r_op_t op, int device, const b2r_launch_cfg_t* hint,
@@ -366,7 +399,7 @@ b2r_status_t b2r_reduce_from_host(const void* host_in, void* out_host, uint64_t 
                                    ws->copy_stream));
     B2R_CUDA_CHECK(cudaEventRecord(ws->ev_copied[b], ws->copy_stream));
     B2R_CUDA_CHECK(cudaStreamWaitEvent(stream, ws->ev_copied[b], 0));
-    B2R_CHECK(reduce_local_impl(ws->d_stage[b], (char*)ws->d_chunk_out + c * acc_sz, n, dtype, op, ws, stream, nullptr, 1));
+    B2R_CHECK(reduce_local_impl(ws->d_stage[b], (char*)ws->d_chunk_out + c * acc_sz, n, dtype, op, ws, stream, nullptr, 1, nullptr));
     B2R_CUDA_CHECK(cudaEventRecord(ws->ev_consumed[b], stream));
   }
   if (nchunks) {

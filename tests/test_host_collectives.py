@@ -1,0 +1,69 @@
+"""CPU-only: the collective algorithms on the host loopback transport (threads as ranks, src/coll/host_algos.h) against
+an element-wise oracle — MPI_Reduce semantics (mpi/reduce.c:76,90): recv[j] = op over ranks of send_r[j], valid at root."""
+import pytest
+import torch
+
+import cuda_mpi_reductions_b200 as b2r
+from cuda_mpi_reductions_b200 import _lib
+from cuda_mpi_reductions_b200.parallel import host_reduce_threads
+
+DTYPES = [torch.int32, torch.float32, torch.float64, torch.bfloat16]
+
+
+def elementwise_oracle(xs, op):
+    """Left-to-right combine in rank order; bf16 combined in fp32 and rounded once (the library's definition)."""
+    if xs[0].dtype == torch.bfloat16:
+        acc = xs[0].float()
+        for x in xs[1:]:
+            acc = acc + x.float() if op == "sum" else (torch.minimum(acc, x.float()) if op == "min" else torch.maximum(acc, x.float()))
+        return acc.bfloat16()
+    acc = xs[0].clone()
+    for x in xs[1:]:
+        b2r.combine_oracle(acc, x, op)
+    return acc
+
+
+@pytest.mark.parametrize("nranks", [1, 2, 3, 4, 7, 8])
+@pytest.mark.parametrize("algo", ["oneshot", "twoshot", "tree"])
+@pytest.mark.parametrize("dtype", DTYPES)
+def test_reduce_and_allreduce(nranks, algo, dtype):
+    for count in (1, 5, 1023):
+        xs = [b2r.fill_host(count, dtype, seed=100 * r + count, mode="signed") for r in range(nranks)]
+        for op in ("sum", "min", "max"):
+            want = elementwise_oracle(xs, op)
+            for root in {0, nranks - 1, nranks // 2}:
+                got = host_reduce_threads(xs, op, root, algo)
+                if algo == "tree" and op == "sum" and dtype.is_floating_point:
+                    tol = {torch.float32: 1e-5, torch.float64: 1e-13, torch.bfloat16: 0.07}[dtype]
+                    assert torch.allclose(got.double(), want.double(), rtol=tol, atol=tol)  # tree order != rank order
+                else:
+                    assert torch.equal(got.view(torch.uint8), want.view(torch.uint8)), (nranks, algo, dtype, op, root, count)
+            allr = host_reduce_threads(xs, op, -1, algo)
+            for r in range(nranks):
+                if algo == "tree" and op == "sum" and dtype.is_floating_point:
+                    assert torch.allclose(allr[r].double(), want.double(), rtol=0.07, atol=0.07)
+                else:
+                    assert torch.equal(allr[r].view(torch.uint8), want.view(torch.uint8))
+            # every rank holds the SAME bits after an allreduce
+            for r in range(1, nranks):
+                assert torch.equal(allr[r].view(torch.uint8), allr[0].view(torch.uint8))
+
+
+def test_int_sum_wraps_across_ranks():
+    xs = [torch.full((64,), 2**31 - 1, dtype=torch.int32) for _ in range(3)]
+    got = host_reduce_threads(xs, "sum", 0, "twoshot")
+    want = ((3 * (2**31 - 1) + 2**31) % 2**32) - 2**31
+    assert (got == want).all()
+
+
+def test_algo_selection_is_pure_and_sensible():
+    sel = _lib.LIB.b2r_select_algo
+    # small messages: one-shot; large: NVLS when available and the instruction exists, else two-shot
+    assert sel(1, 1024, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_ONESHOT
+    assert sel(1, 1 << 30, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS
+    assert sel(1, 1 << 30, _lib.FLOAT32, _lib.SUM, 8, 0) == _lib.ALGO_TWOSHOT
+    assert sel(1, 1 << 30, _lib.FLOAT32, _lib.MIN, 8, 1) == _lib.ALGO_TWOSHOT  # no multimem min for fp32
+    assert sel(1, 1 << 30, _lib.FLOAT64, _lib.MAX, 8, 1) == _lib.ALGO_TWOSHOT
+    assert sel(1, 1 << 30, _lib.BFLOAT16, _lib.MAX, 8, 1) == _lib.ALGO_NVLS
+    assert sel(0, 1 << 30, _lib.INT32, _lib.SUM, 8, 1) == _lib.ALGO_TWOSHOT  # 4-byte multimem ops: P2P vectors are faster
+    assert sel(0, 64, _lib.FLOAT64, _lib.SUM, 2, 0) == _lib.ALGO_ONESHOT
