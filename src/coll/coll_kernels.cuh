@@ -114,16 +114,35 @@ struct VecOps<B2R_BFLOAT16, O> {
   }
 };
 
-// scalar element combine for the (< 16 byte) tail
+// scalar helpers for the (< 16 byte) tail: same accumulator precision and single final rounding as the vector path
+template <int D>
+struct TailAcc { using type = float; };
+template <>
+struct TailAcc<B2R_INT32> { using type = int32_t; };
+template <>
+struct TailAcc<B2R_FLOAT64> { using type = double; };
+
+template <int D>
+__device__ __forceinline__ typename TailAcc<D>::type tail_load(const char* p) {
+  if constexpr (D == B2R_INT32) return *(const volatile int32_t*)p;
+  else if constexpr (D == B2R_FLOAT32) return *(const volatile float*)p;
+  else if constexpr (D == B2R_FLOAT64) return *(const volatile double*)p;
+  else return __uint_as_float(((uint32_t) * (const volatile uint16_t*)p) << 16);
+}
 template <int D, int O>
-__device__ __forceinline__ void combine_tail_elem(char* dst, const char* a, const char* b) {
-  if (D == B2R_INT32) *(int32_t*)dst = OpI32<O>::apply(*(const volatile int32_t*)a, *(const volatile int32_t*)b);
-  else if (D == B2R_FLOAT32) *(float*)dst = OpF32<O>::apply(*(const volatile float*)a, *(const volatile float*)b);
-  else if (D == B2R_FLOAT64) *(double*)dst = OpF64<O>::apply(*(const volatile double*)a, *(const volatile double*)b);
+__device__ __forceinline__ typename TailAcc<D>::type tail_apply(typename TailAcc<D>::type a, typename TailAcc<D>::type b) {
+  if constexpr (D == B2R_INT32) return OpI32<O>::apply(a, b);
+  else if constexpr (D == B2R_FLOAT64) return OpF64<O>::apply(a, b);
+  else return OpF32<O>::apply(a, b);
+}
+template <int D>
+__device__ __forceinline__ void tail_store(char* p, typename TailAcc<D>::type v) {
+  if constexpr (D == B2R_INT32) *(volatile int32_t*)p = v;
+  else if constexpr (D == B2R_FLOAT32) *(volatile float*)p = v;
+  else if constexpr (D == B2R_FLOAT64) *(volatile double*)p = v;
   else {
-    const float x = __uint_as_float(((uint32_t) * (const volatile uint16_t*)a) << 16);
-    const float y = __uint_as_float(((uint32_t) * (const volatile uint16_t*)b) << 16);
-    *(__nv_bfloat16*)dst = __float2bfloat16_rn(OpF32<O>::apply(x, y));
+    __nv_bfloat16 h = __float2bfloat16_rn(v);
+    *(volatile uint16_t*)p = *reinterpret_cast<uint16_t*>(&h);
   }
 }
 
@@ -232,12 +251,9 @@ __device__ __forceinline__ void combine_tail(unsigned long long first_elem, unsi
   constexpr int E = VecOps<D, O>::kElem;
   if (blockIdx.x != 0) return;
   for (unsigned long long e = first_elem + threadIdx.x; e < count; e += blockDim.x) {
-    // combine in a local 8-byte slot, then fan out
-    alignas(8) char tmp[8];
-    for (int k = 0; k < E; ++k) tmp[k] = ((const volatile char*)(src[0] + e * E))[k];
-    for (int s = 1; s < nsrc; ++s) combine_tail_elem<D, O>(tmp, tmp, src[s] + e * E);
-    for (int d = 0; d < ndst; ++d)
-      for (int k = 0; k < E; ++k) ((volatile char*)(dst[d] + e * E))[k] = tmp[k];
+    typename TailAcc<D>::type acc = tail_load<D>(src[0] + e * E);
+    for (int s = 1; s < nsrc; ++s) acc = tail_apply<D, O>(acc, tail_load<D>(src[s] + e * E));
+    for (int d = 0; d < ndst; ++d) tail_store<D>(dst[d] + e * E, acc);
   }
 }
 

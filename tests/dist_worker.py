@@ -1,0 +1,96 @@
+"""Worker for the multi-process tests: launched by torchrun (one process per GPU) or by test_dist_cpu.py (gloo, CPU).
+GPU mode checks the real NVLink path: Communicator.from_torch_distributed() -> VMM export/import over the Unix-socket
+bootstrap -> fused collectives, against torch.distributed (NCCL) and the CPU oracle. Exit code 0 = all checks passed."""
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import cuda_mpi_reductions_b200 as b2r  # noqa: E402
+from cuda_mpi_reductions_b200.parallel import Communicator  # noqa: E402
+
+
+def main():
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ.get("LOCAL_RANK", os.environ["RANK"]))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    comm = Communicator.from_torch_distributed(heap_bytes=256 << 20, timeout_ms=20000)
+    assert comm.rank == rank and comm.size == world
+    if rank == 0:
+        print(f"world={world} multicast={comm.has_multicast}", flush=True)
+    algos = ["oneshot", "twoshot", "tree"] + (["nvls"] if comm.has_multicast else [])
+    fails = 0
+    for dtype in (torch.int32, torch.float32, torch.float64, torch.bfloat16):
+        for count in (1, 1000, 65537, (1 << 22) + 3):
+            x = b2r.fill_device(count, dtype, seed=100 + rank, mode="signed")
+            gathered = [torch.empty_like(x) for _ in range(world)]
+            dist.all_gather(gathered, x)
+            hs = [g.cpu() for g in gathered]
+            for op in ("sum", "min", "max"):
+                for algo in algos:
+                    if algo == "nvls" and dtype in (torch.float32, torch.float64) and op != "sum":
+                        continue
+                    if dtype == torch.bfloat16:
+                        acc = hs[0].float()
+                        for h in hs[1:]:
+                            acc = acc + h.float() if op == "sum" else (torch.minimum(acc, h.float()) if op == "min" else torch.maximum(acc, h.float()))
+                        want = acc.bfloat16()
+                    else:
+                        want = hs[0].clone()
+                        for h in hs[1:]:
+                            b2r.combine_oracle(want, h, op)
+                    out = comm.allreduce(x, op, algo=algo)
+                    comm.check()
+                    exact = algo in ("oneshot", "twoshot") or op != "sum" or dtype == torch.int32
+                    got = out.cpu()
+                    ok = torch.equal(got, want) if exact else torch.allclose(got.double(), want.double(), rtol=2e-2 if dtype == torch.bfloat16 else 1e-5, atol=1e-5)
+                    if not ok:
+                        fails += 1
+                        print(f"[rank {rank}] allreduce MISMATCH dtype={dtype} count={count} op={op} algo={algo}", flush=True)
+                    root = (count + rank * 0) % world
+                    red = comm.reduce(x, op, root=root, algo=algo)
+                    comm.check()
+                    if rank == root:
+                        got = red.cpu()
+                        ok = torch.equal(got, want) if exact else torch.allclose(got.double(), want.double(), rtol=2e-2 if dtype == torch.bfloat16 else 1e-5, atol=1e-5)
+                        if not ok:
+                            fails += 1
+                            print(f"[rank {rank}] reduce MISMATCH dtype={dtype} count={count} op={op} algo={algo} root={root}", flush=True)
+            # scalar sharded
+            for op in ("sum", "max"):
+                whole = torch.cat(hs)
+                want = b2r.reduce_oracle(whole, op)
+                for allflag in (False, True):
+                    o = comm.reduce_scalar_sharded(x, op, root=world - 1, all=allflag)
+                    comm.check()
+                    if o is not None:
+                        g = o.cpu()
+                        tol = {torch.int32: 0, torch.float32: 1e-5, torch.float64: 1e-12, torch.bfloat16: 2.0**-7}[dtype]
+                        if abs(g.double().item() - want.double().item()) > tol * max(1.0, abs(want.double().item())):
+                            fails += 1
+                            print(f"[rank {rank}] scalar MISMATCH dtype={dtype} count={count} op={op} got={g.item()} want={want.item()}", flush=True)
+    # symmetric zero-copy + in place + stress of small back-to-back collectives
+    s = comm.symm_empty(1 << 20, torch.float32)
+    s.fill_(float(rank + 1))
+    for i in range(200):
+        comm.allreduce(s, "max", out=s, algo=algos[i % len(algos)] if algos[i % len(algos)] != "nvls" else "twoshot")
+    comm.check()
+    if not bool((s == world).all()):
+        fails += 1
+        print(f"[rank {rank}] in-place symmetric stress MISMATCH", flush=True)
+    comm.barrier()
+    comm.check()
+    t = torch.tensor([fails], device=dev)
+    dist.all_reduce(t)
+    comm.close()
+    dist.destroy_process_group()
+    if rank == 0:
+        print("DIST_WORKER " + ("PASSED" if t.item() == 0 else f"FAILED ({t.item()} mismatches)"), flush=True)
+    sys.exit(0 if t.item() == 0 else 1)
+
+
+if __name__ == "__main__":
+    main()
