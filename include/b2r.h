@@ -116,6 +116,24 @@ b2r_status_t b2r_reduce_local(const void* in, void* out, uint64_t count, b2r_dty
 b2r_status_t b2r_reduce_local_ex(const void* in, void* out, uint64_t count, b2r_dtype_t dtype, b2r_op_t op,
                                  b2r_workspace_t ws, void* stream, const b2r_launch_cfg_t* cfg);
 
+/* The same reduction for callers that cannot allocate device memory. (No counterpart in the reference: its sample
+ * cudaMallocs its block-partial buffer in the driver, reduction.cpp:721-722.) Who needs it: a process whose device
+ * memory is entirely owned by another allocator, a latency-critical loop that may not run anything that synchronises the
+ * device (cudaMalloc / cudaFree do), or a hook / callback whose contract forbids allocation calls. Instead of a
+ * b2r_workspace the kernel's scratch (block partials + ticket) is a static 8448-byte __device__ array inside libb2r.so,
+ * resident on every GPU that loads the library until the process exits.
+ *  - Limit: at most B2R_NOALLOC_MAX_PARTIALS block partials fit; a geometry that needs more (cfg->ctas / cluster above
+ *    it) returns B2R_ERR_INVALID. The default geometry stays below the limit for every count.
+ *  - This call makes no cudaMalloc / cudaFree / allocating library call. It enqueues a 4-byte memset of the ticket (the
+ *    only scratch word that must start at zero; the array otherwise keeps the previous call's contents) and the kernel.
+ *  - All calls on one GPU share the array: calls that overlap on the GPU race. Keep them on one stream.
+ *  - The first call on each device does a one-time set-up with that device current (looks up the array's device
+ *    address); issue it before any stream capture begins.
+ *  - Launches on the CURRENT device; variants ldg128 / ldg256 only; cfg may be NULL. */
+#define B2R_NOALLOC_MAX_PARTIALS 1024
+b2r_status_t b2r_reduce_local_noalloc(const void* in, void* out, uint64_t count, b2r_dtype_t dtype, b2r_op_t op, void* stream,
+                                      const b2r_launch_cfg_t* cfg);
+
 /* Transform-reduce (vendored scalarProd analogue, scalarProd_kernel.cu:33-80): out[0] = sum_i a[i]*b[i].
  * fp32/fp64/bf16 (bf16 accumulates in fp32) and int32 (wrap). */
 b2r_status_t b2r_dot_local(const void* a, const void* b, void* out, uint64_t count, b2r_dtype_t dtype,
