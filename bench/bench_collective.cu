@@ -1,0 +1,301 @@
+// bench_collective.cu — multi-GPU reduce / allreduce benchmark: the reference's MPI_Reduce loop on NVLink.
+//
+// Counterpart of mpi/reduce.c (main :9-108). Default mode reproduces it: a fixed TOTAL problem (512 Mi int32 / 256 Mi fp64 =
+// 2 GiB each, mpi/constants.h:1-2) is sharded over the P ranks (count = total / P, reduce.c:43-44), one untimed warm-up,
+// then RETRY_COUNT=5 x {MAX, MIN, SUM} x {INT, DOUBLE} element-wise reductions to root 0, printing the reference's rows
+//     # DATATYPE OP NODES GB/sec
+//     INT MAX 8    123.456          <- (total bytes / time) / 2^30, the reference's unit (reduce.c:79,93)
+// so mpi/getAvgs.sh-style tooling and makePlots.gp work unchanged on the output. Differences by design (SURVEY §2.7
+// items 8-10): a device barrier before every timed call, device-event timing, MAX over ranks instead of rank 0's clock;
+// decimal GB/s and bus bandwidth go to the JSONL/CSV sink, not into the reference-format rows.
+//
+//   bench_collective [--gpus=N] [--total-mib=2048] [--retries=5] [--types=INT,DOUBLE[,BF16,FLOAT]] [--coll=reduce|allreduce]
+//                    [--algo=auto|oneshot|twoshot|tree|nvls] [--root=0] [--check] [--jsonl=path] [--raw=path]
+//   bench_collective --sweep [--min-bytes=1024] [--max-bytes=4294967296] [--types=...] [--colls=reduce,allreduce]
+//                    [--algos=auto,oneshot,twoshot,tree,nvls] [--iters=20] [--jsonl=path] [--csv=path]
+// Runs as ONE process driving all GPUs (b2r_comm_init_all); buffers come from the symmetric heap (zero copy).
+#include <algorithm>
+#include <cmath>
+#include <sstream>
+
+#include "bench_common.h"
+
+using namespace b2rbench;
+
+namespace {
+
+struct Rank {
+  int dev;
+  b2r_comm_t comm;
+  cudaStream_t stream;
+  cudaEvent_t e0, e1;
+  void* send;
+  void* recv;
+};
+
+std::vector<std::string> split(const std::string& s, char sep = ',') {
+  std::vector<std::string> out;
+  std::stringstream ss(s);
+  std::string item;
+  while (std::getline(ss, item, sep))
+    if (!item.empty()) out.push_back(item);
+  return out;
+}
+
+const char* ref_type_name(b2r_dtype_t d) {
+  switch (d) {
+    case B2R_INT32: return "INT";
+    case B2R_FLOAT32: return "FLOAT";
+    case B2R_FLOAT64: return "DOUBLE";
+    case B2R_BFLOAT16: return "BF16";
+  }
+  return "?";
+}
+bool parse_ref_type(const std::string& s, b2r_dtype_t* d) { return parse_dtype(s, d); }
+
+b2r_algo_t parse_algo(const std::string& s) {
+  if (s == "oneshot") return B2R_ALGO_ONESHOT;
+  if (s == "twoshot") return B2R_ALGO_TWOSHOT;
+  if (s == "tree") return B2R_ALGO_TREE;
+  if (s == "nvls") return B2R_ALGO_NVLS;
+  return B2R_ALGO_AUTO;
+}
+
+// One timed collective (or `iters` back-to-back): returns milliseconds per call, max over ranks; <0 on failure.
+double timed(std::vector<Rank>& R, bool allreduce, uint64_t count, b2r_dtype_t dt, b2r_op_t op, int root, b2r_algo_t algo, int iters) {
+  for (auto& r : R) {
+    cudaSetDevice(r.dev);
+    if (b2r_barrier(r.comm, r.stream) != B2R_OK) return -1;  // every rank enters the timed region together
+  }
+  for (auto& r : R) {
+    cudaSetDevice(r.dev);
+    cudaEventRecord(r.e0, r.stream);
+  }
+  for (int i = 0; i < iters; ++i) {
+    for (auto& r : R) {
+      cudaSetDevice(r.dev);
+      b2r_status_t st = allreduce ? b2r_allreduce_ex(r.send, r.recv, count, dt, op, r.comm, r.stream, algo)
+                                  : b2r_reduce_ex(r.send, r.recv, count, dt, op, root, r.comm, r.stream, algo);
+      if (st != B2R_OK) {
+        fprintf(stderr, "collective failed on rank %d: %s (%s)\n", (int)(&r - &R[0]), b2r_status_string(st), b2r_last_error_string());
+        return -1;
+      }
+    }
+  }
+  for (auto& r : R) {
+    cudaSetDevice(r.dev);
+    cudaEventRecord(r.e1, r.stream);
+  }
+  double worst = 0;
+  for (auto& r : R) {
+    cudaSetDevice(r.dev);
+    if (b2r_comm_check(r.comm, r.stream) != B2R_OK) {
+      fprintf(stderr, "rank %d: %s\n", (int)(&r - &R[0]), b2r_last_error_string());
+      return -1;
+    }
+    float ms = 0;
+    cudaEventElapsedTime(&ms, r.e0, r.e1);
+    worst = std::max(worst, (double)ms / iters);
+  }
+  return worst;
+}
+
+// Fills the send buffers, runs once, and compares the result at root (and at every rank for allreduce) with the CPU
+// element-wise oracle (exact for integers and min/max; NVLS / tree fp sums within a relative bound).
+bool verify(std::vector<Rank>& R, bool allreduce, uint64_t count, b2r_dtype_t dt, b2r_op_t op, int root, b2r_algo_t algo) {
+  const size_t esz = b2r_dtype_size(dt);
+  const uint64_t n = std::min<uint64_t>(count, 1u << 22);  // oracle on the first 4 Mi elements
+  const int P = (int)R.size();
+  std::vector<std::vector<unsigned char>> h(P, std::vector<unsigned char>(n * esz));
+  for (int r = 0; r < P; ++r) {
+    cudaSetDevice(R[r].dev);
+    BENCH_B2R(b2r_fill_device(R[r].send, count, dt, 4242 + r, 0, 2, R[r].stream));
+    BENCH_B2R(b2r_fill_host(h[r].data(), n, dt, 4242 + r, 0, 2));
+  }
+  if (timed(R, allreduce, count, dt, op, root, algo, 1) < 0) return false;
+  std::vector<const void*> srcs(P);
+  for (int r = 0; r < P; ++r) srcs[r] = h[r].data();
+  std::vector<unsigned char> want(n * esz), got(n * esz);
+  BENCH_B2R(b2r_host_reduce_threads(srcs.data(), want.data(), n, dt, op, P, 0, B2R_ALGO_ONESHOT));
+  bool ok = true;
+  for (int r = 0; r < P; ++r) {
+    if (!allreduce && r != root) continue;
+    cudaSetDevice(R[r].dev);
+    BENCH_CUDA(cudaMemcpy(got.data(), R[r].recv, n * esz, cudaMemcpyDeviceToHost));
+    if (memcmp(got.data(), want.data(), n * esz) == 0) continue;
+    // not bit-identical: acceptable only for fp sums whose order differs (tree, NVLS)
+    double worst = 0;
+    for (uint64_t i = 0; i < n; ++i) {
+      double a = 0, b = 0;
+      if (dt == B2R_INT32) { a = ((int32_t*)got.data())[i]; b = ((int32_t*)want.data())[i]; }
+      else if (dt == B2R_FLOAT32) { a = ((float*)got.data())[i]; b = ((float*)want.data())[i]; }
+      else if (dt == B2R_FLOAT64) { a = ((double*)got.data())[i]; b = ((double*)want.data())[i]; }
+      else {
+        uint32_t x = (uint32_t)((uint16_t*)got.data())[i] << 16, y = (uint32_t)((uint16_t*)want.data())[i] << 16;
+        float fa, fb;
+        memcpy(&fa, &x, 4);
+        memcpy(&fb, &y, 4);
+        a = fa;
+        b = fb;
+      }
+      worst = std::max(worst, std::fabs(a - b) / std::max(1.0, std::fabs(b)));
+    }
+    const double tol = dt == B2R_INT32 ? 0 : (dt == B2R_FLOAT64 ? 1e-13 : (dt == B2R_FLOAT32 ? 1e-5 : 2e-2));
+    if (worst > tol || op != B2R_SUM) {
+      fprintf(stderr, "VERIFY FAILED rank %d %s %s count %llu: max rel err %.3g\n", r, ref_type_name(dt), b2r_op_name(op), (unsigned long long)count, worst);
+      ok = false;
+    }
+  }
+  return ok;
+}
+
+}  // namespace
+
+int main(int argc, char** argv) {
+  Flags f;
+  if (!f.parse(argc, argv)) { fprintf(stderr, "%s\n", f.error().c_str()); return 1; }
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { fprintf(stderr, "no CUDA device\n"); return 2; }
+  const int P = (int)f.i64("gpus", ndev);
+  if (P < 1 || P > ndev) { fprintf(stderr, "--gpus=%d but %d devices are visible\n", P, ndev); return 1; }
+  const bool sweep = f.has("sweep");
+  const uint64_t total_bytes = (uint64_t)f.i64("total-mib", 2048) << 20;
+  const uint64_t max_bytes = sweep ? (uint64_t)f.i64("max-bytes", 1ll << 32) : total_bytes / P;
+  const int root = (int)f.i64("root", 0);
+
+  b2r_comm_config_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.heap_bytes = 2 * (max_bytes + 4096) + (1 << 20);
+  cfg.use_multicast = f.has("no-multicast") ? 0 : -1;
+  cfg.symmetric_only = 1;
+  cfg.timeout_ms = (int)f.i64("timeout-ms", 20000);
+  cfg.max_ctas = (int)f.i64("ctas", 0);
+  std::vector<b2r_comm_t> comms(P);
+  std::vector<int> devs(P);
+  for (int i = 0; i < P; ++i) devs[i] = i;
+  BENCH_B2R(b2r_comm_init_all(comms.data(), P, devs.data(), &cfg));
+  int has_mc = 0;
+  b2r_comm_has_multicast(comms[0], &has_mc);
+  std::vector<Rank> R(P);
+  for (int i = 0; i < P; ++i) {
+    R[i].dev = i;
+    R[i].comm = comms[i];
+    BENCH_CUDA(cudaSetDevice(i));
+    BENCH_CUDA(cudaStreamCreateWithFlags(&R[i].stream, cudaStreamNonBlocking));
+    BENCH_CUDA(cudaEventCreate(&R[i].e0));
+    BENCH_CUDA(cudaEventCreate(&R[i].e1));
+    BENCH_B2R(b2r_symm_alloc(comms[i], max_bytes + 4096, &R[i].send));
+    BENCH_B2R(b2r_symm_alloc(comms[i], max_bytes + 4096, &R[i].recv));
+  }
+  fprintf(stderr, "# b200reduce bench_collective: %d GPUs, multicast(NVLS) %s, %s\n", P, has_mc ? "available" : "not available",
+          sweep ? "size sweep" : "reference loop");
+
+  FILE* jsonl = f.has("jsonl") ? fopen(f.str("jsonl").c_str(), "a") : nullptr;
+  FILE* csv = f.has("csv") ? fopen(f.str("csv").c_str(), "a") : nullptr;
+  FILE* raw = f.has("raw") ? fopen(f.str("raw").c_str(), "a") : nullptr;
+  std::vector<b2r_dtype_t> types;
+  for (auto& t : split(f.str("types", sweep ? "INT,DOUBLE,BF16" : "INT,DOUBLE"))) {
+    b2r_dtype_t d;
+    if (!parse_ref_type(t, &d)) { fprintf(stderr, "unknown type %s\n", t.c_str()); return 1; }
+    types.push_back(d);
+  }
+  bool all_ok = true;
+
+  if (!sweep) {
+    const bool allreduce = f.str("coll", "reduce") == "allreduce";
+    const b2r_algo_t algo = parse_algo(f.str("algo", "auto"));
+    const int retries = (int)f.i64("retries", 5);
+    const b2r_op_t ops[3] = {B2R_MAX, B2R_MIN, B2R_SUM};  // the reference's order (reduce.c:26-28)
+    // data: per-rank seeded "full range" values, like genrand_int32 / genrand_res53 with seed {rank, ...} (reduce.c:38-57)
+    for (b2r_dtype_t dt : types) {
+      const uint64_t count = total_bytes / b2r_dtype_size(dt) / P;
+      for (int r = 0; r < P; ++r) {
+        cudaSetDevice(R[r].dev);
+        BENCH_B2R(b2r_fill_device(R[r].send, count, dt, 0x123 + r, 0, 1, R[r].stream));
+      }
+      if (timed(R, allreduce, count, dt, B2R_SUM, root, algo, 1) < 0) return 3;  // warm-up (reduce.c:61-64)
+    }
+    printf("# DATATYPE OP NODES GB/sec\n");
+    if (raw) fprintf(raw, "# DATATYPE OP NODES GB/sec\n");
+    for (int x = 0; x < retries; ++x) {
+      for (b2r_dtype_t dt : types) {
+        const uint64_t count = total_bytes / b2r_dtype_size(dt) / P;
+        for (b2r_op_t op : ops) {
+          for (auto& r : R) {  // bzero(recv) like reduce.c:74
+            cudaSetDevice(r.dev);
+            cudaMemsetAsync(r.recv, 0, count * b2r_dtype_size(dt), r.stream);
+          }
+          const double ms = timed(R, allreduce, count, dt, op, root, algo, 1);
+          if (ms < 0) return 3;
+          const double gib = (double)total_bytes / (ms * 1e-3) / 1073741824.0;
+          printf("%s %s %d %10.3lf\n", ref_type_name(dt), b2r_op_name(op), P, gib);
+          if (raw) fprintf(raw, "%s %s %d %10.3lf\n", ref_type_name(dt), b2r_op_name(op), P, gib);
+          if (jsonl) {
+            const uint64_t bytes = count * b2r_dtype_size(dt);
+            fprintf(jsonl,
+                    "{\"bench\":\"reduce_c_loop\",\"impl\":\"b2r\",\"coll\":\"%s\",\"dtype\":\"%s\",\"op\":\"%s\",\"gpus\":%d,\"bytes_per_rank\":%llu,"
+                    "\"total_bytes\":%llu,\"ms\":%.5f,\"total_GiBps\":%.3f,\"total_GBps\":%.3f,\"algbw_GBps\":%.3f,\"algo\":\"%s\"}\n",
+                    allreduce ? "allreduce" : "reduce", ref_type_name(dt), b2r_op_name(op), P, (unsigned long long)bytes,
+                    (unsigned long long)total_bytes, ms, gib, total_bytes / ms * 1e-6, bytes / ms * 1e-6,
+                    b2r_algo_name(algo == B2R_ALGO_AUTO ? b2r_select_algo(allreduce, bytes, dt, op, P, has_mc) : algo));
+          }
+        }
+      }
+    }
+    if (f.has("check"))
+      for (b2r_dtype_t dt : types)
+        for (b2r_op_t op : ops) all_ok = verify(R, allreduce, total_bytes / b2r_dtype_size(dt) / P, dt, op, root, algo) && all_ok;
+  } else {
+    const uint64_t min_bytes = (uint64_t)f.i64("min-bytes", 1024);
+    const int iters = (int)f.i64("iters", 20);
+    printf("# %-9s %-6s %-4s %-8s %14s %10s %10s %10s\n", "coll", "dtype", "op", "algo", "bytes", "us", "algbw GB/s", "busbw GB/s");
+    for (auto& coll : split(f.str("colls", "reduce,allreduce"))) {
+      const bool allreduce = coll == "allreduce";
+      for (b2r_dtype_t dt : types) {
+        for (auto& opname : split(f.str("ops", "SUM"))) {
+          b2r_op_t op;
+          if (!parse_op(opname, &op)) continue;
+          for (auto& algoname : split(f.str("algos", "auto"))) {
+            const b2r_algo_t algo = parse_algo(algoname);
+            for (uint64_t bytes = min_bytes; bytes <= max_bytes; bytes *= (uint64_t)f.i64("factor", 4)) {
+              const uint64_t count = bytes / b2r_dtype_size(dt);
+              if (count == 0) continue;
+              if (algo == B2R_ALGO_NVLS && !has_mc) continue;
+              if (algo == B2R_ALGO_NVLS && (dt == B2R_FLOAT32 || dt == B2R_FLOAT64) && op != B2R_SUM) continue;
+              if ((algo == B2R_ALGO_ONESHOT || algo == B2R_ALGO_TREE) && bytes > (64ull << 20)) continue;  // pointless at this size
+              if (f.has("check") && bytes <= (256ull << 20)) all_ok = verify(R, allreduce, count, dt, op, root, algo) && all_ok;
+              const int it = bytes >= (1ull << 30) ? std::max(3, iters / 4) : (bytes >= (64ull << 20) ? std::max(5, iters / 2) : iters * 5);
+              if (timed(R, allreduce, count, dt, op, root, algo, 3) < 0) return 3;
+              const double ms = timed(R, allreduce, count, dt, op, root, algo, it);
+              if (ms < 0) return 3;
+              const double algbw = bytes / ms * 1e-6;
+              const double busbw = allreduce ? algbw * 2.0 * (P - 1) / P : algbw;  // nccl-tests convention
+              const b2r_algo_t used = algo == B2R_ALGO_AUTO ? b2r_select_algo(allreduce, bytes, dt, op, P, has_mc) : algo;
+              printf("  %-9s %-6s %-4s %-8s %14llu %10.2f %10.2f %10.2f\n", coll.c_str(), ref_type_name(dt), b2r_op_name(op), b2r_algo_name(used),
+                     (unsigned long long)bytes, ms * 1e3, algbw, busbw);
+              fflush(stdout);
+              if (csv)
+                fprintf(csv, "b2r,%s,%s,%s,%s,%d,%llu,%.3f,%.3f,%.3f\n", coll.c_str(), ref_type_name(dt), b2r_op_name(op), b2r_algo_name(used), P,
+                        (unsigned long long)bytes, ms * 1e3, algbw, busbw);
+              if (jsonl)
+                fprintf(jsonl,
+                        "{\"bench\":\"collective_sweep\",\"impl\":\"b2r\",\"coll\":\"%s\",\"dtype\":\"%s\",\"op\":\"%s\",\"algo\":\"%s\",\"gpus\":%d,"
+                        "\"bytes\":%llu,\"us\":%.3f,\"algbw_GBps\":%.3f,\"busbw_GBps\":%.3f}\n",
+                        coll.c_str(), ref_type_name(dt), b2r_op_name(op), b2r_algo_name(used), P, (unsigned long long)bytes, ms * 1e3, algbw, busbw);
+            }
+          }
+        }
+      }
+    }
+  }
+  if (jsonl) fclose(jsonl);
+  if (csv) fclose(csv);
+  if (raw) fclose(raw);
+  for (auto& r : R) {
+    cudaSetDevice(r.dev);
+    cudaStreamSynchronize(r.stream);
+  }
+  for (auto& c : comms) b2r_comm_destroy(c);
+  if (f.has("check")) printf("%s\n", all_ok ? "PASSED" : "FAILED");
+  return all_ok ? 0 : 1;
+}
