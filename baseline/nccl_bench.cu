@@ -7,6 +7,7 @@
 
 #include <algorithm>
 #include <sstream>
+#include <thread>
 
 #include "../bench/bench_common.h"
 
@@ -49,22 +50,24 @@ static ncclDataType_t nccl_type(b2r_dtype_t d) {
 static ncclRedOp_t nccl_op(b2r_op_t o) { return o == B2R_SUM ? ncclSum : (o == B2R_MIN ? ncclMin : ncclMax); }
 static const char* ref_type_name(b2r_dtype_t d) { return d == B2R_INT32 ? "INT" : d == B2R_FLOAT32 ? "FLOAT" : d == B2R_FLOAT64 ? "DOUBLE" : "BF16"; }
 
+// one host thread per GPU, like bench_collective (and like one MPI rank per GPU)
 static double timed(std::vector<Rank>& R, bool allreduce, uint64_t count, b2r_dtype_t dt, b2r_op_t op, int root, int iters) {
-  for (auto& r : R) { cudaSetDevice(r.dev); cudaStreamSynchronize(r.stream); }
-  // a tiny allreduce as the entry barrier, then the timed region
-  NCCLCHECK(ncclGroupStart());
-  for (auto& r : R) NCCLCHECK(ncclAllReduce(r.recv, r.recv, 1, ncclInt32, ncclSum, r.comm, r.stream));
-  NCCLCHECK(ncclGroupEnd());
-  for (auto& r : R) { cudaSetDevice(r.dev); cudaEventRecord(r.e0, r.stream); }
-  for (int i = 0; i < iters; ++i) {
-    NCCLCHECK(ncclGroupStart());
-    for (auto& r : R) {
-      if (allreduce) NCCLCHECK(ncclAllReduce(r.send, r.recv, count, nccl_type(dt), nccl_op(op), r.comm, r.stream));
-      else NCCLCHECK(ncclReduce(r.send, r.recv, count, nccl_type(dt), nccl_op(op), root, r.comm, r.stream));
-    }
-    NCCLCHECK(ncclGroupEnd());
+  const int P = (int)R.size();
+  std::vector<std::thread> th;
+  for (int i = 0; i < P; ++i) {
+    th.emplace_back([&, i] {
+      Rank& r = R[i];
+      cudaSetDevice(r.dev);
+      NCCLCHECK(ncclAllReduce(r.recv, r.recv, 1, ncclInt32, ncclSum, r.comm, r.stream));  // entry barrier
+      cudaEventRecord(r.e0, r.stream);
+      for (int k = 0; k < iters; ++k) {
+        if (allreduce) NCCLCHECK(ncclAllReduce(r.send, r.recv, count, nccl_type(dt), nccl_op(op), r.comm, r.stream));
+        else NCCLCHECK(ncclReduce(r.send, r.recv, count, nccl_type(dt), nccl_op(op), root, r.comm, r.stream));
+      }
+      cudaEventRecord(r.e1, r.stream);
+    });
   }
-  for (auto& r : R) { cudaSetDevice(r.dev); cudaEventRecord(r.e1, r.stream); }
+  for (auto& t : th) t.join();
   double worst = 0;
   for (auto& r : R) {
     cudaSetDevice(r.dev);

@@ -171,7 +171,7 @@ def run_b2r(args) -> None:
             b2r.reduce(inputs[i % copies], opc, out=out, workspace=ws)
     else:
         def step(i):
-            comm.reduce_scalar_sharded(inputs[i % copies], args.op, root=0, out=out)
+            comm.reduce_scalar_sharded(inputs[i % copies], args.op, root=0, out=out, cfg=cfg)
 
     # correctness of what is being timed (cheap: one step per distinct input, against the CPU oracle)
     step(0)

@@ -17,6 +17,7 @@
 #include <algorithm>
 #include <cmath>
 #include <sstream>
+#include <thread>
 
 #include "bench_common.h"
 
@@ -62,37 +63,40 @@ b2r_algo_t parse_algo(const std::string& s) {
 }
 
 // One timed collective (or `iters` back-to-back): returns milliseconds per call, max over ranks; <0 on failure.
+// One host thread per GPU issues that GPU's launches (like one MPI rank per GPU would), so the host launch rate of a
+// single thread driving P devices does not masquerade as collective latency.
 double timed(std::vector<Rank>& R, bool allreduce, uint64_t count, b2r_dtype_t dt, b2r_op_t op, int root, b2r_algo_t algo, int iters) {
-  for (auto& r : R) {
-    cudaSetDevice(r.dev);
-    if (b2r_barrier(r.comm, r.stream) != B2R_OK) return -1;  // every rank enters the timed region together
-  }
-  for (auto& r : R) {
-    cudaSetDevice(r.dev);
-    cudaEventRecord(r.e0, r.stream);
-  }
-  for (int i = 0; i < iters; ++i) {
-    for (auto& r : R) {
+  const int P = (int)R.size();
+  std::vector<int> failed(P, 0);
+  std::vector<std::thread> th;
+  for (int i = 0; i < P; ++i) {
+    th.emplace_back([&, i] {
+      Rank& r = R[i];
       cudaSetDevice(r.dev);
-      b2r_status_t st = allreduce ? b2r_allreduce_ex(r.send, r.recv, count, dt, op, r.comm, r.stream, algo)
-                                  : b2r_reduce_ex(r.send, r.recv, count, dt, op, root, r.comm, r.stream, algo);
-      if (st != B2R_OK) {
-        fprintf(stderr, "collective failed on rank %d: %s (%s)\n", (int)(&r - &R[0]), b2r_status_string(st), b2r_last_error_string());
-        return -1;
+      if (b2r_barrier(r.comm, r.stream) != B2R_OK) { failed[i] = 1; return; }  // every rank enters the timed region together
+      cudaEventRecord(r.e0, r.stream);
+      for (int k = 0; k < iters; ++k) {
+        b2r_status_t st = allreduce ? b2r_allreduce_ex(r.send, r.recv, count, dt, op, r.comm, r.stream, algo)
+                                    : b2r_reduce_ex(r.send, r.recv, count, dt, op, root, r.comm, r.stream, algo);
+        if (st != B2R_OK) {
+          fprintf(stderr, "collective failed on rank %d: %s (%s)\n", i, b2r_status_string(st), b2r_last_error_string());
+          failed[i] = 1;
+          return;
+        }
       }
-    }
+      cudaEventRecord(r.e1, r.stream);
+    });
   }
-  for (auto& r : R) {
-    cudaSetDevice(r.dev);
-    cudaEventRecord(r.e1, r.stream);
-  }
+  for (auto& t : th) t.join();
   double worst = 0;
-  for (auto& r : R) {
+  for (int i = 0; i < P; ++i) {
+    Rank& r = R[i];
     cudaSetDevice(r.dev);
     if (b2r_comm_check(r.comm, r.stream) != B2R_OK) {
-      fprintf(stderr, "rank %d: %s\n", (int)(&r - &R[0]), b2r_last_error_string());
+      fprintf(stderr, "rank %d: %s\n", i, b2r_last_error_string());
       return -1;
     }
+    if (failed[i]) return -1;
     float ms = 0;
     cudaEventElapsedTime(&ms, r.e0, r.e1);
     worst = std::max(worst, (double)ms / iters);

@@ -97,6 +97,7 @@ def _declare(lib: C.CDLL) -> None:
         ("b2r_reduce_ex", [vp, vp, u64, i, i, i, vp, vp, i]),
         ("b2r_allreduce_ex", [vp, vp, u64, i, i, vp, vp, i]),
         ("b2r_reduce_scalar_sharded", [vp, vp, u64, i, i, i, i, vp, vp]),
+        ("b2r_reduce_scalar_sharded_ex", [vp, vp, u64, i, i, i, i, vp, vp, C.POINTER(LaunchCfg)]),
         ("b2r_barrier", [vp, vp]),
         ("b2r_select_algo", [i, u64, i, i, i, i]),
         ("b2r_host_reduce_threads", [C.POINTER(vp), vp, u64, i, i, i, i, i]),

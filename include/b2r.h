@@ -221,6 +221,10 @@ b2r_status_t b2r_allreduce_ex(const void* sendbuf, void* recvbuf, uint64_t count
 b2r_status_t b2r_reduce_scalar_sharded(const void* in, void* out, uint64_t count, b2r_dtype_t dtype, b2r_op_t op,
                                        int root, int all, b2r_comm_t comm, void* stream);
 
+/* Same with an explicit launch configuration for the local streaming part (variant, threads, ctas, pdl, ...). */
+b2r_status_t b2r_reduce_scalar_sharded_ex(const void* in, void* out, uint64_t count, b2r_dtype_t dtype, b2r_op_t op,
+                                          int root, int all, b2r_comm_t comm, void* stream, const b2r_launch_cfg_t* cfg);
+
 b2r_status_t b2r_barrier(b2r_comm_t comm, void* stream);
 
 /* Which algorithm AUTO resolves to (pure function; used by tests and the harness). */

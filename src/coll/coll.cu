@@ -28,6 +28,8 @@ struct PendingCall {
   int root, all;
   b2r_algo_t algo;
   cudaStream_t stream;
+  b2r_launch_cfg_t cfg;  // scalar-sharded only
+  bool has_cfg;
 };
 
 namespace {
@@ -39,35 +41,49 @@ int env_int(const char* name, int dflt) {
 
 using CollKernel = void (*)(const CollLaunch);
 
-template <int D, int O>
+template <int D, int O, int UNR>
 CollKernel pick_kind(int kind) {
   switch (kind) {
-    case kCollOneshot: return coll_kernel<D, O, kCollOneshot>;
-    case kCollTwoshot: return coll_kernel<D, O, kCollTwoshot>;
-    case kCollTree: return coll_kernel<D, O, kCollTree>;
-    case kCollNvls: return Nvls<D, O>::kSupported ? coll_kernel<D, O, kCollNvls> : nullptr;
-    case kCollBarrier: return coll_kernel<D, O, kCollBarrier>;
+    case kCollOneshot: return coll_kernel<D, O, kCollOneshot, UNR>;
+    case kCollTwoshot: return coll_kernel<D, O, kCollTwoshot, UNR>;
+    case kCollTree: return coll_kernel<D, O, kCollTree, UNR>;
+    case kCollNvls: return Nvls<D, O>::kSupported ? coll_kernel<D, O, kCollNvls, UNR> : nullptr;
+    case kCollBarrier: return coll_kernel<D, O, kCollBarrier, 4>;
   }
   return nullptr;
 }
 template <int D>
-CollKernel pick_op(int op, int kind) {
+CollKernel pick_op(int op, int kind, int unroll) {
   switch (op) {
-    case B2R_SUM: return pick_kind<D, B2R_SUM>(kind);
-    case B2R_MIN: return pick_kind<D, B2R_MIN>(kind);
-    case B2R_MAX: return pick_kind<D, B2R_MAX>(kind);
+    case B2R_SUM: return unroll == 8 ? pick_kind<D, B2R_SUM, 8>(kind) : pick_kind<D, B2R_SUM, 4>(kind);
+    case B2R_MIN: return unroll == 8 ? pick_kind<D, B2R_MIN, 8>(kind) : pick_kind<D, B2R_MIN, 4>(kind);
+    case B2R_MAX: return unroll == 8 ? pick_kind<D, B2R_MAX, 8>(kind) : pick_kind<D, B2R_MAX, 4>(kind);
   }
   return nullptr;
 }
-CollKernel pick_kernel(b2r_dtype_t dtype, int op, int kind) {
+CollKernel pick_kernel(b2r_dtype_t dtype, int op, int kind, int unroll) {
   switch (dtype) {
-    case B2R_INT32: return pick_op<B2R_INT32>(op, kind);
-    case B2R_FLOAT32: return pick_op<B2R_FLOAT32>(op, kind);
-    case B2R_FLOAT64: return pick_op<B2R_FLOAT64>(op, kind);
-    case B2R_BFLOAT16: return pick_op<B2R_BFLOAT16>(op, kind);
+    case B2R_INT32: return pick_op<B2R_INT32>(op, kind, unroll);
+    case B2R_FLOAT32: return pick_op<B2R_FLOAT32>(op, kind, unroll);
+    case B2R_FLOAT64: return pick_op<B2R_FLOAT64>(op, kind, unroll);
+    case B2R_BFLOAT16: return pick_op<B2R_BFLOAT16>(op, kind, unroll);
   }
   return nullptr;
 }
+
+// launch shape knobs (identical on every rank: they come from the environment / the communicator config)
+int coll_threads() {
+  int t = env_int("B2R_COLL_THREADS", 512);
+  t = std::max(64, std::min(512, t));
+  return t - t % 32;
+}
+int coll_unroll(uint64_t bytes) {
+  const int u = env_int("B2R_COLL_UNROLL", 0);
+  if (u == 4 || u == 8) return u;
+  return bytes >= (8u << 20) ? 8 : 4;
+}
+
+bool kernel_exists(b2r_dtype_t dtype, int op, int kind) { return pick_kernel(dtype, op, kind, 4) != nullptr; }
 
 bool nvls_supported(b2r_dtype_t dtype, b2r_op_t op) {
   if (dtype == B2R_FLOAT32 || dtype == B2R_FLOAT64) return op == B2R_SUM;
@@ -83,7 +99,7 @@ struct RankCall {
 
 // CTAs per rank for a collective over `bytes` (must be a pure function of things every rank knows).
 int coll_ctas(const b2r_comm* c, uint64_t bytes, int nvirtual) {
-  int cap = c->max_ctas > 0 ? c->max_ctas : 128;
+  int cap = c->max_ctas > 0 ? c->max_ctas : env_int("B2R_COLL_CTAS", 128);
   cap = std::min(cap, kCollMaxCtas);
   if (nvirtual > 1) cap = std::max(1, std::min(cap, c->sm_count / nvirtual));  // cooperative launch: all ranks co-resident
   const uint64_t want = (bytes + 65535) / 65536;
@@ -125,8 +141,8 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
     if (!nvls_supported(dtype, op)) return fail(B2R_ERR_UNSUPPORTED, "NVLS has no %s %s instruction", b2r_dtype_name(dtype), b2r_op_name(op));
   }
   const int kind = algo == B2R_ALGO_ONESHOT ? kCollOneshot : algo == B2R_ALGO_TWOSHOT ? kCollTwoshot : algo == B2R_ALGO_TREE ? kCollTree : kCollNvls;
-  CollKernel kernel = pick_kernel(dtype, (int)op, kind);
-  B2R_REQUIRE(kernel != nullptr, "collective: no kernel for dtype %d op %d algo %d", (int)dtype, (int)op, (int)algo);
+  const int threads = coll_threads();
+  B2R_REQUIRE(kernel_exists(dtype, (int)op, kind), "collective: no kernel for dtype %d op %d algo %d", (int)dtype, (int)op, (int)algo);
 
   // Chunking rule (identical on every rank): messages larger than one staging region are cut into stage-sized chunks,
   // unless the communicator was created with symmetric_only (then nothing is ever staged and one launch does it all).
@@ -171,12 +187,13 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
       c->epoch += 8;  // start + end + up to 4 tree rounds, rounded up; same increment on every rank
     }
     const int ctas = coll_ctas(c0, bytes, n);
+    CollKernel kernel = pick_kernel(dtype, (int)op, kind, coll_unroll(bytes));
     if (n == 1) {
-      kernel<<<dim3((unsigned)ctas, 1), 512, 0, rc[0].stream>>>(L);
+      kernel<<<dim3((unsigned)ctas, 1), threads, 0, rc[0].stream>>>(L);
       B2R_CUDA_CHECK(cudaGetLastError());
     } else {
       void* args[] = {(void*)&L};
-      B2R_CUDA_CHECK(cudaLaunchCooperativeKernel((const void*)kernel, dim3((unsigned)ctas, (unsigned)n), dim3(512), args, 0, rc[0].stream));
+      B2R_CUDA_CHECK(cudaLaunchCooperativeKernel((const void*)kernel, dim3((unsigned)ctas, (unsigned)n), dim3((unsigned)threads), args, 0, rc[0].stream));
     }
     for (int i = 0; i < n; ++i) {
       if (!recv_staged[i]) continue;
@@ -204,7 +221,7 @@ b2r_status_t run_barrier(RankCall* rc, int n) {
     A.root = -1;
     c->epoch += 8;
   }
-  CollKernel kernel = coll_kernel<B2R_INT32, B2R_SUM, kCollBarrier>;
+  CollKernel kernel = coll_kernel<B2R_INT32, B2R_SUM, kCollBarrier, 4>;
   if (n == 1) {
     kernel<<<dim3(1, 1), 32, 0, rc[0].stream>>>(L);
     B2R_CUDA_CHECK(cudaGetLastError());
@@ -216,7 +233,7 @@ b2r_status_t run_barrier(RankCall* rc, int n) {
 }
 
 // Scalar-sharded reduce: the local streaming reduction with the cross-GPU mailbox combine fused into its tail.
-b2r_status_t run_scalar(RankCall* rc, int n, uint64_t count, b2r_dtype_t dtype, b2r_op_t op, int root, int all) {
+b2r_status_t run_scalar(RankCall* rc, int n, uint64_t count, b2r_dtype_t dtype, b2r_op_t op, int root, int all, const b2r_launch_cfg_t* ucfg) {
   b2r_comm* c0 = rc[0].c;
   const int P = c0->nranks;
   B2R_REQUIRE(root >= 0 && root < P, "reduce_scalar_sharded: root %d out of range [0,%d)", root, P);
@@ -232,8 +249,8 @@ b2r_status_t run_scalar(RankCall* rc, int n, uint64_t count, b2r_dtype_t dtype, 
     xg.all = all;
     xg.seq = ++c->xg_seq;
     void* out = rc[0].recv ? rc[0].recv : (void*)c->ws->d_partials;  // non-root without `all`: never written
-    if (P == 1) return reduce_local_impl(rc[0].send, out, count, dtype, op, c->ws, rc[0].stream, nullptr, 0, nullptr);
-    return reduce_local_impl(rc[0].send, out, count, dtype, op, c->ws, rc[0].stream, nullptr, 0, &xg);
+    if (P == 1) return reduce_local_impl(rc[0].send, out, count, dtype, op, c->ws, rc[0].stream, ucfg, 0, nullptr);
+    return reduce_local_impl(rc[0].send, out, count, dtype, op, c->ws, rc[0].stream, ucfg, 0, &xg);
   }
   // loopback: every virtual rank in one cooperative launch (LDG128 variant, same grid for all ranks)
   int prev_dev = -1;
@@ -292,7 +309,7 @@ b2r_status_t loopback_submit(b2r_comm* c, const PendingCall& call) {
     rc[r].stream = call.stream;  // everything runs on the last caller's stream
   }
   if (st == B2R_OK) {
-    if (ref.kind == kCallScalar) st = run_scalar(rc.data(), g->nranks, ref.count, ref.dtype, ref.op, ref.root, ref.all);
+    if (ref.kind == kCallScalar) st = run_scalar(rc.data(), g->nranks, ref.count, ref.dtype, ref.op, ref.root, ref.all, nullptr);
     else if (ref.kind == kCallBarrier) st = run_barrier(rc.data(), g->nranks);
     else st = run_collective(rc.data(), g->nranks, ref.kind, ref.count, ref.dtype, ref.op, ref.root, ref.algo);
   }
@@ -305,7 +322,7 @@ b2r_status_t submit(b2r_comm* c, const PendingCall& call) {
   B2R_REQUIRE(c != nullptr, "collective: communicator is NULL");
   if (c->mode == kModeLoopback && c->nranks > 1) return loopback_submit(c, call);
   RankCall rc{c, call.send, call.recv, call.stream};
-  if (call.kind == kCallScalar) return run_scalar(&rc, 1, call.count, call.dtype, call.op, call.root, call.all);
+  if (call.kind == kCallScalar) return run_scalar(&rc, 1, call.count, call.dtype, call.op, call.root, call.all, call.has_cfg ? &call.cfg : nullptr);
   if (call.kind == kCallBarrier) return run_barrier(&rc, 1);
   return run_collective(&rc, 1, call.kind, call.count, call.dtype, call.op, call.root, call.algo);
 }
@@ -323,7 +340,9 @@ b2r_algo_t b2r_select_algo(int is_allreduce, uint64_t bytes, b2r_dtype_t dtype, 
   if (nranks <= 1) return B2R_ALGO_ONESHOT;
   const uint64_t oneshot_max = (uint64_t)std::max(0, env_int("B2R_ONESHOT_MAX_KB", is_allreduce ? 256 : 512)) << 10;
   if (bytes <= oneshot_max) return B2R_ALGO_ONESHOT;
-  const bool nvls_fast = has_multicast && nvls_supported(dtype, op) && (dtype == B2R_FLOAT32 || dtype == B2R_BFLOAT16 || dtype == B2R_FLOAT64);
+  // NVLS moves (1 + 1/P) messages per GPU against two-shot's 2(P-1)/P: a win from 4 GPUs up, a loss at 2 (measured)
+  const bool nvls_fast = has_multicast && nranks >= 4 && nvls_supported(dtype, op) &&
+                         (dtype == B2R_FLOAT32 || dtype == B2R_BFLOAT16 || dtype == B2R_FLOAT64);
   if (nvls_fast && !env_int("B2R_DISABLE_NVLS", 0)) return B2R_ALGO_NVLS;
   return B2R_ALGO_TWOSHOT;  // int32 (4-byte multimem ops) and fp32/fp64 min/max (no multimem form) stay on P2P
 }
@@ -345,10 +364,16 @@ b2r_status_t b2r_reduce(const void* sendbuf, void* recvbuf, uint64_t count, b2r_
 b2r_status_t b2r_allreduce(const void* sendbuf, void* recvbuf, uint64_t count, b2r_dtype_t dtype, b2r_op_t op, b2r_comm_t comm, void* stream) {
   return b2r_allreduce_ex(sendbuf, recvbuf, count, dtype, op, comm, stream, B2R_ALGO_AUTO);
 }
+b2r_status_t b2r_reduce_scalar_sharded_ex(const void* in, void* out, uint64_t count, b2r_dtype_t dtype, b2r_op_t op, int root, int all,
+                                          b2r_comm_t comm, void* stream, const b2r_launch_cfg_t* cfg) {
+  PendingCall pc{kCallScalar, in, out, count, dtype, op, root, all ? 1 : 0, B2R_ALGO_AUTO, (cudaStream_t)stream};
+  pc.has_cfg = cfg != nullptr;
+  if (cfg) pc.cfg = *cfg;
+  return submit(comm, pc);
+}
 b2r_status_t b2r_reduce_scalar_sharded(const void* in, void* out, uint64_t count, b2r_dtype_t dtype, b2r_op_t op, int root, int all,
                                        b2r_comm_t comm, void* stream) {
-  PendingCall pc{kCallScalar, in, out, count, dtype, op, root, all ? 1 : 0, B2R_ALGO_AUTO, (cudaStream_t)stream};
-  return submit(comm, pc);
+  return b2r_reduce_scalar_sharded_ex(in, out, count, dtype, op, root, all, comm, stream, nullptr);
 }
 b2r_status_t b2r_barrier(b2r_comm_t comm, void* stream) {
   PendingCall pc{kCallBarrier, nullptr, nullptr, 0, B2R_INT32, B2R_SUM, -1, 0, B2R_ALGO_AUTO, (cudaStream_t)stream};

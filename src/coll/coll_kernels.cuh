@@ -257,11 +257,10 @@ __device__ __forceinline__ void combine_tail(unsigned long long first_elem, unsi
   }
 }
 
-constexpr int kCollUnroll = 4;
 
 // ------------------------------------------------------------------------------------------------ one-shot
 // Every rank (allreduce) or only the root (reduce) reads all P send buffers and combines them in rank order.
-template <int D, int O>
+template <int D, int O, int UNR>
 __device__ void oneshot_body(const CollArgs& A) {
   const CollCtx& c = A.ctx;
   constexpr int E = VecOps<D, O>::kElem;
@@ -276,7 +275,7 @@ __device__ void oneshot_body(const CollArgs& A) {
       dst[0] = c.heap[c.rank] + A.recv_off;
     }
     __syncthreads();
-    combine_range<D, O, kCollUnroll>(0, nvec, src, c.nranks, dst, 1);
+    combine_range<D, O, UNR>(0, nvec, src, c.nranks, dst, 1);
     combine_tail<D, O>(nvec * (16 / E), A.count, src, c.nranks, dst, 1);
   }
   cta_barrier(A, A.epoch + 2);
@@ -287,7 +286,7 @@ __device__ void oneshot_body(const CollArgs& A) {
 //            peer's recv buffer (all-gather by stores) — per GPU 2(P-1)/P of the message in each direction.
 // reduce   : the P-1 non-root ranks each own a slice and push only to the root, so the root's ingress is exactly one
 //            message (not 2(P-1)/P of it) and every link carries the same load.
-template <int D, int O>
+template <int D, int O, int UNR>
 __device__ void twoshot_body(const CollArgs& A) {
   const CollCtx& c = A.ctx;
   constexpr int E = VecOps<D, O>::kElem;
@@ -317,7 +316,7 @@ __device__ void twoshot_body(const CollArgs& A) {
       }
     }
     __syncthreads();
-    combine_range<D, O, kCollUnroll>(lo, hi, src, P, dst, ndst);
+    combine_range<D, O, UNR>(lo, hi, src, P, dst, ndst);
     if (me == nworkers - 1) combine_tail<D, O>(nvec * (16 / E), A.count, src, P, dst, ndst);
   }
   cta_barrier(A, A.epoch + 2);
@@ -328,7 +327,7 @@ __device__ void twoshot_body(const CollArgs& A) {
 // position v + 2^k and combines it into its own work buffer; the last round writes the final destination. This is the
 // "custom tree vs library reduce" arm of the assignment; on a uniform NVSwitch it moves (P-1) whole messages through
 // log2 P dependent rounds, so it is expected to lose to two-shot for large messages.
-template <int D, int O>
+template <int D, int O, int UNR>
 __device__ void tree_body(const CollArgs& A) {
   const CollCtx& c = A.ctx;
   constexpr int E = VecOps<D, O>::kElem;
@@ -360,7 +359,7 @@ __device__ void tree_body(const CollArgs& A) {
           for (int p = 0; p < P; ++p) dst[p] = c.heap[p] + po.recv[p];  // allreduce: the root broadcasts by stores
       }
       __syncthreads();
-      combine_range<D, O, kCollUnroll>(0, nvec, src, 2, dst, ndst);
+      combine_range<D, O, UNR>(0, nvec, src, 2, dst, ndst);
       combine_tail<D, O>(nvec * (16 / E), A.count, src, 2, dst, ndst);
     }
     cta_barrier(A, A.epoch + 2 + k);
@@ -441,7 +440,7 @@ B2R_NVLS_I32(B2R_MIN, "min.s32")
 B2R_NVLS_I32(B2R_MAX, "max.s32")
 #undef B2R_NVLS_I32
 
-template <int D, int O>
+template <int D, int O, int UNR>
 __device__ void nvls_body(const CollArgs& A) {
   using N = Nvls<D, O>;
   const CollCtx& c = A.ctx;
@@ -473,7 +472,7 @@ __device__ void nvls_body(const CollArgs& A) {
       char* mdst = c.mc + A.recv_off;
       char* ldst = c.heap[c.rank] + A.recv_off;
       const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
-      constexpr int U = 4;
+      constexpr int U = UNR;
       for (unsigned long long base = lo + (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; base < hi; base += stride * U) {
         uint32_t w[U][4];
 #pragma unroll
@@ -518,13 +517,13 @@ __device__ inline void barrier_body(const CollArgs& A) {
 
 enum CollKind { kCollOneshot = 1, kCollTwoshot = 2, kCollTree = 3, kCollNvls = 4, kCollBarrier = 5 };
 
-template <int D, int O, int KIND>
+template <int D, int O, int KIND, int UNR>
 __global__ void __launch_bounds__(512) coll_kernel(const __grid_constant__ CollLaunch L) {
   const CollArgs& A = L.a[blockIdx.y];
-  if (KIND == kCollOneshot) oneshot_body<D, O>(A);
-  else if (KIND == kCollTwoshot) twoshot_body<D, O>(A);
-  else if (KIND == kCollTree) tree_body<D, O>(A);
-  else if (KIND == kCollNvls) nvls_body<D, O>(A);
+  if (KIND == kCollOneshot) oneshot_body<D, O, UNR>(A);
+  else if (KIND == kCollTwoshot) twoshot_body<D, O, UNR>(A);
+  else if (KIND == kCollTree) tree_body<D, O, UNR>(A);
+  else if (KIND == kCollNvls) nvls_body<D, O, UNR>(A);
   else barrier_body(A);
 }
 

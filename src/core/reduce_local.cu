@@ -225,8 +225,7 @@ b2r_status_t reduce_local_impl(const void* in, void* out, uint64_t count, b2r_dt
     p.xg_ctx = xg->ctx;
     p.xg_root = xg->root;
     p.xg_all = xg->all;
-    p.xg_seq = xg->seq;
-    p.pdl = g.pdl = 0;
+    p.xg_seq = xg->seq;  // PDL stays as planned: the mailbox is only touched after griddepcontrol.wait
   }
   return launch_any(dtype, (int)op, g, p, stream);
 }
