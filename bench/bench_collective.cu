@@ -59,6 +59,7 @@ b2r_algo_t parse_algo(const std::string& s) {
   if (s == "twoshot") return B2R_ALGO_TWOSHOT;
   if (s == "tree") return B2R_ALGO_TREE;
   if (s == "nvls") return B2R_ALGO_NVLS;
+  if (s == "push") return B2R_ALGO_PUSH;
   return B2R_ALGO_AUTO;
 }
 

@@ -49,6 +49,7 @@ CollKernel pick_kind(int kind) {
     case kCollTree: return coll_kernel<D, O, kCollTree, UNR>;
     case kCollNvls: return Nvls<D, O>::kSupported ? coll_kernel<D, O, kCollNvls, UNR> : nullptr;
     case kCollBarrier: return coll_kernel<D, O, kCollBarrier, 4>;
+    case kCollPush: return coll_kernel<D, O, kCollPush, 4>;
   }
   return nullptr;
 }
@@ -140,7 +141,8 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
     if (!c0->has_mc) return fail(B2R_ERR_UNSUPPORTED, "NVLS requested but this communicator has no multicast mapping");
     if (!nvls_supported(dtype, op)) return fail(B2R_ERR_UNSUPPORTED, "NVLS has no %s %s instruction", b2r_dtype_name(dtype), b2r_op_name(op));
   }
-  const int kind = algo == B2R_ALGO_ONESHOT ? kCollOneshot : algo == B2R_ALGO_TWOSHOT ? kCollTwoshot : algo == B2R_ALGO_TREE ? kCollTree : kCollNvls;
+  const int kind = algo == B2R_ALGO_ONESHOT ? kCollOneshot : algo == B2R_ALGO_TWOSHOT ? kCollTwoshot : algo == B2R_ALGO_TREE ? kCollTree
+                   : algo == B2R_ALGO_PUSH ? kCollPush : kCollNvls;
   const int threads = coll_threads();
   B2R_REQUIRE(kernel_exists(dtype, (int)op, kind), "collective: no kernel for dtype %d op %d algo %d", (int)dtype, (int)op, (int)algo);
 
@@ -185,8 +187,17 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
       A.epoch = c->epoch;
       A.root = is_all ? -1 : root;
       c->epoch += 8;  // start + end + up to 4 tree rounds, rounded up; same increment on every rank
+      if (kind == kCollPush) A.seq = ++c->push_seq;
     }
-    const int ctas = coll_ctas(c0, bytes, n);
+    int ctas = coll_ctas(c0, bytes, n);
+    if (kind == kCollPush) {
+      // staging ring in the work region: depth x P sources x ctas blocks of (threads x 4) vectors; at least 2 deep
+      const uint64_t block_bytes = (uint64_t)threads * 4 * 16;
+      ctas = std::min(ctas, std::max(1, env_int("B2R_PUSH_CTAS", 64)));
+      ctas = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)ctas, c0->stage_bytes / (2ull * P * block_bytes)));
+      const int depth = (int)std::min<uint64_t>(8, c0->stage_bytes / ((uint64_t)P * ctas * block_bytes));
+      for (int i = 0; i < n; ++i) L.a[n == 1 ? 0 : rc[i].c->rank].ring_depth = depth;
+    }
     CollKernel kernel = pick_kernel(dtype, (int)op, kind, coll_unroll(bytes));
     if (n == 1) {
       kernel<<<dim3((unsigned)ctas, 1), threads, 0, rc[0].stream>>>(L);

@@ -30,7 +30,7 @@ void host_collective_rank(const HostRankView& v, uint64_t count, b2r_dtype_t dty
   if (algo == B2R_ALGO_ONESHOT || algo == B2R_ALGO_AUTO || algo == B2R_ALGO_NVLS) {
     if (root < 0 || root == r) combine_many_host(v.recv[r], v.send, P, 0, count, dtype, op);
     barrier();
-  } else if (algo == B2R_ALGO_TWOSHOT) {
+  } else if (algo == B2R_ALGO_TWOSHOT || algo == B2R_ALGO_PUSH) {  // same slices, same rank-order combine
     int nworkers = root < 0 ? P : P - 1;
     int me = root < 0 ? r : (r == root ? -1 : (r < root ? r : r - 1));
     if (P == 1) { nworkers = 1; me = 0; }

@@ -16,6 +16,8 @@ constexpr size_t kOffMailbox = 32 * 1024;            // XgMailbox (scalar-sharde
 constexpr size_t kOffError = 40 * 1024;              // uint32 error word (device-side timeouts)
 constexpr size_t kOffCtx = 44 * 1024;                // device copy of CollCtx (read by the scalar-sharded kernels)
 constexpr size_t kOffMeta = 64 * 1024;               // PeerMeta meta[kCollMaxCtas][B2R_MAX_RANKS]: per-collective buffer offsets
+constexpr size_t kOffPushData = 128 * 1024;          // uint32 [kCollMaxCtas][B2R_MAX_RANKS]: push algorithm, "block of round i from rank s has landed"
+constexpr size_t kOffPushAck = 160 * 1024;           // uint32 [kCollMaxCtas][B2R_MAX_RANKS]: push algorithm, "worker w has consumed round i"
 constexpr size_t kCtrlBytes = 1 << 20;               // control region size; staging starts here
 
 // Where rank r keeps its send/recv buffer for the collective in flight, published to every peer inside the start

@@ -49,6 +49,7 @@ struct b2r_comm {
   size_t heap_bytes = 0, stage_bytes = 0, user_off = 0, bump = 0;
   uint32_t epoch = 0;   // barrier epoch counter (same sequence on every rank)
   uint32_t xg_seq = 0;  // scalar-sharded call counter
+  uint32_t push_seq = 0;  // push-algorithm call counter (flag values are seq << 16 | round)
   b2r_workspace* ws = nullptr;
   int max_ctas = 0, timeout_ms = 0;
   bool has_mc = false;

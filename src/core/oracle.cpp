@@ -170,6 +170,7 @@ const char* b2r_algo_name(b2r_algo_t a) {
     case B2R_ALGO_TWOSHOT: return "twoshot";
     case B2R_ALGO_TREE: return "tree";
     case B2R_ALGO_NVLS: return "nvls";
+    case B2R_ALGO_PUSH: return "push";
   }
   return "?";
 }

@@ -21,7 +21,7 @@ def main():
     assert comm.rank == rank and comm.size == world
     if rank == 0:
         print(f"world={world} multicast={comm.has_multicast}", flush=True)
-    algos = ["oneshot", "twoshot", "tree"] + (["nvls"] if comm.has_multicast else [])
+    algos = ["oneshot", "twoshot", "tree", "push"] + (["nvls"] if comm.has_multicast else [])
     fails = 0
     for dtype in (torch.int32, torch.float32, torch.float64, torch.bfloat16):
         for count in (1, 1000, 65537, (1 << 22) + 3):
@@ -44,7 +44,7 @@ def main():
                             b2r.combine_oracle(want, h, op)
                     out = comm.allreduce(x, op, algo=algo)
                     comm.check()
-                    exact = algo in ("oneshot", "twoshot") or op != "sum" or dtype == torch.int32
+                    exact = algo in ("oneshot", "twoshot", "push") or op != "sum" or dtype == torch.int32
                     got = out.cpu()
                     ok = torch.equal(got, want) if exact else torch.allclose(got.double(), want.double(), rtol=2e-2 if dtype == torch.bfloat16 else 1e-5, atol=1e-5)
                     if not ok:

@@ -14,7 +14,7 @@ from cuda_mpi_reductions_b200.parallel import Communicator, host_reduce_threads
 pytestmark = pytest.mark.gpu
 
 DTYPES = [torch.int32, torch.float32, torch.float64, torch.bfloat16]
-ALGOS = ["oneshot", "twoshot", "tree"]
+ALGOS = ["oneshot", "twoshot", "tree", "push"]
 COUNTS = [1, 3, 7, 1000, 4099, 65537, (1 << 20) + 5]
 
 
@@ -97,7 +97,7 @@ def test_back_to_back_small_collectives_reuse_flags(comms):
     want = host_reduce_threads(xs_h, "sum", -1, "oneshot")[0]
     outs = None
     for i in range(300):
-        algo = ALGOS[i % 3]
+        algo = ALGOS[i % len(ALGOS)]
         outs = Communicator.group_allreduce(comms, xs, "sum", algo=algo)
     Communicator.group_check(comms)
     for o in outs:

@@ -24,7 +24,7 @@ def elementwise_oracle(xs, op):
 
 
 @pytest.mark.parametrize("nranks", [1, 2, 3, 4, 7, 8])
-@pytest.mark.parametrize("algo", ["oneshot", "twoshot", "tree"])
+@pytest.mark.parametrize("algo", ["oneshot", "twoshot", "tree", "push"])
 @pytest.mark.parametrize("dtype", DTYPES)
 def test_reduce_and_allreduce(nranks, algo, dtype):
     for count in (1, 5, 1023):

@@ -19,7 +19,7 @@ def test_single_process_all_devices():
     n = torch.cuda.device_count()
     comms = Communicator.init_all(list(range(n)), heap_bytes=128 << 20, timeout_ms=20000)
     try:
-        algos = ["oneshot", "twoshot", "tree"] + (["nvls"] if comms[0].has_multicast else [])
+        algos = ["oneshot", "twoshot", "tree", "push"] + (["nvls"] if comms[0].has_multicast else [])
         for dtype in (torch.int32, torch.float32, torch.bfloat16):
             for count in (1, 4099, (1 << 21) + 1):
                 xs_h = [b2r.fill_host(count, dtype, seed=7 * r + count, mode="signed") for r in range(n)]
@@ -52,5 +52,9 @@ def test_one_process_per_gpu_torchrun():
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}", "--master-addr", "127.0.0.1",
            "--master-port", "29533", os.path.join(REPO, "tests", "dist_worker.py")]
     res = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
-    tail = (res.stdout[-3000:] + res.stderr[-3000:])
+    os.makedirs(os.path.join(REPO, "gpurun_out"), exist_ok=True)
+    with open(os.path.join(REPO, "gpurun_out", f"dist_worker_{n}.log"), "w") as f:
+        f.write(res.stdout + "\n==== stderr ====\n" + res.stderr)
+    lines = [l for l in (res.stdout + res.stderr).splitlines() if "MISMATCH" in l or "Error" in l or "error" in l]
+    tail = "\n".join(lines[:40]) + "\n" + res.stdout[-1500:]
     assert res.returncode == 0 and "DIST_WORKER PASSED" in res.stdout, tail
