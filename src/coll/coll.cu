@@ -72,16 +72,44 @@ CollKernel pick_kernel(b2r_dtype_t dtype, int op, int kind, int unroll) {
   return nullptr;
 }
 
-// launch shape knobs (identical on every rank: they come from the environment / the communicator config)
-int coll_threads() {
-  int t = env_int("B2R_COLL_THREADS", 512);
-  t = std::max(64, std::min(512, t));
-  return t - t % 32;
-}
-int coll_unroll(uint64_t bytes) {
-  const int u = env_int("B2R_COLL_UNROLL", 0);
-  if (u == 4 || u == 8) return u;
-  return bytes >= (8u << 20) ? 8 : 4;
+// Launch shape per algorithm (identical on every rank: a pure function of the algorithm, the message size, the
+// communicator config and the environment). Measured on 8x B200 (profiles/collectives.md):
+//   NVLS   wants FEW threads: 32 CTAs x 256 threads x 8 vectors in flight reach 843 GB/s bus bandwidth at 1 GiB, while
+//          128 x 512 threads drop to 530-650 (the switch's reduction engine is the resource, not SM-side parallelism);
+//   pulls  (one-shot / two-shot / tree) want many: 128 CTAs x 512 threads to cover the NVLink load latency;
+//   push   is bounded by its staging ring (see run_collective).
+struct Shape {
+  int ctas, threads, unroll;
+};
+Shape coll_shape(const b2r_comm* c, int kind, uint64_t bytes, int nvirtual) {
+  Shape s;
+  int cap;
+  uint64_t per_cta;
+  if (kind == kCollNvls) {
+    s.threads = 256;
+    s.unroll = bytes >= (8u << 20) ? 8 : 4;
+    cap = 32;
+    per_cta = 32768;
+  } else if (kind == kCollPush) {
+    s.threads = 512;
+    s.unroll = 4;
+    cap = 128;
+    per_cta = 65536;
+  } else {
+    s.threads = 512;
+    s.unroll = bytes >= (8u << 20) ? 8 : 4;
+    cap = 128;
+    per_cta = 65536;
+  }
+  const int et = env_int("B2R_COLL_THREADS", 0), eu = env_int("B2R_COLL_UNROLL", 0), ec = env_int("B2R_COLL_CTAS", 0);
+  if (et >= 64 && et <= 512) s.threads = et - et % 32;
+  if (eu == 4 || eu == 8) s.unroll = eu;
+  if (ec > 0) cap = ec;
+  if (c->max_ctas > 0) cap = std::min(cap, c->max_ctas);
+  cap = std::max(1, std::min(cap, kCollMaxCtas));
+  if (nvirtual > 1) cap = std::max(1, std::min(cap, c->sm_count / nvirtual));  // cooperative launch: all ranks co-resident
+  s.ctas = (int)std::max<uint64_t>(1, std::min<uint64_t>((bytes + per_cta - 1) / per_cta, (uint64_t)cap));
+  return s;
 }
 
 bool kernel_exists(b2r_dtype_t dtype, int op, int kind) { return pick_kernel(dtype, op, kind, 4) != nullptr; }
@@ -97,15 +125,6 @@ struct RankCall {
   void* recv;
   cudaStream_t stream;
 };
-
-// CTAs per rank for a collective over `bytes` (must be a pure function of things every rank knows).
-int coll_ctas(const b2r_comm* c, uint64_t bytes, int nvirtual) {
-  int cap = c->max_ctas > 0 ? c->max_ctas : env_int("B2R_COLL_CTAS", 128);
-  cap = std::min(cap, kCollMaxCtas);
-  if (nvirtual > 1) cap = std::max(1, std::min(cap, c->sm_count / nvirtual));  // cooperative launch: all ranks co-resident
-  const uint64_t want = (bytes + 65535) / 65536;
-  return (int)std::max<uint64_t>(1, std::min<uint64_t>(want, (uint64_t)cap));
-}
 
 // Runs one element-wise collective for the `n` calls in rc (n == 1: this process drives one rank; n == P: loopback).
 b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, b2r_dtype_t dtype, b2r_op_t op, int root, b2r_algo_t algo) {
@@ -143,7 +162,6 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
   }
   const int kind = algo == B2R_ALGO_ONESHOT ? kCollOneshot : algo == B2R_ALGO_TWOSHOT ? kCollTwoshot : algo == B2R_ALGO_TREE ? kCollTree
                    : algo == B2R_ALGO_PUSH ? kCollPush : kCollNvls;
-  const int threads = coll_threads();
   B2R_REQUIRE(kernel_exists(dtype, (int)op, kind), "collective: no kernel for dtype %d op %d algo %d", (int)dtype, (int)op, (int)algo);
 
   // Chunking rule (identical on every rank): messages larger than one staging region are cut into stage-sized chunks,
@@ -189,16 +207,18 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
       c->epoch += 8;  // start + end + up to 4 tree rounds, rounded up; same increment on every rank
       if (kind == kCollPush) A.seq = ++c->push_seq;
     }
-    int ctas = coll_ctas(c0, bytes, n);
+    const Shape shape = coll_shape(c0, kind, bytes, n);
+    int ctas = shape.ctas;
+    const int threads = shape.threads;
     if (kind == kCollPush) {
       // staging ring in the work region: depth x P sources x ctas blocks of (threads x 4) vectors; at least 2 deep
       const uint64_t block_bytes = (uint64_t)threads * 4 * 16;
-      ctas = std::min(ctas, std::max(1, env_int("B2R_PUSH_CTAS", 64)));
+      ctas = std::min(ctas, std::max(1, env_int("B2R_PUSH_CTAS", 128)));
       ctas = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)ctas, c0->stage_bytes / (2ull * P * block_bytes)));
       const int depth = (int)std::min<uint64_t>(8, c0->stage_bytes / ((uint64_t)P * ctas * block_bytes));
       for (int i = 0; i < n; ++i) L.a[n == 1 ? 0 : rc[i].c->rank].ring_depth = depth;
     }
-    CollKernel kernel = pick_kernel(dtype, (int)op, kind, coll_unroll(bytes));
+    CollKernel kernel = pick_kernel(dtype, (int)op, kind, shape.unroll);
     if (n == 1) {
       kernel<<<dim3((unsigned)ctas, 1), threads, 0, rc[0].stream>>>(L);
       B2R_CUDA_CHECK(cudaGetLastError());
@@ -349,13 +369,18 @@ extern "C" {
 // rank pulls the WHOLE message from every peer; two-shot / NVLS move 1/P of it per rank.
 b2r_algo_t b2r_select_algo(int is_allreduce, uint64_t bytes, b2r_dtype_t dtype, b2r_op_t op, int nranks, int has_multicast) {
   if (nranks <= 1) return B2R_ALGO_ONESHOT;
-  const uint64_t oneshot_max = (uint64_t)std::max(0, env_int("B2R_ONESHOT_MAX_KB", is_allreduce ? 256 : 512)) << 10;
+  const int forced = env_int("B2R_ALGO", 0);
+  if (forced >= B2R_ALGO_ONESHOT && forced <= B2R_ALGO_PUSH) return (b2r_algo_t)forced;
+  // NVLS moves (1 + 1/P) messages per GPU against two-shot's 2(P-1)/P and needs one switch round trip for any size:
+  // from 4 GPUs up it wins at EVERY size for the types with 8/16-byte multimem forms (fp32 add, bf16, fp64 add);
+  // at 2 GPUs it loses to the P2P paths (measured). 32-bit integer multimem ops move 4 bytes per instruction and
+  // fp32/fp64 min/max have no multimem form: those stay on P2P.
+  const bool nvls_ok = has_multicast && nranks >= 4 && nvls_supported(dtype, op) && dtype != B2R_INT32 && !env_int("B2R_DISABLE_NVLS", 0);
+  if (nvls_ok) return B2R_ALGO_NVLS;
+  // One-shot reads the WHOLE message from every peer: fine for two GPUs or tiny messages, hopeless beyond.
+  const uint64_t oneshot_max = (uint64_t)std::max(0, env_int("B2R_ONESHOT_MAX_KB", nranks <= 2 ? 512 : 16)) << 10;
   if (bytes <= oneshot_max) return B2R_ALGO_ONESHOT;
-  // NVLS moves (1 + 1/P) messages per GPU against two-shot's 2(P-1)/P: a win from 4 GPUs up, a loss at 2 (measured)
-  const bool nvls_fast = has_multicast && nranks >= 4 && nvls_supported(dtype, op) &&
-                         (dtype == B2R_FLOAT32 || dtype == B2R_BFLOAT16 || dtype == B2R_FLOAT64);
-  if (nvls_fast && !env_int("B2R_DISABLE_NVLS", 0)) return B2R_ALGO_NVLS;
-  return B2R_ALGO_TWOSHOT;  // int32 (4-byte multimem ops) and fp32/fp64 min/max (no multimem form) stay on P2P
+  return B2R_ALGO_TWOSHOT;
 }
 
 b2r_status_t b2r_reduce_ex(const void* sendbuf, void* recvbuf, uint64_t count, b2r_dtype_t dtype, b2r_op_t op, int root, b2r_comm_t comm,

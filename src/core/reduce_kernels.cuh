@@ -70,65 +70,81 @@ __device__ __forceinline__ void store_result(const LocalParams& p, typename R::a
 }
 
 // Scalar-sharded reduce across GPUs, fused into the tail of the local reduction (one kernel per rank; the vendored
-// simpleMultiGPU copies per-GPU partials to the host and sums there, simpleMultiGPU.cpp:264-293). Called by ONE thread
-// that holds this rank's scalar `a`:
-//   post   : store the partial into the root's mailbox over NVLink, then release-store my call number next to it;
-//   root   : acquire all P call numbers, combine the partials in rank order (deterministic), write `out`, push the ack
-//            (and, for the allreduce flavour, the result) to every rank;
-//   others : with `all`, wait for the pushed result.
+// simpleMultiGPU copies per-GPU partials to the host and sums there, simpleMultiGPU.cpp:264-293). Called by ALL threads
+// of the CTA that holds this rank's scalar (`a` is valid in thread 0):
+//   post   : thread 0 stores the partial into the root's mailbox over NVLink, then release-stores the call number;
+//   root   : thread r acquires rank r's call number and fetches its partial (P waits in parallel), thread 0 combines the
+//            partials in rank order (deterministic) and writes `out`, then thread r pushes the ack (and, for the
+//            allreduce flavour, the result) to rank r — P release-stores in parallel cost ONE NVLink round trip, where
+//            a loop in one thread would cost P of them;
+//   others : with `all`, thread 0 waits for the pushed result.
 // Mailbox slots are double-buffered by call parity; a rank may run at most one call ahead of the root's ack.
 template <class R>
 __device__ __forceinline__ void xgpu_finish(const LocalParams& p, typename R::acc_t a) {
   using acc_t = typename R::acc_t;
   using F = typename R::F;
+  __shared__ unsigned long long s_vals[B2R_MAX_RANKS];
+  __shared__ unsigned long long s_res;
+  __shared__ int s_fail;
   const CollCtx& c = *p.xg_ctx;
   const unsigned seq = p.xg_seq, slot = seq & 1u;
-  XgMailbox* my_mb = (XgMailbox*)(c.heap[c.rank] + kOffMailbox);
-  XgMailbox* root_mb = (XgMailbox*)(c.heap[p.xg_root] + kOffMailbox);
-  fault_delay(c);
-  if (seq >= 3 && !wait_flag_ge(&my_mb->ack, seq - 2, c)) return;  // slot still unread by the root
-  unsigned long long bits = 0;
-  if (sizeof(acc_t) == 8) bits = (unsigned long long)__double_as_longlong((double)a);
-  else if (R::kIsInt) bits = (unsigned long long)(unsigned int)(int)a;
-  else bits = (unsigned long long)__float_as_uint((float)a);
-  if (!c.fault_skip_signal) {
-    st_relaxed_sys_u64(&root_mb->val[slot][c.rank], bits);
-    st_release_sys(&root_mb->flag[c.rank], seq);
-  }
+  const int P = c.nranks, me = c.rank, root = p.xg_root;
+  XgMailbox* my_mb = (XgMailbox*)(c.heap[me] + kOffMailbox);
+  auto to_bits = [](acc_t v) -> unsigned long long {
+    if (sizeof(acc_t) == 8) return (unsigned long long)__double_as_longlong((double)v);
+    if (R::kIsInt) return (unsigned long long)(unsigned int)(int)v;
+    return (unsigned long long)__float_as_uint((float)v);
+  };
   auto from_bits = [](unsigned long long b) -> acc_t {
     if (sizeof(acc_t) == 8) return (acc_t)__longlong_as_double((long long)b);
     if (R::kIsInt) return (acc_t)(int)(unsigned int)b;
     return (acc_t)__uint_as_float((unsigned int)b);
   };
-  if (c.rank == p.xg_root) {
-    acc_t acc = F::identity();
-    for (int r = 0; r < c.nranks; ++r) {
-      if (!wait_flag_ge(&my_mb->flag[r], seq, c)) return;
-      acc = F::apply(acc, from_bits(ld_relaxed_sys_u64(&my_mb->val[slot][r])));
+  if (threadIdx.x == 0) {
+    s_fail = 0;
+    fault_delay(c);
+    if (seq >= 3 && !wait_flag_ge(&my_mb->ack, seq - 2, c)) s_fail = 1;  // slot still unread by the root
+    else if (!c.fault_skip_signal) {
+      XgMailbox* root_mb = (XgMailbox*)(c.heap[root] + kOffMailbox);
+      st_relaxed_sys_u64(&root_mb->val[slot][me], to_bits(a));
+      st_release_sys(&root_mb->flag[me], seq);
     }
-    store_result<R>(p, acc);
-    unsigned long long rb = 0;
-    if (sizeof(acc_t) == 8) rb = (unsigned long long)__double_as_longlong((double)acc);
-    else if (R::kIsInt) rb = (unsigned long long)(unsigned int)(int)acc;
-    else rb = (unsigned long long)__float_as_uint((float)acc);
-    for (int r = 0; r < c.nranks; ++r) {
-      XgMailbox* mb = (XgMailbox*)(c.heap[r] + kOffMailbox);
+  }
+  if (me != root && !p.xg_all) return;
+  __syncthreads();
+  if (s_fail) return;
+  if (me == root) {
+    if (threadIdx.x < (unsigned)P) {
+      if (wait_flag_ge(&my_mb->flag[threadIdx.x], seq, c)) s_vals[threadIdx.x] = ld_relaxed_sys_u64(&my_mb->val[slot][threadIdx.x]);
+      else s_fail = 1;
+    }
+    __syncthreads();
+    if (s_fail) return;
+    if (threadIdx.x == 0) {
+      acc_t acc = from_bits(s_vals[0]);
+      for (int r = 1; r < P; ++r) acc = F::apply(acc, from_bits(s_vals[r]));
+      store_result<R>(p, acc);
+      s_res = to_bits(acc);
+    }
+    __syncthreads();
+    if (threadIdx.x < (unsigned)P) {
+      XgMailbox* mb = (XgMailbox*)(c.heap[threadIdx.x] + kOffMailbox);
       if (p.xg_all) {
-        st_relaxed_sys_u64(&mb->result[slot], rb);
+        st_relaxed_sys_u64(&mb->result[slot], s_res);
         st_release_sys(&mb->result_flag, seq);
       }
       st_release_sys(&mb->ack, seq);
     }
-  } else if (p.xg_all) {
-    if (!wait_flag_ge(&my_mb->result_flag, seq, c)) return;
-    store_result<R>(p, from_bits(ld_relaxed_sys_u64(&my_mb->result[slot])));
+  } else if (threadIdx.x == 0) {
+    if (wait_flag_ge(&my_mb->result_flag, seq, c)) store_result<R>(p, from_bits(ld_relaxed_sys_u64(&my_mb->result[slot])));
   }
 }
 
+// `v` is valid in thread 0; every thread of the CTA calls this.
 template <class R>
 __device__ __forceinline__ void finish_scalar(const LocalParams& p, typename R::acc_t v) {
   if (p.xg_ctx) xgpu_finish<R>(p, v);
-  else store_result<R>(p, v);
+  else if (threadIdx.x == 0) store_result<R>(p, v);
 }
 
 // Everything after the streaming loop. `tv` is the per-thread value.
@@ -163,10 +179,8 @@ __device__ __forceinline__ void finish_block(typename R::acc_t tv, const LocalPa
   }
 
   if (nparts == 1) {
-    if (threadIdx.x == 0) {
-      finish_scalar<R>(p, v);
-      if (p.trace) p.trace[4 * blockIdx.x + 3] = globaltimer_ns();
-    }
+    finish_scalar<R>(p, v);
+    if (p.trace && threadIdx.x == 0) p.trace[4 * blockIdx.x + 3] = globaltimer_ns();
     return;
   }
 
@@ -185,11 +199,9 @@ __device__ __forceinline__ void finish_block(typename R::acc_t tv, const LocalPa
   acc_t a = F::identity();
   for (unsigned i = threadIdx.x; i < nparts; i += blockDim.x) a = F::apply(a, ld_cg(partials + i));
   a = block_reduce<R>(a, s_scratch);
-  if (threadIdx.x == 0) {
-    *p.ticket = 0;  // re-arm for the next (stream-ordered) launch
-    finish_scalar<R>(p, a);
-    if (p.trace) p.trace[4 * blockIdx.x + 3] = globaltimer_ns();
-  }
+  if (threadIdx.x == 0) *p.ticket = 0;  // re-arm for the next (stream-ordered) launch
+  finish_scalar<R>(p, a);
+  if (p.trace && threadIdx.x == 0) p.trace[4 * blockIdx.x + 3] = globaltimer_ns();
 }
 
 // Head/tail scalars (fewer than one vector each) are folded in by CTA 0.

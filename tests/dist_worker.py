@@ -12,6 +12,10 @@ import cuda_mpi_reductions_b200 as b2r  # noqa: E402
 from cuda_mpi_reductions_b200.parallel import Communicator  # noqa: E402
 
 
+# absolute slack per rank for reordered fp sums (tree / NVLS): the tree keeps bf16 partials between rounds, values are in [-1, 1]
+ATOL = {torch.int32: 0, torch.float32: 1e-5, torch.float64: 1e-13, torch.bfloat16: 2.0**-7}
+
+
 def main():
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ.get("LOCAL_RANK", os.environ["RANK"]))
     torch.cuda.set_device(local)
@@ -46,7 +50,7 @@ def main():
                     comm.check()
                     exact = algo in ("oneshot", "twoshot", "push") or op != "sum" or dtype == torch.int32
                     got = out.cpu()
-                    ok = torch.equal(got, want) if exact else torch.allclose(got.double(), want.double(), rtol=2e-2 if dtype == torch.bfloat16 else 1e-5, atol=1e-5)
+                    ok = torch.equal(got, want) if exact else torch.allclose(got.double(), want.double(), rtol=2e-2 if dtype == torch.bfloat16 else 1e-5, atol=ATOL[dtype] * world)
                     if not ok:
                         fails += 1
                         print(f"[rank {rank}] allreduce MISMATCH dtype={dtype} count={count} op={op} algo={algo}", flush=True)
@@ -55,7 +59,7 @@ def main():
                     comm.check()
                     if rank == root:
                         got = red.cpu()
-                        ok = torch.equal(got, want) if exact else torch.allclose(got.double(), want.double(), rtol=2e-2 if dtype == torch.bfloat16 else 1e-5, atol=1e-5)
+                        ok = torch.equal(got, want) if exact else torch.allclose(got.double(), want.double(), rtol=2e-2 if dtype == torch.bfloat16 else 1e-5, atol=ATOL[dtype] * world)
                         if not ok:
                             fails += 1
                             print(f"[rank {rank}] reduce MISMATCH dtype={dtype} count={count} op={op} algo={algo} root={root}", flush=True)

@@ -58,12 +58,16 @@ def test_int_sum_wraps_across_ranks():
 
 def test_algo_selection_is_pure_and_sensible():
     sel = _lib.LIB.b2r_select_algo
-    # small messages: one-shot; large: NVLS when available and the instruction exists, else two-shot
-    assert sel(1, 1024, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_ONESHOT
+    # NVLS whenever the switch can do it (>= 4 GPUs, 8/16-byte multimem forms); otherwise one-shot for tiny messages
+    # and two-shot beyond
+    assert sel(1, 1024, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS
     assert sel(1, 1 << 30, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS
+    assert sel(1, 1 << 30, _lib.FLOAT32, _lib.SUM, 2, 1) == _lib.ALGO_TWOSHOT  # NVLS loses at 2 GPUs
     assert sel(1, 1 << 30, _lib.FLOAT32, _lib.SUM, 8, 0) == _lib.ALGO_TWOSHOT
+    assert sel(1, 1024, _lib.FLOAT32, _lib.SUM, 8, 0) == _lib.ALGO_ONESHOT
     assert sel(1, 1 << 30, _lib.FLOAT32, _lib.MIN, 8, 1) == _lib.ALGO_TWOSHOT  # no multimem min for fp32
     assert sel(1, 1 << 30, _lib.FLOAT64, _lib.MAX, 8, 1) == _lib.ALGO_TWOSHOT
     assert sel(1, 1 << 30, _lib.BFLOAT16, _lib.MAX, 8, 1) == _lib.ALGO_NVLS
     assert sel(0, 1 << 30, _lib.INT32, _lib.SUM, 8, 1) == _lib.ALGO_TWOSHOT  # 4-byte multimem ops: P2P vectors are faster
     assert sel(0, 64, _lib.FLOAT64, _lib.SUM, 2, 0) == _lib.ALGO_ONESHOT
+    assert sel(0, 1 << 20, _lib.FLOAT64, _lib.SUM, 1, 0) == _lib.ALGO_ONESHOT
