@@ -7,7 +7,7 @@
 //   --maxblocks=<CTAs>   --cpufinal   --cputhresh=<N>   --shmoo   --device=<N>   --qatest   --noprompt   --prompt
 // and new ones:
 //   --iters=<100>  --warmup=<3>  --norotate (time one L2-resident buffer like the reference does)  --cluster=<1|2|4|8>
-//   --unroll=<4|8>  --stages=<N>  --seed=<N>  --fill=sdk|full|signed  --csv=<path>  --jsonl=<path>  --nolog
+//   --pdl (overlap consecutive launches)  --unroll=<4|8>  --stages=<N>  --seed=<N>  --fill=sdk|full|signed  --csv=<path>  --jsonl=<path>  --nolog
 // It prints the reference's lines ("Reduction, Throughput = ... GB/s, Time = ... s, Size = ... Elements, NumDevsUsed = 1,
 // Workgroup = ...", GPU/CPU result, PASSED/FAILED) so scripts written against the sample keep working, followed by the
 // device-event measurement over rotating inputs (the honest HBM number) and the fraction of the measured roofline.
@@ -192,6 +192,7 @@ int main(int argc, char** argv) {
   o.cfg.cluster = (int)f.i64("cluster", 0);
   o.cfg.unroll = (int)f.i64("unroll", 0);
   o.cfg.stages = (int)f.i64("stages", 0);
+  o.cfg.pdl = f.has("pdl") ? 1 : 0;  // programmatic dependent launch between the back-to-back timed launches
 
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
@@ -263,8 +264,8 @@ int main(int argc, char** argv) {
     log.print("Device-event time (back-to-back, %s): %.3f us -> %.2f GB/s = %.2f GiB/s (%.1f%% of measured HBM copy roofline %.1f GB/s)\n",
               o.rotate ? "rotating inputs > L2" : "single L2-resident input", r.event_ms * 1e3, bytes / r.event_ms * 1e-6,
               bytes / r.event_ms * 1e3 / 1073741824.0, 100.0 * bytes / r.event_ms * 1e-6 / o.hbm_peak_gbs, o.hbm_peak_gbs);
-    log.print("Kernel: %s, %d CTAs x %d threads, cluster %d, unroll %d\n", variant_name(r.geom.variant), r.geom.ctas, r.geom.threads,
-              r.geom.cluster, r.geom.unroll);
+    log.print("Kernel: %s, %d CTAs x %d threads, cluster %d, unroll %d, pdl %d\n", variant_name(r.geom.variant), r.geom.ctas, r.geom.threads,
+              r.geom.cluster, r.geom.unroll, r.geom.pdl);
     log.print("\n");
     print_value(log, "GPU", r.gpu, o.dtype);
     print_value(log, "CPU", r.cpu, o.dtype);

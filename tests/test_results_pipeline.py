@@ -1,0 +1,69 @@
+"""CPU-only: result aggregation and plot-script generation (reference: mpi/getAvgs.sh:3-14, mpi/makePlots.gp:1-39) and
+the mini-MPI plumbing configuration (BASELINE.json config 1: custom tree vs MPI_Reduce on CPU ranks)."""
+import os
+import subprocess
+
+import pytest
+
+from cuda_mpi_reductions_b200.models import MPI_REDUCE, SDK_REDUCTION
+from cuda_mpi_reductions_b200.utils import results
+
+REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_aggregate_matches_reference_layout(tmp_path):
+    collected = tmp_path / "collected.txt"
+    collected.write_text(
+        "# DATATYPE OP NODES GB/sec\n"
+        "INT MAX 64      8.260\nINT MAX 64      8.520\nINT SUM 256     38.0\nINT SUM 64      9.126\nINT SUM 64      9.238\n"
+        "DOUBLE MIN 1024  88.7626\nnoise line\nINT SUM 256     39.29681\n")
+    out = results.aggregate(str(collected), str(tmp_path / "results"))
+    text = open(out[("INT", "SUM")]).read()
+    assert text == "\nINT SUM 64 9.18200\nINT SUM 256 38.64840\n"  # blank first line, ascending nodes, 5 decimals truncated
+    assert open(out[("INT", "MAX")]).read() == "\nINT MAX 64 8.39000\n"
+    assert ("DOUBLE", "MIN") in out
+
+
+def test_reference_results_are_reproduced_from_its_collected_file(tmp_path):
+    ref = "/root/reference/mpi/collected.txt"
+    if not os.path.exists(ref):
+        pytest.skip("reference tree not mounted")
+    out = results.aggregate(ref, str(tmp_path))
+    got = open(out[("INT", "SUM")]).read().split("\n")
+    want = open("/root/reference/mpi/results/INT_SUM.txt").read().split("\n")
+    assert sorted(l for l in got if l) == sorted(l for l in want if l)  # the reference lists nodes in `sort -n | uniq` order too
+
+
+def test_gnuplot_script(tmp_path):
+    (tmp_path / "INT_SUM.txt").write_text("\nINT SUM 2 100.0\n")
+    path = results.write_gnuplot(str(tmp_path), str(tmp_path / "p.gp"), {("INT", "SUM"): 7000.0, ("INT", "MIN"): 6900.0, ("INT", "MAX"): 6950.0})
+    gp = open(path).read()
+    assert 'set output "int.eps"' in gp and "INT_SUM.txt" in gp and "f(x) =" in gp and 'set output "double.eps"' in gp
+
+
+def test_workload_constants_match_the_reference():
+    assert SDK_REDUCTION.elements == 1 << 24 and SDK_REDUCTION.nbytes("int") == 64 << 20
+    assert MPI_REDUCE.count_per_rank("int", 8) == (512 << 20) // 8 and MPI_REDUCE.count_per_rank("double", 1024) == (256 << 20) // 1024
+    assert list(MPI_REDUCE.sweep_bytes())[0] == 1024 and list(MPI_REDUCE.sweep_bytes())[-1] == 1 << 32
+
+
+@pytest.mark.parametrize("np_", [2, 3, 4])
+@pytest.mark.parametrize("algo", ["twoshot", "oneshot", "tree"])
+def test_minimpi_custom_tree_vs_library_reduce(np_, algo):
+    exe, run = os.path.join(REPO, "bin", "tree_reduce"), os.path.join(REPO, "bin", "b2r_mpirun")
+    if not (os.path.exists(exe) and os.path.exists(run)):
+        subprocess.run(["make", "-C", os.path.join(REPO, "minimpi")], check=True, capture_output=True)
+    env = dict(os.environ, MINIMPI_ALGO=algo)
+    res = subprocess.run([run, "-np", str(np_), "--window-mb", "1", exe, "600000", "1"], capture_output=True, text=True, timeout=120, env=env)
+    assert res.returncode == 0 and "PASSED" in res.stdout, res.stdout[-500:] + res.stderr[-500:]
+    rows = list(results.parse_rows(res.stdout.splitlines()))
+    assert {r[0] for r in rows} == {"TREE_INT", "LIB_INT", "TREE_DOUBLE", "LIB_DOUBLE"} and all(r[2] == np_ for r in rows)
+
+
+def test_minimpi_aborts_cleanly_when_not_launched():
+    exe = os.path.join(REPO, "bin", "tree_reduce")
+    if not os.path.exists(exe):
+        pytest.skip("not built")
+    env = {k: v for k, v in os.environ.items() if not k.startswith("MINIMPI_")}
+    res = subprocess.run([exe], capture_output=True, text=True, timeout=30, env=env)
+    assert res.returncode != 0 and "b2r_mpirun" in res.stderr
