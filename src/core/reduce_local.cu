@@ -137,6 +137,11 @@ b2r_status_t plan_local(uint64_t count, b2r_dtype_t dtype, b2r_op_t op, int sm_c
   g->cluster = cluster;
   g->unroll = unroll;
   g->pdl = pdl ? 1 : 0;
+  if (variant == B2R_VARIANT_TMA) {
+    // the single-CTA path above may have lowered `threads`: the tile MUST follow (every consumer thread owns exactly
+    // kTmaVecsPerThread vectors of a full tile; a stale, larger tile would leave part of each full tile unread)
+    tile_bytes = (threads - 32) * 16 * kTmaVecsPerThread;
+  }
   g->smem_bytes = variant == B2R_VARIANT_TMA ? st * tile_bytes + 16 * st : 0;
   *stages = st;
   *tile_vecs = tile_bytes / 16;

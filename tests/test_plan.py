@@ -52,3 +52,10 @@ def test_pdl_plans_one_cta_per_sm():
     p = b2r.plan(1 << 24, torch.int32, cfg={"pdl": 1})
     assert p["pdl"] == 1 and p["ctas"] == 148
     assert b2r.plan(1 << 24, torch.int32)["pdl"] == 0
+
+
+def test_tma_tile_matches_final_thread_count():
+    for n in (256, 1024, 2048, 4096, 1 << 16, 1 << 24):
+        for cfg in ({"variant": "tma"}, {"variant": "tma", "pdl": 1}, {"variant": "tma", "threads": 512}):
+            p = b2r.plan(n, torch.float64, cfg=cfg)
+            assert p["tile_bytes"] == (p["threads"] - 32) * 64, (n, cfg, p)

@@ -242,3 +242,16 @@ def test_reduce_on_non_current_device_pointer_guard():
     b2r.reduce(x, "sum", out=o1, workspace=ws, cfg=cfg)
     o2 = b2r.reduce(o1, "sum", workspace=ws, cfg=cfg)
     assert o2.item() == o1.item()
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
+def test_tma_single_cta_tile_follows_thread_count(dtype):
+    """Regression: for inputs of exactly one planned tile (8 KiB with 160 planned threads) the single-CTA path lowers the
+    thread count; the tile size has to follow or part of the tile is never read (found by bench_reduce --shmoo)."""
+    esz = torch.empty((), dtype=dtype).element_size()
+    for nbytes in (4096, 6144, 8192, 8192 + 16, 14336, 16384, 32768, 65536):
+        n = nbytes // esz
+        x = b2r.fill_host(n, dtype, seed=nbytes, mode="signed")
+        for op in OPS:
+            check(b2r.reduce(x.cuda(), op, cfg={"variant": "tma"}), x, op)
+            check(b2r.reduce(x.cuda(), op, cfg={"variant": "tma", "pdl": 1}), x, op)
