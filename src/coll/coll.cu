@@ -12,6 +12,7 @@
 #include "../comm/comm.h"
 #include "../core/reduce_internal.h"
 #include "../util/check.h"
+#include "../util/nvtx.h"
 #include "coll_kernels.cuh"
 
 namespace b2r {
@@ -132,6 +133,7 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
   const int P = c0->nranks;
   const size_t esz = b2r_dtype_size(dtype);
   const bool is_all = kind_call == kCallAllreduce;
+  NvtxRange nvtx(is_all ? "b2r_allreduce" : "b2r_reduce");
   B2R_REQUIRE(dtype >= B2R_INT32 && dtype <= B2R_BFLOAT16, "collective: bad dtype %d", (int)dtype);
   B2R_REQUIRE(op >= B2R_SUM && op <= B2R_MAX, "collective: bad op %d", (int)op);
   B2R_REQUIRE(is_all || (root >= 0 && root < P), "reduce: root %d out of range [0,%d)", root, P);

@@ -10,6 +10,7 @@
 #include <vector>
 
 #include "../util/check.h"
+#include "../util/nvtx.h"
 #include "b2r.h"
 #include "reduce_kernels.cuh"
 #include "reduce_internal.h"
@@ -213,6 +214,7 @@ b2r_status_t prepare_local(const void* in, void* out, uint64_t count, b2r_dtype_
 b2r_status_t reduce_local_impl(const void* in, void* out, uint64_t count, b2r_dtype_t dtype, b2r_op_t op,
                                b2r_workspace* ws, cudaStream_t stream, const b2r_launch_cfg_t* cfg, int out_as_acc,
                                const XgCall* xg) {
+  NvtxRange nvtx(xg ? "b2r_reduce_scalar_sharded" : "b2r_reduce_local");
   B2R_REQUIRE(ws != nullptr, "b2r_reduce_local: workspace is NULL");
   // launch on the workspace's device whatever the caller's current device is (cheap when they already agree)
   int cur = -1;
@@ -354,6 +356,7 @@ b2r_status_t b2r_workspace_trace_read(b2r_workspace_t ws, uint64_t* stamps, int 
 // combined on the host in chunk order, so bf16 is still rounded only once.
 b2r_status_t b2r_reduce_from_host(const void* host_in, void* out_host, uint64_t count, b2r_dtype_t dtype, b2r_op_t op,
                                   b2r_workspace_t ws, void* stream_) {
+  NvtxRange nvtx("b2r_reduce_from_host");
   B2R_REQUIRE(ws != nullptr && out_host != nullptr, "b2r_reduce_from_host: NULL argument");
   B2R_REQUIRE(host_in != nullptr || count == 0, "b2r_reduce_from_host: host_in is NULL");
   B2R_REQUIRE(dtype >= B2R_INT32 && dtype <= B2R_BFLOAT16, "bad dtype %d", (int)dtype);
