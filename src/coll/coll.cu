@@ -7,6 +7,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <memory>
+#include <mutex>
 #include <vector>
 
 #include "../comm/comm.h"
@@ -120,6 +121,20 @@ bool nvls_supported(b2r_dtype_t dtype, b2r_op_t op) {
   return true;  // bf16x2 add/min/max, 32-bit integer add/min/max
 }
 
+// B2R_WEAK_DATA=1: switch the payload accesses of the collective kernels to weak loads/stores (see coll_kernels.cuh). The
+// constant lives per device; it is written once per device before the first collective launched there.
+b2r_status_t apply_data_flavour(int device) {
+  static std::mutex mu;
+  static bool done[64] = {false};
+  const int weak = env_int("B2R_WEAK_DATA", 0) ? 1 : 0;
+  if (!weak || device < 0 || device >= 64) return B2R_OK;
+  std::lock_guard<std::mutex> lk(mu);
+  if (done[device]) return B2R_OK;
+  B2R_CUDA_CHECK(cudaMemcpyToSymbol(c_weak_data, &weak, sizeof(int)));
+  done[device] = true;
+  return B2R_OK;
+}
+
 struct RankCall {
   b2r_comm* c;
   const void* send;
@@ -155,6 +170,7 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
     if (rc[0].recv != rc[0].send) B2R_CUDA_CHECK(cudaMemcpyAsync(rc[0].recv, rc[0].send, count * esz, cudaMemcpyDeviceToDevice, rc[0].stream));
     return B2R_OK;
   }
+  B2R_CHECK(apply_data_flavour(c0->device));
 
   const uint64_t total_bytes = count * esz;
   if (algo == B2R_ALGO_AUTO) algo = b2r_select_algo(is_all ? 1 : 0, total_bytes, dtype, op, P, c0->has_mc ? 1 : 0);

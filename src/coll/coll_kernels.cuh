@@ -32,16 +32,35 @@ struct CollLaunch {
 };
 
 // ------------------------------------------------------------------------------------------------ memory ops on peer / multicast addresses
+// Bulk data accesses come in two flavours, chosen per process by B2R_WEAK_DATA (0 = default):
+//   strong: ld/st.relaxed.sys  (SASS LDG/STG ... STRONG.SYS) — what every number recorded in profiles/ was measured with;
+//   weak  : plain ld/st.global (SASS LDG.E.128 / STG.E.128)  — what NCCL-style kernels use for payload; ordering is still
+//           provided by the st.release.sys / ld.acquire.sys flags around the data phase (the acquire also invalidates L1).
+// The weak flavour is a candidate for the pull/push paths that plateau below link rate (profiles/multi_gpu.md §3); it is
+// correct under the PTX memory model but not yet measured on NVLink, hence opt-in.
+__constant__ int c_weak_data = 0;
+
 __device__ __forceinline__ V16 ld_peer(const char* p) {  // may be local or remote; never through the read-only path
   V16 v;
-  asm volatile("ld.relaxed.sys.global.L1::no_allocate.v4.b32 {%0,%1,%2,%3}, [%4];"
-               : "=r"(v.w[0]), "=r"(v.w[1]), "=r"(v.w[2]), "=r"(v.w[3])
-               : "l"(p)
-               : "memory");
+  if (c_weak_data) {
+    asm volatile("ld.global.L1::no_allocate.v4.b32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(v.w[0]), "=r"(v.w[1]), "=r"(v.w[2]), "=r"(v.w[3])
+                 : "l"(p)
+                 : "memory");
+  } else {
+    asm volatile("ld.relaxed.sys.global.L1::no_allocate.v4.b32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(v.w[0]), "=r"(v.w[1]), "=r"(v.w[2]), "=r"(v.w[3])
+                 : "l"(p)
+                 : "memory");
+  }
   return v;
 }
 __device__ __forceinline__ void st_peer(char* p, const V16& v) {
-  asm volatile("st.relaxed.sys.global.v4.b32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.w[0]), "r"(v.w[1]), "r"(v.w[2]), "r"(v.w[3]) : "memory");
+  if (c_weak_data) {
+    asm volatile("st.global.v4.b32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.w[0]), "r"(v.w[1]), "r"(v.w[2]), "r"(v.w[3]) : "memory");
+  } else {
+    asm volatile("st.relaxed.sys.global.v4.b32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.w[0]), "r"(v.w[1]), "r"(v.w[2]), "r"(v.w[3]) : "memory");
+  }
 }
 
 // ------------------------------------------------------------------------------------------------ vector combine per (dtype, op)

@@ -213,3 +213,33 @@ def test_delay_injection_is_tolerated(monkeypatch):
     finally:
         for c in cs:
             c.close()
+
+
+def test_weak_payload_flavour_in_a_fresh_process():
+    """B2R_WEAK_DATA=1 switches the payload loads/stores of the collective kernels to weak accesses (a per-process,
+    per-device constant), so it is exercised in a subprocess: every algorithm must still match the host algorithms."""
+    import subprocess
+    import sys
+
+    code = r'''
+import torch, cuda_mpi_reductions_b200 as b2r
+from cuda_mpi_reductions_b200.parallel import Communicator, host_reduce_threads
+cs = Communicator.loopback(4, device=0, heap_bytes=32 << 20)
+for dtype in (torch.int32, torch.float64, torch.bfloat16):
+    for count in (5, 70001, (1 << 20) + 3):
+        xh = [b2r.fill_host(count, dtype, seed=9 * r + count, mode="signed") for r in range(4)]
+        xs = [x.cuda() for x in xh]
+        for algo in ("oneshot", "twoshot", "tree", "push"):
+            want = host_reduce_threads(xh, "sum", -1, algo)[0]
+            outs = Communicator.group_allreduce(cs, xs, "sum", algo=algo)
+            Communicator.group_check(cs)
+            assert all(torch.equal(o.cpu().view(torch.uint8), want.view(torch.uint8)) for o in outs), (dtype, count, algo)
+            red = Communicator.group_reduce(cs, xs, "max", root=2, algo=algo)
+            Communicator.group_check(cs)
+            assert torch.equal(red[2].cpu().view(torch.uint8), host_reduce_threads(xh, "max", 2, algo).view(torch.uint8))
+print("WEAK_OK")
+'''
+    env = dict(os.environ, B2R_WEAK_DATA="1")
+    repo = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    res = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300, env=env, cwd=repo)
+    assert res.returncode == 0 and "WEAK_OK" in res.stdout, res.stdout[-1000:] + res.stderr[-2000:]
