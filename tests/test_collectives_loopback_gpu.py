@@ -243,3 +243,18 @@ print("WEAK_OK")
     repo = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     res = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300, env=env, cwd=repo)
     assert res.returncode == 0 and "WEAK_OK" in res.stdout, res.stdout[-1000:] + res.stderr[-2000:]
+
+
+def test_single_rank_communicator_degenerates_to_a_copy():
+    (c,) = Communicator.loopback(1, device=0, heap_bytes=1 << 20)
+    try:
+        x = b2r.fill_device(1000, torch.float32, seed=1, mode="signed")
+        assert torch.equal(c.allreduce(x, "sum"), x)
+        assert torch.equal(c.reduce(x, "max", root=0), x)
+        got = c.reduce_scalar_sharded(x, "sum")
+        c.check()
+        assert abs(got.item() - x.double().sum().item()) < 1e-3
+        c.barrier()
+        assert c.select_algo(1 << 20, torch.float32) == "oneshot"
+    finally:
+        c.close()
