@@ -60,6 +60,7 @@ b2r_algo_t parse_algo(const std::string& s) {
   if (s == "tree") return B2R_ALGO_TREE;
   if (s == "nvls") return B2R_ALGO_NVLS;
   if (s == "push") return B2R_ALGO_PUSH;
+  if (s == "ring") return B2R_ALGO_RING;
   return B2R_ALGO_AUTO;
 }
 
@@ -266,6 +267,7 @@ int main(int argc, char** argv) {
               const uint64_t count = bytes / b2r_dtype_size(dt);
               if (count == 0) continue;
               if (algo == B2R_ALGO_NVLS && !has_mc) continue;
+              if (algo == B2R_ALGO_RING && allreduce) continue;
               if (algo == B2R_ALGO_NVLS && (dt == B2R_FLOAT32 || dt == B2R_FLOAT64) && op != B2R_SUM) continue;
               if ((algo == B2R_ALGO_ONESHOT || algo == B2R_ALGO_TREE) && bytes > (64ull << 20)) continue;  // pointless at this size
               if (f.has("check") && bytes <= (256ull << 20)) all_ok = verify(R, allreduce, count, dt, op, root, algo) && all_ok;

@@ -56,7 +56,8 @@ typedef enum {
   B2R_ALGO_TWOSHOT = 2, /* reduce-scatter by P2P loads + gather by P2P stores */
   B2R_ALGO_TREE = 3,    /* hand-written binomial tree, log2(P) rounds of pairwise P2P combine */
   B2R_ALGO_NVLS = 4,    /* multimem.ld_reduce / multimem.st through the NVSwitch (needs multicast) */
-  B2R_ALGO_PUSH = 5     /* scatter by P2P stores into the owners' staging, reduce locally, push the result: no remote loads */
+  B2R_ALGO_PUSH = 5,    /* scatter by P2P stores into the owners' staging, reduce locally, push the result: no remote loads */
+  B2R_ALGO_RING = 6     /* reduce only: store-forwarding chain that ends at the root (one neighbour per GPU, no remote loads) */
 } b2r_algo_t;
 
 typedef struct {

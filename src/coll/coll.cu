@@ -52,6 +52,7 @@ CollKernel pick_kind(int kind) {
     case kCollNvls: return Nvls<D, O>::kSupported ? coll_kernel<D, O, kCollNvls, UNR> : nullptr;
     case kCollBarrier: return coll_kernel<D, O, kCollBarrier, 4>;
     case kCollPush: return coll_kernel<D, O, kCollPush, 4>;
+    case kCollRing: return coll_kernel<D, O, kCollRing, 4>;
   }
   return nullptr;
 }
@@ -92,7 +93,7 @@ Shape coll_shape(const b2r_comm* c, int kind, uint64_t bytes, int nvirtual) {
     s.unroll = bytes >= (8u << 20) ? 8 : 4;
     cap = 32;
     per_cta = 32768;
-  } else if (kind == kCollPush) {
+  } else if (kind == kCollPush || kind == kCollRing) {
     s.threads = 512;
     s.unroll = 4;
     cap = 128;
@@ -179,7 +180,8 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
     if (!nvls_supported(dtype, op)) return fail(B2R_ERR_UNSUPPORTED, "NVLS has no %s %s instruction", b2r_dtype_name(dtype), b2r_op_name(op));
   }
   const int kind = algo == B2R_ALGO_ONESHOT ? kCollOneshot : algo == B2R_ALGO_TWOSHOT ? kCollTwoshot : algo == B2R_ALGO_TREE ? kCollTree
-                   : algo == B2R_ALGO_PUSH ? kCollPush : kCollNvls;
+                   : algo == B2R_ALGO_PUSH ? kCollPush : algo == B2R_ALGO_RING ? kCollRing : kCollNvls;
+  if (kind == kCollRing && is_all) return fail(B2R_ERR_UNSUPPORTED, "the ring algorithm implements reduce-to-root only");
   B2R_REQUIRE(kernel_exists(dtype, (int)op, kind), "collective: no kernel for dtype %d op %d algo %d", (int)dtype, (int)op, (int)algo);
 
   // Chunking rule (identical on every rank): messages larger than one staging region are cut into stage-sized chunks,
@@ -223,11 +225,20 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
       A.epoch = c->epoch;
       A.root = is_all ? -1 : root;
       c->epoch += 8;  // start + end + up to 4 tree rounds, rounded up; same increment on every rank
-      if (kind == kCollPush) A.seq = ++c->push_seq;
+      if (kind == kCollPush || kind == kCollRing) A.seq = ++c->push_seq;
     }
     const Shape shape = coll_shape(c0, kind, bytes, n);
     int ctas = shape.ctas;
     const int threads = shape.threads;
+    if (kind == kCollRing) {
+      // staging ring in the work region: depth x ctas blocks of (threads x 8) vectors; at least 2 deep
+      const uint64_t block_bytes = (uint64_t)threads * 8 * 16;
+      ctas = (int)std::max<uint64_t>(1, std::min<uint64_t>((bytes + block_bytes - 1) / block_bytes, (uint64_t)std::max(1, env_int("B2R_RING_CTAS", 64))));
+      ctas = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)ctas, c0->stage_bytes / (2ull * block_bytes)));
+      if (n > 1) ctas = std::max(1, std::min(ctas, c0->sm_count / n));
+      const int depth = (int)std::min<uint64_t>(8, c0->stage_bytes / ((uint64_t)ctas * block_bytes));
+      for (int i = 0; i < n; ++i) L.a[n == 1 ? 0 : rc[i].c->rank].ring_depth = depth;
+    }
     if (kind == kCollPush) {
       // staging ring in the work region: depth x P sources x ctas blocks of (threads x 4) vectors; at least 2 deep
       const uint64_t block_bytes = (uint64_t)threads * 4 * 16;
@@ -383,12 +394,13 @@ using namespace b2r;
 
 extern "C" {
 
-// Size thresholds measured on 8x B200 (profiles/collective_sweep.md). One-shot costs one NVLink round trip but every
+// Size thresholds measured on 8x B200 (profiles/collectives_8gpu.md). One-shot costs one NVLink round trip but every
 // rank pulls the WHOLE message from every peer; two-shot / NVLS move 1/P of it per rank.
 b2r_algo_t b2r_select_algo(int is_allreduce, uint64_t bytes, b2r_dtype_t dtype, b2r_op_t op, int nranks, int has_multicast) {
   if (nranks <= 1) return B2R_ALGO_ONESHOT;
   const int forced = env_int("B2R_ALGO", 0);
   if (forced >= B2R_ALGO_ONESHOT && forced <= B2R_ALGO_PUSH) return (b2r_algo_t)forced;
+  if (forced == B2R_ALGO_RING && !is_allreduce) return B2R_ALGO_RING;
   // NVLS moves (1 + 1/P) messages per GPU against two-shot's 2(P-1)/P and needs one switch round trip for any size:
   // from 4 GPUs up it wins at EVERY size for the types with 8/16-byte multimem forms (fp32 add, bf16, fp64 add);
   // at 2 GPUs it loses to the P2P paths (measured). 32-bit integer multimem ops move 4 bytes per instruction and

@@ -547,6 +547,101 @@ __device__ void push_body(const CollArgs& A) {
   cta_barrier(A, A.epoch + 2);
 }
 
+// ------------------------------------------------------------------------------------------------ ring (store-forwarding chain to the root)
+// What NCCL's reduce does, restated for this runtime: the ranks form a chain that ends at the root (position p = distance
+// to the root); the message is cut into blocks; CTA b of every rank owns blocks b, b+G, ... ("channels"). For each block
+// the rank at position p waits for the running partial from position p+1 in its own staging slot (local memory), combines
+// it with its own block and STORES the result into the slot of position p-1 (the root stores into recv). Every GPU
+// receives one message and sends one message, all of it posted stores to exactly ONE neighbour: no remote loads, no
+// incast. Slots are a ring of `depth` entries per CTA with data flags (downstream) and acks (upstream), values
+// (call << 16 | step): monotonic, never reset. Combination order = chain order (farthest rank first), the host restatement
+// (host_algos.h, B2R_ALGO_RING) folds in the same order, so results are bit-identical to it. Reduce only.
+template <int D, int O, int UNR>
+__device__ void ring_body(const CollArgs& A) {
+  using V = VecOps<D, O>;
+  const CollCtx& c = A.ctx;
+  constexpr int E = V::kElem;
+  constexpr int VPT = 8;  // vectors per thread per block
+  const int P = c.nranks, r = c.rank, root = A.root, G = (int)gridDim.x, b = (int)blockIdx.x;
+  const int pos = (r - root + P) % P;
+  const int pred = pos + 1 < P ? (root + pos + 1) % P : -1;  // sends to me
+  const int succ = pos > 0 ? (root + pos - 1) % P : -1;      // I send to it
+  const unsigned long long nvec = A.count * E / 16;
+  const unsigned int Cv = blockDim.x * VPT;
+  const unsigned long long nblocks = (nvec + Cv - 1) / Cv;
+  const unsigned long long steps = (unsigned long long)b < nblocks ? (nblocks - b + G - 1) / G : 0;
+  const int depth = A.ring_depth;
+  const unsigned int base_val = A.seq << 16;
+
+  __shared__ PeerOffsets po;
+  start_barrier(A, &po);
+  const char* send = c.heap[r] + A.send_off;
+  auto slot = [&](int rank, unsigned long long step) {
+    return c.heap[rank] + A.work_off + (((step % depth) * G + b) * (unsigned long long)Cv) * 16ull;
+  };
+  for (unsigned long long i = 0; i < steps; ++i) {
+    const unsigned long long lo = (b + i * G) * (unsigned long long)Cv;
+    const unsigned int len = (unsigned int)min((unsigned long long)Cv, nvec - lo);
+    if (threadIdx.x == 0 && pred >= 0) {
+      const unsigned int* flag = (const unsigned int*)(c.heap[r] + kOffPushData) + (size_t)b * B2R_MAX_RANKS + pred;
+      wait_flag_ge(flag, base_val + (unsigned int)(i + 1), c);
+    }
+    if (threadIdx.x == 32 && succ >= 0 && i >= (unsigned long long)depth) {
+      const unsigned int* ack = (const unsigned int*)(c.heap[r] + kOffPushAck) + (size_t)b * B2R_MAX_RANKS + succ;
+      wait_flag_ge(ack, base_val + (unsigned int)(i - depth + 1), c);
+    }
+    __syncthreads();
+    char* dst = succ >= 0 ? slot(succ, i) : c.heap[r] + A.recv_off + lo * 16;
+    const char* in = slot(r, i);
+    V16 own[VPT], got[VPT];
+#pragma unroll
+    for (int u = 0; u < VPT; ++u) {
+      const unsigned int j = threadIdx.x + u * blockDim.x;
+      if (j < len) {
+        own[u] = ld_peer(send + (lo + j) * 16);
+        if (pred >= 0) got[u] = ld_peer(in + (unsigned long long)j * 16);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < VPT; ++u) {
+      const unsigned int j = threadIdx.x + u * blockDim.x;
+      if (j < len) {
+        if (pred >= 0) {
+          typename V::Acc acc = V::unpack(got[u]);
+          V::combine(acc, own[u]);
+          st_peer(dst + (unsigned long long)j * 16, V::pack(acc));
+        } else {
+          st_peer(dst + (unsigned long long)j * 16, own[u]);
+        }
+      }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0 && succ >= 0 && !c.fault_skip_signal) {
+      unsigned int* flag = (unsigned int*)(c.heap[succ] + kOffPushData) + (size_t)b * B2R_MAX_RANKS + r;
+      st_release_sys(flag, base_val + (unsigned int)(i + 1));
+    }
+    if (threadIdx.x == 32 && pred >= 0 && !c.fault_skip_signal) {
+      unsigned int* ack = (unsigned int*)(c.heap[pred] + kOffPushAck) + (size_t)b * B2R_MAX_RANKS + r;
+      st_release_sys(ack, base_val + (unsigned int)(i + 1));
+    }
+  }
+  // the (< 16 byte) tail: the root pulls it, folding in chain order
+  if (pos == 0 && nvec * (16 / E) < A.count) {
+    __shared__ const char* src[B2R_MAX_RANKS];
+    __shared__ char* dst1[1];
+    if (threadIdx.x == 0) {
+      for (int q = 0; q < P; ++q) {
+        const int rank_q = (root + (P - 1 - q)) % P;  // farthest position first
+        src[q] = c.heap[rank_q] + po.send[rank_q];
+      }
+      dst1[0] = c.heap[r] + A.recv_off;
+    }
+    __syncthreads();
+    combine_tail<D, O>(nvec * (16 / E), A.count, src, P, dst1, 1);
+  }
+  cta_barrier(A, A.epoch + 2);
+}
+
 // ------------------------------------------------------------------------------------------------ NVLS (multimem)
 // The switch performs the combine: multimem.ld_reduce on the multicast address returns op over all ranks' copies;
 // multimem.st writes all ranks' copies. Supported by the hardware for: fp32 add (v4), bf16x2 add/min/max (v4, fp32
@@ -692,7 +787,7 @@ __device__ inline void barrier_body(const CollArgs& A) {
   start_barrier(A, &po);
 }
 
-enum CollKind { kCollOneshot = 1, kCollTwoshot = 2, kCollTree = 3, kCollNvls = 4, kCollBarrier = 5, kCollPush = 6 };
+enum CollKind { kCollOneshot = 1, kCollTwoshot = 2, kCollTree = 3, kCollNvls = 4, kCollBarrier = 5, kCollPush = 6, kCollRing = 7 };
 
 template <int D, int O, int KIND, int UNR>
 __global__ void __launch_bounds__(512) coll_kernel(const __grid_constant__ CollLaunch L) {
@@ -702,6 +797,7 @@ __global__ void __launch_bounds__(512) coll_kernel(const __grid_constant__ CollL
   else if (KIND == kCollTree) tree_body<D, O, UNR>(A);
   else if (KIND == kCollNvls) nvls_body<D, O, UNR>(A);
   else if (KIND == kCollPush) push_body<D, O, UNR>(A);
+  else if (KIND == kCollRing) ring_body<D, O, UNR>(A);
   else barrier_body(A);
 }
 

@@ -46,6 +46,15 @@ void host_collective_rank(const HostRankView& v, uint64_t count, b2r_dtype_t dty
       }
     }
     barrier();
+  } else if (algo == B2R_ALGO_RING) {
+    // chain ending at the root: left fold from the farthest position down to the root (same association order as ring_body)
+    const int rt = root < 0 ? 0 : root;
+    if (r == rt) {
+      std::vector<const void*> order(P);
+      for (int q = 0; q < P; ++q) order[q] = v.send[(rt + (P - 1 - q)) % P];
+      combine_many_host(v.recv[r], order.data(), P, 0, count, dtype, op);
+    }
+    barrier();
   } else {  // B2R_ALGO_TREE
     const int rt = root < 0 ? 0 : root;
     const int pos = (r - rt + P) % P;

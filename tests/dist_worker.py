@@ -55,6 +55,17 @@ def main():
                         fails += 1
                         print(f"[rank {rank}] allreduce MISMATCH dtype={dtype} count={count} op={op} algo={algo}", flush=True)
                     root = (count + rank * 0) % world
+                    for ralgo in ([algo, "ring"] if algo == "twoshot" else [algo]):
+                        red = comm.reduce(x, op, root=root, algo=ralgo)
+                        comm.check()
+                        if rank == root:
+                            rexact = ralgo in ("oneshot", "twoshot", "push") or op != "sum" or dtype == torch.int32
+                            got = red.cpu()
+                            ok = torch.equal(got, want) if rexact else torch.allclose(got.double(), want.double(), rtol=2e-2 if dtype == torch.bfloat16 else 1e-5, atol=ATOL[dtype] * world)
+                            if not ok:
+                                fails += 1
+                                print(f"[rank {rank}] reduce MISMATCH dtype={dtype} count={count} op={op} algo={ralgo} root={root}", flush=True)
+                    continue
                     red = comm.reduce(x, op, root=root, algo=algo)
                     comm.check()
                     if rank == root:

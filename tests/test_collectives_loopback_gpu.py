@@ -45,11 +45,11 @@ def test_allreduce(comms, algo, dtype):
                 assert torch.equal(bits(outs[r].cpu()), bits(want)), (P, algo, dtype, op, count, r)
 
 
-@pytest.mark.parametrize("algo", ALGOS)
+@pytest.mark.parametrize("algo", ALGOS + ["ring"])
 @pytest.mark.parametrize("dtype", [torch.int32, torch.float64, torch.bfloat16])
 def test_reduce_every_root(comms, algo, dtype):
     P = len(comms)
-    for count in (1, 1000, 65537):
+    for count in (1, 1000, 65537, (1 << 21) + 9):
         xs_h = [b2r.fill_host(count, dtype, seed=17 * r + count, mode="signed") for r in range(P)]
         xs = [x.cuda() for x in xs_h]
         for root in range(P):
@@ -258,3 +258,14 @@ def test_single_rank_communicator_degenerates_to_a_copy():
         assert c.select_algo(1 << 20, torch.float32) == "oneshot"
     finally:
         c.close()
+
+
+def test_ring_is_reduce_only(comms):
+    x = torch.zeros(64, device="cuda")
+    with pytest.raises(b2r.B2RError):
+        for c in comms:
+            c.allreduce(x, "sum", algo="ring")
+    # the failed group call must not leave a half-recorded collective behind
+    outs = Communicator.group_allreduce(comms, [x] * len(comms), "sum", algo="twoshot")
+    Communicator.group_check(comms)
+    assert all(float(o.sum()) == 0.0 for o in outs)

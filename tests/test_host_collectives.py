@@ -10,6 +10,12 @@ from cuda_mpi_reductions_b200.parallel import host_reduce_threads
 DTYPES = [torch.int32, torch.float32, torch.float64, torch.bfloat16]
 
 
+def chain_oracle(xs, op, root):
+    """Left fold from the farthest chain position down to the root (the ring algorithm's association order)."""
+    P = len(xs)
+    return elementwise_oracle([xs[(root + (P - 1 - q)) % P] for q in range(P)], op)
+
+
 def elementwise_oracle(xs, op):
     """Left-to-right combine in rank order; bf16 combined in fp32 and rounded once (the library's definition)."""
     if xs[0].dtype == torch.bfloat16:
@@ -71,3 +77,15 @@ def test_algo_selection_is_pure_and_sensible():
     assert sel(0, 1 << 30, _lib.INT32, _lib.SUM, 8, 1) == _lib.ALGO_TWOSHOT  # 4-byte multimem ops: P2P vectors are faster
     assert sel(0, 64, _lib.FLOAT64, _lib.SUM, 2, 0) == _lib.ALGO_ONESHOT
     assert sel(0, 1 << 20, _lib.FLOAT64, _lib.SUM, 1, 0) == _lib.ALGO_ONESHOT
+
+
+@pytest.mark.parametrize("nranks", [1, 2, 3, 5, 8])
+@pytest.mark.parametrize("dtype", DTYPES)
+def test_ring_reduce_folds_in_chain_order(nranks, dtype):
+    for count in (1, 7, 1025):
+        xs = [b2r.fill_host(count, dtype, seed=50 * r + count, mode="signed") for r in range(nranks)]
+        for op in ("sum", "min", "max"):
+            for root in {0, nranks - 1, nranks // 2}:
+                got = host_reduce_threads(xs, op, root, "ring")
+                want = chain_oracle(xs, op, root)
+                assert torch.equal(got.view(torch.uint8), want.view(torch.uint8)), (nranks, dtype, op, root, count)
