@@ -50,9 +50,14 @@ void host_collective_rank(const HostRankView& v, uint64_t count, b2r_dtype_t dty
     // chain ending at the root: left fold from the farthest position down to the root (same association order as ring_body)
     const int rt = root < 0 ? 0 : root;
     if (r == rt) {
-      std::vector<const void*> order(P);
-      for (int q = 0; q < P; ++q) order[q] = v.send[(rt + (P - 1 - q)) % P];
-      combine_many_host(v.recv[r], order.data(), P, 0, count, dtype, op);
+      // hop by hop: the running partial travels in the buffer's own dtype, so bf16 is rounded at EVERY hop (unlike the
+      // one-shot / two-shot / push / NVLS paths, which combine all P contributions in fp32 and round once)
+      const size_t esz = b2r_dtype_size(dtype);
+      memcpy(v.recv[r], v.send[(rt + P - 1) % P], count * esz);
+      for (int q = 1; q < P; ++q) {
+        const void* pair[2] = {v.recv[r], v.send[(rt + (P - 1 - q)) % P]};
+        combine_many_host(v.recv[r], pair, 2, 0, count, dtype, op);
+      }
     }
     barrier();
   } else {  // B2R_ALGO_TREE

@@ -13,7 +13,11 @@ DTYPES = [torch.int32, torch.float32, torch.float64, torch.bfloat16]
 def chain_oracle(xs, op, root):
     """Left fold from the farthest chain position down to the root (the ring algorithm's association order)."""
     P = len(xs)
-    return elementwise_oracle([xs[(root + (P - 1 - q)) % P] for q in range(P)], op)
+    order = [xs[(root + (P - 1 - q)) % P] for q in range(P)]
+    acc = order[0].clone()
+    for x in order[1:]:  # pairwise: bf16 partials are rounded at every hop of the chain
+        acc = elementwise_oracle([acc, x], op)
+    return acc
 
 
 def elementwise_oracle(xs, op):
