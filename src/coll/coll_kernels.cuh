@@ -625,19 +625,18 @@ __device__ void ring_body(const CollArgs& A) {
       st_release_sys(ack, base_val + (unsigned int)(i + 1));
     }
   }
-  // the (< 16 byte) tail: the root pulls it, folding in chain order
-  if (pos == 0 && nvec * (16 / E) < A.count) {
-    __shared__ const char* src[B2R_MAX_RANKS];
-    __shared__ char* dst1[1];
-    if (threadIdx.x == 0) {
-      for (int q = 0; q < P; ++q) {
-        const int rank_q = (root + (P - 1 - q)) % P;  // farthest position first
-        src[q] = c.heap[rank_q] + po.send[rank_q];
+  // the (< 16 byte) tail: the root pulls it, folding in chain order and — like the vector path, whose partials travel as
+  // bf16 — rounding bf16 after every hop
+  if (pos == 0 && nvec * (16 / E) < A.count && blockIdx.x == 0) {
+    for (unsigned long long e = nvec * (16 / E) + threadIdx.x; e < A.count; e += blockDim.x) {
+      typename TailAcc<D>::type acc = tail_load<D>(c.heap[(root + P - 1) % P] + po.send[(root + P - 1) % P] + e * E);
+      for (int q = 1; q < P; ++q) {
+        const int rank_q = (root + (P - 1 - q)) % P;
+        acc = tail_apply<D, O>(acc, tail_load<D>(c.heap[rank_q] + po.send[rank_q] + e * E));
+        if constexpr (D == B2R_BFLOAT16) acc = __bfloat162float(__float2bfloat16_rn(acc));
       }
-      dst1[0] = c.heap[r] + A.recv_off;
+      tail_store<D>(c.heap[r] + A.recv_off + e * E, acc);
     }
-    __syncthreads();
-    combine_tail<D, O>(nvec * (16 / E), A.count, src, P, dst1, 1);
   }
   cta_barrier(A, A.epoch + 2);
 }
