@@ -231,13 +231,21 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
     int ctas = shape.ctas;
     const int threads = shape.threads;
     if (kind == kCollRing) {
-      // staging ring in the work region: depth x ctas blocks of (threads x 8) vectors; at least 2 deep
-      const uint64_t block_bytes = (uint64_t)threads * 8 * 16;
-      ctas = (int)std::max<uint64_t>(1, std::min<uint64_t>((bytes + block_bytes - 1) / block_bytes, (uint64_t)std::max(1, env_int("B2R_RING_CTAS", 64))));
-      ctas = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)ctas, c0->stage_bytes / (2ull * block_bytes)));
-      if (n > 1) ctas = std::max(1, std::min(ctas, c0->sm_count / n));
-      const int depth = (int)std::min<uint64_t>(8, c0->stage_bytes / ((uint64_t)ctas * block_bytes));
-      for (int i = 0; i < n; ++i) L.a[n == 1 ? 0 : rc[i].c->rank].ring_depth = depth;
+      // staging ring in the work region: depth x ctas steps of sub_blocks x (threads x 8) vectors; at least 2 deep.
+      // Large messages use big steps (default 8 sub-blocks = 512 KiB with 512 threads) to amortise the per-step fence.
+      const uint64_t sub_bytes = (uint64_t)threads * 8 * 16;
+      int subs = std::max(1, env_int("B2R_RING_SUBBLOCKS", 8));
+      int cap = std::max(1, env_int("B2R_RING_CTAS", 32));
+      if (n > 1) cap = std::max(1, std::min(cap, c0->sm_count / n));
+      while (subs > 1 && bytes < (uint64_t)cap * sub_bytes * subs * 2) subs /= 2;  // small message: keep all CTAs busy
+      const uint64_t step_bytes = sub_bytes * subs;
+      ctas = (int)std::max<uint64_t>(1, std::min<uint64_t>((bytes + step_bytes - 1) / step_bytes, (uint64_t)cap));
+      ctas = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)ctas, c0->stage_bytes / (2ull * step_bytes)));
+      const int depth = (int)std::min<uint64_t>(8, c0->stage_bytes / ((uint64_t)ctas * step_bytes));
+      for (int i = 0; i < n; ++i) {
+        L.a[n == 1 ? 0 : rc[i].c->rank].ring_depth = depth;
+        L.a[n == 1 ? 0 : rc[i].c->rank].sub_blocks = subs;
+      }
     }
     if (kind == kCollPush) {
       // staging ring in the work region: depth x P sources x ctas blocks of (threads x 4) vectors; at least 2 deep

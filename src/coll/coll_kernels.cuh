@@ -23,8 +23,9 @@ struct CollArgs {
   unsigned long long count;                         // elements
   unsigned int epoch;                               // barrier values epoch+1, epoch+2, ...
   int root;                                         // >= 0: reduce to root; -1: allreduce
-  unsigned int seq;                                 // push algorithm: call number (flag values are seq<<16 | round)
-  int ring_depth;                                   // push algorithm: staging slots per (source, CTA)
+  unsigned int seq;                                 // push / ring: call number (flag values are seq<<16 | round)
+  int ring_depth;                                   // push / ring: staging slots per (source, CTA)
+  int sub_blocks;                                   // ring: sub-blocks of (threads x 8) vectors moved per flag/fence
 };
 constexpr int kLoopMaxRanks = 8;
 struct CollLaunch {
@@ -561,13 +562,17 @@ __device__ void ring_body(const CollArgs& A) {
   using V = VecOps<D, O>;
   const CollCtx& c = A.ctx;
   constexpr int E = V::kElem;
-  constexpr int VPT = 8;  // vectors per thread per block
+  constexpr int VPT = 8;  // vectors per thread per sub-block
   const int P = c.nranks, r = c.rank, root = A.root, G = (int)gridDim.x, b = (int)blockIdx.x;
   const int pos = (r - root + P) % P;
   const int pred = pos + 1 < P ? (root + pos + 1) % P : -1;  // sends to me
   const int succ = pos > 0 ? (root + pos - 1) % P : -1;      // I send to it
   const unsigned long long nvec = A.count * E / 16;
-  const unsigned int Cv = blockDim.x * VPT;
+  // One step = sub_blocks sub-blocks of (threads x 8) vectors, then ONE release-store of the data flag: the fence in
+  // front of that store waits for the step's outstanding remote stores, so its cost is amortised over the whole step
+  // (64 KiB steps measured 407 GB/s at 2 GPUs where the link sustains 630+).
+  const unsigned int Sv = blockDim.x * VPT;
+  const unsigned int Cv = Sv * (unsigned int)max(1, A.sub_blocks);
   const unsigned long long nblocks = (nvec + Cv - 1) / Cv;
   const unsigned long long steps = (unsigned long long)b < nblocks ? (nblocks - b + G - 1) / G : 0;
   const int depth = A.ring_depth;
@@ -593,25 +598,27 @@ __device__ void ring_body(const CollArgs& A) {
     __syncthreads();
     char* dst = succ >= 0 ? slot(succ, i) : c.heap[r] + A.recv_off + lo * 16;
     const char* in = slot(r, i);
-    V16 own[VPT], got[VPT];
+    for (unsigned int sb = 0; sb < len; sb += Sv) {
+      V16 own[VPT], got[VPT];
 #pragma unroll
-    for (int u = 0; u < VPT; ++u) {
-      const unsigned int j = threadIdx.x + u * blockDim.x;
-      if (j < len) {
-        own[u] = ld_peer(send + (lo + j) * 16);
-        if (pred >= 0) got[u] = ld_peer(in + (unsigned long long)j * 16);
+      for (int u = 0; u < VPT; ++u) {
+        const unsigned int j = sb + threadIdx.x + u * blockDim.x;
+        if (j < len) {
+          own[u] = ld_peer(send + (lo + j) * 16);
+          if (pred >= 0) got[u] = ld_peer(in + (unsigned long long)j * 16);
+        }
       }
-    }
 #pragma unroll
-    for (int u = 0; u < VPT; ++u) {
-      const unsigned int j = threadIdx.x + u * blockDim.x;
-      if (j < len) {
-        if (pred >= 0) {
-          typename V::Acc acc = V::unpack(got[u]);
-          V::combine(acc, own[u]);
-          st_peer(dst + (unsigned long long)j * 16, V::pack(acc));
-        } else {
-          st_peer(dst + (unsigned long long)j * 16, own[u]);
+      for (int u = 0; u < VPT; ++u) {
+        const unsigned int j = sb + threadIdx.x + u * blockDim.x;
+        if (j < len) {
+          if (pred >= 0) {
+            typename V::Acc acc = V::unpack(got[u]);
+            V::combine(acc, own[u]);
+            st_peer(dst + (unsigned long long)j * 16, V::pack(acc));
+          } else {
+            st_peer(dst + (unsigned long long)j * 16, own[u]);
+          }
         }
       }
     }
