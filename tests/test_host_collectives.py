@@ -80,6 +80,7 @@ def test_algo_selection_is_pure_and_sensible():
     assert sel(1, 1 << 30, _lib.BFLOAT16, _lib.MAX, 8, 1) == _lib.ALGO_NVLS
     assert sel(0, 1 << 30, _lib.INT32, _lib.SUM, 8, 1) == _lib.ALGO_TWOSHOT  # 4-byte multimem ops: P2P vectors are faster
     assert sel(0, 64, _lib.FLOAT64, _lib.SUM, 2, 0) == _lib.ALGO_ONESHOT
+    assert sel(0, 1 << 30, _lib.FLOAT64, _lib.SUM, 2, 1) == _lib.ALGO_ONESHOT  # 2-GPU reduce: the root pulls, at any size
     assert sel(0, 1 << 20, _lib.FLOAT64, _lib.SUM, 1, 0) == _lib.ALGO_ONESHOT
 
 
