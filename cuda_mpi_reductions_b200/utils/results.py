@@ -3,7 +3,7 @@
   aggregate  collected rows "DTYPE OP NODES GB/sec" (what bench_collective / reduce.c print) -> results/<DTYPE>_<OP>.txt
              with the reference's layout: first line blank, then "DTYPE OP NODES AVG" per distinct node count, 5 decimals
              (bc scale=5 truncates; so do we), node counts in ascending order.
-  plot       writes a gnuplot script equivalent to makePlots.gp: one figure per datatype, the per-op curves over the
+  plot       writes a gnuplot script with the same content as the reference's figures: one figure per datatype, the per-op curves over the
              number of ranks plus three horizontal lines for the single-GPU throughput (the reference hard-codes them from
              CUdata.txt; here they are read from a bench_reduce JSONL or passed explicitly). gnuplot itself is not on the
              image: the script + data are the deliverable.
@@ -77,41 +77,39 @@ def single_gpu_lines(jsonl_path: str) -> dict:
     return out
 
 
-def write_gnuplot(results_dir: str, out_path: str, single_gpu: dict | None = None, dtypes=("INT", "DOUBLE"), xlabel="Number of GPUs (ranks)") -> str:
+def write_gnuplot(results_dir: str, out_path: str, single_gpu: dict | None = None, dtypes=("INT", "DOUBLE"), xlabel="GPUs (ranks)") -> str:
+    """One figure per datatype: bandwidth of the whole problem over the number of ranks for SUM / MIN / MAX (read from
+    results/<DTYPE>_<OP>.txt, columns 3 and 4 like the reference's plot) plus dashed horizontal lines for the single-GPU
+    scalar reduction of the same datatype. Our own script: SVG output, log-scaled y axis, explicit GiB/s units."""
     single_gpu = single_gpu or {}
-    lines = [
-        "# generated by cuda_mpi_reductions_b200.utils.results (counterpart of the reference's mpi/makePlots.gp)",
-        "set term postscript eps enhanced color",
-        'set style line 1 lt 1 lw 3 lc rgb "red" pt 2',
-        'set style line 2 lt 1 lw 3 lc rgb "blue" pt 2',
-        'set style line 3 lt 1 lw 3 lc rgb "green" pt 2',
-        'set style line 4 lt 2 lw 5 lc rgb "red"',
-        'set style line 5 lt 2 lw 5 lc rgb "blue"',
-        'set style line 6 lt 2 lw 5 lc rgb "green"',
-        f'set xlabel "{xlabel}"',
-        'set ylabel "Bandwidth (GiB/sec of the whole problem)"',
-        "set key bottom right",
-        "set logscale y",
+    colours = {"SUM": "#2ca02c", "MIN": "#1f77b4", "MAX": "#d62728"}
+    out = [
+        "# gnuplot script written by cuda_mpi_reductions_b200.utils.results.write_gnuplot",
+        "# data: <results>/<DTYPE>_<OP>.txt rows 'DTYPE OP RANKS GiB/s' (first line blank)",
+        "set terminal svg size 900,600 dynamic font 'Helvetica,13'",
+        "set datafile missing ''",
+        "set grid ytics lc rgb '#cccccc'",
+        "set logscale y 10",
+        f"set xlabel '{xlabel}'",
+        "set ylabel 'bandwidth of the whole problem [GiB/s]'",
+        "set key outside right center box",
         "",
     ]
     for dt in dtypes:
-        consts = {op: single_gpu.get((dt, op)) for op in OPS}
-        for name, op in (("f", "SUM"), ("g", "MIN"), ("h", "MAX")):
-            if consts[op] is not None:
-                lines.append(f"{name}(x) = {consts[op] / 1.073741824:.4f}   # single B200, {dt} {op}, GiB/s")
-        lines.append(f'set output "{dt.lower()}.eps"')
-        curves = [
-            f'"{os.path.join(results_dir, f"{dt}_MAX.txt")}" using 3:4 ls 1 title "NVLink Max" with linespoints',
-            f'"{os.path.join(results_dir, f"{dt}_MIN.txt")}" using 3:4 ls 2 title "NVLink Min" with linespoints',
-            f'"{os.path.join(results_dir, f"{dt}_SUM.txt")}" using 3:4 ls 3 title "NVLink Sum" with linespoints',
-        ]
-        for name, op, ls in (("f", "SUM", 4), ("g", "MIN", 5), ("h", "MAX", 6)):
-            if consts[op] is not None:
-                curves.append(f'{name}(x) ls {ls} title "1 GPU {op.capitalize()}"')
-        lines.append("plot " + ", \\\n     ".join(curves))
-        lines.append("")
+        out.append(f"set output '{dt.lower()}_reduce.svg'")
+        out.append(f"set title '{dt}: element-wise reduce to root over NVLink vs one-GPU scalar reduction'")
+        terms = []
+        for op in OPS:
+            path = os.path.join(results_dir, f"{dt}_{op}.txt")
+            terms.append(f"'{path}' using 3:4 with linespoints lw 2 pt 7 lc rgb '{colours[op]}' title 'reduce {op}'")
+        for op in OPS:
+            v = single_gpu.get((dt, op))
+            if v is not None:
+                terms.append(f"{v / 1.073741824:.3f} with lines dt 2 lw 2 lc rgb '{colours[op]}' title 'one GPU {op}'")
+        out.append("plot \\\n  " + ", \\\n  ".join(terms))
+        out.append("")
     with open(out_path, "w") as f:
-        f.write("\n".join(lines))
+        f.write("\n".join(out))
     return out_path
 
 
@@ -131,7 +129,7 @@ def main(argv=None):
             print(f"{dt} {op} -> {path}")
     else:
         sg = single_gpu_lines(args.single_gpu) if args.single_gpu else {}
-        print(write_gnuplot(args.results, args.out or os.path.join(args.results, "makePlots.gp"), sg))
+        print(write_gnuplot(args.results, args.out or os.path.join(args.results, "plots.gp"), sg))
 
 
 if __name__ == "__main__":

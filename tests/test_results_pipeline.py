@@ -38,7 +38,8 @@ def test_gnuplot_script(tmp_path):
     (tmp_path / "INT_SUM.txt").write_text("\nINT SUM 2 100.0\n")
     path = results.write_gnuplot(str(tmp_path), str(tmp_path / "p.gp"), {("INT", "SUM"): 7000.0, ("INT", "MIN"): 6900.0, ("INT", "MAX"): 6950.0})
     gp = open(path).read()
-    assert 'set output "int.eps"' in gp and "INT_SUM.txt" in gp and "f(x) =" in gp and 'set output "double.eps"' in gp
+    assert "int_reduce.svg" in gp and "INT_SUM.txt" in gp and "one GPU SUM" in gp and "double_reduce.svg" in gp
+    assert f"{7000.0 / 1.073741824:.3f}" in gp  # single-GPU GB/s converted to the GiB/s of the curves
 
 
 def test_workload_constants_match_the_reference():
