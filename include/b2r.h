@@ -240,6 +240,17 @@ b2r_algo_t b2r_select_algo(int is_allreduce, uint64_t bytes, b2r_dtype_t dtype, 
 b2r_status_t b2r_host_reduce_threads(const void* const* sendbufs, void* recvbuf, uint64_t count, b2r_dtype_t dtype,
                                      b2r_op_t op, int nranks, int root, b2r_algo_t algo);
 
+/* Multi-PROCESS flavour of the host transport: every process opens the same POSIX shared-memory segment (rank 0 creates it
+ * and removes it on destroy) and the collectives run the same algorithms with a process-shared barrier. Used by the Python
+ * HostCommunicator (CPU tensors under torch.distributed/gloo) and, through the same class, by the bundled mini-MPI.
+ * root >= 0: reduce to root; root == -1: allreduce. `shm_name` must start with '/' and be the same on every rank. */
+typedef struct b2r_host_comm* b2r_host_comm_t;
+b2r_status_t b2r_host_comm_init(b2r_host_comm_t* comm, const char* shm_name, int rank, int nranks, uint64_t window_bytes);
+b2r_status_t b2r_host_comm_destroy(b2r_host_comm_t comm);
+b2r_status_t b2r_host_comm_reduce(b2r_host_comm_t comm, const void* sendbuf, void* recvbuf, uint64_t count, b2r_dtype_t dtype,
+                                  b2r_op_t op, int root, b2r_algo_t algo);
+b2r_status_t b2r_host_comm_barrier(b2r_host_comm_t comm);
+
 #ifdef __cplusplus
 }
 #endif

@@ -10,10 +10,11 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <new>
 #include <string>
 #include <vector>
 
-#include "minimpi_shm.h"
+#include "../src/coll/host_shm.h"
 
 int main(int argc, char** argv) {
   int np = 2;
@@ -28,8 +29,8 @@ int main(int argc, char** argv) {
     fprintf(stderr, "usage: b2r_mpirun -np N [--window-mb M] prog [args...]\n");
     return 2;
   }
-  minimpi::Control tmp;
-  minimpi::layout(&tmp, np, window_mb << 20, 4 << 20);
+  b2r::ShmControl tmp;
+  b2r::shm_layout(&tmp, np, window_mb << 20, 4 << 20);
   std::string name = "/b2r-minimpi-" + std::to_string(getpid());
   int fd = shm_open(name.c_str(), O_CREAT | O_EXCL | O_RDWR, 0600);
   if (fd < 0) { perror("b2r_mpirun: shm_open"); return 2; }
@@ -37,8 +38,8 @@ int main(int argc, char** argv) {
   void* base = mmap(nullptr, tmp.total_bytes, PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
   close(fd);
   if (base == MAP_FAILED) { perror("b2r_mpirun: mmap"); shm_unlink(name.c_str()); return 2; }
-  minimpi::Control* ctl = new (base) minimpi::Control();
-  minimpi::layout(ctl, np, window_mb << 20, 4 << 20);
+  b2r::ShmControl* ctl = new (base) b2r::ShmControl();
+  b2r::shm_layout(ctl, np, window_mb << 20, 4 << 20);
   ctl->bar_count.store(0);
   ctl->bar_gen.store(0);
   ctl->abort_flag.store(0);
