@@ -277,7 +277,8 @@ def run_b2r(args) -> None:
             "e2e": {"value": e2e_value, "unit": "GB/s", "h2d_bytes_per_step": nbytes, "d2h_bytes_per_step": nchunks * acc_sz,
                     "steps": e2e_steps, "ms_per_step": e2e_s * 1e3 / e2e_steps,
                     "api": "cuda_mpi_reductions_b200.reduce_from_host(pinned_tensor)" if comm is None else "Communicator.reduce_scalar_sharded_from_host(pinned_tensor)"},
-            "gpu_launches": steps,
+            "gpu_launches": steps * world,  # one kernel of ours per GPU per step inside the timed region
+            "gpu_launches_per_gpu": steps,
             "hbm_fraction_of_measured": value / world / hbm,
             "impl": "b2r",
         }
