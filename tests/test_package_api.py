@@ -1,0 +1,56 @@
+"""CPU-only: the Python surface behaves sensibly without a GPU — helpers work, GPU entry points fail loudly instead of
+silently falling back (the driver records which native libraries the GPU tests really loaded)."""
+import ctypes as C
+import os
+
+import pytest
+import torch
+
+import cuda_mpi_reductions_b200 as b2r
+from cuda_mpi_reductions_b200 import _lib
+from cuda_mpi_reductions_b200.utils import ClockSampler, rotating_copies
+
+
+def test_native_library_is_the_in_tree_build():
+    assert os.path.exists(_lib.LIB_PATH) and _lib.LIB_PATH.startswith(_lib.REPO_ROOT)
+    assert _lib.LIB.b2r_version() >= 1
+    for name in ("b2r_reduce_local", "b2r_reduce_local_noalloc", "b2r_allreduce", "b2r_reduce", "b2r_reduce_scalar_sharded_ex",
+                 "b2r_comm_init_rank", "b2r_comm_init_all", "b2r_comm_init_loopback", "b2r_host_comm_init", "b2r_bootstrap_selftest"):
+        assert hasattr(_lib.LIB, name), name
+
+
+def test_cpu_tensors_are_rejected_by_gpu_ops():
+    x = torch.ones(16)
+    with pytest.raises(ValueError):
+        b2r.reduce(x, "sum")
+    with pytest.raises(TypeError):
+        b2r.reduce_oracle(torch.ones(4, dtype=torch.float16), "sum")
+    with pytest.raises(ValueError):
+        b2r.reduce_oracle(x, "mean")
+
+
+def test_gpu_entry_points_fail_loudly_without_a_device():
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    h = C.c_void_p()
+    st = _lib.LIB.b2r_workspace_create(C.byref(h), 0)
+    assert st == _lib.ERR_CUDA and b"b2r_workspace_create" in _lib.LIB.b2r_last_error_string() or st == _lib.ERR_CUDA
+    arr = (C.c_void_p * 2)()
+    assert _lib.LIB.b2r_comm_init_loopback(arr, 2, 0, None) != _lib.OK
+    assert _lib.LIB.b2r_comm_init_all(arr, 2, None, None) != _lib.OK
+
+
+def test_status_strings_and_launch_config():
+    assert _lib.LIB.b2r_status_string(_lib.ERR_TIMEOUT).decode() == "cross-GPU wait timed out"
+    cfg = b2r.launch_config(variant="tma", threads=288, pdl=1)
+    assert (cfg.variant, cfg.threads, cfg.pdl) == (_lib.VARIANT_TMA, 288, 1)
+    with pytest.raises(TypeError):
+        b2r.launch_config(blocks=3)
+
+
+def test_rotating_copies_and_clock_sampler_fallback():
+    assert rotating_copies(64 << 20) == 8 and rotating_copies(1 << 30) == 2 and rotating_copies(1024) == 64 and rotating_copies(0) == 1
+    s = ClockSampler(0).start()
+    s.stop()
+    summ = s.summary(0.0, 1e12)
+    assert set(summ) >= {"sm_mhz", "sm_max_mhz", "reasons", "samples", "window", "backend"}
