@@ -36,7 +36,7 @@ HDRS     := $(wildcard include/*.h) $(wildcard src/*/*.h) $(wildcard src/*/*.cuh
 LIB      := $(LIBDIR)/libb2r.so
 BENCHES  := $(BINDIR)/local_sweep $(BINDIR)/bench_reduce $(BINDIR)/bench_collective
 
-.PHONY: all lib bins minimpi baseline clean sass
+.PHONY: all lib bins minimpi baseline examples clean sass
 all: lib bins minimpi
 
 lib: $(LIB)
@@ -68,6 +68,11 @@ minimpi:
 
 baseline:
 	$(Q)bash baseline/build_baselines.sh
+
+# MPI-launched GPU example (one mini-MPI rank per GPU; MPI carries only rank/size/bootstrap id)
+examples: lib minimpi
+	@mkdir -p $(BINDIR)
+	$(Q)$(NVCC) $(NVCCFLAGS) -Iminimpi -o $(BINDIR)/reduce_gpu_mpi examples/reduce_gpu_mpi.cu minimpi/minimpi.o -L$(LIBDIR) -lb2r -lrt -Xlinker -rpath,'$$ORIGIN/../$(LIBDIR)'
 
 sass: $(LIB)
 	@mkdir -p profiles/sass
