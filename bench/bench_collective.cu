@@ -11,6 +11,7 @@
 //
 //   bench_collective [--gpus=N] [--total-mib=2048] [--retries=5] [--types=INT,DOUBLE[,BF16,FLOAT]] [--coll=reduce|allreduce]
 //                    [--algo=auto|oneshot|twoshot|tree|nvls] [--root=0] [--check] [--jsonl=path] [--raw=path]
+//   bench_collective --tune=ring|push|nvls|twoshot [--coll=] [--bytes=] [--type=] [--iters=]   (in-process launch-shape grid)
 //   bench_collective --sweep [--min-bytes=1024] [--max-bytes=4294967296] [--types=...] [--colls=reduce,allreduce]
 //                    [--algos=auto,oneshot,twoshot,tree,nvls] [--iters=20] [--jsonl=path] [--csv=path]
 // Runs as ONE process driving all GPUs (b2r_comm_init_all); buffers come from the symmetric heap (zero copy).
@@ -164,9 +165,10 @@ int main(int argc, char** argv) {
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { fprintf(stderr, "no CUDA device\n"); return 2; }
   const int P = (int)f.i64("gpus", ndev);
   if (P < 1 || P > ndev) { fprintf(stderr, "--gpus=%d but %d devices are visible\n", P, ndev); return 1; }
-  const bool sweep = f.has("sweep");
+  const bool tune = f.has("tune");
+  const bool sweep = f.has("sweep") || tune;
   const uint64_t total_bytes = (uint64_t)f.i64("total-mib", 2048) << 20;
-  const uint64_t max_bytes = sweep ? (uint64_t)f.i64("max-bytes", 1ll << 32) : total_bytes / P;
+  const uint64_t max_bytes = tune ? (uint64_t)f.i64("bytes", 256ll << 20) : (sweep ? (uint64_t)f.i64("max-bytes", 1ll << 32) : total_bytes / P);
   const int root = (int)f.i64("root", 0);
 
   b2r_comm_config_t cfg;
@@ -207,7 +209,43 @@ int main(int argc, char** argv) {
   }
   bool all_ok = true;
 
-  if (!sweep) {
+  if (tune) {
+    // In-process launch-shape sweep: the library reads its B2R_* knobs from the environment at every call, so one process
+    // (one communicator set-up, the expensive part at 8 GPUs) can walk a whole grid. --tune=ring|push|nvls|twoshot
+    //   [--coll=reduce|allreduce] [--bytes=268435456] [--type=FLOAT] [--iters=10]
+    const std::string which = f.str("tune", "ring");
+    const b2r_algo_t algo = parse_algo(which);
+    const bool allreduce = f.str("coll", which == "ring" ? "reduce" : "allreduce") == "allreduce";
+    b2r_dtype_t dt = f.has("types") && !types.empty() ? types[0] : B2R_FLOAT32;
+    if (f.has("type")) parse_dtype(f.str("type"), &dt);
+    const uint64_t bytes = max_bytes, count = bytes / b2r_dtype_size(dt);
+    const int iters = (int)f.i64("iters", 10);
+    struct Knob { const char* name; std::vector<int> values; };
+    std::vector<Knob> knobs;
+    if (which == "ring") knobs = {{"B2R_RING_CTAS", {16, 32, 64}}, {"B2R_RING_SUBBLOCKS", {2, 4, 8, 16}}, {"B2R_COLL_THREADS", {256, 512}}};
+    else if (which == "push") knobs = {{"B2R_PUSH_CTAS", {32, 64, 128}}, {"B2R_COLL_THREADS", {256, 512}}};
+    else if (which == "nvls") knobs = {{"B2R_COLL_CTAS", {8, 16, 32, 64, 128}}, {"B2R_COLL_THREADS", {128, 256, 512}}, {"B2R_COLL_UNROLL", {4, 8}}};
+    else knobs = {{"B2R_COLL_CTAS", {32, 64, 128, 148}}, {"B2R_COLL_THREADS", {256, 512}}, {"B2R_COLL_UNROLL", {4, 8}}};
+    printf("# tune %s %s %s %llu bytes on %d GPUs: knobs -> us, algbw GB/s\n", which.c_str(), allreduce ? "allreduce" : "reduce", ref_type_name(dt),
+           (unsigned long long)bytes, P);
+    std::vector<size_t> idx(knobs.size(), 0);
+    for (;;) {
+      std::string label;
+      for (size_t k = 0; k < knobs.size(); ++k) {
+        setenv(knobs[k].name, std::to_string(knobs[k].values[idx[k]]).c_str(), 1);
+        label += std::string(knobs[k].name + 4) + "=" + std::to_string(knobs[k].values[idx[k]]) + " ";
+      }
+      if (timed(R, allreduce, count, dt, B2R_SUM, root, algo, 2) < 0) return 3;
+      const double ms = timed(R, allreduce, count, dt, B2R_SUM, root, algo, iters);
+      if (ms < 0) return 3;
+      printf("  %-60s %10.2f %10.2f\n", label.c_str(), ms * 1e3, bytes / ms * 1e-6);
+      fflush(stdout);
+      size_t k = 0;
+      while (k < knobs.size() && ++idx[k] == knobs[k].values.size()) idx[k++] = 0;
+      if (k == knobs.size()) break;
+    }
+    for (auto& kn : knobs) unsetenv(kn.name);
+  } else if (!sweep) {
     const bool allreduce = f.str("coll", "reduce") == "allreduce";
     const b2r_algo_t algo = parse_algo(f.str("algo", "auto"));
     const int retries = (int)f.i64("retries", 5);
