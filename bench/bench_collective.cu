@@ -62,6 +62,7 @@ b2r_algo_t parse_algo(const std::string& s) {
   if (s == "nvls") return B2R_ALGO_NVLS;
   if (s == "push") return B2R_ALGO_PUSH;
   if (s == "ring") return B2R_ALGO_RING;
+  if (s == "ll") return B2R_ALGO_LL;
   return B2R_ALGO_AUTO;
 }
 

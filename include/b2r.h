@@ -57,7 +57,9 @@ typedef enum {
   B2R_ALGO_TREE = 3,    /* hand-written binomial tree, log2(P) rounds of pairwise P2P combine */
   B2R_ALGO_NVLS = 4,    /* multimem.ld_reduce / multimem.st through the NVSwitch (needs multicast) */
   B2R_ALGO_PUSH = 5,    /* scatter by P2P stores into the owners' staging, reduce locally, push the result: no remote loads */
-  B2R_ALGO_RING = 6     /* reduce only: store-forwarding chain that ends at the root (one neighbour per GPU, no remote loads) */
+  B2R_ALGO_RING = 6,    /* reduce only: store-forwarding chain that ends at the root (one neighbour per GPU, no remote loads) */
+  B2R_ALGO_LL = 7       /* EXPERIMENTAL small-message path (see b2r_ll_max_bytes): flag-in-data packets pushed into the consumers'
+                           slots, no barrier at either end; never chosen by AUTO, not yet validated on hardware */
 } b2r_algo_t;
 
 typedef struct {
@@ -228,6 +230,9 @@ b2r_status_t b2r_reduce_scalar_sharded_ex(const void* in, void* out, uint64_t co
                                           int root, int all, b2r_comm_t comm, void* stream, const b2r_launch_cfg_t* cfg);
 
 b2r_status_t b2r_barrier(b2r_comm_t comm, void* stream);
+
+/* Largest message (bytes per rank) the LL path accepts on a communicator of `nranks` ranks; 0 if nranks is out of range. */
+uint64_t b2r_ll_max_bytes(int nranks);
 
 /* Which algorithm AUTO resolves to (pure function; used by tests and the harness). */
 b2r_algo_t b2r_select_algo(int is_allreduce, uint64_t bytes, b2r_dtype_t dtype, b2r_op_t op, int nranks,

@@ -53,6 +53,7 @@ CollKernel pick_kind(int kind) {
     case kCollBarrier: return coll_kernel<D, O, kCollBarrier, 4>;
     case kCollPush: return coll_kernel<D, O, kCollPush, 4>;
     case kCollRing: return coll_kernel<D, O, kCollRing, 4>;
+    case kCollLL: return coll_kernel<D, O, kCollLL, 4>;
   }
   return nullptr;
 }
@@ -180,8 +181,19 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
     if (!nvls_supported(dtype, op)) return fail(B2R_ERR_UNSUPPORTED, "NVLS has no %s %s instruction", b2r_dtype_name(dtype), b2r_op_name(op));
   }
   const int kind = algo == B2R_ALGO_ONESHOT ? kCollOneshot : algo == B2R_ALGO_TWOSHOT ? kCollTwoshot : algo == B2R_ALGO_TREE ? kCollTree
-                   : algo == B2R_ALGO_PUSH ? kCollPush : algo == B2R_ALGO_RING ? kCollRing : kCollNvls;
+                   : algo == B2R_ALGO_PUSH ? kCollPush : algo == B2R_ALGO_RING ? kCollRing : algo == B2R_ALGO_LL ? kCollLL : kCollNvls;
   if (kind == kCollRing && is_all) return fail(B2R_ERR_UNSUPPORTED, "the ring algorithm implements reduce-to-root only");
+  if (kind == kCollLL) {
+    // LL never touches a peer's send/recv buffer: any 16-byte aligned device pointer works, nothing is staged or chunked
+    if (total_bytes > ll_max_msg_bytes(P))
+      return fail(B2R_ERR_INVALID, "the LL path carries at most %zu bytes per rank on %d ranks (got %llu)", ll_max_msg_bytes(P), P,
+                  (unsigned long long)total_bytes);
+    for (int i = 0; i < n; ++i) {
+      const bool gets_result = is_all || rc[i].c->rank == root;
+      B2R_REQUIRE(((uintptr_t)rc[i].send % 16) == 0 && (!gets_result || ((uintptr_t)rc[i].recv % 16) == 0),
+                  "the LL path needs 16-byte aligned buffers (rank %d)", rc[i].c->rank);
+    }
+  }
   B2R_REQUIRE(kernel_exists(dtype, (int)op, kind), "collective: no kernel for dtype %d op %d algo %d", (int)dtype, (int)op, (int)algo);
 
   // Chunking rule (identical on every rank): messages larger than one staging region are cut into stage-sized chunks,
@@ -202,6 +214,17 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
       const bool gets_result = is_all || c->rank == root;
       const char* send = (const char*)rc[i].send + first * esz;
       char* recv = rc[i].recv ? (char*)rc[i].recv + first * esz : nullptr;
+      if (kind == kCollLL) {
+        CollArgs& A = L.a[n == 1 ? 0 : c->rank];
+        A.ctx = c->ctx;
+        A.send_ptr = send;
+        A.recv_ptr = gets_result ? recv : nullptr;
+        A.count = cnt;
+        A.epoch = c->epoch;
+        A.root = is_all ? -1 : root;
+        A.seq = ++c->ll_seq;  // its own consecutive numbering: the slot parity and the n-2 acknowledgement rule depend on it
+        continue;
+      }
       int64_t soff = c->heap_offset(send, bytes);
       int64_t roff = (gets_result && recv) ? c->heap_offset(recv, bytes) : -1;
       // in place is only safe zero-copy for two-shot / NVLS (a slice is read and written by its single owner)
@@ -229,7 +252,12 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
     }
     const Shape shape = coll_shape(c0, kind, bytes, n);
     int ctas = shape.ctas;
-    const int threads = shape.threads;
+    int threads = shape.threads;
+    if (kind == kCollLL) {  // one CTA; just enough threads for one vector each, up to kLLThreads x kLLVecPerThread vectors
+      const uint64_t nvec = (bytes + 15) / 16;
+      ctas = 1;
+      threads = nvec <= 128 ? 128 : nvec <= 256 ? 256 : kLLThreads;
+    }
     if (kind == kCollRing) {
       // staging ring in the work region: depth x ctas steps of sub_blocks x (threads x 8) vectors; at least 2 deep.
       // Large messages use big steps (default 8 sub-blocks = 512 KiB with 512 threads) to amortise the per-step fence.
@@ -404,9 +432,14 @@ extern "C" {
 
 // Size thresholds measured on 8x B200 (profiles/collectives_8gpu.md). One-shot costs one NVLink round trip but every
 // rank pulls the WHOLE message from every peer; two-shot / NVLS move 1/P of it per rank.
+uint64_t b2r_ll_max_bytes(int nranks) { return (nranks >= 2 && nranks <= B2R_MAX_RANKS) ? (uint64_t)ll_max_msg_bytes(nranks) : 0; }
+
 b2r_algo_t b2r_select_algo(int is_allreduce, uint64_t bytes, b2r_dtype_t dtype, b2r_op_t op, int nranks, int has_multicast) {
   if (nranks <= 1) return B2R_ALGO_ONESHOT;
   const int forced = env_int("B2R_ALGO", 0);
+  // the experimental LL path only ever runs when asked for, and only for messages that fit its slots (and are staged-free:
+  // run_collective checks the 16-byte alignment); everything else falls through to the normal choice
+  if (forced == B2R_ALGO_LL && nranks <= B2R_MAX_RANKS && bytes <= ll_max_msg_bytes(nranks)) return B2R_ALGO_LL;
   if (forced >= B2R_ALGO_ONESHOT && forced <= B2R_ALGO_PUSH) return (b2r_algo_t)forced;
   if (forced == B2R_ALGO_RING && !is_allreduce) return B2R_ALGO_RING;
   // NVLS moves (1 + 1/P) messages per GPU against two-shot's 2(P-1)/P and needs one switch round trip for any size:

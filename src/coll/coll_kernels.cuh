@@ -26,6 +26,8 @@ struct CollArgs {
   unsigned int seq;                                 // push / ring: call number (flag values are seq<<16 | round)
   int ring_depth;                                   // push / ring: staging slots per (source, CTA)
   int sub_blocks;                                   // ring: sub-blocks of (threads x 8) vectors moved per flag/fence
+  const char* send_ptr;                             // LL: this rank's buffers as plain device pointers (peers never touch them,
+  char* recv_ptr;                                   //     so they need not live in the heap); 16-byte aligned
 };
 constexpr int kLoopMaxRanks = 8;
 struct CollLaunch {
@@ -787,13 +789,176 @@ __device__ void nvls_body(const CollArgs& A) {
   cta_barrier(A, A.epoch + 2);
 }
 
+// ------------------------------------------------------------------------------------------------ LL (small messages, no barriers)  [EXPERIMENTAL]
+// The barrier-framed kernels above pay two NVLink round trips (start + end barrier) whatever the size: 12.5-14.5 us for a
+// 1 KiB-256 KiB reduce at 8 GPUs where NCCL's LL protocol needs 8-12. Here the synchronisation rides with the data, as in
+// that protocol: every 16-byte vector is pushed into the consumer's slot as four 8-byte packets {32 data bits, call number};
+// a packet is valid as soon as its upper half equals the call number the consumer is waiting for, so arrival needs no
+// separate flag and no fence, and a sender is done once its stores are issued. One NVLink one-way trip end to end.
+//   consumers : reduce -> the root; allreduce -> every rank (each combines all P contributions itself, in rank order, so the
+//               bits equal the one-shot kernel's and the host restatement's).
+//   slots     : [call parity][source rank] in the consumer's control region — two calls may be in flight; before writing
+//               call n a sender checks that the consumer has acknowledged call n-2 (every rank acknowledges every call to
+//               every peer when its own work for that call is finished; the check is off the critical path).
+//   geometry  : ONE CTA per rank (<= 512 threads x 4 vectors = 32 KiB; the slot size caps it lower for P > 8): the
+//               acknowledgement then covers the whole message and needs no cross-CTA bookkeeping.
+// Packets are written and read with 8-byte-element vector accesses (each element is one scalar access in the PTX memory
+// model, hence never torn). Call numbers are 32 bits and never reset: 2^32 LL calls per communicator.
+__device__ __forceinline__ void ll_store_vec(char* p, const V16& v, unsigned int seq) {
+  const unsigned long long hi = (unsigned long long)seq << 32;
+  const unsigned long long a = hi | v.w[0], b = hi | v.w[1], c = hi | v.w[2], d = hi | v.w[3];
+  asm volatile("st.relaxed.sys.global.v2.b64 [%0], {%1,%2};" ::"l"(p), "l"(a), "l"(b) : "memory");
+  asm volatile("st.relaxed.sys.global.v2.b64 [%0], {%1,%2};" ::"l"(p + 16), "l"(c), "l"(d) : "memory");
+}
+__device__ __forceinline__ void ll_load_vec(const char* p, unsigned long long* pk) {
+  asm volatile("ld.relaxed.sys.global.v2.b64 {%0,%1}, [%2];" : "=l"(pk[0]), "=l"(pk[1]) : "l"(p) : "memory");
+  asm volatile("ld.relaxed.sys.global.v2.b64 {%0,%1}, [%2];" : "=l"(pk[2]), "=l"(pk[3]) : "l"(p + 16) : "memory");
+}
+__device__ __forceinline__ bool ll_valid(const unsigned long long* pk, unsigned int seq) {
+  return (unsigned int)(pk[0] >> 32) == seq && (unsigned int)(pk[1] >> 32) == seq && (unsigned int)(pk[2] >> 32) == seq &&
+         (unsigned int)(pk[3] >> 32) == seq;
+}
+// the last (< 16 byte) piece of a message as a zero-padded vector, and back; E = element size (2, 4 or 8)
+template <int E>
+__device__ __forceinline__ V16 ll_load_tail(const char* p, unsigned int tail_bytes) {
+  V16 v;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    uint32_t w = 0;
+    if (4u * j + 4u <= tail_bytes) w = *(const volatile uint32_t*)(p + 4 * j);
+    else if (E == 2 && 4u * j + 2u <= tail_bytes) w = *(const volatile uint16_t*)(p + 4 * j);
+    v.w[j] = w;
+  }
+  return v;
+}
+template <int E>
+__device__ __forceinline__ void ll_store_tail(char* p, const V16& v, unsigned int tail_bytes) {
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    if (4u * j + 4u <= tail_bytes) *(volatile uint32_t*)(p + 4 * j) = v.w[j];
+    else if (E == 2 && 4u * j + 2u <= tail_bytes) *(volatile uint16_t*)(p + 4 * j) = (uint16_t)(v.w[j] & 0xffffu);
+  }
+}
+
+template <int D, int O>
+__device__ void ll_body(const CollArgs& A) {
+  using V = VecOps<D, O>;
+  const CollCtx& c = A.ctx;
+  constexpr int E = V::kElem;
+  const int P = c.nranks, me = c.rank, root = A.root;
+  const unsigned int seq = A.seq;
+  const bool consumer = root < 0 || root == me;
+  const unsigned long long bytes = A.count * E;
+  const unsigned int nfull = (unsigned int)(bytes / 16), tail_bytes = (unsigned int)(bytes % 16);
+  const unsigned int nvec = nfull + (tail_bytes ? 1u : 0u);  // <= blockDim.x * kLLVecPerThread (checked by the host)
+  const size_t slot = ll_slot_bytes(P);
+  const size_t parity_off = kOffLL + (size_t)(seq & 1u) * P * slot;
+
+  // ---- flow control: the slots of this parity were last used by call seq-2; its consumers must be done with them
+  if (threadIdx.x == 0) fault_delay(c);
+  if (seq > 2 && threadIdx.x < (unsigned)P && (int)threadIdx.x != me && (root < 0 || (int)threadIdx.x == root)) {
+    const unsigned int* ack = (const unsigned int*)(c.heap[me] + kOffLLAck) + threadIdx.x;
+    wait_flag_ge(ack, seq - 2, c);  // on time-out the error word is set; the slots are always valid memory, so carry on
+  }
+  __syncthreads();
+
+  // ---- my contribution: read once, keep in registers, push to every consumer
+  V16 own[kLLVecPerThread];
+#pragma unroll
+  for (int u = 0; u < kLLVecPerThread; ++u) {
+    const unsigned int v = threadIdx.x + u * blockDim.x;
+    if (v < nfull) own[u] = ld_peer(A.send_ptr + (size_t)v * 16);
+    else if (v < nvec) own[u] = ll_load_tail<E>(A.send_ptr + (size_t)nfull * 16, tail_bytes);
+  }
+  if (!c.fault_skip_signal) {
+    for (int d = 0; d < P; ++d) {
+      if (d == me || (root >= 0 && d != root)) continue;
+      char* base = c.heap[d] + parity_off + (size_t)me * slot;
+#pragma unroll
+      for (int u = 0; u < kLLVecPerThread; ++u) {
+        const unsigned int v = threadIdx.x + u * blockDim.x;
+        if (v < nvec) ll_store_vec(base + (size_t)v * 32, own[u], seq);
+      }
+    }
+  }
+
+  // ---- consumers: wait for each peer's packets (four sources polled at a time), combine in rank order, store
+  if (consumer) {
+    unsigned int* err = (unsigned int*)(c.heap[me] + kOffError);
+    const char* mine = c.heap[me] + parity_off;
+#pragma unroll
+    for (int u = 0; u < kLLVecPerThread; ++u) {
+      const unsigned int v = threadIdx.x + u * blockDim.x;
+      if (v >= nvec) continue;
+      typename V::Acc acc;
+      bool ok = true;
+      for (int p0 = 0; p0 < P && ok; p0 += 4) {
+        unsigned long long pk[4][4];
+        unsigned long long t0 = 0;
+        unsigned int spins = 0;
+        while (true) {
+          bool all = true;
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            if (p0 + k < P && p0 + k != me) ll_load_vec(mine + (size_t)(p0 + k) * slot + (size_t)v * 32, pk[k]);
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            if (p0 + k < P && p0 + k != me) all = all && ll_valid(pk[k], seq);
+          if (all) break;
+          if (++spins >= 64) {
+            spins = 0;
+            const unsigned long long now = coll_globaltimer();
+            if (t0 == 0) t0 = now;
+            const bool late = c.timeout_ns && now - t0 > c.timeout_ns;
+            if (late) atomicExch(err, 1u);
+            if (late || ld_volatile_u32(err)) {  // give up as soon as anybody on this rank has
+              ok = false;
+              break;
+            }
+            __nanosleep(32);
+          }
+        }
+        if (!ok) break;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const int p = p0 + k;
+          if (p >= P) continue;
+          V16 x;
+          if (p == me) x = own[u];
+          else {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) x.w[j] = (uint32_t)pk[k][j];
+          }
+          if (p == 0) acc = V::unpack(x);
+          else V::combine(acc, x);
+        }
+      }
+      if (ok) {
+        const V16 r = V::pack(acc);
+        if (v < nfull) st_peer(A.recv_ptr + (size_t)v * 16, r);
+        else ll_store_tail<E>(A.recv_ptr + (size_t)nfull * 16, r, tail_bytes);
+      }
+    }
+  }
+
+  // ---- acknowledge the call to every peer. A consumer releases (its reads of the slots are complete before the ack is
+  // visible); a rank that consumed nothing has nothing to order, and a release would only make it wait for its own packets
+  // to be acknowledged by the link.
+  __syncthreads();
+  if (threadIdx.x < (unsigned)P && (int)threadIdx.x != me && !c.fault_skip_signal) {
+    unsigned int* ack = (unsigned int*)(c.heap[threadIdx.x] + kOffLLAck) + me;
+    if (consumer) st_release_sys(ack, seq);
+    else st_relaxed_sys_u32(ack, seq);
+  }
+}
+
 // barrier-only kernel body
 __device__ inline void barrier_body(const CollArgs& A) {
   __shared__ PeerOffsets po;
   start_barrier(A, &po);
 }
 
-enum CollKind { kCollOneshot = 1, kCollTwoshot = 2, kCollTree = 3, kCollNvls = 4, kCollBarrier = 5, kCollPush = 6, kCollRing = 7 };
+enum CollKind { kCollOneshot = 1, kCollTwoshot = 2, kCollTree = 3, kCollNvls = 4, kCollBarrier = 5, kCollPush = 6, kCollRing = 7, kCollLL = 8 };
 
 template <int D, int O, int KIND, int UNR>
 __global__ void __launch_bounds__(512) coll_kernel(const __grid_constant__ CollLaunch L) {
@@ -804,6 +969,7 @@ __global__ void __launch_bounds__(512) coll_kernel(const __grid_constant__ CollL
   else if (KIND == kCollNvls) nvls_body<D, O, UNR>(A);
   else if (KIND == kCollPush) push_body<D, O, UNR>(A);
   else if (KIND == kCollRing) ring_body<D, O, UNR>(A);
+  else if (KIND == kCollLL) ll_body<D, O>(A);
   else barrier_body(A);
 }
 

@@ -18,7 +18,18 @@ constexpr size_t kOffCtx = 44 * 1024;                // device copy of CollCtx (
 constexpr size_t kOffMeta = 64 * 1024;               // PeerMeta meta[kCollMaxCtas][B2R_MAX_RANKS]: per-collective buffer offsets
 constexpr size_t kOffPushData = 128 * 1024;          // uint32 [kCollMaxCtas][B2R_MAX_RANKS]: push algorithm, "block of round i from rank s has landed"
 constexpr size_t kOffPushAck = 160 * 1024;           // uint32 [kCollMaxCtas][B2R_MAX_RANKS]: push algorithm, "worker w has consumed round i"
+constexpr size_t kOffLLAck = 176 * 1024;             // uint32 [B2R_MAX_RANKS]: LL path, "rank r has finished LL call n" (flow control)
+constexpr size_t kOffLL = 192 * 1024;                // LL path: packet slots [call parity][source rank][ll_slot_bytes(P)], to the end of the region
 constexpr size_t kCtrlBytes = 1 << 20;               // control region size; staging starts here
+
+// LL ("low latency") small-message path: every 16-byte vector travels as four 8-byte packets {32 data bits, 32-bit call
+// number}, so a slot holds half its size in payload. One CTA of up to kLLThreads threads, kLLVecPerThread vectors each.
+constexpr int kLLThreads = 512;
+constexpr int kLLVecPerThread = 4;
+constexpr size_t ll_slot_bytes(int nranks) { return ((kCtrlBytes - kOffLL) / (2 * (size_t)nranks)) & ~(size_t)255; }
+constexpr size_t ll_max_msg_bytes(int nranks) {
+  return ll_slot_bytes(nranks) / 2 < (size_t)kLLThreads * kLLVecPerThread * 16 ? ll_slot_bytes(nranks) / 2 : (size_t)kLLThreads * kLLVecPerThread * 16;
+}
 
 // Where rank r keeps its send/recv buffer for the collective in flight, published to every peer inside the start
 // barrier, so buffers do NOT have to sit at the same heap offset on every rank (only the NVLS path needs that).
@@ -48,6 +59,9 @@ struct XgMailbox {
 #if defined(__CUDACC__)
 __device__ __forceinline__ void st_release_sys(unsigned int* p, unsigned int v) {
   asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void st_relaxed_sys_u32(unsigned int* p, unsigned int v) {
+  asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 __device__ __forceinline__ void st_relaxed_sys_u64(unsigned long long* p, unsigned long long v) {
   asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");

@@ -50,6 +50,7 @@ struct b2r_comm {
   uint32_t epoch = 0;   // barrier epoch counter (same sequence on every rank)
   uint32_t xg_seq = 0;  // scalar-sharded call counter
   uint32_t push_seq = 0;  // push-algorithm call counter (flag values are seq << 16 | round)
+  uint32_t ll_seq = 0;    // LL path call counter (consecutive: slot parity and the n-2 acknowledgement rule depend on it)
   b2r_workspace* ws = nullptr;
   int max_ctas = 0, timeout_ms = 0;
   bool has_mc = false;

@@ -1,0 +1,143 @@
+"""GPU, opt-in: the EXPERIMENTAL LL small-message path (`algo="ll"`, src/coll/coll_kernels.cuh `ll_body`).
+
+The kernel was written after the round's GPU budget was spent, so it has been compiled and inspected (SASS, registers)
+but not run. Until it has passed on hardware these tests only run when asked for:
+
+    B2R_TEST_EXPERIMENTAL=1 python -m pytest tests/test_experimental_ll_gpu.py -m gpu -x -q
+
+The host-side pieces that do not need a GPU (size limit, selection rule, the CPU restatement) are covered in
+tests/test_plan.py and tests/test_host_collectives.py and always run.
+
+What is checked: every root / allreduce, all dtypes and ops, sizes around every boundary of the kernel (1 element, the
+< 16-byte tail, one vector per thread, several vectors per thread, the largest message), plain `torch.empty` buffers that
+are NOT in the symmetric heap (LL never lets a peer touch them), in place, and long back-to-back sequences that mix
+roots, sizes and other algorithms — the slot parity / acknowledgement protocol only shows its bugs there. Results must be
+bit-identical to the rank-order fold of the host restatement (the same order the one-shot kernel uses)."""
+import os
+
+import pytest
+import torch
+
+import cuda_mpi_reductions_b200 as b2r
+from cuda_mpi_reductions_b200 import _lib
+from cuda_mpi_reductions_b200.parallel import Communicator, host_reduce_threads
+
+pytestmark = [
+    pytest.mark.gpu,
+    pytest.mark.skipif(os.environ.get("B2R_TEST_EXPERIMENTAL", "0") in ("", "0"), reason="experimental path: set B2R_TEST_EXPERIMENTAL=1"),
+]
+
+DTYPES = [torch.int32, torch.float32, torch.float64, torch.bfloat16]
+
+
+@pytest.fixture(scope="module", params=[2, 3, 4, 8])
+def comms(request):
+    cs = Communicator.loopback(request.param, device=0, heap_bytes=16 << 20)
+    yield cs
+    for c in cs:
+        c.close()
+
+
+def bits(t):
+    return t.reshape(-1).view(torch.uint8)
+
+
+def counts_for(P, dtype):
+    esz = torch.empty(0, dtype=dtype).element_size()
+    biggest = _lib.LIB.b2r_ll_max_bytes(P) // esz
+    per_vec = 16 // esz
+    return sorted({1, 2, 3, per_vec - 1, per_vec, per_vec + 1, 127 * per_vec + 1, 128 * per_vec, 129 * per_vec, 512 * per_vec,
+                   512 * per_vec + 3, 1300 * per_vec + 1, biggest - 1, biggest} - {0})
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
+def test_ll_allreduce(comms, dtype):
+    P = len(comms)
+    for count in counts_for(P, dtype):
+        xs_h = [b2r.fill_host(count, dtype, seed=101 * r + count, mode="signed") for r in range(P)]
+        xs = [x.cuda() for x in xs_h]
+        for op in ("sum", "min", "max"):
+            want = host_reduce_threads(xs_h, op, -1, "ll")[0]
+            outs = Communicator.group_allreduce(comms, xs, op, algo="ll")
+            Communicator.group_check(comms)
+            for r in range(P):
+                assert torch.equal(bits(outs[r].cpu()), bits(want)), (P, dtype, op, count, r)
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
+def test_ll_reduce_every_root(comms, dtype):
+    P = len(comms)
+    for count in counts_for(P, dtype)[::2]:
+        xs_h = [b2r.fill_host(count, dtype, seed=7 * r + count, mode="signed") for r in range(P)]
+        xs = [x.cuda() for x in xs_h]
+        for root in range(P):
+            for op in ("sum", "max"):
+                want = host_reduce_threads(xs_h, op, root, "ll")
+                outs = Communicator.group_reduce(comms, xs, op, root=root, algo="ll")
+                Communicator.group_check(comms)
+                assert torch.equal(bits(outs[root].cpu()), bits(want)), (P, dtype, op, count, root)
+        for r in range(P):  # send buffers are never modified
+            assert torch.equal(bits(xs[r].cpu()), bits(xs_h[r]))
+
+
+def test_ll_in_place_and_bitwise_equal_to_oneshot(comms):
+    P = len(comms)
+    count = 1001
+    xs_h = [b2r.fill_host(count, torch.float32, seed=3 + r, mode="signed") for r in range(P)]
+    ref = Communicator.group_allreduce(comms, [x.cuda() for x in xs_h], "sum", algo="oneshot")
+    xs = [x.cuda() for x in xs_h]
+    outs = Communicator.group_allreduce(comms, xs, "sum", algo="ll", outs=xs)
+    Communicator.group_check(comms)
+    for r in range(P):
+        assert outs[r].data_ptr() == xs[r].data_ptr()
+        assert torch.equal(bits(xs[r].cpu()), bits(ref[r].cpu()))
+
+
+def test_ll_back_to_back_mixed_sequence(comms):
+    """600 calls with no host synchronisation in between: roots rotate, sizes change (so the slots hold stale packets of
+    older, longer messages), reduce and allreduce alternate, and every 7th call is a barrier-framed algorithm."""
+    P = len(comms)
+    dtype = torch.int32
+    sizes = [1, 5, 64, 257, 2048, 4099]
+    data = {n: [b2r.fill_host(n, dtype, seed=11 * r + n, mode="full") for r in range(P)] for n in sizes}
+    dev = {n: [x.cuda() for x in xs] for n, xs in data.items()}
+    want_all = {n: host_reduce_threads(xs, "sum", -1, "ll")[0] for n, xs in data.items()}
+    checks = []
+    for i in range(600):
+        n = sizes[(i * 5) % len(sizes)]
+        if i % 7 == 6:
+            outs = Communicator.group_allreduce(comms, dev[n], "sum", algo="twoshot")
+            checks.append((n, None, outs))
+        elif i % 2 == 0:
+            outs = Communicator.group_allreduce(comms, dev[n], "sum", algo="ll")
+            checks.append((n, None, outs))
+        else:
+            root = i % P
+            outs = Communicator.group_reduce(comms, dev[n], "sum", root=root, algo="ll")
+            checks.append((n, root, outs))
+        if len(checks) > 40:  # keep the newest results alive, verify and drop the older ones
+            torch.cuda.synchronize()
+            for n2, root2, outs2 in checks:
+                for r in (range(P) if root2 is None else [root2]):
+                    assert torch.equal(outs2[r].cpu(), want_all[n2]), (i, n2, root2, r)
+            checks = []
+    Communicator.group_check(comms)
+    for n2, root2, outs2 in checks:
+        for r in (range(P) if root2 is None else [root2]):
+            assert torch.equal(outs2[r].cpu(), want_all[n2])
+
+
+def test_ll_rejects_what_it_cannot_carry(comms):
+    P = len(comms)
+    too_big = _lib.LIB.b2r_ll_max_bytes(P) // 4 + 1
+    xs = [torch.zeros(too_big, dtype=torch.int32, device="cuda") for _ in range(P)]
+    with pytest.raises(b2r.B2RError, match="LL path carries at most"):
+        Communicator.group_allreduce(comms, xs, "sum", algo="ll")
+    # misaligned views (4-byte aligned, not 16)
+    base = [torch.zeros(64, dtype=torch.int32, device="cuda") for _ in range(P)]
+    with pytest.raises(b2r.B2RError, match="16-byte aligned"):
+        Communicator.group_allreduce(comms, [b[1:33] for b in base], "sum", algo="ll")
+    # the communicator is still usable
+    ok = Communicator.group_allreduce(comms, [b[:32] for b in base], "sum", algo="ll")
+    Communicator.group_check(comms)
+    assert all(int(o.abs().sum()) == 0 for o in ok)

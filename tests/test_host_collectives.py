@@ -94,3 +94,31 @@ def test_ring_reduce_folds_in_chain_order(nranks, dtype):
                 got = host_reduce_threads(xs, op, root, "ring")
                 want = chain_oracle(xs, op, root)
                 assert torch.equal(got.view(torch.uint8), want.view(torch.uint8)), (nranks, dtype, op, root, count)
+
+
+def test_ll_path_limits_and_selection(monkeypatch):
+    """Host-side rules of the experimental LL path: size limit per communicator size, never chosen by AUTO, chosen under
+    B2R_ALGO=7 only for messages that fit, and its CPU restatement is the rank-order fold (== one-shot)."""
+    lim = _lib.LIB.b2r_ll_max_bytes
+    assert [lim(p) for p in (0, 1, 2, 4, 8, 16, 17)] == [0, 0, 32768, 32768, 26624, 13312, 0]
+    for p in (2, 3, 4, 8, 16):  # two parities x P sources x (2 x payload) must fit between kOffLL and the end of the control region
+        assert 2 * p * 2 * lim(p) <= (1 << 20) - 192 * 1024 and lim(p) % 16 == 0
+    sel = _lib.LIB.b2r_select_algo
+    monkeypatch.delenv("B2R_ALGO", raising=False)
+    for nbytes in (4, 1024, 26624):
+        for all_ in (0, 1):
+            assert sel(all_, nbytes, _lib.INT32, _lib.SUM, 8, 1) != _lib.ALGO_LL
+    monkeypatch.setenv("B2R_ALGO", str(_lib.ALGO_LL))
+    assert sel(0, 26624, _lib.INT32, _lib.SUM, 8, 1) == _lib.ALGO_LL
+    assert sel(1, 4, _lib.FLOAT64, _lib.MAX, 2, 0) == _lib.ALGO_LL
+    assert sel(0, 26625, _lib.INT32, _lib.SUM, 8, 1) == _lib.ALGO_TWOSHOT  # too big: the normal choice
+    assert sel(1, 1 << 20, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS
+    monkeypatch.delenv("B2R_ALGO")
+    xs = [b2r.fill_host(1001, torch.bfloat16, seed=9 * r, mode="signed") for r in range(5)]
+    for root in (-1, 0, 3):
+        a = host_reduce_threads(xs, "sum", root, "ll")
+        b = host_reduce_threads(xs, "sum", root, "oneshot")
+        assert torch.equal(a.view(torch.uint8), b.view(torch.uint8))
+    name = _lib.LIB.b2r_algo_name
+    name.restype = __import__("ctypes").c_char_p
+    assert name(_lib.ALGO_LL) == b"ll" and name(_lib.ALGO_RING) == b"ring"
