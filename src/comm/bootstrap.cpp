@@ -6,6 +6,7 @@
 #include <sys/un.h>
 #include <unistd.h>
 
+#include <algorithm>
 #include <chrono>
 #include <cstring>
 #include <thread>
@@ -36,6 +37,7 @@ b2r_status_t recv_all(int fd, void* buf, size_t n) {
     ssize_t k = ::recv(fd, p, n, 0);
     if (k < 0) {
       if (errno == EINTR) continue;
+      if (errno == EAGAIN || errno == EWOULDBLOCK) return fail(B2R_ERR_TIMEOUT, "bootstrap recv: the peer sent nothing before the deadline");
       return fail(B2R_ERR_SYSTEM, "bootstrap recv: %s", strerror(errno));
     }
     if (k == 0) return fail(B2R_ERR_SYSTEM, "bootstrap recv: peer closed the connection");
@@ -96,6 +98,23 @@ b2r_status_t recv_fd(int sock, int* fd, int* tag) {
   return B2R_OK;
 }
 
+// receive timeout of a socket; 0 = block for ever
+void set_recv_timeout(int fd, int ms) {
+  timeval tv;
+  tv.tv_sec = ms / 1000;
+  tv.tv_usec = (ms % 1000) * 1000;
+  ::setsockopt(fd, SOL_SOCKET, SO_RCVTIMEO, &tv, sizeof(tv));
+}
+
+// The rendezvous socket lives in the abstract namespace, which any local process may connect to; the descriptors that
+// travel over it grant access to GPU memory. Only peers running as the same user are let in.
+bool same_user(int fd) {
+  ucred cred;
+  socklen_t len = sizeof(cred);
+  if (::getsockopt(fd, SOL_SOCKET, SO_PEERCRED, &cred, &len) != 0) return false;
+  return cred.uid == ::geteuid();
+}
+
 socklen_t make_addr(const std::string& id, sockaddr_un* a) {
   memset(a, 0, sizeof(*a));
   a->sun_family = AF_UNIX;
@@ -134,8 +153,20 @@ b2r_status_t Bootstrap::init(const std::string& id, int rank, int nranks, int ti
       if (left <= 0 || ::poll(&p, 1, left) <= 0) return fail(B2R_ERR_TIMEOUT, "bootstrap: only %d of %d ranks connected", got + 1, nranks);
       int s = ::accept4(listen_fd_, nullptr, nullptr, SOCK_CLOEXEC);
       if (s < 0) continue;
+      if (!same_user(s)) {  // not one of ours: drop it and keep waiting
+        ::close(s);
+        continue;
+      }
       int r = -1;
-      B2R_CHECK(recv_all(s, &r, sizeof(r)));
+      // a rank sends its number right after connecting; a client that connects and then says nothing is dropped after
+      // two seconds instead of hanging rank 0, and the wait for the real ranks goes on
+      set_recv_timeout(s, std::max(1, std::min(left, 2000)));
+      b2r_status_t st = recv_all(s, &r, sizeof(r));
+      set_recv_timeout(s, 0);
+      if (st != B2R_OK) {
+        ::close(s);
+        continue;
+      }
       if (r <= 0 || r >= nranks || peers_[r] != -1) {
         ::close(s);
         return fail(B2R_ERR_SYSTEM, "bootstrap: bad or duplicate rank %d", r);

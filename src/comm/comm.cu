@@ -112,6 +112,15 @@ b2r_status_t vmm_prop(int device, bool exportable, CUmemAllocationProp* prop) {
   return B2R_OK;
 }
 
+// error path of the init functions: free the members created so far (the heaps and mappings go with the group)
+void discard_members(CommGroup* g) {
+  for (b2r_comm* m : g->members) {
+    if (m->ws) b2r_workspace_destroy(m->ws);
+    delete m;
+  }
+  g->members.clear();
+}
+
 bool device_supports_multicast(const DriverApi* d, int device) {
   if (!d->MulticastCreate) return false;
   CUdevice cudev;
@@ -177,7 +186,11 @@ b2r_status_t b2r_comm_init_loopback(b2r_comm_t* comms, int nranks, int device, c
     c->group = group;
     group->members.push_back(c);
     b2r_status_t st = finish_init(c);
-    if (st != B2R_OK) return st;
+    if (st != B2R_OK) {
+      discard_members(group.get());
+      for (int k = 0; k < r; ++k) comms[k] = nullptr;  // nothing usable is handed back
+      return st;
+    }
     comms[r] = c;
   }
   group->alive = nranks;
@@ -283,7 +296,11 @@ b2r_status_t b2r_comm_init_all(b2r_comm_t* comms, int ndev, const int* devices, 
     c->group = group;
     group->members.push_back(c);
     b2r_status_t st = finish_init(c);
-    if (st != B2R_OK) return st;
+    if (st != B2R_OK) {
+      discard_members(group.get());
+      for (int k = 0; k < i; ++k) comms[k] = nullptr;  // nothing usable is handed back
+      return st;
+    }
     comms[i] = c;
   }
   group->alive = ndev;
@@ -414,9 +431,13 @@ b2r_status_t b2r_comm_init_rank(b2r_comm_t* comm, int nranks, int rank, int devi
   c->group = group;
   group->members.push_back(c);
   group->alive = 1;
-  B2R_CHECK(finish_init(c));
+  b2r_status_t st = finish_init(c);
+  if (st == B2R_OK) st = boot->barrier();  // nobody signals into a control region that is not zeroed yet
+  if (st != B2R_OK) {
+    discard_members(group.get());
+    return st;
+  }
   c->boot = boot.release();
-  B2R_CHECK(c->boot->barrier());  // nobody signals into a control region that is not zeroed yet
   *comm = c;
   return B2R_OK;
 }
