@@ -54,6 +54,7 @@ CollKernel pick_kind(int kind) {
     case kCollPush: return coll_kernel<D, O, kCollPush, 4>;
     case kCollRing: return coll_kernel<D, O, kCollRing, 4>;
     case kCollLL: return coll_kernel<D, O, kCollLL, 4>;
+    case kCollRingAll: return coll_kernel<D, O, kCollRingAll, 4>;
   }
   return nullptr;
 }
@@ -94,7 +95,7 @@ Shape coll_shape(const b2r_comm* c, int kind, uint64_t bytes, int nvirtual) {
     s.unroll = bytes >= (8u << 20) ? 8 : 4;
     cap = 32;
     per_cta = 32768;
-  } else if (kind == kCollPush || kind == kCollRing) {
+  } else if (kind == kCollPush || kind == kCollRing || kind == kCollRingAll) {
     s.threads = 512;
     s.unroll = 4;
     cap = 128;
@@ -180,9 +181,13 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
     if (!c0->has_mc) return fail(B2R_ERR_UNSUPPORTED, "NVLS requested but this communicator has no multicast mapping");
     if (!nvls_supported(dtype, op)) return fail(B2R_ERR_UNSUPPORTED, "NVLS has no %s %s instruction", b2r_dtype_name(dtype), b2r_op_name(op));
   }
-  const int kind = algo == B2R_ALGO_ONESHOT ? kCollOneshot : algo == B2R_ALGO_TWOSHOT ? kCollTwoshot : algo == B2R_ALGO_TREE ? kCollTree
-                   : algo == B2R_ALGO_PUSH ? kCollPush : algo == B2R_ALGO_RING ? kCollRing : algo == B2R_ALGO_LL ? kCollLL : kCollNvls;
-  if (kind == kCollRing && is_all) return fail(B2R_ERR_UNSUPPORTED, "the ring algorithm implements reduce-to-root only");
+  int kind = algo == B2R_ALGO_ONESHOT ? kCollOneshot : algo == B2R_ALGO_TWOSHOT ? kCollTwoshot : algo == B2R_ALGO_TREE ? kCollTree
+             : algo == B2R_ALGO_PUSH ? kCollPush : algo == B2R_ALGO_RING ? kCollRing : algo == B2R_ALGO_LL ? kCollLL : kCollNvls;
+  if (kind == kCollRing && is_all) {
+    // the ring allreduce (P chains + all-gather by stores) exists but has not run on hardware yet: opt-in only
+    if (!env_int("B2R_EXPERIMENTAL", 0)) return fail(B2R_ERR_UNSUPPORTED, "the ring algorithm implements reduce-to-root only");
+    kind = kCollRingAll;
+  }
   if (kind == kCollLL) {
     // LL never touches a peer's send/recv buffer: any 16-byte aligned device pointer works, nothing is staged or chunked
     if (total_bytes > ll_max_msg_bytes(P))
@@ -248,7 +253,7 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
       A.epoch = c->epoch;
       A.root = is_all ? -1 : root;
       c->epoch += 8;  // start + end + up to 4 tree rounds, rounded up; same increment on every rank
-      if (kind == kCollPush || kind == kCollRing) A.seq = ++c->push_seq;
+      if (kind == kCollPush || kind == kCollRing || kind == kCollRingAll) A.seq = ++c->push_seq;
     }
     const Shape shape = coll_shape(c0, kind, bytes, n);
     int ctas = shape.ctas;
@@ -258,7 +263,7 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
       ctas = 1;
       threads = nvec <= 128 ? 128 : nvec <= 256 ? 256 : kLLThreads;
     }
-    if (kind == kCollRing) {
+    if (kind == kCollRing || kind == kCollRingAll) {
       // staging ring in the work region: depth x ctas steps of sub_blocks x (threads x 8) vectors; at least 2 deep.
       // Large messages use big steps (default 8 sub-blocks = 512 KiB with 512 threads) to amortise the per-step fence.
       const uint64_t sub_bytes = (uint64_t)threads * 8 * 16;
@@ -269,6 +274,12 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
       const uint64_t step_bytes = sub_bytes * subs;
       ctas = (int)std::max<uint64_t>(1, std::min<uint64_t>((bytes + step_bytes - 1) / step_bytes, (uint64_t)cap));
       ctas = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)ctas, c0->stage_bytes / (2ull * step_bytes)));
+      if (kind == kCollRingAll) {  // one chain per rank: a multiple of P CTAs, at least one channel per chain
+        ctas = std::max(P, ctas - ctas % P);
+        B2R_REQUIRE((uint64_t)ctas * step_bytes * 2 <= c0->stage_bytes && ctas <= kCollMaxCtas && (n == 1 || ctas * n <= c0->sm_count),
+                    "ring allreduce: %d CTAs x %llu-byte steps do not fit (staging %zu bytes, %d SMs)", ctas, (unsigned long long)step_bytes,
+                    c0->stage_bytes, c0->sm_count);
+      }
       const int depth = (int)std::min<uint64_t>(8, c0->stage_bytes / ((uint64_t)ctas * step_bytes));
       for (int i = 0; i < n; ++i) {
         L.a[n == 1 ? 0 : rc[i].c->rank].ring_depth = depth;

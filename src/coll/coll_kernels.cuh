@@ -650,6 +650,110 @@ __device__ void ring_body(const CollArgs& A) {
   cta_barrier(A, A.epoch + 2);
 }
 
+// ------------------------------------------------------------------------------------------------ ring allreduce  [EXPERIMENTAL]
+// P chains at once, each exactly the reduce ring above: chain c ends at rank c and reduces slice c of the message, and the
+// chain root, instead of keeping the result, stores it into EVERY rank's recv buffer (all-gather by stores). CTA b works
+// for chain b % P as its channel b / P (the host launches a multiple of P CTAs), with its own staging slots and flag row, so
+// the chains never share anything. Per GPU: (P-1)/P of a message forwarded to ONE neighbour per chain plus (P-1)/P of a
+// message of result stores — no remote loads anywhere, which is what the pull two-shot (0.83x NCCL for int32 / min / max at
+// >= 256 MiB) pays for. Every rank sits on every chain, so a block of the send buffer has been consumed by its owner before
+// the chain root can overwrite it: in place is safe. Folding order = chain order per slice; host_algos.h restates it.
+template <int D, int O, int UNR>
+__device__ void ringall_body(const CollArgs& A) {
+  using V = VecOps<D, O>;
+  const CollCtx& c = A.ctx;
+  constexpr int E = V::kElem;
+  constexpr int VPT = 8;
+  const int P = c.nranks, r = c.rank, G = (int)gridDim.x, b = (int)blockIdx.x;
+  const int chain = b % P, ch = b / P, Gc = G / P;  // G is a multiple of P (host)
+  const int pos = (r - chain + P) % P;
+  const int pred = pos + 1 < P ? (chain + pos + 1) % P : -1;  // sends to me
+  const int succ = pos > 0 ? (chain + pos - 1) % P : -1;      // I send to it; -1: I am this chain's root
+  const unsigned long long nvec = A.count * E / 16;
+  const unsigned long long s_lo = nvec * (unsigned long long)chain / P, s_hi = nvec * (unsigned long long)(chain + 1) / P;
+  const unsigned int Sv = blockDim.x * VPT;
+  const unsigned int Cv = Sv * (unsigned int)max(1, A.sub_blocks);
+  const unsigned long long nblocks = (s_hi - s_lo + Cv - 1) / Cv;
+  const unsigned long long steps = (unsigned long long)ch < nblocks ? (nblocks - ch + Gc - 1) / Gc : 0;
+  const int depth = A.ring_depth;
+  const unsigned int base_val = A.seq << 16;
+
+  __shared__ PeerOffsets po;
+  __shared__ char* rdst[B2R_MAX_RANKS];
+  start_barrier(A, &po);
+  if (threadIdx.x < (unsigned)P) rdst[threadIdx.x] = c.heap[threadIdx.x] + po.recv[threadIdx.x];
+  __syncthreads();
+  const char* send = c.heap[r] + A.send_off;
+  auto slot = [&](int rank, unsigned long long step) {
+    return c.heap[rank] + A.work_off + (((step % depth) * G + b) * (unsigned long long)Cv) * 16ull;
+  };
+  for (unsigned long long i = 0; i < steps; ++i) {
+    const unsigned long long lo = s_lo + (ch + i * Gc) * (unsigned long long)Cv;
+    const unsigned int len = (unsigned int)min((unsigned long long)Cv, s_hi - lo);
+    if (threadIdx.x == 0 && pred >= 0) {
+      const unsigned int* flag = (const unsigned int*)(c.heap[r] + kOffPushData) + (size_t)b * B2R_MAX_RANKS + pred;
+      wait_flag_ge(flag, base_val + (unsigned int)(i + 1), c);
+    }
+    if (threadIdx.x == 32 && succ >= 0 && i >= (unsigned long long)depth) {
+      const unsigned int* ack = (const unsigned int*)(c.heap[r] + kOffPushAck) + (size_t)b * B2R_MAX_RANKS + succ;
+      wait_flag_ge(ack, base_val + (unsigned int)(i - depth + 1), c);
+    }
+    __syncthreads();
+    char* fwd = succ >= 0 ? slot(succ, i) : nullptr;
+    const char* in = slot(r, i);
+    for (unsigned int sb = 0; sb < len; sb += Sv) {
+      V16 own[VPT], got[VPT];
+#pragma unroll
+      for (int u = 0; u < VPT; ++u) {
+        const unsigned int j = sb + threadIdx.x + u * blockDim.x;
+        if (j < len) {
+          own[u] = ld_peer(send + (lo + j) * 16);
+          if (pred >= 0) got[u] = ld_peer(in + (unsigned long long)j * 16);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < VPT; ++u) {
+        const unsigned int j = sb + threadIdx.x + u * blockDim.x;
+        if (j < len) {
+          V16 res = own[u];
+          if (pred >= 0) {
+            typename V::Acc acc = V::unpack(got[u]);
+            V::combine(acc, own[u]);
+            res = V::pack(acc);
+          }
+          if (fwd) st_peer(fwd + (unsigned long long)j * 16, res);
+          else
+            for (int p = 0; p < P; ++p) st_peer(rdst[p] + (lo + j) * 16, res);
+        }
+      }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0 && succ >= 0 && !c.fault_skip_signal) {
+      unsigned int* flag = (unsigned int*)(c.heap[succ] + kOffPushData) + (size_t)b * B2R_MAX_RANKS + r;
+      st_release_sys(flag, base_val + (unsigned int)(i + 1));
+    }
+    if (threadIdx.x == 32 && pred >= 0 && !c.fault_skip_signal) {
+      unsigned int* ack = (unsigned int*)(c.heap[pred] + kOffPushAck) + (size_t)b * B2R_MAX_RANKS + r;
+      st_release_sys(ack, base_val + (unsigned int)(i + 1));
+    }
+  }
+  // the (< 16 byte) tail rides with the last chain: its root (rank P-1, channel 0) pulls it in chain order, rounding bf16
+  // after every hop like the vector path, and stores it everywhere
+  if (r == P - 1 && b == P - 1 && nvec * (16 / E) < A.count) {
+    for (unsigned long long e = nvec * (16 / E) + threadIdx.x; e < A.count; e += blockDim.x) {
+      const int far = (P - 1 + P - 1) % P;
+      typename TailAcc<D>::type acc = tail_load<D>(c.heap[far] + po.send[far] + e * E);
+      for (int q = 1; q < P; ++q) {
+        const int rank_q = (P - 1 + (P - 1 - q)) % P;
+        acc = tail_apply<D, O>(acc, tail_load<D>(c.heap[rank_q] + po.send[rank_q] + e * E));
+        if constexpr (D == B2R_BFLOAT16) acc = __bfloat162float(__float2bfloat16_rn(acc));
+      }
+      for (int p = 0; p < P; ++p) tail_store<D>(rdst[p] + e * E, acc);
+    }
+  }
+  cta_barrier(A, A.epoch + 2);
+}
+
 // ------------------------------------------------------------------------------------------------ NVLS (multimem)
 // The switch performs the combine: multimem.ld_reduce on the multicast address returns op over all ranks' copies;
 // multimem.st writes all ranks' copies. Supported by the hardware for: fp32 add (v4), bf16x2 add/min/max (v4, fp32
@@ -958,7 +1062,7 @@ __device__ inline void barrier_body(const CollArgs& A) {
   start_barrier(A, &po);
 }
 
-enum CollKind { kCollOneshot = 1, kCollTwoshot = 2, kCollTree = 3, kCollNvls = 4, kCollBarrier = 5, kCollPush = 6, kCollRing = 7, kCollLL = 8 };
+enum CollKind { kCollOneshot = 1, kCollTwoshot = 2, kCollTree = 3, kCollNvls = 4, kCollBarrier = 5, kCollPush = 6, kCollRing = 7, kCollLL = 8, kCollRingAll = 9 };
 
 template <int D, int O, int KIND, int UNR>
 __global__ void __launch_bounds__(512) coll_kernel(const __grid_constant__ CollLaunch L) {
@@ -970,6 +1074,7 @@ __global__ void __launch_bounds__(512) coll_kernel(const __grid_constant__ CollL
   else if (KIND == kCollPush) push_body<D, O, UNR>(A);
   else if (KIND == kCollRing) ring_body<D, O, UNR>(A);
   else if (KIND == kCollLL) ll_body<D, O>(A);
+  else if (KIND == kCollRingAll) ringall_body<D, O, UNR>(A);
   else barrier_body(A);
 }
 

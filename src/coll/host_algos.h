@@ -47,17 +47,29 @@ void host_collective_rank(const HostRankView& v, uint64_t count, b2r_dtype_t dty
     }
     barrier();
   } else if (algo == B2R_ALGO_RING) {
-    // chain ending at the root: left fold from the farthest position down to the root (same association order as ring_body)
-    const int rt = root < 0 ? 0 : root;
-    if (r == rt) {
-      // hop by hop: the running partial travels in the buffer's own dtype, so bf16 is rounded at EVERY hop (unlike the
-      // one-shot / two-shot / push / NVLS paths, which combine all P contributions in fp32 and round once)
-      const size_t esz = b2r_dtype_size(dtype);
-      memcpy(v.recv[r], v.send[(rt + P - 1) % P], count * esz);
+    // Chain ending at a root: left fold from the farthest position down to the root (same association order as ring_body).
+    // Hop by hop: the running partial travels in the buffer's own dtype, so bf16 is rounded at EVERY hop (unlike the
+    // one-shot / two-shot / push / NVLS paths, which combine all P contributions in fp32 and round once).
+    const size_t esz = b2r_dtype_size(dtype);
+    auto chain_fold = [&](int rt, uint64_t first, uint64_t n) {  // recv[rt][first, first+n) = fold over the chain that ends at rt
+      if (n == 0) return;
+      memcpy((char*)v.recv[rt] + first * esz, (const char*)v.send[(rt + P - 1) % P] + first * esz, n * esz);
       for (int q = 1; q < P; ++q) {
-        const void* pair[2] = {v.recv[r], v.send[(rt + (P - 1 - q)) % P]};
-        combine_many_host(v.recv[r], pair, 2, 0, count, dtype, op);
+        const void* pair[2] = {v.recv[rt], v.send[(rt + (P - 1 - q)) % P]};
+        combine_many_host(v.recv[rt], pair, 2, first, n, dtype, op);
       }
+    };
+    if (root >= 0) {
+      if (r == root) chain_fold(root, 0, count);
+    } else {
+      // allreduce = P chains at once: chain c ends at rank c and reduces slice c (cut at 16-byte vectors like the device
+      // kernel; the sub-vector tail rides with the last chain), then every chain root copies its slice to every rank
+      const uint64_t per_vec = 16 / esz, nvec = count / per_vec;
+      const uint64_t lo = nvec * (uint64_t)r / P * per_vec;
+      const uint64_t hi = r == P - 1 ? count : nvec * (uint64_t)(r + 1) / P * per_vec;
+      chain_fold(r, lo, hi - lo);
+      for (int p = 0; p < P; ++p)
+        if (p != r && hi > lo) memcpy((char*)v.recv[p] + lo * esz, (const char*)v.recv[r] + lo * esz, (hi - lo) * esz);
     }
     barrier();
   } else {  // B2R_ALGO_TREE

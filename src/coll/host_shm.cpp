@@ -123,7 +123,6 @@ b2r_status_t HostShmComm::reduce(const void* sendbuf, void* recvbuf, uint64_t co
   B2R_REQUIRE(dtype >= B2R_INT32 && dtype <= B2R_BFLOAT16 && op >= B2R_SUM && op <= B2R_MAX, "host comm: bad dtype/op");
   B2R_REQUIRE(sendbuf != nullptr || count == 0, "host comm: sendbuf is NULL");
   if (algo == B2R_ALGO_AUTO || algo == B2R_ALGO_NVLS) algo = B2R_ALGO_TWOSHOT;
-  if (algo == B2R_ALGO_RING && root < 0) algo = B2R_ALGO_TWOSHOT;
   const size_t esz = b2r_dtype_size(dtype);
   const size_t chunk_elems = ctl_->window_bytes / esz;
   std::vector<const void*> send(size_);

@@ -1,9 +1,10 @@
-"""GPU, opt-in: the EXPERIMENTAL LL small-message path (`algo="ll"`, src/coll/coll_kernels.cuh `ll_body`).
+"""GPU, opt-in: the EXPERIMENTAL collective paths of src/coll/coll_kernels.cuh — the LL small-message path (`algo="ll"`,
+`ll_body`) and the ring allreduce (`algo="ring"` on allreduce with B2R_EXPERIMENTAL=1, `ringall_body`).
 
-The kernel was written after the round's GPU budget was spent, so it has been compiled and inspected (SASS, registers)
-but not run. Until it has passed on hardware these tests only run when asked for:
+Both kernels were written after the round's GPU budget was spent, so they have been compiled and inspected (SASS,
+registers) but not run. Until they have passed on hardware these tests only run when asked for:
 
-    B2R_TEST_EXPERIMENTAL=1 python -m pytest tests/test_experimental_ll_gpu.py -m gpu -x -q
+    B2R_TEST_EXPERIMENTAL=1 python -m pytest tests/test_experimental_gpu.py -m gpu -x -q
 
 The host-side pieces that do not need a GPU (size limit, selection rule, the CPU restatement) are covered in
 tests/test_plan.py and tests/test_host_collectives.py and always run.
@@ -141,3 +142,46 @@ def test_ll_rejects_what_it_cannot_carry(comms):
     ok = Communicator.group_allreduce(comms, [b[:32] for b in base], "sum", algo="ll")
     Communicator.group_check(comms)
     assert all(int(o.abs().sum()) == 0 for o in ok)
+
+
+# ------------------------------------------------------------------------------------------------ ring allreduce (B2R_EXPERIMENTAL=1)
+@pytest.fixture()
+def experimental(monkeypatch):
+    monkeypatch.setenv("B2R_EXPERIMENTAL", "1")
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
+def test_ring_allreduce_matches_host_restatement(comms, experimental, dtype):
+    """P chains + all-gather by stores (`ringall_body`): bit-identical to the per-slice chain fold of host_algos.h."""
+    P = len(comms)
+    for count in (1, 3, 7, 1000, 4099, 65537, (1 << 21) + 9, (3 << 21) + 5):
+        xs_h = [b2r.fill_host(count, dtype, seed=41 * r + count, mode="signed") for r in range(P)]
+        xs = [x.cuda() for x in xs_h]
+        for op in ("sum", "min", "max"):
+            want = host_reduce_threads(xs_h, op, -1, "ring")[0]
+            outs = Communicator.group_allreduce(comms, xs, op, algo="ring")
+            Communicator.group_check(comms)
+            for r in range(P):
+                assert torch.equal(bits(outs[r].cpu()), bits(want)), (P, dtype, op, count, r)
+        for r in range(P):
+            assert torch.equal(bits(xs[r].cpu()), bits(xs_h[r]))
+
+
+def test_ring_allreduce_in_place_symmetric_and_back_to_back(comms, experimental):
+    P = len(comms)
+    count = 300001
+    for c in comms:
+        c.symm_free_all()
+    bufs = [c.symm_empty(count, torch.int32) for c in comms]
+    xs_h = [b2r.fill_host(count, torch.int32, seed=77 + r, mode="full") for r in range(P)]
+    want = host_reduce_threads(xs_h, "sum", -1, "ring")[0]
+    for it in range(20):
+        for bf, x in zip(bufs, xs_h):
+            bf.copy_(x)
+        algo = "ring" if it % 3 else "twoshot"  # interleave with a barrier-framed algorithm that shares the flag rows
+        Communicator.group_allreduce(comms, bufs, "sum", algo=algo, outs=bufs)
+    Communicator.group_check(comms)
+    for r in range(P):
+        assert torch.equal(bufs[r].cpu(), want)
+    for c in comms:
+        c.symm_free_all()

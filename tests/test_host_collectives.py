@@ -122,3 +122,24 @@ def test_ll_path_limits_and_selection(monkeypatch):
     name = _lib.LIB.b2r_algo_name
     name.restype = __import__("ctypes").c_char_p
     assert name(_lib.ALGO_LL) == b"ll" and name(_lib.ALGO_RING) == b"ring"
+
+
+@pytest.mark.parametrize("nranks", [1, 2, 3, 5, 8])
+@pytest.mark.parametrize("dtype", DTYPES)
+def test_ring_allreduce_is_one_chain_per_slice(nranks, dtype):
+    """Ring allreduce = P chains at once: chain c ends at rank c and folds slice c (cut at 16-byte vectors, the
+    sub-vector tail rides with the last chain); every rank ends up with the same bits."""
+    per_vec = 16 // torch.empty(0, dtype=dtype).element_size()
+    for count in (1, per_vec - 1, per_vec, 7 * per_vec + 1, 1025):
+        xs = [b2r.fill_host(count, dtype, seed=13 * r + count, mode="signed") for r in range(nranks)]
+        nvec = count // per_vec
+        for op in ("sum", "min", "max"):
+            rows = host_reduce_threads(xs, op, -1, "ring")
+            want = torch.empty_like(xs[0])
+            for c in range(nranks):
+                lo = nvec * c // nranks * per_vec
+                hi = count if c == nranks - 1 else nvec * (c + 1) // nranks * per_vec
+                if hi > lo:
+                    want[lo:hi] = chain_oracle([x[lo:hi] for x in xs], op, c)
+            for r in range(nranks):
+                assert torch.equal(rows[r].view(torch.uint8), want.view(torch.uint8)), (nranks, dtype, op, count, r)
