@@ -10,10 +10,10 @@
 // decimal GB/s and bus bandwidth go to the JSONL/CSV sink, not into the reference-format rows.
 //
 //   bench_collective [--gpus=N] [--total-mib=2048] [--retries=5] [--types=INT,DOUBLE[,BF16,FLOAT]] [--coll=reduce|allreduce]
-//                    [--algo=auto|oneshot|twoshot|tree|nvls] [--root=0] [--check] [--jsonl=path] [--raw=path]
+//                    [--algo=auto|oneshot|twoshot|tree|nvls|push|ring|ll] [--root=0] [--check] [--jsonl=path] [--raw=path]
 //   bench_collective --tune=ring|push|nvls|twoshot [--coll=] [--bytes=] [--type=] [--iters=]   (in-process launch-shape grid)
 //   bench_collective --sweep [--min-bytes=1024] [--max-bytes=4294967296] [--types=...] [--colls=reduce,allreduce]
-//                    [--algos=auto,oneshot,twoshot,tree,nvls] [--iters=20] [--jsonl=path] [--csv=path]
+//                    [--algos=auto,oneshot,twoshot,tree,nvls,push,ring,ll] [--iters=20] [--jsonl=path] [--csv=path]
 // Runs as ONE process driving all GPUs (b2r_comm_init_all); buffers come from the symmetric heap (zero copy).
 #include <algorithm>
 #include <cmath>
@@ -306,7 +306,8 @@ int main(int argc, char** argv) {
               const uint64_t count = bytes / b2r_dtype_size(dt);
               if (count == 0) continue;
               if (algo == B2R_ALGO_NVLS && !has_mc) continue;
-              if (algo == B2R_ALGO_RING && allreduce) continue;
+              if (algo == B2R_ALGO_RING && allreduce && !(getenv("B2R_EXPERIMENTAL") && atoi(getenv("B2R_EXPERIMENTAL")))) continue;
+              if (algo == B2R_ALGO_LL && bytes > b2r_ll_max_bytes(P)) continue;
               if (algo == B2R_ALGO_NVLS && (dt == B2R_FLOAT32 || dt == B2R_FLOAT64) && op != B2R_SUM) continue;
               if ((algo == B2R_ALGO_ONESHOT || algo == B2R_ALGO_TREE) && bytes > (64ull << 20)) continue;  // pointless at this size
               if (f.has("check") && bytes <= (256ull << 20)) all_ok = verify(R, allreduce, count, dt, op, root, algo) && all_ok;
