@@ -441,10 +441,10 @@ using namespace b2r;
 
 extern "C" {
 
-// Size thresholds measured on 8x B200 (profiles/collectives_8gpu.md). One-shot costs one NVLink round trip but every
-// rank pulls the WHOLE message from every peer; two-shot / NVLS move 1/P of it per rank.
 uint64_t b2r_ll_max_bytes(int nranks) { return (nranks >= 2 && nranks <= B2R_MAX_RANKS) ? (uint64_t)ll_max_msg_bytes(nranks) : 0; }
 
+// Size thresholds measured on 8x B200 (profiles/collectives_8gpu.md). One-shot costs one NVLink round trip but every
+// rank pulls the WHOLE message from every peer; two-shot / NVLS move 1/P of it per rank.
 b2r_algo_t b2r_select_algo(int is_allreduce, uint64_t bytes, b2r_dtype_t dtype, b2r_op_t op, int nranks, int has_multicast) {
   if (nranks <= 1) return B2R_ALGO_ONESHOT;
   const int forced = env_int("B2R_ALGO", 0);
