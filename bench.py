@@ -223,6 +223,11 @@ def run_b2r(args) -> None:
     # ---- end-to-end arm: host (pinned) -> device copy of every step's input + scalar back on the host
     e2e_steps = args.e2e_steps or max(3, min(steps, 40))
     host_copies = 2
+    # the pinned inputs of this rank belong on the socket its GPU hangs off (8 ranks sharing the inter-socket link halved the
+    # per-GPU rate in round 1); best effort, B2R_NUMA_BIND=0 disables it
+    from cuda_mpi_reductions_b200.utils.numa import bind_to_gpu_node
+
+    numa = bind_to_gpu_node(local_rank)
     host_in = [b2r.fill_host(args.n, dtype, seed=77 + 1000 * rank + c, mode="sdk", pin_memory=True) for c in range(host_copies)]
     if comm is None:
         def e2e_step(i):
@@ -276,7 +281,8 @@ def run_b2r(args) -> None:
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": "GB/s", "h2d_bytes_per_step": nbytes, "d2h_bytes_per_step": nchunks * acc_sz,
                     "steps": e2e_steps, "ms_per_step": e2e_s * 1e3 / e2e_steps,
-                    "api": "cuda_mpi_reductions_b200.reduce_from_host(pinned_tensor)" if comm is None else "Communicator.reduce_scalar_sharded_from_host(pinned_tensor)"},
+                    "api": "cuda_mpi_reductions_b200.reduce_from_host(pinned_tensor)" if comm is None else "Communicator.reduce_scalar_sharded_from_host(pinned_tensor)",
+                    "numa_rank0": numa},
             "gpu_launches": steps * world,  # one kernel of ours per GPU per step inside the timed region
             "gpu_launches_per_gpu": steps,
             "hbm_fraction_of_measured": value / world / hbm,

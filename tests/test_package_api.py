@@ -54,3 +54,34 @@ def test_rotating_copies_and_clock_sampler_fallback():
     s.stop()
     summ = s.summary(0.0, 1e12)
     assert set(summ) >= {"sm_mhz", "sm_max_mhz", "reasons", "samples", "window", "backend"}
+
+
+def test_numa_binding_helpers(tmp_path, monkeypatch):
+    """utils/numa.py on a fake sysfs tree: cpulist parsing, node lookup, and every 'leave it alone' exit."""
+    import os
+
+    from cuda_mpi_reductions_b200.utils import numa
+
+    assert numa.parse_cpulist("0-3,8,10-11\n") == {0, 1, 2, 3, 8, 10, 11}
+    assert numa.parse_cpulist("") == set()
+    allowed = sorted(os.sched_getaffinity(0))
+    root = tmp_path / "sys"
+    (root / "bus/pci/devices/0000:1b:00.0").mkdir(parents=True)
+    (root / "bus/pci/devices/0000:1b:00.0/numa_node").write_text("1\n")
+    (root / "bus/pci/devices/0000:9c:00.0").mkdir(parents=True)
+    (root / "bus/pci/devices/0000:9c:00.0/numa_node").write_text("-1\n")
+    (root / "devices/system/node/node1").mkdir(parents=True)
+    (root / "devices/system/node/node1/cpulist").write_text(f"{allowed[0]}\n")
+    assert numa.gpu_numa_node("0000:1b:00.0", str(root)) == 1
+    assert numa.gpu_numa_node("0000:9c:00.0", str(root)) is None  # the platform does not say
+    assert numa.gpu_numa_node("0000:aa:00.0", str(root)) is None  # no such device
+    info = numa.bind_to_gpu_node(0, str(root), pci_addr="0000:1b:00.0", apply=False)  # dry run: the test process keeps its CPUs
+    assert info["node"] == 1 and info["cpus"] == 1 and info["bound"]
+    assert not numa.bind_to_gpu_node(0, str(root), pci_addr="0000:9c:00.0", apply=False)["bound"]
+    (root / "devices/system/node/node1/cpulist").write_text("100000\n")  # a CPU outside this process's cpuset
+    assert not numa.bind_to_gpu_node(0, str(root), pci_addr="0000:1b:00.0", apply=False)["bound"]
+    monkeypatch.setenv("B2R_NUMA_BIND", "0")
+    assert numa.bind_to_gpu_node(0, str(root), pci_addr="0000:1b:00.0")["why"].startswith("disabled")
+    monkeypatch.delenv("B2R_NUMA_BIND")
+    assert numa.bind_to_gpu_node(0, apply=False)["bound"] in (True, False)  # real sysfs, with or without a GPU: must not raise
+    assert sorted(os.sched_getaffinity(0)) == allowed
