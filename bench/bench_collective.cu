@@ -223,7 +223,9 @@ int main(int argc, char** argv) {
     const int iters = (int)f.i64("iters", 10);
     struct Knob { const char* name; std::vector<int> values; };
     std::vector<Knob> knobs;
-    if (which == "ring") knobs = {{"B2R_RING_CTAS", {16, 32, 64}}, {"B2R_RING_SUBBLOCKS", {2, 4, 8, 16}}, {"B2R_COLL_THREADS", {256, 512}}};
+    // ring: total time ~ (steps per CTA + P - 2) x step period, so a long chain wants MANY short steps spread over many CTAs
+    // (8 GPUs, 256 MiB: 32 CTAs x 512 KiB is 16 steps + 6 of pipeline fill; 128 x 64 KiB is 32 + 6 at the same bytes per fence round)
+    if (which == "ring") knobs = {{"B2R_RING_CTAS", {32, 64, 128}}, {"B2R_RING_SUBBLOCKS", {1, 2, 4, 8}}, {"B2R_COLL_THREADS", {256, 512}}};
     else if (which == "push") knobs = {{"B2R_PUSH_CTAS", {32, 64, 128}}, {"B2R_COLL_THREADS", {256, 512}}};
     else if (which == "nvls") knobs = {{"B2R_COLL_CTAS", {8, 16, 32, 64, 128}}, {"B2R_COLL_THREADS", {128, 256, 512}}, {"B2R_COLL_UNROLL", {4, 8}}};
     else knobs = {{"B2R_COLL_CTAS", {32, 64, 128, 148}}, {"B2R_COLL_THREADS", {256, 512}}, {"B2R_COLL_UNROLL", {4, 8}}};
