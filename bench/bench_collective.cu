@@ -224,8 +224,9 @@ int main(int argc, char** argv) {
     struct Knob { const char* name; std::vector<int> values; };
     std::vector<Knob> knobs;
     // ring: total time ~ (steps per CTA + P - 2) x step period, so a long chain wants MANY short steps spread over many CTAs
-    // (8 GPUs, 256 MiB: 32 CTAs x 512 KiB is 16 steps + 6 of pipeline fill; 128 x 64 KiB is 32 + 6 at the same bytes per fence round)
-    if (which == "ring") knobs = {{"B2R_RING_CTAS", {32, 64, 128}}, {"B2R_RING_SUBBLOCKS", {1, 2, 4, 8}}, {"B2R_COLL_THREADS", {256, 512}}};
+    // (8 GPUs, 256 MiB: 32 CTAs x 512 KiB is 16 steps + 6 of pipeline fill; 128 x 64 KiB is 32 + 6 at the same bytes per fence round);
+    // 256 threads x >= 148 CTAs puts two CTAs on an SM, so one streams while the other sits in its release fence
+    if (which == "ring") knobs = {{"B2R_RING_CTAS", {32, 64, 128, 256}}, {"B2R_RING_SUBBLOCKS", {1, 2, 4, 8}}, {"B2R_COLL_THREADS", {256, 512}}};
     else if (which == "push") knobs = {{"B2R_PUSH_CTAS", {32, 64, 128}}, {"B2R_COLL_THREADS", {256, 512}}};
     else if (which == "nvls") knobs = {{"B2R_COLL_CTAS", {8, 16, 32, 64, 128}}, {"B2R_COLL_THREADS", {128, 256, 512}}, {"B2R_COLL_UNROLL", {4, 8}}};
     else knobs = {{"B2R_COLL_CTAS", {32, 64, 128, 148}}, {"B2R_COLL_THREADS", {256, 512}}, {"B2R_COLL_UNROLL", {4, 8}}};
