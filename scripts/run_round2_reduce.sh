@@ -1,7 +1,7 @@
 #!/bin/bash
 # First things to run in the next round.
 #   scripts/run_round2_reduce.sh validate      one GPU: the experimental kernels written blind at the end of round 1 (LL small-message path,
-#                                              ring allreduce) against their host restatements on the loopback transport
+#                                              ring allreduce, pipelined ring) against their host restatements on the loopback transport
 #   scripts/run_round2_reduce.sh N             one `gpurun --gpus N` call, N = 4 or 8: where do the store-forwarding ring, the LL path and the ring
 #                                              allreduce stand against what AUTO picks today and against NCCL, and which launch shape does the ring want?
 # One process per tool (communicator set-up dominates short runs at 8 GPUs — the round-1 tuning loops burned 84 GPU-minutes on it).
@@ -15,6 +15,7 @@ OUT=gpurun_out/round2_reduce_$N
 mkdir -p $OUT
 export B2R_EXPERIMENTAL=1
 timeout 120 bin/bench_collective --gpus=$N --tune=ring --bytes=268435456 --iters=8 > $OUT/tune_ring_256m.txt 2>&1
+B2R_RING_V2=1 timeout 120 bin/bench_collective --gpus=$N --tune=ring --bytes=268435456 --iters=8 > $OUT/tune_ring2_256m.txt 2>&1
 timeout 120 bin/bench_collective --gpus=$N --tune=ring --coll=allreduce --type=INT --bytes=268435456 --iters=8 > $OUT/tune_ringall_256m.txt 2>&1
 timeout 120 bin/bench_collective --gpus=$N --tune=push --coll=reduce --bytes=268435456 --iters=8 > $OUT/tune_push_256m.txt 2>&1
 timeout 120 bin/bench_collective --gpus=$N --sweep --types=FLOAT,INT --colls=reduce --algos=ring,nvls,twoshot --min-bytes=1048576 --max-bytes=1073741824 --factor=4 --check > $OUT/reduce_algos.txt 2>&1
@@ -23,6 +24,7 @@ timeout 120 bin/bench_collective --gpus=$N --sweep --types=FLOAT,INT --colls=red
 timeout 100 bin/nccl_bench --gpus=$N --sweep --types=FLOAT,INT --colls=reduce,allreduce --min-bytes=1024 --max-bytes=16384 --factor=2 > $OUT/nccl_small.txt 2>/dev/null
 timeout 100 bin/nccl_bench --gpus=$N --sweep --types=FLOAT,INT --colls=reduce,allreduce --min-bytes=1048576 --max-bytes=1073741824 --factor=4 > $OUT/nccl_large.txt 2>/dev/null
 sort -k5 -n -r $OUT/tune_ring_256m.txt | head -5
+sort -k5 -n -r $OUT/tune_ring2_256m.txt | head -5
 sort -k5 -n -r $OUT/tune_ringall_256m.txt | head -3
 grep -E "ring|FAIL|PASS" $OUT/reduce_algos.txt $OUT/allreduce_ring.txt | tail -24
 grep -E " ll |FAIL|PASS" $OUT/small_ll.txt | tail -24

@@ -55,6 +55,7 @@ CollKernel pick_kind(int kind) {
     case kCollRing: return coll_kernel<D, O, kCollRing, 4>;
     case kCollLL: return coll_kernel<D, O, kCollLL, 4>;
     case kCollRingAll: return coll_kernel<D, O, kCollRingAll, 4>;
+    case kCollRing2: return coll_kernel<D, O, kCollRing2, 4>;
   }
   return nullptr;
 }
@@ -95,7 +96,7 @@ Shape coll_shape(const b2r_comm* c, int kind, uint64_t bytes, int nvirtual) {
     s.unroll = bytes >= (8u << 20) ? 8 : 4;
     cap = 32;
     per_cta = 32768;
-  } else if (kind == kCollPush || kind == kCollRing || kind == kCollRingAll) {
+  } else if (kind == kCollPush || kind == kCollRing || kind == kCollRingAll || kind == kCollRing2) {
     s.threads = 512;
     s.unroll = 4;
     cap = 128;
@@ -188,6 +189,8 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
     if (!env_int("B2R_EXPERIMENTAL", 0)) return fail(B2R_ERR_UNSUPPORTED, "the ring algorithm implements reduce-to-root only");
     kind = kCollRingAll;
   }
+  // the pipelined ring (waiter / data / signal warps) replaces ring_body only when asked for: not yet run on hardware
+  if (kind == kCollRing && env_int("B2R_RING_V2", 0)) kind = kCollRing2;
   if (kind == kCollLL) {
     // LL never touches a peer's send/recv buffer: any 16-byte aligned device pointer works, nothing is staged or chunked
     if (total_bytes > ll_max_msg_bytes(P))
@@ -253,7 +256,7 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
       A.epoch = c->epoch;
       A.root = is_all ? -1 : root;
       c->epoch += 8;  // start + end + up to 4 tree rounds, rounded up; same increment on every rank
-      if (kind == kCollPush || kind == kCollRing || kind == kCollRingAll) A.seq = ++c->push_seq;
+      if (kind == kCollPush || kind == kCollRing || kind == kCollRingAll || kind == kCollRing2) A.seq = ++c->push_seq;
     }
     const Shape shape = coll_shape(c0, kind, bytes, n);
     int ctas = shape.ctas;
@@ -263,10 +266,11 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
       ctas = 1;
       threads = nvec <= 128 ? 128 : nvec <= 256 ? 256 : kLLThreads;
     }
-    if (kind == kCollRing || kind == kCollRingAll) {
+    if (kind == kCollRing || kind == kCollRingAll || kind == kCollRing2) {
       // staging ring in the work region: depth x ctas steps of sub_blocks x (threads x 8) vectors; at least 2 deep.
       // Large messages use big steps (default 8 sub-blocks = 512 KiB with 512 threads) to amortise the per-step fence.
-      const uint64_t sub_bytes = (uint64_t)threads * 8 * 16;
+      if (kind == kCollRing2) threads = std::max(threads, 96);  // waiter warp + signal warp + at least one data warp
+      const uint64_t sub_bytes = (uint64_t)(kind == kCollRing2 ? threads - 64 : threads) * 8 * 16;
       int subs = std::max(1, env_int("B2R_RING_SUBBLOCKS", 8));
       int cap = std::max(1, env_int("B2R_RING_CTAS", 32));
       if (n > 1) cap = std::max(1, std::min(cap, c0->sm_count / n));

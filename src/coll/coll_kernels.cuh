@@ -650,6 +650,154 @@ __device__ void ring_body(const CollArgs& A) {
   cta_barrier(A, A.epoch + 2);
 }
 
+// ------------------------------------------------------------------------------------------------ pipelined ring (reduce to root)  [EXPERIMENTAL]
+// ring_body runs every step as wait -> move -> __syncthreads -> release fence -> signal, so each step pays the fence
+// (one NVLink round trip) and the flag hop serially: ~8 us of latency per step, fitted on the 2-GPU runs. To keep the link
+// busy the steps must then be large (bytes per round >= link rate x latency ~ 6.5 MB), which leaves few steps per channel
+// — and an 8-long chain loses (P-2) step times to pipeline fill (13% at 256 MiB). Here the three jobs run concurrently in
+// one CTA and are coupled only by two shared-memory counters:
+//   waiter warp : polls the data flag (from the predecessor) and the slot-reuse ack (from the successor) for step i, then
+//                 publishes ready = i+1;
+//   data warps  : wait for ready > i, move their part of step i (load own + staged partial, combine, store downstream) and
+//                 add themselves to `done`; no block-wide barrier, they start step i+1 at once;
+//   signal warp : waits for done == data warps x (i+1), acks step i upstream and release-stores the data flag downstream.
+// The fence now overlaps the next steps' traffic; it only delays when the successor SEES a step, not how fast steps are
+// produced, so steps can be small and many. Same chain order, same staging slots and flag words as ring_body (results are
+// bit-identical to it and to the host restatement). Ordering: data stores -> __syncwarp -> red.release.cta(done) ->
+// ld.acquire.cta by the signal warp -> st.release.sys(flag) is one causality chain, and the mirror image on the way in.
+__device__ __forceinline__ void st_release_cta_shared(uint32_t addr, unsigned int v) {
+  asm volatile("st.release.cta.shared.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned int ld_acquire_cta_shared(uint32_t addr) {
+  unsigned int v;
+  asm volatile("ld.acquire.cta.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ void red_release_cta_shared_add(uint32_t addr, unsigned int v) {
+  asm volatile("red.release.cta.shared.add.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+
+template <int D, int O, int UNR>
+__device__ void ring2_body(const CollArgs& A) {
+  using V = VecOps<D, O>;
+  const CollCtx& c = A.ctx;
+  constexpr int E = V::kElem;
+  constexpr int VPT = 8;
+  const int P = c.nranks, r = c.rank, root = A.root, G = (int)gridDim.x, b = (int)blockIdx.x;
+  const int pos = (r - root + P) % P;
+  const int pred = pos + 1 < P ? (root + pos + 1) % P : -1;
+  const int succ = pos > 0 ? (root + pos - 1) % P : -1;
+  const unsigned int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const unsigned int ndw = (blockDim.x >> 5) - 2;  // data warps; then the waiter warp, then the signal warp
+  const unsigned int ndata = ndw * 32;
+  const unsigned long long nvec = A.count * E / 16;
+  const unsigned int Sv = ndata * VPT;
+  const unsigned int Cv = Sv * (unsigned int)max(1, A.sub_blocks);
+  const unsigned long long nblocks = (nvec + Cv - 1) / Cv;
+  const unsigned long long steps = (unsigned long long)b < nblocks ? (nblocks - b + G - 1) / G : 0;
+  const int depth = A.ring_depth;
+  const unsigned int base_val = A.seq << 16;
+
+  __shared__ PeerOffsets po;
+  __shared__ unsigned int s_ready, s_done;
+  if (threadIdx.x == 0) {
+    s_ready = 0;
+    s_done = 0;
+  }
+  start_barrier(A, &po);  // contains __syncthreads on both sides: the counters are visible to everybody
+  const uint32_t a_ready = smem_u32(&s_ready), a_done = smem_u32(&s_done);
+  const char* send = c.heap[r] + A.send_off;
+  auto slot = [&](int rank, unsigned long long step) {
+    return c.heap[rank] + A.work_off + (((step % depth) * G + b) * (unsigned long long)Cv) * 16ull;
+  };
+
+  if (warp == ndw) {
+    // ---- waiter: a timed-out wait still publishes the step (the error word is set; everything touched is valid memory)
+    for (unsigned long long i = 0; i < steps; ++i) {
+      if (lane == 0 && pred >= 0) {
+        const unsigned int* flag = (const unsigned int*)(c.heap[r] + kOffPushData) + (size_t)b * B2R_MAX_RANKS + pred;
+        wait_flag_ge(flag, base_val + (unsigned int)(i + 1), c);
+      }
+      if (lane == 1 && succ >= 0 && i >= (unsigned long long)depth) {
+        const unsigned int* ack = (const unsigned int*)(c.heap[r] + kOffPushAck) + (size_t)b * B2R_MAX_RANKS + succ;
+        wait_flag_ge(ack, base_val + (unsigned int)(i - depth + 1), c);
+      }
+      __syncwarp();
+      if (lane == 0) st_release_cta_shared(a_ready, (unsigned int)(i + 1));
+    }
+  } else if (warp == ndw + 1) {
+    // ---- signaller
+    for (unsigned long long i = 0; i < steps; ++i) {
+      if (lane == 0) {
+        while (ld_acquire_cta_shared(a_done) < ndw * (unsigned int)(i + 1)) __nanosleep(32);
+        if (!c.fault_skip_signal) {
+          if (pred >= 0) {  // the staged partial of step i has been read: its slot may be refilled
+            unsigned int* ack = (unsigned int*)(c.heap[pred] + kOffPushAck) + (size_t)b * B2R_MAX_RANKS + r;
+            st_relaxed_sys_u32(ack, base_val + (unsigned int)(i + 1));
+          }
+          if (succ >= 0) {  // release: every data warp's stores of step i are visible before the flag is
+            unsigned int* flag = (unsigned int*)(c.heap[succ] + kOffPushData) + (size_t)b * B2R_MAX_RANKS + r;
+            st_release_sys(flag, base_val + (unsigned int)(i + 1));
+          }
+        }
+      }
+      __syncwarp();
+    }
+  } else {
+    // ---- data warps
+    const unsigned int dt = threadIdx.x;  // 0 .. ndata-1
+    for (unsigned long long i = 0; i < steps; ++i) {
+      const unsigned long long lo = (b + i * G) * (unsigned long long)Cv;
+      const unsigned int len = (unsigned int)min((unsigned long long)Cv, nvec - lo);
+      if (lane == 0)
+        while (ld_acquire_cta_shared(a_ready) < (unsigned int)(i + 1)) __nanosleep(20);
+      __syncwarp();
+      char* dst = succ >= 0 ? slot(succ, i) : c.heap[r] + A.recv_off + lo * 16;
+      const char* in = slot(r, i);
+      for (unsigned int sb = 0; sb < len; sb += Sv) {
+        V16 own[VPT], got[VPT];
+#pragma unroll
+        for (int u = 0; u < VPT; ++u) {
+          const unsigned int j = sb + dt + u * ndata;
+          if (j < len) {
+            own[u] = ld_peer(send + (lo + j) * 16);
+            if (pred >= 0) got[u] = ld_peer(in + (unsigned long long)j * 16);
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < VPT; ++u) {
+          const unsigned int j = sb + dt + u * ndata;
+          if (j < len) {
+            if (pred >= 0) {
+              typename V::Acc acc = V::unpack(got[u]);
+              V::combine(acc, own[u]);
+              st_peer(dst + (unsigned long long)j * 16, V::pack(acc));
+            } else {
+              st_peer(dst + (unsigned long long)j * 16, own[u]);
+            }
+          }
+        }
+      }
+      __syncwarp();
+      if (lane == 0) red_release_cta_shared_add(a_done, 1u);
+    }
+  }
+  __syncthreads();
+  // the (< 16 byte) tail: exactly as in ring_body
+  if (pos == 0 && nvec * (16 / E) < A.count && blockIdx.x == 0) {
+    for (unsigned long long e = nvec * (16 / E) + threadIdx.x; e < A.count; e += blockDim.x) {
+      typename TailAcc<D>::type acc = tail_load<D>(c.heap[(root + P - 1) % P] + po.send[(root + P - 1) % P] + e * E);
+      for (int q = 1; q < P; ++q) {
+        const int rank_q = (root + (P - 1 - q)) % P;
+        acc = tail_apply<D, O>(acc, tail_load<D>(c.heap[rank_q] + po.send[rank_q] + e * E));
+        if constexpr (D == B2R_BFLOAT16) acc = __bfloat162float(__float2bfloat16_rn(acc));
+      }
+      tail_store<D>(c.heap[r] + A.recv_off + e * E, acc);
+    }
+  }
+  cta_barrier(A, A.epoch + 2);
+}
+
 // ------------------------------------------------------------------------------------------------ ring allreduce  [EXPERIMENTAL]
 // P chains at once, each exactly the reduce ring above: chain c ends at rank c and reduces slice c of the message, and the
 // chain root, instead of keeping the result, stores it into EVERY rank's recv buffer (all-gather by stores). CTA b works
@@ -1062,7 +1210,7 @@ __device__ inline void barrier_body(const CollArgs& A) {
   start_barrier(A, &po);
 }
 
-enum CollKind { kCollOneshot = 1, kCollTwoshot = 2, kCollTree = 3, kCollNvls = 4, kCollBarrier = 5, kCollPush = 6, kCollRing = 7, kCollLL = 8, kCollRingAll = 9 };
+enum CollKind { kCollOneshot = 1, kCollTwoshot = 2, kCollTree = 3, kCollNvls = 4, kCollBarrier = 5, kCollPush = 6, kCollRing = 7, kCollLL = 8, kCollRingAll = 9, kCollRing2 = 10 };
 
 template <int D, int O, int KIND, int UNR>
 __global__ void __launch_bounds__(512) coll_kernel(const __grid_constant__ CollLaunch L) {
@@ -1075,6 +1223,7 @@ __global__ void __launch_bounds__(512) coll_kernel(const __grid_constant__ CollL
   else if (KIND == kCollRing) ring_body<D, O, UNR>(A);
   else if (KIND == kCollLL) ll_body<D, O>(A);
   else if (KIND == kCollRingAll) ringall_body<D, O, UNR>(A);
+  else if (KIND == kCollRing2) ring2_body<D, O, UNR>(A);
   else barrier_body(A);
 }
 

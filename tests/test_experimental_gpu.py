@@ -185,3 +185,42 @@ def test_ring_allreduce_in_place_symmetric_and_back_to_back(comms, experimental)
         assert torch.equal(bufs[r].cpu(), want)
     for c in comms:
         c.symm_free_all()
+
+
+# ------------------------------------------------------------------------------------------------ pipelined ring (B2R_RING_V2=1)
+@pytest.mark.parametrize("shape", [(512, 8), (256, 1), (96, 2)])
+def test_pipelined_ring_is_bit_identical_to_the_ring(comms, monkeypatch, shape):
+    """`ring2_body` (waiter / data / signal warps, no block-wide barrier per step) against the host chain fold, every root,
+    for launch shapes from one data warp to fourteen and for single- and multi-sub-block steps."""
+    threads, subs = shape
+    monkeypatch.setenv("B2R_RING_V2", "1")
+    monkeypatch.setenv("B2R_COLL_THREADS", str(threads))
+    monkeypatch.setenv("B2R_RING_SUBBLOCKS", str(subs))
+    P = len(comms)
+    for dtype in (torch.int32, torch.float64, torch.bfloat16):
+        for count in (1, 1000, 65537, (1 << 21) + 9, (5 << 20) + 3):
+            xs_h = [b2r.fill_host(count, dtype, seed=19 * r + count, mode="signed") for r in range(P)]
+            xs = [x.cuda() for x in xs_h]
+            for root in sorted({0, P - 1, P // 2}):
+                for op in ("sum", "min"):
+                    want = host_reduce_threads(xs_h, op, root, "ring")
+                    outs = Communicator.group_reduce(comms, xs, op, root=root, algo="ring")
+                    Communicator.group_check(comms)
+                    assert torch.equal(bits(outs[root].cpu()), bits(want)), (P, shape, dtype, op, count, root)
+
+
+def test_pipelined_ring_back_to_back_with_other_algorithms(comms, monkeypatch):
+    monkeypatch.setenv("B2R_RING_V2", "1")
+    P = len(comms)
+    count = 200003
+    xs_h = [b2r.fill_host(count, torch.int32, seed=5 + r, mode="full") for r in range(P)]
+    xs = [x.cuda() for x in xs_h]
+    want = host_reduce_threads(xs_h, "sum", 0, "ring")
+    outs = None
+    for it in range(60):
+        algo = ("ring", "twoshot", "ring", "push")[it % 4]  # the push algorithm shares the ring's flag words and call counter
+        outs = Communicator.group_reduce(comms, xs, "sum", root=it % P, algo=algo)
+        if it % P == 0:
+            keep = outs
+    Communicator.group_check(comms)
+    assert torch.equal(keep[0].cpu(), want)
