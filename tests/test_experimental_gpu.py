@@ -134,14 +134,17 @@ def test_ll_rejects_what_it_cannot_carry(comms):
     xs = [torch.zeros(too_big, dtype=torch.int32, device="cuda") for _ in range(P)]
     with pytest.raises(b2r.B2RError, match="LL path carries at most"):
         Communicator.group_allreduce(comms, xs, "sum", algo="ll")
-    # misaligned views (4-byte aligned, not 16)
-    base = [torch.zeros(64, dtype=torch.int32, device="cuda") for _ in range(P)]
-    with pytest.raises(b2r.B2RError, match="16-byte aligned"):
-        Communicator.group_allreduce(comms, [b[1:33] for b in base], "sum", algo="ll")
-    # the communicator is still usable
-    ok = Communicator.group_allreduce(comms, [b[:32] for b in base], "sum", algo="ll")
+    # misaligned views (4-byte aligned, not 16) are bounced through the rank's own staging, not rejected
+    P = len(comms)
+    base_h = [b2r.fill_host(64, torch.int32, seed=90 + r, mode="full") for r in range(P)]
+    base = [x.cuda() for x in base_h]
+    want = host_reduce_threads([x[1:33].contiguous() for x in base_h], "sum", -1, "ll")[0]
+    outs_store = [torch.zeros(40, dtype=torch.int32, device="cuda") for _ in range(P)]
+    outs = Communicator.group_allreduce(comms, [b[1:33] for b in base], "sum", algo="ll", outs=[o[3:35] for o in outs_store])
     Communicator.group_check(comms)
-    assert all(int(o.abs().sum()) == 0 for o in ok)
+    for r in range(P):
+        assert torch.equal(outs[r].cpu(), want)
+        assert int(outs_store[r][:3].abs().sum()) == 0 and int(outs_store[r][35:].abs().sum()) == 0  # nothing written around the view
 
 
 # ------------------------------------------------------------------------------------------------ ring allreduce (B2R_EXPERIMENTAL=1)

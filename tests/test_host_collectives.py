@@ -143,3 +143,28 @@ def test_ring_allreduce_is_one_chain_per_slice(nranks, dtype):
                     want[lo:hi] = chain_oracle([x[lo:hi] for x in xs], op, c)
             for r in range(nranks):
                 assert torch.equal(rows[r].view(torch.uint8), want.view(torch.uint8)), (nranks, dtype, op, count, r)
+
+
+def test_auto_switches_for_unmeasured_paths_are_off_by_default(monkeypatch):
+    """B2R_AUTO_LL_MAX_BYTES / B2R_AUTO_RING_MIN_MB let the next round try crossovers without a rebuild; unset = old choice."""
+    sel = _lib.LIB.b2r_select_algo
+    for var in ("B2R_ALGO", "B2R_AUTO_LL_MAX_BYTES", "B2R_AUTO_RING_MIN_MB"):
+        monkeypatch.delenv(var, raising=False)
+    before = [sel(a, n, d, _lib.SUM, p, 1) for a in (0, 1) for n in (64, 8192, 1 << 20, 1 << 28) for d in (_lib.INT32, _lib.FLOAT32) for p in (2, 8)]
+    monkeypatch.setenv("B2R_AUTO_LL_MAX_BYTES", "8192")
+    assert sel(0, 8192, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_LL
+    assert sel(1, 64, _lib.INT32, _lib.MIN, 2, 0) == _lib.ALGO_LL
+    assert sel(0, 8193, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS
+    monkeypatch.setenv("B2R_AUTO_LL_MAX_BYTES", str(1 << 30))  # capped by what the slots hold
+    assert sel(0, 26624, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_LL
+    assert sel(0, 26628, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS
+    monkeypatch.delenv("B2R_AUTO_LL_MAX_BYTES")
+    monkeypatch.setenv("B2R_AUTO_RING_MIN_MB", "64")
+    assert sel(0, 64 << 20, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_RING
+    assert sel(0, 64 << 20, _lib.INT32, _lib.MAX, 4, 0) == _lib.ALGO_RING
+    assert sel(0, (64 << 20) - 4, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS
+    assert sel(1, 1 << 30, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS  # allreduce: the ring is reduce-only
+    assert sel(0, 1 << 30, _lib.FLOAT64, _lib.SUM, 2, 1) == _lib.ALGO_ONESHOT  # two GPUs: the root pulls
+    monkeypatch.delenv("B2R_AUTO_RING_MIN_MB")
+    after = [sel(a, n, d, _lib.SUM, p, 1) for a in (0, 1) for n in (64, 8192, 1 << 20, 1 << 28) for d in (_lib.INT32, _lib.FLOAT32) for p in (2, 8)]
+    assert before == after
