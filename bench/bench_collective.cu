@@ -239,6 +239,7 @@ int main(int argc, char** argv) {
         setenv(knobs[k].name, std::to_string(knobs[k].values[idx[k]]).c_str(), 1);
         label += std::string(knobs[k].name + 4) + "=" + std::to_string(knobs[k].values[idx[k]]) + " ";
       }
+      b2r_refresh_env();  // the library caches B2R_* lookups; make it read the new knob values
       if (timed(R, allreduce, count, dt, B2R_SUM, root, algo, 2) < 0) return 3;
       const double ms = timed(R, allreduce, count, dt, B2R_SUM, root, algo, iters);
       if (ms < 0) return 3;
@@ -249,6 +250,7 @@ int main(int argc, char** argv) {
       if (k == knobs.size()) break;
     }
     for (auto& kn : knobs) unsetenv(kn.name);
+    b2r_refresh_env();
   } else if (!sweep) {
     const bool allreduce = f.str("coll", "reduce") == "allreduce";
     const b2r_algo_t algo = parse_algo(f.str("algo", "auto"));

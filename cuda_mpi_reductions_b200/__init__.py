@@ -5,12 +5,12 @@ szabodabo/CUDA-MPI-Reductions: the single-GPU reduction sample (cuda/C/src/reduc
 benchmark (mpi/reduce.c); see SURVEY.md for the full map.
 """
 from . import _lib
-from ._lib import B2RError, build
+from ._lib import B2RError, build, refresh_env
 from .ops.local import Workspace, reduce, reduce_from_host, dot, plan, trace_last, launch_config
 from .ops.oracle import reduce_oracle, combine_oracle, fill_host, fill_device
 
 __all__ = [
-    "B2RError", "build", "Workspace", "reduce", "reduce_from_host", "dot", "plan", "trace_last", "launch_config",
+    "B2RError", "build", "refresh_env", "Workspace", "reduce", "reduce_from_host", "dot", "plan", "trace_last", "launch_config",
     "reduce_oracle", "combine_oracle", "fill_host", "fill_device",
 ]
 __version__ = "0.1.0"

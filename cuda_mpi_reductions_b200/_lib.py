@@ -107,6 +107,8 @@ def _declare(lib: C.CDLL) -> None:
             sig(name, args)
     if hasattr(lib, "b2r_ll_max_bytes"):
         sig("b2r_ll_max_bytes", [i], u64)
+    if hasattr(lib, "b2r_refresh_env"):
+        sig("b2r_refresh_env", [], None)
 
 
 def _load() -> C.CDLL:
@@ -126,3 +128,9 @@ def check(status: int, where: str) -> None:
     if status != OK:
         detail = LIB.b2r_last_error_string().decode() or LIB.b2r_status_string(status).decode()
         raise B2RError(status, where, detail)
+
+
+def refresh_env() -> None:
+    """Makes the library re-read its B2R_* tuning variables (it caches them: a getenv per launch costs microseconds).
+    Call after changing such a variable at run time (os.environ[...] = ...)."""
+    LIB.b2r_refresh_env()

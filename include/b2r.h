@@ -143,9 +143,14 @@ b2r_status_t b2r_reduce_local_noalloc(const void* in, void* out, uint64_t count,
 b2r_status_t b2r_dot_local(const void* a, const void* b, void* out, uint64_t count, b2r_dtype_t dtype,
                            b2r_workspace_t ws, void* stream);
 
-/* The launch geometry the dispatcher would pick (for logging / tests). */
+/* The launch geometry the dispatcher would pick (for logging / tests). Re-reads the B2R_* geometry variables first. */
 b2r_status_t b2r_plan_local(uint64_t count, b2r_dtype_t dtype, b2r_op_t op, int device, const b2r_launch_cfg_t* hint,
                             b2r_launch_cfg_t* chosen);
+
+/* The single-GPU launch path reads B2R_VARIANT / _THREADS / _CTAS_PER_SM / _CLUSTER / _UNROLL / _STAGES / _PDL once, at the
+ * first launch (seven getenv calls cost 2-3 us per launch, a third of a 64 MiB reduction). A program that changes them at
+ * run time calls this (or b2r_plan_local) afterwards. */
+void b2r_refresh_env(void);
 
 /* In-kernel phase stamps (vendored `clock` sample analogue, clock_kernel.cu:18-54). When enabled every CTA
  * records %globaltimer at start / after streaming loop / after block+cluster combine / at exit. */

@@ -13,6 +13,7 @@
 #include "../comm/comm.h"
 #include "../core/reduce_internal.h"
 #include "../util/check.h"
+#include "../util/env.h"
 #include "../util/nvtx.h"
 #include "coll_kernels.cuh"
 
@@ -35,11 +36,6 @@ struct PendingCall {
 };
 
 namespace {
-
-int env_int(const char* name, int dflt) {
-  const char* v = getenv(name);
-  return (v && *v) ? atoi(v) : dflt;
-}
 
 using CollKernel = void (*)(const CollLaunch);
 
@@ -107,7 +103,7 @@ Shape coll_shape(const b2r_comm* c, int kind, uint64_t bytes, int nvirtual) {
     cap = 128;
     per_cta = 65536;
   }
-  const int et = env_int("B2R_COLL_THREADS", 0), eu = env_int("B2R_COLL_UNROLL", 0), ec = env_int("B2R_COLL_CTAS", 0);
+  const int et = B2R_ENV_INT("B2R_COLL_THREADS", 0), eu = B2R_ENV_INT("B2R_COLL_UNROLL", 0), ec = B2R_ENV_INT("B2R_COLL_CTAS", 0);
   if (et >= 64 && et <= 512) s.threads = et - et % 32;
   if (eu == 4 || eu == 8) s.unroll = eu;
   if (ec > 0) cap = ec;
@@ -125,12 +121,44 @@ bool nvls_supported(b2r_dtype_t dtype, b2r_op_t op) {
   return true;  // bf16x2 add/min/max, 32-bit integer add/min/max
 }
 
+// What AUTO resolves to, on cached environment values (the public b2r_select_algo below refreshes them first).
+b2r_algo_t select_algo_cached(int is_allreduce, uint64_t bytes, b2r_dtype_t dtype, b2r_op_t op, int nranks, int has_multicast) {
+  if (nranks <= 1) return B2R_ALGO_ONESHOT;
+  const int forced = B2R_ENV_INT("B2R_ALGO", 0);
+  // the experimental LL path only ever runs when asked for, and only for messages that fit its slots (and are staged-free:
+  // run_collective checks the 16-byte alignment); everything else falls through to the normal choice
+  if (forced == B2R_ALGO_LL && nranks <= B2R_MAX_RANKS && bytes <= ll_max_msg_bytes(nranks)) return B2R_ALGO_LL;
+  if (forced >= B2R_ALGO_ONESHOT && forced <= B2R_ALGO_PUSH) return (b2r_algo_t)forced;
+  if (forced == B2R_ALGO_RING && !is_allreduce) return B2R_ALGO_RING;
+  // Switches for the paths that have not been measured at 8 GPUs yet; both are off unless the variable is set, so that the
+  // crossovers found by `scripts/run_round2_reduce.sh` can be tried (and then made the default) without a rebuild:
+  //   B2R_AUTO_LL_MAX_BYTES=n   messages of at most n bytes take the LL path (capped by what its slots hold)
+  //   B2R_AUTO_RING_MIN_MB=m    reduce-to-root of at least m MiB takes the store-forwarding ring
+  const uint64_t auto_ll = (uint64_t)std::max(0, B2R_ENV_INT("B2R_AUTO_LL_MAX_BYTES", 0));
+  if (auto_ll && nranks <= B2R_MAX_RANKS && bytes <= std::min<uint64_t>(auto_ll, ll_max_msg_bytes(nranks))) return B2R_ALGO_LL;
+  const uint64_t auto_ring = (uint64_t)std::max(0, B2R_ENV_INT("B2R_AUTO_RING_MIN_MB", 0));
+  if (auto_ring && !is_allreduce && nranks > 2 && bytes >= (auto_ring << 20)) return B2R_ALGO_RING;
+  // NVLS moves (1 + 1/P) messages per GPU against two-shot's 2(P-1)/P and needs one switch round trip for any size:
+  // from 4 GPUs up it wins at EVERY size for the types with 8/16-byte multimem forms (fp32 add, bf16, fp64 add);
+  // at 2 GPUs it loses to the P2P paths (measured). 32-bit integer multimem ops move 4 bytes per instruction and
+  // fp32/fp64 min/max have no multimem form: those stay on P2P.
+  const bool nvls_ok = has_multicast && nranks >= 4 && nvls_supported(dtype, op) && dtype != B2R_INT32 && !B2R_ENV_INT("B2R_DISABLE_NVLS", 0);
+  if (nvls_ok) return B2R_ALGO_NVLS;
+  // Two GPUs, reduce: the root simply pulls the peer's message — one message of ingress, 632 GB/s at 64 MiB, better than
+  // two-shot (481) and the ring (567) there.
+  if (!is_allreduce && nranks == 2) return B2R_ALGO_ONESHOT;
+  // One-shot reads the WHOLE message from every peer: fine for two GPUs or tiny messages, hopeless beyond.
+  const uint64_t oneshot_max = (uint64_t)std::max(0, B2R_ENV_INT("B2R_ONESHOT_MAX_KB", nranks <= 2 ? 512 : 16)) << 10;
+  if (bytes <= oneshot_max) return B2R_ALGO_ONESHOT;
+  return B2R_ALGO_TWOSHOT;
+}
+
 // B2R_WEAK_DATA=1: switch the payload accesses of the collective kernels to weak loads/stores (see coll_kernels.cuh). The
 // constant lives per device; it is written once per device before the first collective launched there.
 b2r_status_t apply_data_flavour(int device) {
   static std::mutex mu;
   static bool done[64] = {false};
-  const int weak = env_int("B2R_WEAK_DATA", 0) ? 1 : 0;
+  const int weak = B2R_ENV_INT("B2R_WEAK_DATA", 0) ? 1 : 0;
   if (!weak || device < 0 || device >= 64) return B2R_OK;
   std::lock_guard<std::mutex> lk(mu);
   if (done[device]) return B2R_OK;
@@ -177,7 +205,7 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
   B2R_CHECK(apply_data_flavour(c0->device));
 
   const uint64_t total_bytes = count * esz;
-  if (algo == B2R_ALGO_AUTO) algo = b2r_select_algo(is_all ? 1 : 0, total_bytes, dtype, op, P, c0->has_mc ? 1 : 0);
+  if (algo == B2R_ALGO_AUTO) algo = select_algo_cached(is_all ? 1 : 0, total_bytes, dtype, op, P, c0->has_mc ? 1 : 0);
   if (algo == B2R_ALGO_NVLS) {
     if (!c0->has_mc) return fail(B2R_ERR_UNSUPPORTED, "NVLS requested but this communicator has no multicast mapping");
     if (!nvls_supported(dtype, op)) return fail(B2R_ERR_UNSUPPORTED, "NVLS has no %s %s instruction", b2r_dtype_name(dtype), b2r_op_name(op));
@@ -186,11 +214,11 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
              : algo == B2R_ALGO_PUSH ? kCollPush : algo == B2R_ALGO_RING ? kCollRing : algo == B2R_ALGO_LL ? kCollLL : kCollNvls;
   if (kind == kCollRing && is_all) {
     // the ring allreduce (P chains + all-gather by stores) exists but has not run on hardware yet: opt-in only
-    if (!env_int("B2R_EXPERIMENTAL", 0)) return fail(B2R_ERR_UNSUPPORTED, "the ring algorithm implements reduce-to-root only");
+    if (!B2R_ENV_INT("B2R_EXPERIMENTAL", 0)) return fail(B2R_ERR_UNSUPPORTED, "the ring algorithm implements reduce-to-root only");
     kind = kCollRingAll;
   }
   // the pipelined ring (waiter / data / signal warps) replaces ring_body only when asked for: not yet run on hardware
-  if (kind == kCollRing && env_int("B2R_RING_V2", 0)) kind = kCollRing2;
+  if (kind == kCollRing && B2R_ENV_INT("B2R_RING_V2", 0)) kind = kCollRing2;
   if (kind == kCollLL) {
     // LL never touches a peer's send/recv buffer: any device pointer works, nothing is chunked, and only a buffer that is not
     // 16-byte aligned is bounced through this rank's own staging (a purely local decision: ranks need not agree on it)
@@ -275,8 +303,8 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
       // Large messages use big steps (default 8 sub-blocks = 512 KiB with 512 threads) to amortise the per-step fence.
       if (kind == kCollRing2) threads = std::max(threads, 96);  // waiter warp + signal warp + at least one data warp
       const uint64_t sub_bytes = (uint64_t)(kind == kCollRing2 ? threads - 64 : threads) * 8 * 16;
-      int subs = std::max(1, env_int("B2R_RING_SUBBLOCKS", 8));
-      int cap = std::max(1, env_int("B2R_RING_CTAS", 32));
+      int subs = std::max(1, B2R_ENV_INT("B2R_RING_SUBBLOCKS", 8));
+      int cap = std::max(1, B2R_ENV_INT("B2R_RING_CTAS", 32));
       if (n > 1) cap = std::max(1, std::min(cap, c0->sm_count / n));
       while (subs > 1 && bytes < (uint64_t)cap * sub_bytes * subs * 2) subs /= 2;  // small message: keep all CTAs busy
       const uint64_t step_bytes = sub_bytes * subs;
@@ -297,7 +325,7 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
     if (kind == kCollPush) {
       // staging ring in the work region: depth x P sources x ctas blocks of (threads x 4) vectors; at least 2 deep
       const uint64_t block_bytes = (uint64_t)threads * 4 * 16;
-      ctas = std::min(ctas, std::max(1, env_int("B2R_PUSH_CTAS", 128)));
+      ctas = std::min(ctas, std::max(1, B2R_ENV_INT("B2R_PUSH_CTAS", 128)));
       ctas = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)ctas, c0->stage_bytes / (2ull * P * block_bytes)));
       const int depth = (int)std::min<uint64_t>(8, c0->stage_bytes / ((uint64_t)P * ctas * block_bytes));
       for (int i = 0; i < n; ++i) L.a[n == 1 ? 0 : rc[i].c->rank].ring_depth = depth;
@@ -453,35 +481,10 @@ uint64_t b2r_ll_max_bytes(int nranks) { return (nranks >= 2 && nranks <= B2R_MAX
 
 // Size thresholds measured on 8x B200 (profiles/collectives_8gpu.md). One-shot costs one NVLink round trip but every
 // rank pulls the WHOLE message from every peer; two-shot / NVLS move 1/P of it per rank.
+// Public, for tests and harnesses: looks at the environment as it is now (the launch path uses cached values, util/env.h).
 b2r_algo_t b2r_select_algo(int is_allreduce, uint64_t bytes, b2r_dtype_t dtype, b2r_op_t op, int nranks, int has_multicast) {
-  if (nranks <= 1) return B2R_ALGO_ONESHOT;
-  const int forced = env_int("B2R_ALGO", 0);
-  // the experimental LL path only ever runs when asked for, and only for messages that fit its slots (and are staged-free:
-  // run_collective checks the 16-byte alignment); everything else falls through to the normal choice
-  if (forced == B2R_ALGO_LL && nranks <= B2R_MAX_RANKS && bytes <= ll_max_msg_bytes(nranks)) return B2R_ALGO_LL;
-  if (forced >= B2R_ALGO_ONESHOT && forced <= B2R_ALGO_PUSH) return (b2r_algo_t)forced;
-  if (forced == B2R_ALGO_RING && !is_allreduce) return B2R_ALGO_RING;
-  // Switches for the paths that have not been measured at 8 GPUs yet; both are off unless the variable is set, so that the
-  // crossovers found by `scripts/run_round2_reduce.sh` can be tried (and then made the default) without a rebuild:
-  //   B2R_AUTO_LL_MAX_BYTES=n   messages of at most n bytes take the LL path (capped by what its slots hold)
-  //   B2R_AUTO_RING_MIN_MB=m    reduce-to-root of at least m MiB takes the store-forwarding ring
-  const uint64_t auto_ll = (uint64_t)std::max(0, env_int("B2R_AUTO_LL_MAX_BYTES", 0));
-  if (auto_ll && nranks <= B2R_MAX_RANKS && bytes <= std::min<uint64_t>(auto_ll, ll_max_msg_bytes(nranks))) return B2R_ALGO_LL;
-  const uint64_t auto_ring = (uint64_t)std::max(0, env_int("B2R_AUTO_RING_MIN_MB", 0));
-  if (auto_ring && !is_allreduce && nranks > 2 && bytes >= (auto_ring << 20)) return B2R_ALGO_RING;
-  // NVLS moves (1 + 1/P) messages per GPU against two-shot's 2(P-1)/P and needs one switch round trip for any size:
-  // from 4 GPUs up it wins at EVERY size for the types with 8/16-byte multimem forms (fp32 add, bf16, fp64 add);
-  // at 2 GPUs it loses to the P2P paths (measured). 32-bit integer multimem ops move 4 bytes per instruction and
-  // fp32/fp64 min/max have no multimem form: those stay on P2P.
-  const bool nvls_ok = has_multicast && nranks >= 4 && nvls_supported(dtype, op) && dtype != B2R_INT32 && !env_int("B2R_DISABLE_NVLS", 0);
-  if (nvls_ok) return B2R_ALGO_NVLS;
-  // Two GPUs, reduce: the root simply pulls the peer's message — one message of ingress, 632 GB/s at 64 MiB, better than
-  // two-shot (481) and the ring (567) there.
-  if (!is_allreduce && nranks == 2) return B2R_ALGO_ONESHOT;
-  // One-shot reads the WHOLE message from every peer: fine for two GPUs or tiny messages, hopeless beyond.
-  const uint64_t oneshot_max = (uint64_t)std::max(0, env_int("B2R_ONESHOT_MAX_KB", nranks <= 2 ? 512 : 16)) << 10;
-  if (bytes <= oneshot_max) return B2R_ALGO_ONESHOT;
-  return B2R_ALGO_TWOSHOT;
+  env_refresh();
+  return select_algo_cached(is_allreduce, bytes, dtype, op, nranks, has_multicast);
 }
 
 b2r_status_t b2r_reduce_ex(const void* sendbuf, void* recvbuf, uint64_t count, b2r_dtype_t dtype, b2r_op_t op, int root, b2r_comm_t comm,

@@ -10,6 +10,7 @@
 #include <vector>
 
 #include "../util/check.h"
+#include "../util/env.h"
 #include "../util/nvtx.h"
 #include "b2r.h"
 #include "reduce_kernels.cuh"
@@ -19,12 +20,6 @@
 namespace b2r {
 
 namespace {
-
-int env_int(const char* name, int dflt) {
-  const char* v = getenv(name);
-  if (!v || !*v) return dflt;
-  return atoi(v);
-}
 
 struct Tuned {
   int variant, threads, ctas_per_sm, cluster, unroll, stages, tile_bytes;
@@ -69,7 +64,7 @@ Tuned tuned_defaults(b2r_dtype_t dtype, b2r_op_t op, uint64_t bytes, int pdl) {
 b2r_status_t plan_local(uint64_t count, b2r_dtype_t dtype, b2r_op_t op, int sm_count, const b2r_launch_cfg_t* hint,
                         LaunchGeom* g, int* stages, int* tile_vecs) {
   const uint64_t bytes = count * b2r_dtype_size(dtype);
-  int pdl = env_int("B2R_PDL", 0);
+  int pdl = B2R_ENV_INT("B2R_PDL", 0);  // cached: see util/env.h
   if (hint && hint->pdl) pdl = hint->pdl > 0;
   Tuned t = tuned_defaults(dtype, op, bytes, pdl);
   if (hint && hint->variant && hint->variant != t.variant) {
@@ -77,12 +72,12 @@ b2r_status_t plan_local(uint64_t count, b2r_dtype_t dtype, b2r_op_t op, int sm_c
     if (hint->variant == B2R_VARIANT_TMA) { t.threads = pdl ? 288 : 160; t.ctas_per_sm = pdl ? 1 : 3; t.stages = 4; }
     else { t.threads = 512; t.ctas_per_sm = pdl ? 1 : 4; }
   }
-  t.variant = env_int("B2R_VARIANT", t.variant);
-  t.threads = env_int("B2R_THREADS", t.threads);
-  t.ctas_per_sm = env_int("B2R_CTAS_PER_SM", t.ctas_per_sm);
-  t.cluster = env_int("B2R_CLUSTER", t.cluster);
-  t.unroll = env_int("B2R_UNROLL", t.unroll);
-  t.stages = env_int("B2R_STAGES", t.stages);
+  t.variant = B2R_ENV_INT("B2R_VARIANT", t.variant);
+  t.threads = B2R_ENV_INT("B2R_THREADS", t.threads);
+  t.ctas_per_sm = B2R_ENV_INT("B2R_CTAS_PER_SM", t.ctas_per_sm);
+  t.cluster = B2R_ENV_INT("B2R_CLUSTER", t.cluster);
+  t.unroll = B2R_ENV_INT("B2R_UNROLL", t.unroll);
+  t.stages = B2R_ENV_INT("B2R_STAGES", t.stages);
 
   int variant = t.variant, threads = t.threads, cluster = t.cluster, unroll = t.unroll;
   int st = t.stages, tile_bytes = t.tile_bytes;
@@ -307,10 +302,13 @@ b2r_status_t b2r_reduce_local_ex(const void* in, void* out, uint64_t count, b2r_
   return reduce_local_impl(in, out, count, dtype, op, ws, (cudaStream_t)stream, cfg, 0, nullptr);
 }
 
+void b2r_refresh_env(void) { env_refresh(); }
+
 b2r_status_t b2r_plan_local(uint64_t count, b2r_dtype_t dtype, b2r_op_t op, int device, const b2r_launch_cfg_t* hint,
                             b2r_launch_cfg_t* chosen) {
   B2R_REQUIRE(chosen != nullptr, "b2r_plan_local: chosen is NULL");
   B2R_REQUIRE(dtype >= B2R_INT32 && dtype <= B2R_BFLOAT16, "b2r_plan_local: bad dtype %d", (int)dtype);
+  env_refresh();  // the introspection call always looks at the environment as it is NOW (and the launch path follows)
   int sm = 148;  // B200; used when no device is present (planning is a pure function of the SM count)
   if (device >= 0) {
     int v = 0;
@@ -370,7 +368,7 @@ b2r_status_t b2r_reduce_from_host(const void* host_in, void* out_host, uint64_t 
   B2R_CUDA_CHECK(cudaSetDevice(ws->device));
   struct Restore { int d; ~Restore() { cudaSetDevice(d); } } restore{prev};
 
-  const uint64_t chunk_bytes = (uint64_t)std::max(1, env_int("B2R_H2D_CHUNK_MB", 8)) << 20;
+  const uint64_t chunk_bytes = (uint64_t)std::max(1, B2R_ENV_INT("B2R_H2D_CHUNK_MB", 8)) << 20;
   const uint64_t chunk_elems = chunk_bytes / esz;
   const uint64_t nchunks = count == 0 ? 0 : (count + chunk_elems - 1) / chunk_elems;
   B2R_REQUIRE(nchunks <= kMaxChunks, "b2r_reduce_from_host: %llu chunks > %d; raise B2R_H2D_CHUNK_MB",

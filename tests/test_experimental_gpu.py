@@ -23,6 +23,13 @@ import cuda_mpi_reductions_b200 as b2r
 from cuda_mpi_reductions_b200 import _lib
 from cuda_mpi_reductions_b200.parallel import Communicator, host_reduce_threads
 
+@pytest.fixture(autouse=True)
+def _reread_environment_afterwards():
+    """Tests here change B2R_* variables; the library caches them, so make it look again once monkeypatch has restored them."""
+    yield
+    b2r.refresh_env()
+
+
 pytestmark = [
     pytest.mark.gpu,
     pytest.mark.skipif(os.environ.get("B2R_TEST_EXPERIMENTAL", "0") in ("", "0"), reason="experimental path: set B2R_TEST_EXPERIMENTAL=1"),
@@ -151,6 +158,10 @@ def test_ll_rejects_what_it_cannot_carry(comms):
 @pytest.fixture()
 def experimental(monkeypatch):
     monkeypatch.setenv("B2R_EXPERIMENTAL", "1")
+    b2r.refresh_env()  # the library caches its B2R_* lookups
+    yield
+    monkeypatch.delenv("B2R_EXPERIMENTAL")
+    b2r.refresh_env()
 
 
 @pytest.mark.parametrize("dtype", DTYPES)
@@ -199,6 +210,7 @@ def test_pipelined_ring_is_bit_identical_to_the_ring(comms, monkeypatch, shape):
     monkeypatch.setenv("B2R_RING_V2", "1")
     monkeypatch.setenv("B2R_COLL_THREADS", str(threads))
     monkeypatch.setenv("B2R_RING_SUBBLOCKS", str(subs))
+    b2r.refresh_env()
     P = len(comms)
     for dtype in (torch.int32, torch.float64, torch.bfloat16):
         for count in (1, 1000, 65537, (1 << 21) + 9, (5 << 20) + 3):
@@ -214,6 +226,7 @@ def test_pipelined_ring_is_bit_identical_to_the_ring(comms, monkeypatch, shape):
 
 def test_pipelined_ring_back_to_back_with_other_algorithms(comms, monkeypatch):
     monkeypatch.setenv("B2R_RING_V2", "1")
+    b2r.refresh_env()
     P = len(comms)
     count = 200003
     xs_h = [b2r.fill_host(count, torch.int32, seed=5 + r, mode="full") for r in range(P)]

@@ -85,3 +85,28 @@ def test_numa_binding_helpers(tmp_path, monkeypatch):
     monkeypatch.delenv("B2R_NUMA_BIND")
     assert numa.bind_to_gpu_node(0, apply=False)["bound"] in (True, False)  # real sysfs, with or without a GPU: must not raise
     assert sorted(os.sched_getaffinity(0)) == allowed
+
+
+def test_cached_environment_lookups(tmp_path, monkeypatch):
+    """src/util/env.h: B2R_* variables are read once per call site and again after b2r_refresh_env() — first as a C++ unit
+    test of the header, then through the library (the introspection calls refresh on their own)."""
+    import shutil
+    import subprocess
+
+    import torch
+
+    import cuda_mpi_reductions_b200 as b2r
+
+    repo = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    gxx = shutil.which("g++")
+    if gxx:
+        exe = tmp_path / "env_cache_test"
+        subprocess.run([gxx, "-std=c++17", "-O1", "-I", os.path.join(repo, "src"), os.path.join(repo, "tests/cpp/env_cache_test.cpp"), "-o", str(exe)],
+                       check=True)
+        res = subprocess.run([str(exe)], capture_output=True, text=True)
+        assert res.returncode == 0 and res.stdout.strip() == "OK", res.stderr
+    monkeypatch.setenv("B2R_THREADS", "96")
+    assert b2r.plan(1 << 24, torch.int32)["threads"] == 96  # plan() looks at the environment as it is now
+    monkeypatch.delenv("B2R_THREADS")
+    b2r.refresh_env()
+    assert b2r.plan(1 << 24, torch.int32)["threads"] != 96
