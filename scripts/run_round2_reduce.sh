@@ -20,6 +20,8 @@ timeout 120 bin/bench_collective --gpus=$N --tune=ring --coll=allreduce --type=I
 timeout 120 bin/bench_collective --gpus=$N --tune=push --coll=reduce --bytes=268435456 --iters=8 > $OUT/tune_push_256m.txt 2>&1
 timeout 120 bin/bench_collective --gpus=$N --sweep --types=FLOAT,INT --colls=reduce --algos=ring,nvls,twoshot --min-bytes=1048576 --max-bytes=1073741824 --factor=4 --check > $OUT/reduce_algos.txt 2>&1
 timeout 120 bin/bench_collective --gpus=$N --sweep --types=INT --ops=SUM,MIN --colls=allreduce --algos=ring,twoshot --min-bytes=1048576 --max-bytes=1073741824 --factor=4 --check > $OUT/allreduce_ring.txt 2>&1
+# 32-bit integer multimem ops move 4 bytes per instruction: never measured against the P2P two-shot at scale
+timeout 120 bin/bench_collective --gpus=$N --sweep --types=INT --ops=SUM,MAX --colls=reduce,allreduce --algos=nvls,twoshot --min-bytes=65536 --max-bytes=268435456 --factor=16 --check > $OUT/int_nvls.txt 2>&1
 timeout 120 bin/bench_collective --gpus=$N --sweep --types=FLOAT,INT --colls=reduce,allreduce --algos=auto,ll --min-bytes=1024 --max-bytes=16384 --factor=2 --check > $OUT/small_ll.txt 2>&1
 timeout 100 bin/nccl_bench --gpus=$N --sweep --types=FLOAT,INT --colls=reduce,allreduce --min-bytes=1024 --max-bytes=16384 --factor=2 > $OUT/nccl_small.txt 2>/dev/null
 timeout 100 bin/nccl_bench --gpus=$N --sweep --types=FLOAT,INT --colls=reduce,allreduce --min-bytes=1048576 --max-bytes=1073741824 --factor=4 > $OUT/nccl_large.txt 2>/dev/null
@@ -28,3 +30,4 @@ sort -k5 -n -r $OUT/tune_ring2_256m.txt | head -5
 sort -k5 -n -r $OUT/tune_ringall_256m.txt | head -3
 grep -E "ring|FAIL|PASS" $OUT/reduce_algos.txt $OUT/allreduce_ring.txt | tail -24
 grep -E " ll |FAIL|PASS" $OUT/small_ll.txt | tail -24
+grep -E "nvls|twoshot|FAIL|PASS" $OUT/int_nvls.txt | tail -16
