@@ -1,4 +1,4 @@
-"""GPU, opt-in: the EXPERIMENTAL collective paths of src/coll/coll_kernels.cuh — the LL small-message path (`algo="ll"`,
+"""GPU, opt-in: the EXPERIMENTAL collective paths of src/coll/coll_experimental.cuh — the LL small-message path (`algo="ll"`,
 `ll_body`) and the ring allreduce (`algo="ring"` on allreduce with B2R_EXPERIMENTAL=1, `ringall_body`).
 
 Both kernels were written after the round's GPU budget was spent, so they have been compiled and inspected (SASS,

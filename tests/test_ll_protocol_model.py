@@ -1,4 +1,4 @@
-"""CPU-only: an executable model of the LL small-message protocol (`ll_body`, src/coll/coll_kernels.cuh).
+"""CPU-only: an executable model of the LL small-message protocol (`ll_body`, src/coll/coll_experimental.cuh).
 
 The device kernel could not be run when it was written, so its protocol — flag-in-data packets, two slot parities, the
 "acknowledge every call to every peer, wait for n-2 before reusing a parity" rule, no barrier at either end — is
