@@ -31,3 +31,5 @@ sort -k5 -n -r $OUT/tune_ringall_256m.txt | head -3
 grep -E "ring|FAIL|PASS" $OUT/reduce_algos.txt $OUT/allreduce_ring.txt | tail -24
 grep -E " ll |FAIL|PASS" $OUT/small_ll.txt | tail -24
 grep -E "nvls|twoshot|FAIL|PASS" $OUT/int_nvls.txt | tail -16
+# per-size table, best algorithm of ours vs NCCL, and the crossover points for b2r_select_algo
+python scripts/compare_sweeps.py $OUT/*.txt --md $OUT/comparison.md | tail -40

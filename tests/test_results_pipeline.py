@@ -68,3 +68,33 @@ def test_minimpi_aborts_cleanly_when_not_launched():
     env = {k: v for k, v in os.environ.items() if not k.startswith("MINIMPI_")}
     res = subprocess.run([exe], capture_output=True, text=True, timeout=30, env=env)
     assert res.returncode != 0 and "b2r_mpirun" in res.stderr
+
+
+def test_compare_sweeps_tool(tmp_path):
+    """scripts/compare_sweeps.py: parses both tools' sweep rows, keeps the fastest duplicate, ranks ours against NCCL and
+    reports the size ranges each algorithm wins."""
+    import subprocess
+    import sys
+
+    repo = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    ours = tmp_path / "ours.txt"
+    ours.write_text(
+        "# coll      dtype  op   algo              bytes         us algbw GB/s busbw GB/s\n"
+        "  reduce    FLOAT  SUM  ll                 1024       6.00       0.17       0.17\n"
+        "  reduce    FLOAT  SUM  nvls               1024      12.50       0.08       0.08\n"
+        "  reduce    FLOAT  SUM  nvls            1048576      17.80      58.90      58.90\n"
+        "  reduce    FLOAT  SUM  ring            1048576      30.00      34.95      34.95\n"
+        "  reduce    FLOAT  SUM  nvls          268435456     522.00     514.24     514.24\n"
+        "  reduce    FLOAT  SUM  ring          268435456     430.00     624.27     624.27\n"
+        "  reduce    FLOAT  SUM  ring          268435456     440.00     610.08     610.08\n"
+        "PASSED\n")
+    nccl = tmp_path / "nccl.txt"
+    nccl.write_text("  reduce    FLOAT  SUM  nccl               1024       8.30       0.12       0.12\n"
+                    "  reduce    FLOAT  SUM  nccl          268435456     445.70     602.28     602.28\n")
+    md = tmp_path / "t.md"
+    res = subprocess.run([sys.executable, os.path.join(repo, "scripts/compare_sweeps.py"), str(ours), str(nccl), "--md", str(md)],
+                         capture_output=True, text=True)
+    assert res.returncode == 0, res.stderr
+    out = res.stdout
+    assert "1 KiB: ll (>= 1.38x NCCL)" in out and "1 MiB: nvls" in out and "256 MiB: ring (>= 1.04x NCCL)" in out
+    assert md.read_text().count("\n") == 5  # header, rule, three sizes
