@@ -40,7 +40,9 @@ def parse_args():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=2000)
     ap.add_argument("--warmup", type=int, default=50)
-    ap.add_argument("--impl", default="b2r", choices=["b2r", "reference"])
+    ap.add_argument("--impl", default="b2r", choices=["b2r", "reference", "torch_nccl"],
+                    help="b2r: this library; reference: the unmodified SDK sample; torch_nccl: what a PyTorch user would write (torch reduction "
+                         "kernel + NCCL reduce of the scalar) — the library baseline of BASELINE.json config 4")
     ap.add_argument("--e2e-steps", type=int, default=0, help="steps of the end-to-end arm (default min(steps, 40))")
     ap.add_argument("--dtype", default="int32", choices=["int32", "float32", "float64", "bfloat16"])
     ap.add_argument("--op", default="sum", choices=["sum", "min", "max"])
@@ -296,6 +298,82 @@ def run_b2r(args) -> None:
         dist.destroy_process_group()
 
 
+# --------------------------------------------------------------------------------------------- library baseline arm
+def run_torch_nccl(args) -> None:
+    """Same metric, same shapes, same timing rules as run_b2r, done with libraries only: torch's own reduction kernel on
+    every GPU, then (N > 1) an NCCL reduce of the per-GPU scalars to rank 0. None of this repository's kernels run here."""
+    import torch
+
+    from cuda_mpi_reductions_b200.utils import rotating_copies
+
+    rank, local_rank, world = dist_env()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (run it through gpurun)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    dtype = getattr(torch, args.dtype)
+    nbytes = args.n * torch.empty((), dtype=dtype).element_size()
+    steps, warmup = args.steps, max(args.warmup, 3)
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.init_process_group("nccl", device_id=dev)
+    copies = rotating_copies(nbytes)
+    gen = torch.Generator(device=dev).manual_seed(1000 * rank)
+    big = torch.randint(0, 256, (copies * args.n,), dtype=torch.int32, device=dev, generator=gen).to(dtype)
+    inputs = [big[c * args.n:(c + 1) * args.n] for c in range(copies)]
+    if args.op == "sum":  # accumulate like the library does: wider than the input for int32 / bf16
+        acc_dtype = torch.int64 if dtype == torch.int32 else (torch.float32 if dtype == torch.bfloat16 else dtype)
+        out = torch.empty((), dtype=acc_dtype, device=dev)
+
+        def local(x):
+            torch.sum(x, dim=0, dtype=acc_dtype, out=out)
+    else:
+        out = torch.empty((), dtype=dtype, device=dev)
+        pick = torch.amin if args.op == "min" else torch.amax
+
+        def local(x):
+            pick(x, dim=0, out=out)
+    red_op = None
+    if world > 1:
+        red_op = {"sum": dist.ReduceOp.SUM, "min": dist.ReduceOp.MIN, "max": dist.ReduceOp.MAX}[args.op]
+
+    def step(i):
+        local(inputs[i % copies])
+        if world > 1:
+            dist.reduce(out, dst=0, op=red_op)
+
+    for i in range(warmup):
+        step(i)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for i in range(steps):
+        step(i)
+    ev1.record()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    ms = ev0.elapsed_time(ev1)
+    if world > 1:
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = t.item()
+    if rank == 0:
+        total_bytes = world * nbytes
+        print(json.dumps({
+            "impl": "torch_nccl", "metric": METRIC, "value": total_bytes * steps / (ms * 1e-3) * 1e-9, "unit": "GB/s", "n_gpus": world,
+            "steps": steps, "warmup": warmup, "ms_per_step": ms / steps, "higher_is_better": True, "scaling": "weak", "dtype": args.dtype,
+            "data": "synthetic (torch.randint 0..255)",
+            "config": {"model": "torch reduction kernel per GPU + ncclReduce of the scalars to rank 0", "elements_per_gpu": args.n, "op": args.op,
+                       "cache_control": f"{copies} rotating inputs of {nbytes >> 20} MiB"},
+        }), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     args = parse_args()
     if args.gpus > 1 and "WORLD_SIZE" not in os.environ:
@@ -306,6 +384,8 @@ def main():
         raise SystemExit(subprocess.call(cmd))
     if args.impl == "reference":
         run_reference(args)
+    elif args.impl == "torch_nccl":
+        run_torch_nccl(args)
     else:
         run_b2r(args)
 

@@ -31,5 +31,10 @@ sort -k5 -n -r $OUT/tune_ringall_256m.txt | head -3
 grep -E "ring|FAIL|PASS" $OUT/reduce_algos.txt $OUT/allreduce_ring.txt | tail -24
 grep -E " ll |FAIL|PASS" $OUT/small_ll.txt | tail -24
 grep -E "nvls|twoshot|FAIL|PASS" $OUT/int_nvls.txt | tail -16
+# BASELINE.json config 4: 1 GiB fp64 sharded over the GPUs, fused local reduce + NVLink combine vs torch reduction + ncclReduce of the scalars
+PER=$((134217728 / N))
+python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29531 bench.py --gpus $N --dtype float64 --n $PER --steps 300 --warmup 20 > $OUT/config4_b2r.json 2>$OUT/config4_b2r.err
+python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29532 bench.py --gpus $N --dtype float64 --n $PER --steps 300 --warmup 20 --impl torch_nccl > $OUT/config4_torch_nccl.json 2>$OUT/config4_torch_nccl.err
+tail -c 600 $OUT/config4_b2r.json; tail -c 400 $OUT/config4_torch_nccl.json
 # per-size table, best algorithm of ours vs NCCL, and the crossover points for b2r_select_algo
 python scripts/compare_sweeps.py $OUT/*.txt --md $OUT/comparison.md | tail -40
