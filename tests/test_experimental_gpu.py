@@ -240,3 +240,31 @@ def test_pipelined_ring_back_to_back_with_other_algorithms(comms, monkeypatch):
             keep = outs
     Communicator.group_check(comms)
     assert torch.equal(keep[0].cpu(), want)
+
+
+# ------------------------------------------------------------------------------------------------ not experimental code, but tests not yet run
+def test_symmetric_only_mode_and_max_ctas():
+    """`symmetric_only=True` (nothing is ever staged: one launch per message, buffers must live in the heap) and `max_ctas`
+    were exercised by bench_collective at 8 GPUs in round 1 but had no unit test; written without a GPU at hand, hence here."""
+    cs = Communicator.loopback(4, device=0, heap_bytes=64 << 20, symmetric_only=True, max_ctas=8)
+    try:
+        count = (3 << 20) + 5
+        bufs = [c.symm_empty(count, torch.float32) for c in cs]
+        outs = [c.symm_empty(count, torch.float32) for c in cs]
+        xs_h = [b2r.fill_host(count, torch.float32, seed=60 + r, mode="signed") for r in range(4)]
+        for bf, x in zip(bufs, xs_h):
+            bf.copy_(x)
+        for algo in ("twoshot", "oneshot", "push"):
+            want = host_reduce_threads(xs_h, "sum", -1, algo)[0]
+            Communicator.group_allreduce(cs, bufs, "sum", algo=algo, outs=outs)
+            Communicator.group_check(cs)
+            for o in outs:
+                assert torch.equal(bits(o.cpu()), bits(want)), algo
+        plain = [x.cuda() for x in xs_h]  # not in the heap: must be refused, not staged
+        with pytest.raises(b2r.B2RError, match="symmetric"):
+            Communicator.group_allreduce(cs, plain, "sum", algo="twoshot")
+        Communicator.group_allreduce(cs, bufs, "max", algo="twoshot", outs=outs)  # still usable afterwards
+        Communicator.group_check(cs)
+    finally:
+        for c in cs:
+            c.close()
