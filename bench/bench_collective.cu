@@ -312,7 +312,11 @@ int main(int argc, char** argv) {
               if (count == 0) continue;
               if (algo == B2R_ALGO_NVLS && !has_mc) continue;
               if (algo == B2R_ALGO_RING && allreduce && !(getenv("B2R_EXPERIMENTAL") && atoi(getenv("B2R_EXPERIMENTAL")))) continue;
-              if (algo == B2R_ALGO_LL && bytes > b2r_ll_max_bytes(P)) continue;
+              if (algo == B2R_ALGO_LL) {
+                uint64_t ll_max = 0;
+                b2r_comm_ll_max_bytes(R[0].comm, &ll_max);
+                if (bytes > ll_max) continue;
+              }
               if (algo == B2R_ALGO_NVLS && (dt == B2R_FLOAT32 || dt == B2R_FLOAT64) && op != B2R_SUM) continue;
               if ((algo == B2R_ALGO_ONESHOT || algo == B2R_ALGO_TREE) && bytes > (64ull << 20)) continue;  // pointless at this size
               if (f.has("check") && bytes <= (256ull << 20)) all_ok = verify(R, allreduce, count, dt, op, root, algo) && all_ok;

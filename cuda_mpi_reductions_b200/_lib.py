@@ -107,6 +107,8 @@ def _declare(lib: C.CDLL) -> None:
             sig(name, args)
     if hasattr(lib, "b2r_ll_max_bytes"):
         sig("b2r_ll_max_bytes", [i], u64)
+    if hasattr(lib, "b2r_comm_ll_max_bytes"):
+        sig("b2r_comm_ll_max_bytes", [vp, C.POINTER(C.c_uint64)])
     if hasattr(lib, "b2r_refresh_env"):
         sig("b2r_refresh_env", [], None)
 

@@ -185,6 +185,13 @@ class Communicator:
         """Synchronises the current stream and raises B2RError(ERR_TIMEOUT) if a cross-GPU wait gave up."""
         _lib.check(_lib.LIB.b2r_comm_check(self._h, self._stream()), "b2r_comm_check")
 
+    @property
+    def ll_max_bytes(self) -> int:
+        """Largest message (bytes per rank) the experimental LL path accepts on this communicator."""
+        n = C.c_uint64()
+        _lib.check(_lib.LIB.b2r_comm_ll_max_bytes(self._h, C.byref(n)), "b2r_comm_ll_max_bytes")
+        return int(n.value)
+
     def select_algo(self, nbytes: int, dtype: torch.dtype, op="sum", allreduce: bool = True) -> str:
         a = _lib.LIB.b2r_select_algo(int(allreduce), nbytes, b2r_dtype(dtype), op_code(op), self.size, int(self.has_multicast))
         return {v: k for k, v in _lib.ALGOS.items()}[a]

@@ -238,6 +238,9 @@ b2r_status_t b2r_barrier(b2r_comm_t comm, void* stream);
 
 /* Largest message (bytes per rank) the LL path accepts on a communicator of `nranks` ranks; 0 if nranks is out of range. */
 uint64_t b2r_ll_max_bytes(int nranks);
+/* The same for an existing communicator: larger when it was created with B2R_LL_BIG_MB=n (n MiB of extra LL slots behind
+ * the user heap, 16 CTAs, up to 256 KiB per rank; experimental like the rest of the LL path). */
+b2r_status_t b2r_comm_ll_max_bytes(b2r_comm_t comm, uint64_t* bytes);
 
 /* Which algorithm AUTO resolves to (pure function; used by tests and the harness). */
 b2r_algo_t b2r_select_algo(int is_allreduce, uint64_t bytes, b2r_dtype_t dtype, b2r_op_t op, int nranks,

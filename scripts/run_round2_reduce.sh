@@ -23,13 +23,14 @@ timeout 120 bin/bench_collective --gpus=$N --sweep --types=INT --ops=SUM,MIN --c
 # 32-bit integer multimem ops move 4 bytes per instruction: never measured against the P2P two-shot at scale
 timeout 120 bin/bench_collective --gpus=$N --sweep --types=INT --ops=SUM,MAX --colls=reduce,allreduce --algos=nvls,twoshot --min-bytes=65536 --max-bytes=268435456 --factor=16 --check > $OUT/int_nvls.txt 2>&1
 timeout 120 bin/bench_collective --gpus=$N --sweep --types=FLOAT,INT --colls=reduce,allreduce --algos=auto,ll --min-bytes=1024 --max-bytes=16384 --factor=2 --check > $OUT/small_ll.txt 2>&1
-timeout 100 bin/nccl_bench --gpus=$N --sweep --types=FLOAT,INT --colls=reduce,allreduce --min-bytes=1024 --max-bytes=16384 --factor=2 > $OUT/nccl_small.txt 2>/dev/null
+B2R_LL_BIG_MB=16 timeout 120 bin/bench_collective --gpus=$N --sweep --types=FLOAT,INT --colls=reduce,allreduce --algos=auto,ll --min-bytes=32768 --max-bytes=262144 --factor=2 --check > $OUT/mid_ll_big.txt 2>&1
+timeout 100 bin/nccl_bench --gpus=$N --sweep --types=FLOAT,INT --colls=reduce,allreduce --min-bytes=1024 --max-bytes=262144 --factor=2 > $OUT/nccl_small.txt 2>/dev/null
 timeout 100 bin/nccl_bench --gpus=$N --sweep --types=FLOAT,INT --colls=reduce,allreduce --min-bytes=1048576 --max-bytes=1073741824 --factor=4 > $OUT/nccl_large.txt 2>/dev/null
 sort -k5 -n -r $OUT/tune_ring_256m.txt | head -5
 sort -k5 -n -r $OUT/tune_ring2_256m.txt | head -5
 sort -k5 -n -r $OUT/tune_ringall_256m.txt | head -3
 grep -E "ring|FAIL|PASS" $OUT/reduce_algos.txt $OUT/allreduce_ring.txt | tail -24
-grep -E " ll |FAIL|PASS" $OUT/small_ll.txt | tail -24
+grep -E " ll |FAIL|PASS" $OUT/small_ll.txt $OUT/mid_ll_big.txt | tail -40
 grep -E "nvls|twoshot|FAIL|PASS" $OUT/int_nvls.txt | tail -16
 # BASELINE.json config 4: 1 GiB fp64 sharded over the GPUs, fused local reduce + NVLink combine vs torch reduction + ncclReduce of the scalars
 PER=$((134217728 / N))

@@ -121,13 +121,21 @@ bool nvls_supported(b2r_dtype_t dtype, b2r_op_t op) {
   return true;  // bf16x2 add/min/max, 32-bit integer add/min/max
 }
 
+// Largest message the LL path can carry on this communicator: the small instance in the control region, or the large one
+// behind the user heap when the communicator was created with B2R_LL_BIG_MB.
+uint64_t ll_limit(const b2r_comm* c) {
+  const uint64_t small = ll_max_msg_bytes(c->nranks);
+  const uint64_t big = c->ll_big_bytes ? ll_big_max_msg_bytes(c->ll_big_bytes, c->nranks) : 0;
+  return std::max(small, big);
+}
+
 // What AUTO resolves to, on cached environment values (the public b2r_select_algo below refreshes them first).
-b2r_algo_t select_algo_cached(int is_allreduce, uint64_t bytes, b2r_dtype_t dtype, b2r_op_t op, int nranks, int has_multicast) {
+b2r_algo_t select_algo_cached(int is_allreduce, uint64_t bytes, b2r_dtype_t dtype, b2r_op_t op, int nranks, int has_multicast, uint64_t ll_max) {
   if (nranks <= 1) return B2R_ALGO_ONESHOT;
   const int forced = B2R_ENV_INT("B2R_ALGO", 0);
   // the experimental LL path only ever runs when asked for, and only for messages that fit its slots (and are staged-free:
   // run_collective checks the 16-byte alignment); everything else falls through to the normal choice
-  if (forced == B2R_ALGO_LL && nranks <= B2R_MAX_RANKS && bytes <= ll_max_msg_bytes(nranks)) return B2R_ALGO_LL;
+  if (forced == B2R_ALGO_LL && nranks <= B2R_MAX_RANKS && bytes <= ll_max) return B2R_ALGO_LL;
   if (forced >= B2R_ALGO_ONESHOT && forced <= B2R_ALGO_PUSH) return (b2r_algo_t)forced;
   if (forced == B2R_ALGO_RING && !is_allreduce) return B2R_ALGO_RING;
   // Switches for the paths that have not been measured at 8 GPUs yet; both are off unless the variable is set, so that the
@@ -135,7 +143,7 @@ b2r_algo_t select_algo_cached(int is_allreduce, uint64_t bytes, b2r_dtype_t dtyp
   //   B2R_AUTO_LL_MAX_BYTES=n   messages of at most n bytes take the LL path (capped by what its slots hold)
   //   B2R_AUTO_RING_MIN_MB=m    reduce-to-root of at least m MiB takes the store-forwarding ring
   const uint64_t auto_ll = (uint64_t)std::max(0, B2R_ENV_INT("B2R_AUTO_LL_MAX_BYTES", 0));
-  if (auto_ll && nranks <= B2R_MAX_RANKS && bytes <= std::min<uint64_t>(auto_ll, ll_max_msg_bytes(nranks))) return B2R_ALGO_LL;
+  if (auto_ll && nranks <= B2R_MAX_RANKS && bytes <= std::min<uint64_t>(auto_ll, ll_max)) return B2R_ALGO_LL;
   const uint64_t auto_ring = (uint64_t)std::max(0, B2R_ENV_INT("B2R_AUTO_RING_MIN_MB", 0));
   if (auto_ring && !is_allreduce && nranks > 2 && bytes >= (auto_ring << 20)) return B2R_ALGO_RING;
   // NVLS moves (1 + 1/P) messages per GPU against two-shot's 2(P-1)/P and needs one switch round trip for any size:
@@ -205,7 +213,7 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
   B2R_CHECK(apply_data_flavour(c0->device));
 
   const uint64_t total_bytes = count * esz;
-  if (algo == B2R_ALGO_AUTO) algo = select_algo_cached(is_all ? 1 : 0, total_bytes, dtype, op, P, c0->has_mc ? 1 : 0);
+  if (algo == B2R_ALGO_AUTO) algo = select_algo_cached(is_all ? 1 : 0, total_bytes, dtype, op, P, c0->has_mc ? 1 : 0, ll_limit(c0));
   if (algo == B2R_ALGO_NVLS) {
     if (!c0->has_mc) return fail(B2R_ERR_UNSUPPORTED, "NVLS requested but this communicator has no multicast mapping");
     if (!nvls_supported(dtype, op)) return fail(B2R_ERR_UNSUPPORTED, "NVLS has no %s %s instruction", b2r_dtype_name(dtype), b2r_op_name(op));
@@ -222,9 +230,9 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
   if (kind == kCollLL) {
     // LL never touches a peer's send/recv buffer: any device pointer works, nothing is chunked, and only a buffer that is not
     // 16-byte aligned is bounced through this rank's own staging (a purely local decision: ranks need not agree on it)
-    if (total_bytes > ll_max_msg_bytes(P))
-      return fail(B2R_ERR_INVALID, "the LL path carries at most %zu bytes per rank on %d ranks (got %llu)", ll_max_msg_bytes(P), P,
-                  (unsigned long long)total_bytes);
+    if (total_bytes > ll_limit(c0))
+      return fail(B2R_ERR_INVALID, "the LL path carries at most %llu bytes per rank on this communicator of %d ranks (got %llu)",
+                  (unsigned long long)ll_limit(c0), P, (unsigned long long)total_bytes);
   }
   B2R_REQUIRE(kernel_exists(dtype, (int)op, kind), "collective: no kernel for dtype %d op %d algo %d", (int)dtype, (int)op, (int)algo);
 
@@ -262,7 +270,23 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
         A.count = cnt;
         A.epoch = c->epoch;
         A.root = is_all ? -1 : root;
-        A.seq = ++c->ll_seq;  // its own consecutive numbering: the slot parity and the n-2 acknowledgement rule depend on it
+        // small instance (control region, one CTA) when the message fits it, else the large one; each has its own slots,
+        // acknowledgement words and consecutive call numbering (the slot parity and the n-2 rule depend on it)
+        LLLayout lay;
+        if (bytes <= ll_max_msg_bytes(P)) {
+          lay.region_off = kOffLL;
+          lay.ack_off = kOffLLAck;
+          lay.slot_bytes = (unsigned int)ll_slot_bytes(P);
+          lay.vec_per_cta = (unsigned int)(kLLThreads * kLLVecPerThread);
+          A.seq = ++c->ll_seq;
+        } else {
+          lay.slot_bytes = (unsigned int)ll_big_slot_bytes(c->ll_big_bytes, P);
+          lay.region_off = c->ll_big_off;
+          lay.ack_off = c->ll_big_off + 2ull * P * lay.slot_bytes;
+          lay.vec_per_cta = (unsigned int)kLLBigVecPerCta;
+          A.seq = ++c->ll_big_seq;
+        }
+        ll_set_layout(A, lay);
         continue;
       }
       int64_t soff = c->heap_offset(send, bytes);
@@ -293,10 +317,15 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
     const Shape shape = coll_shape(c0, kind, bytes, n);
     int ctas = shape.ctas;
     int threads = shape.threads;
-    if (kind == kCollLL) {  // one CTA; just enough threads for one vector each, up to kLLThreads x kLLVecPerThread vectors
-      const uint64_t nvec = (bytes + 15) / 16;
-      ctas = 1;
-      threads = nvec <= 128 ? 128 : nvec <= 256 ? 256 : kLLThreads;
+    if (kind == kCollLL) {
+      if (bytes <= ll_max_msg_bytes(P)) {  // one CTA; just enough threads for one vector each, up to kLLThreads x kLLVecPerThread vectors
+        const uint64_t nvec = (bytes + 15) / 16;
+        ctas = 1;
+        threads = nvec <= 128 ? 128 : nvec <= 256 ? 256 : kLLThreads;
+      } else {  // the large instance: always the same grid, whatever the length (fixed partition, see ll_body)
+        ctas = kLLBigCtas;
+        threads = kLLThreads;
+      }
     }
     if (kind == kCollRing || kind == kCollRingAll || kind == kCollRing2) {
       // staging ring in the work region: depth x ctas steps of sub_blocks x (threads x 8) vectors; at least 2 deep.
@@ -477,6 +506,12 @@ using namespace b2r;
 
 extern "C" {
 
+b2r_status_t b2r_comm_ll_max_bytes(b2r_comm_t comm, uint64_t* bytes) {
+  B2R_REQUIRE(comm && bytes, "b2r_comm_ll_max_bytes: NULL argument");
+  *bytes = comm->nranks >= 2 ? ll_limit(comm) : 0;
+  return B2R_OK;
+}
+
 uint64_t b2r_ll_max_bytes(int nranks) { return (nranks >= 2 && nranks <= B2R_MAX_RANKS) ? (uint64_t)ll_max_msg_bytes(nranks) : 0; }
 
 // Size thresholds measured on 8x B200 (profiles/collectives_8gpu.md). One-shot costs one NVLink round trip but every
@@ -484,7 +519,7 @@ uint64_t b2r_ll_max_bytes(int nranks) { return (nranks >= 2 && nranks <= B2R_MAX
 // Public, for tests and harnesses: looks at the environment as it is now (the launch path uses cached values, util/env.h).
 b2r_algo_t b2r_select_algo(int is_allreduce, uint64_t bytes, b2r_dtype_t dtype, b2r_op_t op, int nranks, int has_multicast) {
   env_refresh();
-  return select_algo_cached(is_allreduce, bytes, dtype, op, nranks, has_multicast);
+  return select_algo_cached(is_allreduce, bytes, dtype, op, nranks, has_multicast, nranks <= B2R_MAX_RANKS ? ll_max_msg_bytes(std::max(nranks, 1)) : 0);
 }
 
 b2r_status_t b2r_reduce_ex(const void* sendbuf, void* recvbuf, uint64_t count, b2r_dtype_t dtype, b2r_op_t op, int root, b2r_comm_t comm,

@@ -270,8 +270,13 @@ __device__ void ringall_body(const CollArgs& A) {
 //   slots     : [call parity][source rank] in the consumer's control region — two calls may be in flight; before writing
 //               call n a sender checks that the consumer has acknowledged call n-2 (every rank acknowledges every call to
 //               every peer when its own work for that call is finished; the check is off the critical path).
-//   geometry  : ONE CTA per rank (<= 512 threads x 4 vectors = 32 KiB; the slot size caps it lower for P > 8): the
-//               acknowledgement then covers the whole message and needs no cross-CTA bookkeeping.
+//   geometry  : a FIXED partition — CTA b of every rank owns vectors [b x vpc, (b+1) x vpc) of the message whatever its
+//               length, and every call launches the same number of CTAs (those past the end of a short message only take
+//               part in the acknowledgements). So CTA b's slots are only ever touched by CTA b of the peers, and one
+//               acknowledgement word per (CTA, peer) is all the flow control needs. Two instances of this layout exist:
+//               the small one in the control region (1 CTA, <= 26 KiB at 8 ranks) and, when the communicator was created
+//               with B2R_LL_BIG_MB set, a large one behind the user heap (16 CTAs x 16 KiB = 256 KiB). The host passes the
+//               layout in fields of CollArgs that LL does not otherwise need (see ll_layout below).
 // Packets are written and read with 8-byte-element vector accesses (each element is one scalar access in the PTX memory
 // model, hence never torn). Call numbers are 32 bits and never reset: 2^32 LL calls per communicator.
 __device__ __forceinline__ void ll_store_vec(char* p, const V16& v, unsigned int seq) {
@@ -310,6 +315,29 @@ __device__ __forceinline__ void ll_store_tail(char* p, const V16& v, unsigned in
   }
 }
 
+// Where an LL call keeps its slots and acknowledgement words. Carried in CollArgs fields the LL path has no other use for, so
+// that sizeof(CollArgs) — and with it the code of every other kernel — stays what the GPU test-suite has passed on.
+struct LLLayout {
+  unsigned long long region_off;  // A.work_off : slots [call parity][source rank][slot_bytes]
+  unsigned long long ack_off;     // A.send_off : uint32 ack[CTA][B2R_MAX_RANKS]
+  unsigned int slot_bytes;        // A.sub_blocks
+  unsigned int vec_per_cta;       // A.ring_depth
+};
+__host__ __device__ inline LLLayout ll_layout(const CollArgs& A) {
+  LLLayout l;
+  l.region_off = A.work_off;
+  l.ack_off = A.send_off;
+  l.slot_bytes = (unsigned int)A.sub_blocks;
+  l.vec_per_cta = (unsigned int)A.ring_depth;
+  return l;
+}
+inline void ll_set_layout(CollArgs& A, const LLLayout& l) {
+  A.work_off = l.region_off;
+  A.send_off = l.ack_off;
+  A.sub_blocks = (int)l.slot_bytes;
+  A.ring_depth = (int)l.vec_per_cta;
+}
+
 template <int D, int O>
 __device__ void ll_body(const CollArgs& A) {
   using V = VecOps<D, O>;
@@ -320,14 +348,19 @@ __device__ void ll_body(const CollArgs& A) {
   const bool consumer = root < 0 || root == me;
   const unsigned long long bytes = A.count * E;
   const unsigned int nfull = (unsigned int)(bytes / 16), tail_bytes = (unsigned int)(bytes % 16);
-  const unsigned int nvec = nfull + (tail_bytes ? 1u : 0u);  // <= blockDim.x * kLLVecPerThread (checked by the host)
-  const size_t slot = ll_slot_bytes(P);
-  const size_t parity_off = kOffLL + (size_t)(seq & 1u) * P * slot;
+  const unsigned int nvec = nfull + (tail_bytes ? 1u : 0u);
+  const LLLayout lay = ll_layout(A);
+  const size_t slot = lay.slot_bytes;
+  const size_t parity_off = lay.region_off + (size_t)(seq & 1u) * P * slot;
+  // this CTA's share of the message: [v0, vend), at most blockDim.x * kLLVecPerThread vectors (the host sizes vec_per_cta so)
+  const unsigned int v0 = blockIdx.x * lay.vec_per_cta;
+  const unsigned int vend = min(nvec, v0 + lay.vec_per_cta);
+  const size_t my_acks = lay.ack_off + (size_t)blockIdx.x * B2R_MAX_RANKS * sizeof(unsigned int);
 
   // ---- flow control: the slots of this parity were last used by call seq-2; its consumers must be done with them
   if (threadIdx.x == 0) fault_delay(c);
   if (seq > 2 && threadIdx.x < (unsigned)P && (int)threadIdx.x != me && (root < 0 || (int)threadIdx.x == root)) {
-    const unsigned int* ack = (const unsigned int*)(c.heap[me] + kOffLLAck) + threadIdx.x;
+    const unsigned int* ack = (const unsigned int*)(c.heap[me] + my_acks) + threadIdx.x;
     wait_flag_ge(ack, seq - 2, c);  // on time-out the error word is set; the slots are always valid memory, so carry on
   }
   __syncthreads();
@@ -336,9 +369,11 @@ __device__ void ll_body(const CollArgs& A) {
   V16 own[kLLVecPerThread];
 #pragma unroll
   for (int u = 0; u < kLLVecPerThread; ++u) {
-    const unsigned int v = threadIdx.x + u * blockDim.x;
-    if (v < nfull) own[u] = ld_peer(A.send_ptr + (size_t)v * 16);
-    else if (v < nvec) own[u] = ll_load_tail<E>(A.send_ptr + (size_t)nfull * 16, tail_bytes);
+    const unsigned int v = v0 + threadIdx.x + u * blockDim.x;
+    if (v < vend) {
+      if (v < nfull) own[u] = ld_peer(A.send_ptr + (size_t)v * 16);
+      else own[u] = ll_load_tail<E>(A.send_ptr + (size_t)nfull * 16, tail_bytes);
+    }
   }
   if (!c.fault_skip_signal) {
     for (int d = 0; d < P; ++d) {
@@ -346,8 +381,8 @@ __device__ void ll_body(const CollArgs& A) {
       char* base = c.heap[d] + parity_off + (size_t)me * slot;
 #pragma unroll
       for (int u = 0; u < kLLVecPerThread; ++u) {
-        const unsigned int v = threadIdx.x + u * blockDim.x;
-        if (v < nvec) ll_store_vec(base + (size_t)v * 32, own[u], seq);
+        const unsigned int v = v0 + threadIdx.x + u * blockDim.x;
+        if (v < vend) ll_store_vec(base + (size_t)v * 32, own[u], seq);
       }
     }
   }
@@ -358,8 +393,8 @@ __device__ void ll_body(const CollArgs& A) {
     const char* mine = c.heap[me] + parity_off;
 #pragma unroll
     for (int u = 0; u < kLLVecPerThread; ++u) {
-      const unsigned int v = threadIdx.x + u * blockDim.x;
-      if (v >= nvec) continue;
+      const unsigned int v = v0 + threadIdx.x + u * blockDim.x;
+      if (v >= vend) continue;
       typename V::Acc acc;
       bool ok = true;
       for (int p0 = 0; p0 < P && ok; p0 += 4) {
@@ -416,7 +451,7 @@ __device__ void ll_body(const CollArgs& A) {
   // to be acknowledged by the link.
   __syncthreads();
   if (threadIdx.x < (unsigned)P && (int)threadIdx.x != me && !c.fault_skip_signal) {
-    unsigned int* ack = (unsigned int*)(c.heap[threadIdx.x] + kOffLLAck) + me;
+    unsigned int* ack = (unsigned int*)(c.heap[threadIdx.x] + my_acks) + me;
     if (consumer) st_release_sys(ack, seq);
     else st_relaxed_sys_u32(ack, seq);
   }

@@ -30,6 +30,18 @@ constexpr size_t ll_slot_bytes(int nranks) { return ((kCtrlBytes - kOffLL) / (2 
 constexpr size_t ll_max_msg_bytes(int nranks) {
   return ll_slot_bytes(nranks) / 2 < (size_t)kLLThreads * kLLVecPerThread * 16 ? ll_slot_bytes(nranks) / 2 : (size_t)kLLThreads * kLLVecPerThread * 16;
 }
+// The optional large instance of the same layout (communicators created with B2R_LL_BIG_MB=n get n MiB behind the user heap):
+// kLLBigCtas CTAs own kLLBigVecPerCta vectors each, the acknowledgement words sit at the end of the region.
+constexpr int kLLBigCtas = 16;
+constexpr int kLLBigVecPerCta = 1024;  // 16 KiB of payload per CTA, two vectors per thread
+constexpr size_t kLLBigAckBytes = (size_t)kLLBigCtas * B2R_MAX_RANKS * sizeof(unsigned int);
+constexpr size_t ll_big_slot_bytes(size_t region_bytes, int nranks) {
+  return region_bytes <= kLLBigAckBytes ? 0 : ((region_bytes - kLLBigAckBytes) / (2 * (size_t)nranks)) & ~(size_t)255;
+}
+constexpr size_t ll_big_max_msg_bytes(size_t region_bytes, int nranks) {
+  return ll_big_slot_bytes(region_bytes, nranks) / 2 < (size_t)kLLBigCtas * kLLBigVecPerCta * 16 ? ll_big_slot_bytes(region_bytes, nranks) / 2
+                                                                                                   : (size_t)kLLBigCtas * kLLBigVecPerCta * 16;
+}
 
 // Where rank r keeps its send/recv buffer for the collective in flight, published to every peer inside the start
 // barrier, so buffers do NOT have to sit at the same heap offset on every rank (only the NVLS path needs that).

@@ -65,7 +65,7 @@ void parse_fault_injection(CollCtx* ctx, int rank) {
 }
 
 struct Sizes {
-  size_t stage_bytes, user_bytes, heap_bytes;
+  size_t stage_bytes, user_bytes, heap_bytes, ll_big_bytes;
 };
 
 Sizes compute_sizes(const b2r_comm_config_t* cfg, size_t granularity) {
@@ -73,7 +73,9 @@ Sizes compute_sizes(const b2r_comm_config_t* cfg, size_t granularity) {
   s.stage_bytes = (size_t)std::max(1, env_int("B2R_STAGE_MB", 64)) << 20;
   s.user_bytes = cfg && cfg->heap_bytes ? (size_t)cfg->heap_bytes : ((size_t)256 << 20);
   s.user_bytes = round_up(s.user_bytes, 256);
-  s.heap_bytes = round_up(kCtrlBytes + 3 * s.stage_bytes + s.user_bytes, granularity);
+  // optional large LL region (experimental, off unless asked for; like B2R_STAGE_MB it must be the same on every rank)
+  s.ll_big_bytes = (size_t)std::max(0, env_int("B2R_LL_BIG_MB", 0)) << 20;
+  s.heap_bytes = round_up(kCtrlBytes + 3 * s.stage_bytes + s.user_bytes + s.ll_big_bytes, granularity);
   return s;
 }
 
@@ -81,6 +83,9 @@ void fill_common(b2r_comm* c, const b2r_comm_config_t* cfg, const Sizes& s) {
   c->heap_bytes = s.heap_bytes;
   c->stage_bytes = s.stage_bytes;
   c->user_off = kCtrlBytes + 3 * s.stage_bytes;
+  c->ll_big_bytes = s.ll_big_bytes;
+  c->ll_big_off = s.ll_big_bytes ? c->user_off + s.user_bytes : 0;
+  c->user_end = s.ll_big_bytes ? c->ll_big_off : s.heap_bytes;
   c->symmetric_only = cfg && cfg->symmetric_only;
   c->bump = c->user_off;
   c->timeout_ms = cfg && cfg->timeout_ms ? cfg->timeout_ms : env_int("B2R_TIMEOUT_MS", 10000);
@@ -97,6 +102,7 @@ b2r_status_t finish_init(b2r_comm* c) {
   struct Restore { int d; ~Restore() { cudaSetDevice(d); } } restore{prev};
   B2R_CUDA_CHECK(cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, c->device));
   B2R_CUDA_CHECK(cudaMemset(c->my_heap(), 0, kCtrlBytes));
+  if (c->ll_big_bytes) B2R_CUDA_CHECK(cudaMemset(c->my_heap() + c->ll_big_off, 0, c->ll_big_bytes));  // LL flags must start at zero
   B2R_CUDA_CHECK(cudaMemcpy(c->my_heap() + kOffCtx, &c->ctx, sizeof(CollCtx), cudaMemcpyHostToDevice));
   B2R_CUDA_CHECK(cudaDeviceSynchronize());
   B2R_CHECK(b2r_workspace_create(&c->ws, c->device));
@@ -481,9 +487,9 @@ b2r_status_t b2r_comm_has_multicast(b2r_comm_t c, int* yes) {
 b2r_status_t b2r_symm_alloc(b2r_comm_t c, uint64_t bytes, void** ptr) {
   B2R_REQUIRE(c && ptr, "b2r_symm_alloc: NULL argument");
   const size_t need = round_up((size_t)std::max<uint64_t>(bytes, 1), 256);
-  if (c->bump + need > c->heap_bytes)
+  if (c->bump + need > c->user_end)
     return fail(B2R_ERR_NOMEM, "b2r_symm_alloc: %llu bytes requested, %zu left in the symmetric heap (raise b2r_comm_config_t.heap_bytes)",
-                (unsigned long long)bytes, c->heap_bytes - c->bump);
+                (unsigned long long)bytes, c->user_end - c->bump);
   *ptr = c->my_heap() + c->bump;
   c->bump += need;
   return B2R_OK;

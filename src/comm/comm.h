@@ -47,10 +47,13 @@ struct b2r_comm {
   int rank = 0, nranks = 1, device = 0, sm_count = 0;
   b2r::CollCtx ctx;
   size_t heap_bytes = 0, stage_bytes = 0, user_off = 0, bump = 0;
+  size_t user_end = 0;                       // first byte past the user allocations (== heap_bytes without an LL-big region)
+  size_t ll_big_off = 0, ll_big_bytes = 0;   // optional large LL region behind the user heap (B2R_LL_BIG_MB at creation)
   uint32_t epoch = 0;   // barrier epoch counter (same sequence on every rank)
   uint32_t xg_seq = 0;  // scalar-sharded call counter
   uint32_t push_seq = 0;  // push-algorithm call counter (flag values are seq << 16 | round)
   uint32_t ll_seq = 0;    // LL path call counter (consecutive: slot parity and the n-2 acknowledgement rule depend on it)
+  uint32_t ll_big_seq = 0;  // the same for the large LL region (separate slots and acknowledgements, separate numbering)
   b2r_workspace* ws = nullptr;
   int max_ctas = 0, timeout_ms = 0;
   bool has_mc = false;

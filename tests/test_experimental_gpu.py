@@ -268,3 +268,77 @@ def test_symmetric_only_mode_and_max_ctas():
     finally:
         for c in cs:
             c.close()
+
+
+# ------------------------------------------------------------------------------------------------ LL, large instance (B2R_LL_BIG_MB at creation)
+@pytest.fixture(scope="module", params=[2, 4, 8])
+def big_comms(request):
+    old = os.environ.get("B2R_LL_BIG_MB")
+    os.environ["B2R_LL_BIG_MB"] = "16"
+    try:
+        cs = Communicator.loopback(request.param, device=0, heap_bytes=16 << 20)
+    finally:
+        if old is None:
+            del os.environ["B2R_LL_BIG_MB"]
+        else:
+            os.environ["B2R_LL_BIG_MB"] = old
+    yield cs
+    for c in cs:
+        c.close()
+
+
+def test_ll_big_limits(big_comms, comms):
+    P = len(big_comms)
+    assert big_comms[0].ll_max_bytes == 256 << 10  # 16 CTAs x 1024 vectors; the 16 MiB region would hold more
+    assert comms[0].ll_max_bytes == _lib.LIB.b2r_ll_max_bytes(len(comms))  # no big region: the small instance only
+    x = [torch.zeros((256 << 10) // 4 + 4, dtype=torch.int32, device="cuda") for _ in range(P)]
+    with pytest.raises(b2r.B2RError, match="LL path carries at most"):
+        Communicator.group_allreduce(big_comms, x, "sum", algo="ll")
+
+
+@pytest.mark.parametrize("dtype", [torch.int32, torch.float64, torch.bfloat16])
+def test_ll_big_reduce_and_allreduce(big_comms, dtype):
+    """Sizes on both sides of the small/large switch, around CTA boundaries of the fixed partition (1024 vectors per CTA),
+    the largest message, and long mixed sequences (the two instances keep separate call counters and acknowledgements)."""
+    P = len(big_comms)
+    esz = torch.empty(0, dtype=dtype).element_size()
+    per_vec = 16 // esz
+    small_max = _lib.LIB.b2r_ll_max_bytes(P) // esz
+    counts = sorted({small_max, small_max + 1, 1024 * per_vec - 1, 1024 * per_vec, 1024 * per_vec + 1, 3 * 1024 * per_vec + 5,
+                     15 * 1024 * per_vec + 7, (256 << 10) // esz - 1, (256 << 10) // esz})
+    for count in counts:
+        xs_h = [b2r.fill_host(count, dtype, seed=23 * r + count, mode="signed") for r in range(P)]
+        xs = [x.cuda() for x in xs_h]
+        for op in ("sum", "max"):
+            want = host_reduce_threads(xs_h, op, -1, "ll")[0]
+            outs = Communicator.group_allreduce(big_comms, xs, op, algo="ll")
+            Communicator.group_check(big_comms)
+            for r in range(P):
+                assert torch.equal(bits(outs[r].cpu()), bits(want)), (P, dtype, op, count, r)
+            root = count % P
+            outs = Communicator.group_reduce(big_comms, xs, op, root=root, algo="ll")
+            Communicator.group_check(big_comms)
+            assert torch.equal(bits(outs[root].cpu()), bits(want)), (P, dtype, op, count, root)
+
+
+def test_ll_big_back_to_back_mixed_with_small(big_comms):
+    P = len(big_comms)
+    sizes = [5, 3000, 9000, 20000, 65536]  # int32 counts: the first three use the small instance, the last two the large one at 8 ranks
+    data = {n: [b2r.fill_host(n, torch.int32, seed=31 * r + n, mode="full") for r in range(P)] for n in sizes}
+    dev = {n: [x.cuda() for x in xs] for n, xs in data.items()}
+    want = {n: host_reduce_threads(xs, "sum", -1, "ll")[0] for n, xs in data.items()}
+    checks = []
+    for i in range(300):
+        n = sizes[(i * 3) % len(sizes)]
+        if i % 2:
+            root = i % P
+            checks.append((n, root, Communicator.group_reduce(big_comms, dev[n], "sum", root=root, algo="ll")))
+        else:
+            checks.append((n, None, Communicator.group_allreduce(big_comms, dev[n], "sum", algo="ll")))
+        if len(checks) >= 30:
+            torch.cuda.synchronize()
+            for n2, root2, outs2 in checks:
+                for r in (range(P) if root2 is None else [root2]):
+                    assert torch.equal(outs2[r].cpu(), want[n2]), (i, n2, root2, r)
+            checks = []
+    Communicator.group_check(big_comms)

@@ -168,3 +168,14 @@ def test_auto_switches_for_unmeasured_paths_are_off_by_default(monkeypatch):
     monkeypatch.delenv("B2R_AUTO_RING_MIN_MB")
     after = [sel(a, n, d, _lib.SUM, p, 1) for a in (0, 1) for n in (64, 8192, 1 << 20, 1 << 28) for d in (_lib.INT32, _lib.FLOAT32) for p in (2, 8)]
     assert before == after
+
+
+def test_ll_big_region_arithmetic():
+    """Sizes of the optional large LL instance (coll_ctx.h), restated: 16 CTAs x 1024 vectors, acknowledgement words at the
+    end of the region, two parities x P sources x slot, payload = half a slot."""
+    ack = 16 * 16 * 4
+    for region_mb, P, want in ((16, 8, 256 << 10), (16, 16, 262016), (16, 2, 256 << 10), (4, 8, 130944), (1, 16, 16256)):
+        region = region_mb << 20
+        slot = ((region - ack) // (2 * P)) & ~255
+        assert min(slot // 2, 16 * 1024 * 16) == want, (region_mb, P)
+        assert 2 * P * slot + ack <= region

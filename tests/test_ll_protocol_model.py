@@ -8,6 +8,9 @@ protocol lets them; the scheduler is biased so that some rank is usually much sl
 deadlock, every consumer's result equals the rank-order sum, under rotating roots, reduce/allreduce mixes and message
 sizes that shrink and grow (so slots keep stale packets of older, longer messages).
 
+The multi-CTA instances of the kernel use a fixed partition of the message with one set of acknowledgement words per CTA,
+so every CTA column runs exactly this protocol on its own share; one column is what is modelled.
+
 The model has teeth: with the n-2 rule switched off it finds corrupted results (second test)."""
 import random
 
