@@ -163,6 +163,7 @@ def run_b2r(args) -> None:
     # pdl=1: programmatic dependent launch — step i+1 may begin streaming its (ready, independent) input while step i is
     # draining; every step still reads its whole input from HBM and finishes its own scalar.
     cfg = b2r.launch_config(pdl=1)
+    host_path = "regular method"
     if comm is None:
         opc = {"sum": 0, "min": 1, "max": 2}[args.op]
 
@@ -172,27 +173,52 @@ def run_b2r(args) -> None:
         def step_plain(i):
             b2r.reduce(inputs[i % copies], opc, out=out, workspace=ws)
     else:
-        def step(i):
+        def step_regular(i):
             comm.reduce_scalar_sharded(inputs[i % copies], args.op, root=0, out=out, cfg=cfg)
 
+        # Persistent form of the same call: arguments converted to C types once, one ctypes call per step (~1.5 us less host
+        # time per launch; the GPU side of a step is 9 us). Falls back to the regular method if anything about it is off.
+        step = step_regular
+        if os.environ.get("B2R_BENCH_PREPARED", "1") != "0":
+            try:
+                step, _ = comm.prepare_reduce_scalar_sharded(inputs, args.op, root=0, out=out, cfg=cfg)
+                host_path = "prepared call (Communicator.prepare_reduce_scalar_sharded)"
+            except Exception as e:  # noqa: BLE001
+                print(f"[rank {rank}] prepared call unavailable ({e}); using the regular method", file=sys.stderr)
+                step = step_regular
+
     # correctness of what is being timed (cheap: one step per distinct input, against the CPU oracle)
-    step(0)
-    torch.cuda.synchronize()
-    if comm is None:
-        want = b2r.reduce_oracle(inputs[0].cpu(), args.op)
-        assert out.cpu().item() == want.item(), f"self-check failed: got {out.item()} want {want.item()}"
-    else:
+    def verified() -> tuple[bool, str]:
+        out.zero_()
+        step(0)
+        torch.cuda.synchronize()
+        if comm is None:
+            want = b2r.reduce_oracle(inputs[0].cpu(), args.op)
+            return out.cpu().item() == want.item(), f"got {out.item()} want {want.item()}"
         import torch.distributed as dist
 
         local = b2r.reduce_oracle(inputs[0].cpu(), args.op).to(dev).to(torch.int64 if dtype == torch.int32 else dtype)
         dist.all_reduce(local, op={"sum": dist.ReduceOp.SUM, "min": dist.ReduceOp.MIN, "max": dist.ReduceOp.MAX}[args.op])
+        verdict = torch.ones((), dtype=torch.int32, device=dev)
+        msg = ""
         if rank == 0:
             w = local.item()
             if dtype == torch.int32:
                 w = (w + 2**31) % 2**32 - 2**31
-                assert out.item() == w, f"self-check failed: got {out.item()} want {w}"
+                good = out.item() == w
             else:
-                assert abs(out.item() - w) <= 1e-5 * abs(w) + 1e-6, f"self-check failed: got {out.item()} want {w}"
+                good = abs(out.item() - w) <= 1e-5 * abs(w) + 1e-6
+            msg = f"got {out.item()} want {w}"
+            verdict.fill_(1 if good else 0)
+        dist.broadcast(verdict, src=0)  # every rank must take the same decision below
+        return bool(verdict.item()), msg
+
+    ok, msg = verified()
+    if not ok and comm is not None and step is not step_regular:
+        print(f"[rank {rank}] prepared call failed the self-check ({msg}); using the regular method", file=sys.stderr)
+        step, host_path = step_regular, "regular method (prepared call failed its self-check)"
+        ok, msg = verified()
+    assert ok, f"self-check failed: {msg}"
 
     sampler = ClockSampler(local_rank).start() if rank == 0 else None
     for i in range(warmup):
@@ -279,7 +305,7 @@ def run_b2r(args) -> None:
                        "global_elements": world * args.n, "parallelism": f"dp{world} (sharded scalar reduce to root over NVLink)" if world > 1 else "single-gpu",
                        "cache_control": f"{copies} rotating inputs of {nbytes >> 20} MiB (total {copies * nbytes >> 20} MiB > 4x L2)",
                        "geometry": b2r.plan(args.n, dtype, args.op, device=local_rank, cfg=cfg),
-                       "launch": "programmatic dependent launch between consecutive steps (cfg pdl=1)"},
+                       "launch": "programmatic dependent launch between consecutive steps (cfg pdl=1)", "host_path": host_path},
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": "GB/s", "h2d_bytes_per_step": nbytes, "d2h_bytes_per_step": nchunks * acc_sz,
                     "steps": e2e_steps, "ms_per_step": e2e_s * 1e3 / e2e_steps,

@@ -162,6 +162,39 @@ class Communicator:
             self._finish(st, "b2r_reduce_scalar_sharded")
         return out
 
+    def prepare_reduce_scalar_sharded(self, xs: list[torch.Tensor], op="sum", root: int = 0, all: bool = False,
+                                      out: torch.Tensor | None = None, cfg: _lib.LaunchCfg | None = None):
+        """Persistent form of reduce_scalar_sharded (MPI-4's MPI_Reduce_init / MPI_Start idea) for loops that reduce the same
+        few buffers over and over: every argument is converted to its C type ONCE, and the returned `start(i)` launches the
+        reduction of xs[i % len(xs)] with one ctypes call — about 1.7 us less host time per launch than the regular method,
+        which matters when the GPU side is 9 us. Returns (start, out); `out` is rewritten by every start(). The CUDA stream
+        that is current NOW is the one all launches go to; buffers, `out` and `cfg` must stay alive and unchanged in
+        shape as long as `start` is used."""
+        assert xs, "at least one buffer"
+        x0 = xs[0]
+        for x in xs:
+            if x.device != self.device or not x.is_contiguous() or x.dtype != x0.dtype or x.numel() != x0.numel():
+                raise ValueError("prepared buffers must be contiguous tensors of one dtype and length on this communicator's device")
+        if out is None and (all or self.rank == root):
+            out = torch.empty((), dtype=x0.dtype, device=self.device)
+        n = x0.numel()
+        common = (C.c_void_p(out.data_ptr() if out is not None else 0), C.c_uint64(n), C.c_int(b2r_dtype(x0.dtype)),
+                  C.c_int(op if isinstance(op, int) else op_code(op)), C.c_int(root), C.c_int(1 if all else 0), self._h,
+                  C.c_void_p(_raw_stream(self.device_index)), C.byref(cfg) if cfg is not None else None)
+        argsets = [(C.c_void_p(x.data_ptr() if n else 0),) + common for x in xs]
+        keep = (list(xs), out, cfg)  # the closure keeps everything alive
+        k = len(argsets)
+        fn = _SCALAR_EX
+        finish = self._finish
+
+        def start(i: int = 0) -> None:
+            st = fn(*argsets[i % k])
+            if st:
+                finish(st, "b2r_reduce_scalar_sharded")
+
+        start.keepalive = keep
+        return start, out
+
     def reduce_scalar_sharded_from_host(self, x: torch.Tensor, op="sum", root: int = 0, all: bool = False):
         """End-to-end flavour: `x` is this rank's shard in (pinned) HOST memory; it is copied to the GPU, reduced across
         ranks, and the scalar is read back to the host on the ranks that own it (None elsewhere). Synchronous."""

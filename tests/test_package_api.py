@@ -110,3 +110,46 @@ def test_cached_environment_lookups(tmp_path, monkeypatch):
     monkeypatch.delenv("B2R_THREADS")
     b2r.refresh_env()
     assert b2r.plan(1 << 24, torch.int32)["threads"] != 96
+
+
+def test_prepared_scalar_sharded_call_passes_the_same_arguments(monkeypatch):
+    """Communicator.prepare_reduce_scalar_sharded converts its arguments once; the native call must receive exactly what
+    the regular method passes (checked with the native entry point and the stream lookup replaced by recorders)."""
+    import ctypes as C
+
+    import torch
+
+    import cuda_mpi_reductions_b200 as b2r
+    from cuda_mpi_reductions_b200.parallel import comm as cm
+
+    calls = []
+
+    def record(*a):
+        vals = []
+        for v in a:
+            if v is None or isinstance(v, int):
+                vals.append(v)
+            elif hasattr(v, "value"):
+                vals.append(v.value)
+            else:  # byref(cfg): compare the pointed-to launch configuration
+                vals.append(bytes(C.string_at(C.addressof(v._obj), C.sizeof(v._obj))))
+        calls.append(tuple(0 if v is None else v for v in vals))
+        return 0
+
+    monkeypatch.setattr(cm, "_SCALAR_EX", record)
+    monkeypatch.setattr(cm, "_raw_stream", lambda idx: 0xABC0)
+    c = object.__new__(cm.Communicator)
+    c.device, c.device_index, c._h, c.rank = torch.device("cpu"), 0, C.c_void_p(0x1234), 0
+    xs = [torch.zeros(1000, dtype=torch.float64) for _ in range(3)]
+    out = torch.zeros((), dtype=torch.float64)
+    cfg = b2r.launch_config(pdl=1)
+    for x in xs:
+        c.reduce_scalar_sharded(x, "max", root=0, out=out, cfg=cfg)
+    regular, calls[:] = list(calls), []
+    start, out2 = c.prepare_reduce_scalar_sharded(xs, "max", root=0, out=out, cfg=cfg)
+    assert out2 is out
+    for i in range(5):
+        start(i)
+    assert calls[:3] == regular and calls[3:] == regular[:2]  # wraps around the buffer list
+    with pytest.raises(ValueError):
+        c.prepare_reduce_scalar_sharded([xs[0], torch.zeros(7, dtype=torch.float64)], "max")
