@@ -34,7 +34,7 @@ CPP_OBJS := $(patsubst src/%.cpp,$(OBJDIR)/%.cpp.o,$(CPP_SRCS))
 HDRS     := $(wildcard include/*.h) $(wildcard src/*/*.h) $(wildcard src/*/*.cuh) $(wildcard src/*/*.inl)
 
 LIB      := $(LIBDIR)/libb2r.so
-BENCHES  := $(BINDIR)/local_sweep $(BINDIR)/bench_reduce $(BINDIR)/bench_collective
+BENCHES  := $(BINDIR)/local_sweep $(BINDIR)/bench_reduce $(BINDIR)/bench_collective $(BINDIR)/launch_gap
 
 .PHONY: all lib bins minimpi baseline examples clean sass
 all: lib bins minimpi

@@ -15,3 +15,6 @@ mkdir -p "$OUT"
 # -arch=sm_100 (not sm_100a): nothing in the 2012 source needs arch-specific features. math_functions.h is found in the toolkit.
 $NVCC -arch=sm_100 -O2 -Xcompiler -fno-strict-aliasing -w -I"$HERE/shim" -I"$SRC" -x cu "$SRC/reduction.cpp" "$SRC/reduction_kernel.cu" -o "$OUT/reduction"
 echo "built $OUT/reduction"
+# end-to-end driver around the SAME unmodified kernel file (see ref_e2e.cu): per-step H2D + two-pass reduce + D2H
+$NVCC -arch=sm_100 -O2 -Xcompiler -fno-strict-aliasing -w -I"$SRC" "$HERE/ref_e2e.cu" "$SRC/reduction_kernel.cu" -o "$OUT/ref_e2e"
+echo "built $OUT/ref_e2e"

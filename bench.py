@@ -160,9 +160,10 @@ def run_b2r(args) -> None:
     out = torch.empty((), dtype=dtype, device=dev)
     ws = b2r.Workspace(dev)
 
-    # pdl=1: programmatic dependent launch — step i+1 may begin streaming its (ready, independent) input while step i is
-    # draining; every step still reads its whole input from HBM and finishes its own scalar.
-    cfg = b2r.launch_config(pdl=1)
+    # pdl=PDL_INPUT_READY: programmatic dependent launch with early streaming — the inputs were filled long before the loop,
+    # so step i+1 may begin streaming its (complete, independent) input while step i is draining; every step still reads its
+    # whole input from HBM and finishes its own scalar.
+    cfg = b2r.launch_config(pdl=b2r.PDL_INPUT_READY)
     host_path = "regular method"
     if comm is None:
         opc = {"sum": 0, "min": 1, "max": 2}[args.op]
@@ -305,7 +306,7 @@ def run_b2r(args) -> None:
                        "global_elements": world * args.n, "parallelism": f"dp{world} (sharded scalar reduce to root over NVLink)" if world > 1 else "single-gpu",
                        "cache_control": f"{copies} rotating inputs of {nbytes >> 20} MiB (total {copies * nbytes >> 20} MiB > 4x L2)",
                        "geometry": b2r.plan(args.n, dtype, args.op, device=local_rank, cfg=cfg),
-                       "launch": "programmatic dependent launch between consecutive steps (cfg pdl=1)", "host_path": host_path},
+                       "launch": "programmatic dependent launch between consecutive steps (cfg pdl=PDL_INPUT_READY: inputs complete before the loop)", "host_path": host_path},
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": "GB/s", "h2d_bytes_per_step": nbytes, "d2h_bytes_per_step": nchunks * acc_sz,
                     "steps": e2e_steps, "ms_per_step": e2e_s * 1e3 / e2e_steps,

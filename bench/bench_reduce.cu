@@ -192,7 +192,7 @@ int main(int argc, char** argv) {
   o.cfg.cluster = (int)f.i64("cluster", 0);
   o.cfg.unroll = (int)f.i64("unroll", 0);
   o.cfg.stages = (int)f.i64("stages", 0);
-  o.cfg.pdl = f.has("pdl") ? 1 : 0;  // programmatic dependent launch between the back-to-back timed launches
+  o.cfg.pdl = f.has("pdl") ? (int)f.i64("pdl", B2R_PDL_INPUT_READY) : 0;  // --pdl: the timed launches reduce buffers filled long ago (early streaming); --pdl=1: safe flavour
 
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {

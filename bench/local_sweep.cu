@@ -5,6 +5,7 @@
 //
 //   local_sweep [--type=int|float|double|bf16] [--method=SUM|MIN|MAX] [--n=16777216] [--iters=50] [--csv=path] [--quick]
 #include <algorithm>
+#include <string>
 
 #include "bench_common.h"
 
@@ -13,6 +14,7 @@ using namespace b2rbench;
 struct Row {
   int variant, threads, cps, unroll, stages, cluster;
   double gbs, us;
+  int dyn_pct = 0, tile_rounds = 0;
 };
 
 int main(int argc, char** argv) {
@@ -27,7 +29,7 @@ int main(int argc, char** argv) {
   const uint64_t n = (uint64_t)f.i64("n", 1 << 24);
   const int iters = (int)f.i64("iters", 50);
   const bool quick = f.has("quick");
-  const int pdl = f.has("pdl") ? 1 : 0;
+  const int pdl = f.has("pdl") ? (int)f.i64("pdl", B2R_PDL_INPUT_READY) : 0;
   const size_t bytes = n * b2r_dtype_size(dt);
   const int copies = rotating_copies(bytes, (size_t)1 << 30);
 
@@ -48,9 +50,11 @@ int main(int argc, char** argv) {
 
   std::vector<Row> rows;
   EventTimer et;
+  int dyn_pct = -1, tile_rounds = 1;  // the classic grid below measures the static split
   auto run = [&](int variant, int threads, int cps, int unroll, int stages, int cluster) {
     b2r_launch_cfg_t cfg;
     memset(&cfg, 0, sizeof(cfg));
+    cfg.dyn_pct = dyn_pct;
     cfg.variant = variant;
     cfg.threads = threads;
     cfg.ctas = cps * prop.multiProcessorCount;
@@ -66,8 +70,42 @@ int main(int argc, char** argv) {
     for (int i = 0; i < iters; ++i) b2r_reduce_local_ex(d_in + (i % copies) * bytes, d_out, n, dt, op, ws, nullptr, &cfg);
     et.stop(nullptr);
     const double ms = et.ms() / iters;
-    rows.push_back({variant, threads, cps, unroll, stages, cluster, bytes / ms * 1e-6, ms * 1e3});
+    Row r{variant, threads, cps, unroll, stages, cluster, bytes / ms * 1e-6, ms * 1e3};
+    r.dyn_pct = dyn_pct;
+    r.tile_rounds = tile_rounds;
+    rows.push_back(r);
   };
+
+  if (f.has("dyn")) {
+    // --dyn: the dynamically scheduled tail (share of the input x tile size) against the static split, plain stream order,
+    // for the register-streaming geometries that matter at this size
+    for (int pct : {-1, 10, 25, 40, 60, 90})
+      for (int rounds : {1, 2, 4}) {
+        if (pct < 0 && rounds > 1) continue;
+        dyn_pct = pct;
+        tile_rounds = rounds;
+        setenv("B2R_DYN_TILE_ROUNDS", std::to_string(rounds).c_str(), 1);
+        b2r_refresh_env();
+        for (int threads : {256, 512})
+          for (int cps : {2, 4, 8}) {
+            if (threads * cps > 2048 || threads * cps < 1024) continue;
+            for (int unroll : {4, 8}) run(B2R_VARIANT_LDG128, threads, cps, unroll, 0, 1);
+          }
+        run(B2R_VARIANT_LDG256, 512, 2, 4, 0, 1);
+        run(B2R_VARIANT_LDG256, 256, 4, 4, 0, 1);
+      }
+    std::sort(rows.begin(), rows.end(), [](const Row& a, const Row& b) { return a.gbs > b.gbs; });
+    printf("%-8s %7s %6s %6s %8s %6s %10s %9s\n", "variant", "threads", "cta/SM", "unroll", "dyn_pct", "rounds", "GB/s", "us");
+    for (size_t i = 0; i < rows.size(); ++i) {
+      const Row& r = rows[i];
+      if (i < 30 || r.dyn_pct < 0)
+        printf("%-8s %7d %6d %6d %8d %6d %10.1f %9.2f\n", variant_name(r.variant), r.threads, r.cps, r.unroll, r.dyn_pct, r.tile_rounds, r.gbs, r.us);
+    }
+    b2r_workspace_destroy(ws);
+    cudaFree(d_in);
+    cudaFree(d_out);
+    return 0;
+  }
 
   const int thr_ldg[] = {128, 256, 512};
   const int cps_ldg[] = {1, 2, 4, 8, 16};

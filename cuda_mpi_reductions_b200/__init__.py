@@ -5,7 +5,7 @@ szabodabo/CUDA-MPI-Reductions: the single-GPU reduction sample (cuda/C/src/reduc
 benchmark (mpi/reduce.c); see SURVEY.md for the full map.
 """
 from . import _lib
-from ._lib import B2RError, build, refresh_env
+from ._lib import B2RError, build, refresh_env, PDL_OFF, PDL_SAFE, PDL_INPUT_READY
 from .ops.local import Workspace, reduce, reduce_from_host, dot, plan, trace_last, launch_config
 from .ops.oracle import reduce_oracle, combine_oracle, fill_host, fill_device
 

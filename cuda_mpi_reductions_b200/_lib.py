@@ -30,7 +30,10 @@ DTYPE_SIZE = {INT32: 4, FLOAT32: 4, FLOAT64: 8, BFLOAT16: 2}
 
 
 class LaunchCfg(C.Structure):
-    _fields_ = [(n, C.c_int) for n in ("variant", "threads", "ctas", "cluster", "stages", "tile_bytes", "unroll", "pdl")]
+    _fields_ = [(n, C.c_int) for n in ("variant", "threads", "ctas", "cluster", "stages", "tile_bytes", "unroll", "pdl", "dyn_pct")]
+
+
+PDL_OFF, PDL_SAFE, PDL_INPUT_READY = -1, 1, 2  # b2r_launch_cfg_t.pdl (include/b2r.h)
 
 
 class CommConfig(C.Structure):

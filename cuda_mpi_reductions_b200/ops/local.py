@@ -59,7 +59,9 @@ def _workspace_for(device: torch.device, stream: int) -> Workspace:
 
 
 def launch_config(**kw) -> _lib.LaunchCfg:
-    """Builds a reusable launch configuration (variant=, threads=, ctas=, cluster=, unroll=, stages=, pdl=).
+    """Builds a reusable launch configuration (variant=, threads=, ctas=, cluster=, unroll=, stages=, pdl=, dyn_pct=).
+    pdl: PDL_SAFE (1) lets consecutive launches overlap their launch latency; PDL_INPUT_READY (2) additionally lets a launch
+    stream its input while the previous kernel drains — only for inputs that were complete before that kernel started.
     Passing the same object to many reduce() calls avoids re-parsing a dict on every launch."""
     c = _lib.LaunchCfg()
     for k, v in kw.items():
@@ -157,7 +159,7 @@ def plan(n: int, dtype: torch.dtype, op="sum", device: int = -1, cfg=None) -> di
     _lib.check(st, "b2r_plan_local")
     names = {v: k for k, v in _lib.VARIANTS.items()}
     return {"variant": names[chosen.variant], "threads": chosen.threads, "ctas": chosen.ctas, "cluster": chosen.cluster,
-            "unroll": chosen.unroll, "stages": chosen.stages, "tile_bytes": chosen.tile_bytes, "pdl": chosen.pdl}
+            "unroll": chosen.unroll, "stages": chosen.stages, "tile_bytes": chosen.tile_bytes, "pdl": chosen.pdl, "dyn_pct": chosen.dyn_pct}
 
 
 def trace_last(workspace: Workspace, max_ctas: int = 4096) -> torch.Tensor:

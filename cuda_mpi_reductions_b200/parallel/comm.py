@@ -148,7 +148,7 @@ class Communicator:
         """Scalar op over the elements of EVERY rank's shard `x` (shards may have different contents, same length per
         call): one fused kernel per rank — local streaming reduction, partial stored into the root's mailbox over NVLink,
         root combines in rank order. Result at root (every rank if all=True) as a 0-dim tensor. `cfg` is a
-        launch_config() for the streaming part (e.g. pdl=1 for back-to-back calls on ready inputs). The host path is kept
+        launch_config() for the streaming part (e.g. pdl=PDL_INPUT_READY for back-to-back calls on inputs that are already complete). The host path is kept
         thin: at ~10 us per 64 MiB shard the Python call is otherwise the bottleneck."""
         if x.device != self.device or not x.is_contiguous():
             x = self._prep(x)

@@ -18,7 +18,7 @@ BAD = {"hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown"}
 
 
 class ClockSampler:
-    def __init__(self, device_index: int = 0, period_s: float = 0.002):
+    def __init__(self, device_index: int = 0, period_s: float = 0.0005):
         self.device_index = device_index
         self.period_s = period_s
         self.samples: list[tuple[float, int, int]] = []  # (t, sm_mhz, reasons bitmask)
@@ -28,6 +28,8 @@ class ClockSampler:
         self._nvml = None
         self._handle = None
         self.backend = "none"
+        self.first_error: str | None = None  # the first exception a poll raised (round 1 swallowed them all and reported nothing)
+        self.polls = 0
 
     def start(self) -> "ClockSampler":
         try:
@@ -39,7 +41,8 @@ class ClockSampler:
             self.sm_max_mhz = int(pynvml.nvmlDeviceGetMaxClockInfo(self._handle, pynvml.NVML_CLOCK_SM))
             self.backend = "nvml"
             self._thread = threading.Thread(target=self._run_nvml, daemon=True)
-        except Exception:
+        except Exception as e:  # noqa: BLE001
+            self.first_error = f"nvml init: {type(e).__name__}: {e}"
             self.backend = "nvidia-smi"
             self._thread = threading.Thread(target=self._run_smi, daemon=True)
         self._thread.start()
@@ -55,8 +58,10 @@ class ClockSampler:
                 except Exception:
                     reasons = int(n.nvmlDeviceGetCurrentClocksThrottleReasons(self._handle))
                 self.samples.append((time.perf_counter(), mhz, reasons))
-            except Exception:
-                pass
+            except Exception as e:  # noqa: BLE001
+                if self.first_error is None:
+                    self.first_error = f"nvml poll: {type(e).__name__}: {e}"
+            self.polls += 1
             time.sleep(self.period_s)
 
     def _run_smi(self) -> None:
@@ -80,6 +85,14 @@ class ClockSampler:
         finally:
             p.kill()
 
+    def wait_for_samples(self, n: int = 1, timeout_s: float = 2.0) -> bool:
+        """Blocks until at least `n` samples exist (the first NVML query of a process can take milliseconds — longer than a
+        whole 20-step timed region)."""
+        t_end = time.perf_counter() + timeout_s
+        while len(self.samples) < n and time.perf_counter() < t_end:
+            time.sleep(0.001)
+        return len(self.samples) >= n
+
     def stop(self) -> None:
         self._stop.set()
         if self._thread:
@@ -96,11 +109,11 @@ class ClockSampler:
             window = "nearest_samples"
         if not inside:
             return {"sm_mhz": None, "sm_max_mhz": self.sm_max_mhz or None, "reasons": [], "samples": 0, "window": "none",
-                    "backend": self.backend}
+                    "backend": self.backend, "polls": self.polls, "error": self.first_error}
         mask = 0
         for s in inside:
             mask |= s[2]
         reasons = sorted(name for bit, name in _REASONS.items() if mask & bit and name != "gpu_idle")
         return {"sm_mhz": int(statistics.median(s[1] for s in inside)), "sm_max_mhz": self.sm_max_mhz or None, "reasons": reasons,
-                "samples": len(inside), "window": window, "backend": self.backend,
-                "rejected": bool(BAD & set(reasons))}
+                "samples": len(inside), "window": window, "backend": self.backend, "sm_min_mhz": int(min(s[1] for s in inside)),
+                "rejected": bool(BAD & set(reasons)), "error": self.first_error}

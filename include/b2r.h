@@ -70,11 +70,26 @@ typedef struct {
   int stages;      /* TMA ring depth; 0 = auto */
   int tile_bytes;  /* TMA tile bytes (multiple of 16*32*consumer warps); 0 = auto */
   int unroll;      /* LDG loads in flight per thread: 4 or 8; 0 = auto */
-  int pdl;         /* 1 = programmatic dependent launch: this launch may start streaming its input while the previous
-                      kernel in the stream is still finishing (it waits before touching the workspace / out). Only safe
-                      when the input is NOT produced by a kernel that signals programmatic completion early; back-to-back
-                      reductions of ready inputs are the intended use. 0 = plain stream order (default). */
+  int pdl;         /* programmatic dependent launch (PDL) between consecutive kernels of the stream:
+                        0  default: flavour 1, unless the environment says B2R_PDL=0 (then plain stream order);
+                        1  B2R_PDL_SAFE: the launch may be scheduled while the previous kernel is still finishing, but it
+                           waits for that kernel's completion (and the visibility of its writes) before its first load, so
+                           it is correct whatever produced the input. Hides launch latency only;
+                        2  B2R_PDL_INPUT_READY: the caller DECLARES that the input was complete before the previous kernel
+                           in the stream started (e.g. back-to-back reductions of buffers filled long ago). The launch
+                           streams its input while the previous kernel drains and waits only before it touches the
+                           workspace and `out`. Never implied by the environment: reading an input that the previous
+                           kernel is still writing would be a silent race;
+                       <0  off, whatever the environment says. */
+  int dyn_pct;     /* share (percent, 1..90) of the input that CTAs claim tile by tile at the end of the launch instead of by
+                      the static split: evens out CTAs that started late. 0 = auto, <0 = static split only. Ignored by the
+                      TMA variant, by clusters and by pdl = 2. Results do not depend on it for integers; for floating-point
+                      types they are bit-reproducible for a given (count, alignment, geometry, dyn_pct). */
 } b2r_launch_cfg_t;
+
+#define B2R_PDL_OFF (-1)
+#define B2R_PDL_SAFE 1
+#define B2R_PDL_INPUT_READY 2
 
 size_t b2r_dtype_size(b2r_dtype_t dtype);
 const char* b2r_status_string(b2r_status_t s);
@@ -212,8 +227,9 @@ b2r_status_t b2r_comm_check(b2r_comm_t comm, void* stream);
 /* ------------------------------------------------------------------ collectives (MPI_Reduce semantics)
  * recvbuf[j] = op over ranks r of sendbuf_r[j], j < count. b2r_reduce: valid at `root` only (recvbuf may be
  * NULL elsewhere). sendbuf is not modified unless sendbuf == recvbuf (in place). All ranks call in the same
- * order with the same count/dtype/op/root/algo. fp sums combine in ascending rank order on the P2P paths
- * (bit-reproducible); the NVLS path's order is defined by the switch. */
+ * order with the same count/dtype/op/root/algo. fp sums are deterministic on the P2P paths (bit-reproducible run to run):
+ * ascending rank order for one-shot / two-shot / push / LL, chain order (farthest rank first) for the ring, pairwise order
+ * rotated by the root for the tree; the NVLS path's order is defined by the switch. */
 b2r_status_t b2r_reduce(const void* sendbuf, void* recvbuf, uint64_t count, b2r_dtype_t dtype, b2r_op_t op, int root,
                         b2r_comm_t comm, void* stream);
 b2r_status_t b2r_allreduce(const void* sendbuf, void* recvbuf, uint64_t count, b2r_dtype_t dtype, b2r_op_t op,

@@ -38,11 +38,10 @@ int main(int argc, char** argv) {
   void* base = mmap(nullptr, tmp.total_bytes, PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
   close(fd);
   if (base == MAP_FAILED) { perror("b2r_mpirun: mmap"); shm_unlink(name.c_str()); return 2; }
-  b2r::ShmControl* ctl = new (base) b2r::ShmControl();
+  // the segment is fresh and zero-filled (barrier words, abort flag): write the layout, then publish `ready` (host_shm.cpp)
+  b2r::ShmControl* ctl = (b2r::ShmControl*)base;
   b2r::shm_layout(ctl, np, window_mb << 20, 4 << 20);
-  ctl->bar_count.store(0);
-  ctl->bar_gen.store(0);
-  ctl->abort_flag.store(0);
+  ctl->ready.store(1, std::memory_order_release);
 
   std::vector<pid_t> pids;
   for (int r = 0; r < np; ++r) {

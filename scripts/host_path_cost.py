@@ -29,7 +29,7 @@ def per_call(f):
 
 
 def main():
-    cfg = b2r.launch_config(pdl=1)
+    cfg = b2r.launch_config(pdl=b2r.PDL_INPUT_READY)
     chosen = _lib.LaunchCfg()
     rows = []
     rows.append(("trivial ctypes call (1 int argument)", per_call(lambda: _lib.LIB.b2r_dtype_size(0))))

@@ -22,7 +22,7 @@ for rep in range(2):  # first pass warms up (module load), second pass is what t
     b2r.reduce(xi, "sum", workspace=ws, cfg={"variant": "ldg128"})
     b2r.reduce(x, "min", workspace=ws, cfg={"variant": "ldg256", "cluster": 2})
     b2r.reduce(xd, "sum", workspace=ws, cfg={"variant": "tma"})
-    b2r.reduce(xb, "sum", workspace=ws, cfg={"variant": "tma", "pdl": 1})
+    b2r.reduce(xb, "sum", workspace=ws, cfg={"variant": "tma", "pdl": 2})
     b2r.reduce(xb, "max", workspace=ws, cfg={"variant": "ldg128"})
     b2r.dot(x, x, workspace=ws)
     torch.cuda.synchronize()

@@ -16,12 +16,15 @@ namespace b2r {
 //   waiter warp : polls the data flag (from the predecessor) and the slot-reuse ack (from the successor) for step i, then
 //                 publishes ready = i+1;
 //   data warps  : wait for ready > i, move their part of step i (load own + staged partial, combine, store downstream) and
-//                 add themselves to `done`; no block-wide barrier, they start step i+1 at once;
-//   signal warp : waits for done == data warps x (i+1), acks step i upstream and release-stores the data flag downstream.
+//                 publish their own progress word (steps finished); no block-wide barrier, they start step i+1 at once;
+//   signal warp : lane w watches data warp w's progress word; once EVERY data warp has finished step i it acks the step
+//                 upstream and release-stores the data flag downstream. (A single shared counter is not enough: a fast warp's
+//                 step i+1 would be counted towards step i while a slow warp is still moving it — seen as a wrong fp64 MIN at
+//                 8 ranks x 6 data warps on the first hardware run.)
 // The fence now overlaps the next steps' traffic; it only delays when the successor SEES a step, not how fast steps are
 // produced, so steps can be small and many. Same chain order, same staging slots and flag words as ring_body (results are
 // bit-identical to it and to the host restatement). Ordering: data stores -> __syncwarp -> red.release.cta(done) ->
-// ld.acquire.cta by the signal warp -> st.release.sys(flag) is one causality chain, and the mirror image on the way in.
+// ld.acquire.cta by the signal warp -> __syncwarp -> st.release.sys(flag) is one causality chain, and the mirror image on the way in.
 __device__ __forceinline__ void st_release_cta_shared(uint32_t addr, unsigned int v) {
   asm volatile("st.release.cta.shared.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
 }
@@ -56,13 +59,11 @@ __device__ void ring2_body(const CollArgs& A) {
   const unsigned int base_val = A.seq << 16;
 
   __shared__ PeerOffsets po;
-  __shared__ unsigned int s_ready, s_done;
-  if (threadIdx.x == 0) {
-    s_ready = 0;
-    s_done = 0;
-  }
+  __shared__ unsigned int s_ready, s_prog[16];  // s_prog[w]: steps data warp w has finished (blockDim <= 512: at most 14 data warps)
+  if (threadIdx.x == 0) s_ready = 0;
+  if (threadIdx.x < 16) s_prog[threadIdx.x] = 0;
   start_barrier(A, &po);  // contains __syncthreads on both sides: the counters are visible to everybody
-  const uint32_t a_ready = smem_u32(&s_ready), a_done = smem_u32(&s_done);
+  const uint32_t a_ready = smem_u32(&s_ready), a_prog = smem_u32(s_prog);
   const char* send = c.heap[r] + A.send_off;
   auto slot = [&](int rank, unsigned long long step) {
     return c.heap[rank] + A.work_off + (((step % depth) * G + b) * (unsigned long long)Cv) * 16ull;
@@ -85,8 +86,10 @@ __device__ void ring2_body(const CollArgs& A) {
   } else if (warp == ndw + 1) {
     // ---- signaller
     for (unsigned long long i = 0; i < steps; ++i) {
+      if (lane < ndw)
+        while (ld_acquire_cta_shared(a_prog + 4u * lane) < (unsigned int)(i + 1)) __nanosleep(20);
+      __syncwarp();
       if (lane == 0) {
-        while (ld_acquire_cta_shared(a_done) < ndw * (unsigned int)(i + 1)) __nanosleep(32);
         if (!c.fault_skip_signal) {
           if (pred >= 0) {  // the staged partial of step i has been read: its slot may be refilled
             unsigned int* ack = (unsigned int*)(c.heap[pred] + kOffPushAck) + (size_t)b * B2R_MAX_RANKS + r;
@@ -136,7 +139,7 @@ __device__ void ring2_body(const CollArgs& A) {
         }
       }
       __syncwarp();
-      if (lane == 0) red_release_cta_shared_add(a_done, 1u);
+      if (lane == 0) st_release_cta_shared(a_prog + 4u * warp, (unsigned int)(i + 1));
     }
   }
   __syncthreads();

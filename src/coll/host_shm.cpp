@@ -1,6 +1,7 @@
 // host_shm.cpp — see host_shm.h.
 #include "host_shm.h"
 
+#include <chrono>
 #include <errno.h>
 #include <fcntl.h>
 #include <sched.h>
@@ -10,6 +11,8 @@
 #include <unistd.h>
 
 #include <algorithm>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <vector>
@@ -74,17 +77,17 @@ b2r_status_t HostShmComm::open(const std::string& name, int rank, int nranks, si
   base_ = (char*)p;
   ctl_ = (ShmControl*)base_;
   if (create) {
-    new (ctl_) ShmControl();
+    // A fresh POSIX shm segment is zero-filled, so the barrier words and the abort flag already hold their initial value:
+    // they are NOT stored to here (an opener that raced ahead may already have arrived at the first barrier, and a late
+    // store of 0 would wipe its arrival). Only the layout is written, then `ready` is published with release semantics.
     shm_layout(ctl_, nranks, window_bytes, 4 << 20);
-    ctl_->bar_count.store(0);
-    ctl_->bar_gen.store(0);
-    ctl_->abort_flag.store(0);
-    std::atomic_thread_fence(std::memory_order_seq_cst);
+    ctl_->ready.store(1, std::memory_order_release);
   } else {
-    for (int tries = 0; ctl_->total_bytes == 0 || ctl_->nranks != nranks; ++tries) {  // creator still initialising
-      if (tries > 4000) return fail(B2R_ERR_TIMEOUT, "host comm: segment %s was never initialised for %d ranks", name.c_str(), nranks);
+    for (int tries = 0; ctl_->ready.load(std::memory_order_acquire) == 0; ++tries) {  // creator still initialising
+      if (tries > 4000) return fail(B2R_ERR_TIMEOUT, "host comm: segment %s was never initialised", name.c_str());
       usleep(5000);
     }
+    if (ctl_->nranks != nranks) return fail(B2R_ERR_INVALID, "host comm: segment %s was created for %d ranks, not %d", name.c_str(), ctl_->nranks, nranks);
   }
   return B2R_OK;
 }
@@ -109,10 +112,20 @@ void HostShmComm::barrier() {
     ctl_->bar_count.store(0, std::memory_order_relaxed);
     ctl_->bar_gen.fetch_add(1, std::memory_order_release);
   } else {
+    // deadline: a peer that died (or never came) must not hang the survivors forever (B2R_HOST_BARRIER_TIMEOUT_S, default 600)
+    static const double limit_s = [] { const char* v = getenv("B2R_HOST_BARRIER_TIMEOUT_S"); return v && *v ? atof(v) : 600.0; }();
+    const auto t0 = std::chrono::steady_clock::now();
     unsigned spins = 0;
     while (ctl_->bar_gen.load(std::memory_order_acquire) == gen) {
       if (aborted()) _exit(3);
-      if (++spins > 2000) sched_yield();
+      if (++spins > 2000) {
+        sched_yield();
+        if ((spins & 0xfff) == 0 && limit_s > 0 && std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count() > limit_s) {
+          fprintf(stderr, "b2r host comm: rank %d waited %.0f s in a barrier; a peer is gone, aborting the job\n", rank_, limit_s);
+          abort();
+          _exit(3);
+        }
+      }
     }
   }
 }

@@ -13,6 +13,7 @@ namespace b2r {
 
 struct ShmControl {
   std::atomic<unsigned> bar_count, bar_gen, abort_flag;
+  std::atomic<unsigned> ready;  // 0 in a fresh (zero-filled) segment; the creator release-stores 1 as the LAST step of its set-up
   int nranks;
   size_t window_bytes;                                 // per-rank staging for collectives
   size_t off_windows, off_results, off_work, off_p2p;  // byte offsets from the segment base

@@ -87,9 +87,23 @@ b2r_status_t b2r_fill_device(void* dst, uint64_t count, b2r_dtype_t dtype, uint6
 
 b2r_status_t b2r_dot_local(const void* a, const void* b, void* out, uint64_t count, b2r_dtype_t dtype,
                            b2r_workspace_t ws, void* stream_) {
+  // same contract as b2r_reduce_local: validated up front, launched on the workspace's device whatever the caller's current
+  // device is, and recorded as the workspace's last output so that a following reduction of `out` never overlaps with it
   B2R_REQUIRE(ws != nullptr && out != nullptr, "b2r_dot_local: NULL argument");
   B2R_REQUIRE((a && b) || count == 0, "b2r_dot_local: NULL input");
+  B2R_REQUIRE(dtype >= B2R_INT32 && dtype <= B2R_BFLOAT16, "b2r_dot_local: bad dtype %d", (int)dtype);
+  const size_t esz = b2r_dtype_size(dtype);
+  B2R_REQUIRE(((uintptr_t)a % esz) == 0 && ((uintptr_t)b % esz) == 0 && ((uintptr_t)out % esz) == 0,
+              "b2r_dot_local: pointers must be aligned to the element size %zu", esz);
   cudaStream_t stream = (cudaStream_t)stream_;
+  int cur = -1;
+  B2R_CUDA_CHECK(cudaGetDevice(&cur));
+  struct DeviceGuard {
+    int prev;
+    bool active;
+    ~DeviceGuard() { if (active) cudaSetDevice(prev); }
+  } guard{cur, cur != ws->device};
+  if (guard.active) B2R_CUDA_CHECK(cudaSetDevice(ws->device));
   LocalParams p;
   memset(&p, 0, sizeof(p));
   p.n = count;
@@ -104,9 +118,10 @@ b2r_status_t b2r_dot_local(const void* a, const void* b, void* out, uint64_t cou
     case B2R_FLOAT32: dot_kernel<B2R_FLOAT32><<<blocks, threads, 0, stream>>>(a, b, p); break;
     case B2R_FLOAT64: dot_kernel<B2R_FLOAT64><<<blocks, threads, 0, stream>>>(a, b, p); break;
     case B2R_BFLOAT16: dot_kernel<B2R_BFLOAT16><<<blocks, threads, 0, stream>>>(a, b, p); break;
-    default: return fail(B2R_ERR_INVALID, "b2r_dot_local: bad dtype %d", (int)dtype);
   }
   B2R_CUDA_CHECK(cudaGetLastError());
+  ws->last_out = out;
+  ws->last_ctas = blocks;
   return B2R_OK;
 }
 

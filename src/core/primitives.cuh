@@ -157,6 +157,7 @@ struct Reducer<B2R_INT32, O> {
   using F = OpI32<O>;
   static constexpr int kElemBytes = 4;
   static constexpr bool kIsInt = true;
+  static constexpr bool kPackedSum = (O == B2R_SUM);  // grid stage in one 64-bit atomic (finish_grid_packed)
   struct Thread {
     int32_t a[4];
     __device__ __forceinline__ void init() {
@@ -181,6 +182,7 @@ struct Reducer<B2R_FLOAT32, O> {
   using F = OpF32<O>;
   static constexpr int kElemBytes = 4;
   static constexpr bool kIsInt = false;
+  static constexpr bool kPackedSum = false;
   struct Thread {
     float a[4];
     __device__ __forceinline__ void init() {
@@ -205,6 +207,7 @@ struct Reducer<B2R_FLOAT64, O> {
   using F = OpF64<O>;
   static constexpr int kElemBytes = 8;
   static constexpr bool kIsInt = false;
+  static constexpr bool kPackedSum = false;
   struct Thread {
     double a[2];
     __device__ __forceinline__ void init() { a[0] = a[1] = F::identity(); }
@@ -228,6 +231,7 @@ struct Reducer<B2R_BFLOAT16, B2R_SUM> {
   using F = OpF32<B2R_SUM>;
   static constexpr int kElemBytes = 2;
   static constexpr bool kIsInt = false;
+  static constexpr bool kPackedSum = false;
   struct Thread {
     float a[8];
     __device__ __forceinline__ void init() {
@@ -258,6 +262,7 @@ struct Reducer<B2R_BFLOAT16, O> {
   using F = OpF32<O>;
   static constexpr int kElemBytes = 2;
   static constexpr bool kIsInt = false;
+  static constexpr bool kPackedSum = false;
   __device__ __forceinline__ static uint32_t packed_identity() { return O == B2R_MIN ? 0x7f807f80u : 0xff80ff80u; }
   __device__ __forceinline__ static uint32_t apply2(uint32_t a, uint32_t b) {
     uint32_t r;

@@ -42,7 +42,14 @@ struct LocalParams {
   int stages;                 // TMA ring depth
   int tile_vecs;              // TMA tile size in 16-byte vectors
   int out_as_acc;             // store the scalar as acc_t (fp32 for bf16) instead of the input dtype
-  int pdl;                    // launched with programmatic stream serialization (see b2r_launch_cfg_t.pdl)
+  int pdl;                    // 0 plain; 1 programmatic launch, wait before the first load; 2 wait only before the workspace
+                              // (caller declared the input complete; see b2r_launch_cfg_t.pdl)
+  unsigned* tile_ctr;         // dynamic tail: next unclaimed tile (zero between launches, re-armed with the ticket)
+  uint64_t dyn_first;         // dynamic tail: first vector of the dynamically scheduled region (== nvec: none)
+  unsigned dyn_tile_vecs;     // dynamic tail: vectors per tile (multiple of blockDim.x)
+  unsigned dyn_ntiles;        // dynamic tail: number of tiles
+  unsigned long long* acc64;  // int32 SUM: packed {arrivals << 48 | running sum} accumulator, zero between launches (nullptr: use partials)
+  unsigned prefetch_lines;    // pdl == 1: 128-byte lines per thread to pull into L2 while waiting for the previous kernel (0 = none)
 };
 
 // CTA c of G gets vectors [split(c), split(c+1)); boundaries are multiples of `align` vectors (128 bytes).
@@ -53,14 +60,19 @@ __device__ __forceinline__ uint64_t split_point(uint64_t nvec, unsigned G, unsig
   return s - (s % align);
 }
 
-// Programmatic dependent launch: let the next kernel of the stream start while we are still running ...
+// Programmatic dependent launch: let the next kernel of the stream be scheduled while we are still running ...
 __device__ __forceinline__ void pdl_launch_dependents(const LocalParams& p) {
   if (p.pdl) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 }
-// ... and, as the dependent, wait for the previous kernel (and the visibility of its writes) before touching
-// anything it may still be using: the shared workspace (partials, ticket) and `out`.
+// ... and, as the dependent, wait for the previous kernel (and the visibility of its writes). Default flavour (pdl == 1):
+// before the FIRST LOAD, so an input written by the preceding kernel is read correctly whatever that kernel is — only launch
+// latency and the prologue overlap. Flavour 2 (the caller declared the input complete before the previous kernel started):
+// the input is streamed first and the wait comes just before the shared workspace (partials, ticket) and `out` are touched.
+__device__ __forceinline__ void pdl_wait_before_input(const LocalParams& p) {
+  if (p.pdl == 1) asm volatile("griddepcontrol.wait;" ::: "memory");
+}
 __device__ __forceinline__ void pdl_wait_prior(const LocalParams& p) {
-  if (p.pdl) asm volatile("griddepcontrol.wait;" ::: "memory");
+  if (p.pdl == 2) asm volatile("griddepcontrol.wait;" ::: "memory");
 }
 
 template <class R>
@@ -72,13 +84,14 @@ __device__ __forceinline__ void store_result(const LocalParams& p, typename R::a
 // Scalar-sharded reduce across GPUs, fused into the tail of the local reduction (one kernel per rank; the vendored
 // simpleMultiGPU copies per-GPU partials to the host and sums there, simpleMultiGPU.cpp:264-293). Called by ALL threads
 // of the CTA that holds this rank's scalar (`a` is valid in thread 0):
-//   post   : thread 0 stores the partial into the root's mailbox over NVLink, then release-stores the call number;
-//   root   : thread r acquires rank r's call number and fetches its partial (P waits in parallel), thread 0 combines the
-//            partials in rank order (deterministic) and writes `out`, then thread r pushes the ack (and, for the
-//            allreduce flavour, the result) to rank r — P release-stores in parallel cost ONE NVLink round trip, where
-//            a loop in one thread would cost P of them;
-//   others : with `all`, thread 0 waits for the pushed result.
-// Mailbox slots are double-buffered by call parity; a rank may run at most one call ahead of the root's ack.
+//   post   : thread 0 stores the partial into the root's mailbox over NVLink as ONE self-flagged 16-byte packet (XgPacket)
+//            and is done — no fence, no wait on the exit path of a non-root rank;
+//   root   : thread r polls rank r's packet of this call (P waits in parallel, all on local memory), thread 0 combines the
+//            partials in rank order (deterministic) and writes `out`, then thread r pushes the result packet (allreduce
+//            flavour) and the acknowledgement to rank r — P stores in parallel cost one NVLink trip, not P;
+//   others : with `all`, thread 0 waits for the result packet.
+// Slots rotate over kXgSlots calls; a rank may run up to kXgSlots calls ahead of the root's acknowledgement, so in a stream of
+// back-to-back calls the root finds the packets already there and nobody waits for anybody.
 template <class R>
 __device__ __forceinline__ void xgpu_finish(const LocalParams& p, typename R::acc_t a) {
   using acc_t = typename R::acc_t;
@@ -87,7 +100,7 @@ __device__ __forceinline__ void xgpu_finish(const LocalParams& p, typename R::ac
   __shared__ unsigned long long s_res;
   __shared__ int s_fail;
   const CollCtx& c = *p.xg_ctx;
-  const unsigned seq = p.xg_seq, slot = seq & 1u;
+  const unsigned seq = p.xg_seq, slot = seq % (unsigned)kXgSlots;
   const int P = c.nranks, me = c.rank, root = p.xg_root;
   XgMailbox* my_mb = (XgMailbox*)(c.heap[me] + kOffMailbox);
   auto to_bits = [](acc_t v) -> unsigned long long {
@@ -103,11 +116,11 @@ __device__ __forceinline__ void xgpu_finish(const LocalParams& p, typename R::ac
   if (threadIdx.x == 0) {
     s_fail = 0;
     fault_delay(c);
-    if (seq >= 3 && !wait_flag_ge(&my_mb->ack, seq - 2, c)) s_fail = 1;  // slot still unread by the root
+    // the slot was last used by call seq - kXgSlots: the root must have read it
+    if (seq > (unsigned)kXgSlots && !wait_flag_ge(&my_mb->ack, seq - (unsigned)kXgSlots, c)) s_fail = 1;
     else if (!c.fault_skip_signal) {
       XgMailbox* root_mb = (XgMailbox*)(c.heap[root] + kOffMailbox);
-      st_relaxed_sys_u64(&root_mb->val[slot][me], to_bits(a));
-      st_release_sys(&root_mb->flag[me], seq);
+      xg_post(&root_mb->val[slot][me], to_bits(a), seq);
     }
   }
   if (me != root && !p.xg_all) return;
@@ -115,7 +128,8 @@ __device__ __forceinline__ void xgpu_finish(const LocalParams& p, typename R::ac
   if (s_fail) return;
   if (me == root) {
     if (threadIdx.x < (unsigned)P) {
-      if (wait_flag_ge(&my_mb->flag[threadIdx.x], seq, c)) s_vals[threadIdx.x] = ld_relaxed_sys_u64(&my_mb->val[slot][threadIdx.x]);
+      unsigned long long bits = 0;
+      if (xg_wait(&my_mb->val[slot][threadIdx.x], seq, c, &bits)) s_vals[threadIdx.x] = bits;
       else s_fail = 1;
     }
     __syncthreads();
@@ -129,14 +143,13 @@ __device__ __forceinline__ void xgpu_finish(const LocalParams& p, typename R::ac
     __syncthreads();
     if (threadIdx.x < (unsigned)P) {
       XgMailbox* mb = (XgMailbox*)(c.heap[threadIdx.x] + kOffMailbox);
-      if (p.xg_all) {
-        st_relaxed_sys_u64(&mb->result[slot], s_res);
-        st_release_sys(&mb->result_flag, seq);
-      }
+      if (p.xg_all) xg_post(&mb->result[slot], s_res, seq);
+      // release: this thread's read of the slot (program order, then bar.sync) is complete before the slot may be reused
       st_release_sys(&mb->ack, seq);
     }
   } else if (threadIdx.x == 0) {
-    if (wait_flag_ge(&my_mb->result_flag, seq, c)) store_result<R>(p, from_bits(ld_relaxed_sys_u64(&my_mb->result[slot])));
+    unsigned long long bits = 0;
+    if (xg_wait(&my_mb->result[slot], seq, c, &bits)) store_result<R>(p, from_bits(bits));
   }
 }
 
@@ -147,6 +160,75 @@ __device__ __forceinline__ void finish_scalar(const LocalParams& p, typename R::
   else if (threadIdx.x == 0) store_result<R>(p, v);
 }
 
+// int32 SUM only: the grid stage in ONE atomic. The accumulator word carries the arrival count in its top 16 bits and the
+// running sum of the partials (each taken as an unsigned 32-bit value; at most 2^16 of them, so the sum stays below 2^48 and
+// never carries into the count) below. The returned old value tells the last arriver both that it is last and what the
+// others added up to; the wrapped 32-bit total is the low word. Integer addition is exact in any order, so this is still
+// bit-exact. It replaces store-partial / ticket / re-read all partials / second block reduce: one L2 round trip instead of
+// three on the exit path of every launch. The values travel inside the atomic itself, so it can be relaxed.
+__device__ __forceinline__ unsigned long long atom_add_relaxed_gpu_u64(unsigned long long* p, unsigned long long v) {
+  unsigned long long old;
+  asm volatile("atom.relaxed.gpu.global.add.u64 %0, [%1], %2;" : "=l"(old) : "l"(p), "l"(v) : "memory");
+  return old;
+}
+template <class R>
+__device__ __forceinline__ void finish_grid_packed(const LocalParams& p, unsigned narrivals, int v) {
+  __shared__ int s_last, s_total;
+  if (threadIdx.x == 0) {
+    const unsigned long long mine = (1ull << 48) | (unsigned long long)(unsigned int)v;
+    const unsigned long long old = atom_add_relaxed_gpu_u64(p.acc64, mine);
+    s_last = (unsigned)(old >> 48) == narrivals - 1;
+    if (s_last) {
+      s_total = (int)(unsigned int)(old + mine);
+      *p.acc64 = 0;  // re-arm for the next (stream-ordered) launch
+      if (p.tile_ctr) *p.tile_ctr = 0;
+    }
+  }
+  __syncthreads();
+  if (s_last) finish_scalar<R>(p, (typename R::acc_t)s_total);
+  if (p.trace && threadIdx.x == 0) p.trace[4 * blockIdx.x + 3] = globaltimer_ns();
+}
+
+// Safe programmatic launch (pdl == 1): the CTA is resident before the previous kernel of the stream has finished and has
+// nothing to do until griddepcontrol.wait returns. Pulling the head of its slice into L2 meanwhile is harmless whatever the
+// previous kernel is doing to the buffer — L2 is the coherence point of device memory, a line prefetched early simply
+// receives the producer's later writes — and it puts the HBM channels to work during the previous kernel's exit path.
+__device__ __forceinline__ void prefetch_l2_range(const char* base, uint64_t bytes, unsigned lines_per_thread) {
+  for (unsigned j = 0; j < lines_per_thread; ++j) {
+    const uint64_t off = ((uint64_t)threadIdx.x + (uint64_t)j * blockDim.x) * 128ull;
+    if (off < bytes) asm volatile("prefetch.global.L2 [%0];" ::"l"(base + off));
+  }
+}
+
+// Grid stage: every CTA (or cluster leader) that calls this has already stored its partial(s); it takes a ticket with
+// atom.acq_rel.gpu (release ours, acquire everybody else's if we turn out to be last), and the last arriver re-reduces
+// partials[0, nparts) in index order, re-arms the ticket (and the dynamic-tile counter) and finishes the scalar.
+template <class R>
+__device__ __forceinline__ void finish_grid(const LocalParams& p, unsigned nparts, unsigned narrivals, typename R::acc_t* s_scratch) {
+  using acc_t = typename R::acc_t;
+  using F = typename R::F;
+  __shared__ int s_is_last;
+  acc_t* partials = (acc_t*)p.partials;
+  if (threadIdx.x == 0) {
+    unsigned t = atom_add_acq_rel_gpu(p.ticket, 1u);
+    s_is_last = (t == narrivals - 1);
+  }
+  __syncthreads();
+  if (!s_is_last) {
+    if (p.trace && threadIdx.x == 0) p.trace[4 * blockIdx.x + 3] = globaltimer_ns();
+    return;
+  }
+  acc_t a = F::identity();
+  for (unsigned i = threadIdx.x; i < nparts; i += blockDim.x) a = F::apply(a, ld_cg(partials + i));
+  a = block_reduce<R>(a, s_scratch);
+  if (threadIdx.x == 0) {  // re-arm for the next (stream-ordered) launch
+    *p.ticket = 0;
+    if (p.tile_ctr) *p.tile_ctr = 0;
+  }
+  finish_scalar<R>(p, a);
+  if (p.trace && threadIdx.x == 0) p.trace[4 * blockIdx.x + 3] = globaltimer_ns();
+}
+
 // Everything after the streaming loop. `tv` is the per-thread value.
 template <class R, bool CLUSTER>
 __device__ __forceinline__ void finish_block(typename R::acc_t tv, const LocalParams& p) {
@@ -154,7 +236,6 @@ __device__ __forceinline__ void finish_block(typename R::acc_t tv, const LocalPa
   using F = typename R::F;
   __shared__ acc_t s_scratch[32];
   __shared__ acc_t s_cluster[8];
-  __shared__ int s_is_last;
 
   acc_t v = block_reduce<R>(tv, s_scratch);
   pdl_wait_prior(p);
@@ -183,25 +264,14 @@ __device__ __forceinline__ void finish_block(typename R::acc_t tv, const LocalPa
     if (p.trace && threadIdx.x == 0) p.trace[4 * blockIdx.x + 3] = globaltimer_ns();
     return;
   }
-
-  acc_t* partials = (acc_t*)p.partials;
-  if (threadIdx.x == 0) {
-    partials[part] = v;
-    // release our partial, acquire everybody else's if we turn out to be last
-    unsigned t = atom_add_acq_rel_gpu(p.ticket, 1u);
-    s_is_last = (t == nparts - 1);
+  if constexpr (R::kPackedSum) {
+    if (p.acc64) {
+      finish_grid_packed<R>(p, nparts, (int)v);
+      return;
+    }
   }
-  __syncthreads();
-  if (!s_is_last) {
-    if (p.trace && threadIdx.x == 0) p.trace[4 * blockIdx.x + 3] = globaltimer_ns();
-    return;
-  }
-  acc_t a = F::identity();
-  for (unsigned i = threadIdx.x; i < nparts; i += blockDim.x) a = F::apply(a, ld_cg(partials + i));
-  a = block_reduce<R>(a, s_scratch);
-  if (threadIdx.x == 0) *p.ticket = 0;  // re-arm for the next (stream-ordered) launch
-  finish_scalar<R>(p, a);
-  if (p.trace && threadIdx.x == 0) p.trace[4 * blockIdx.x + 3] = globaltimer_ns();
+  if (threadIdx.x == 0) ((acc_t*)p.partials)[part] = v;
+  finish_grid<R>(p, nparts, nparts, s_scratch);
 }
 
 // Head/tail scalars (fewer than one vector each) are folded in by CTA 0.
@@ -216,26 +286,12 @@ __device__ __forceinline__ void add_edges(typename R::Thread& acc, const LocalPa
 }
 
 // ------------------------------------------------------------------------------------------------ LDG variant
-template <int D, int O, int VECW, int UNROLL, bool CLUSTER>
-__device__ __forceinline__ void reduce_ldg_body(const LocalParams& p) {
-  using R = Reducer<D, O>;
-  using Vec = typename std::conditional<VECW == 8, V32, V16>::type;
-  constexpr unsigned kAlign = 128 / sizeof(Vec);
-
-  pdl_launch_dependents(p);
-  if (p.trace && threadIdx.x == 0) p.trace[4 * blockIdx.x + 0] = globaltimer_ns();
-
-  typename R::Thread acc;
-  acc.init();
-
-  const Vec* __restrict__ vp = (const Vec*)((const char*)p.in + p.head * R::kElemBytes);
-  const uint64_t lo = split_point(p.nvec, gridDim.x, blockIdx.x, kAlign);
-  const uint64_t hi = split_point(p.nvec, gridDim.x, blockIdx.x + 1, kAlign);
+// One pass over vectors [lo, hi) of the body: UNROLL independent vector loads are issued back to back, then consumed
+// (UNROLL * sizeof(Vec) bytes in flight per thread).
+template <class R, class Vec, int VECW, int UNROLL>
+__device__ __forceinline__ void stream_range(typename R::Thread& acc, const Vec* __restrict__ vp, uint64_t lo, uint64_t hi) {
   const unsigned nt = blockDim.x;
-
   uint64_t i = lo + threadIdx.x;
-  // UNROLL independent vector loads are issued back to back, then consumed: UNROLL*sizeof(Vec) bytes in
-  // flight per thread.
   for (; i + (uint64_t)(UNROLL - 1) * nt < hi; i += (uint64_t)UNROLL * nt) {
     Vec v[UNROLL];
 #pragma unroll
@@ -251,15 +307,102 @@ __device__ __forceinline__ void reduce_ldg_body(const LocalParams& p) {
     acc.add16(v.w);
     if (VECW == 8) acc.add16(v.w + 4);
   }
-  add_edges<R>(acc, p, p.nvec * (sizeof(Vec) / R::kElemBytes));
-  if (p.trace && threadIdx.x == 0) p.trace[4 * blockIdx.x + 1] = globaltimer_ns();
+}
 
-  finish_block<R, CLUSTER>(acc.collapse(), p);
+// DYN = false: every CTA owns one contiguous slice (balanced static split) and that is all.
+// DYN = true : the static split covers only vectors [0, dyn_first); the rest is cut into tiles that CTAs claim with an atomic
+//   counter as they run out of work, so CTAs that were scheduled late or sit behind a slow HBM channel do not set the kernel's
+//   duration (trace of the static version at 64 MiB: streaming ended between 9.2 and 12.3 us across CTAs). Most of the input
+//   still streams without any block-wide barrier; only the tail pays one bar.sync per tile, and the next tile index is always
+//   requested one tile ahead so the atomic's latency is hidden.
+//   Determinism: integer results do not depend on who adds what, so an integer CTA keeps accumulating in its registers. A
+//   floating-point CTA writes one partial for its static slice and one partial PER TILE (partials[G + tile]); the last
+//   arriver folds all of them in index order, so the bits do not depend on which CTA happened to claim which tile.
+template <int D, int O, int VECW, int UNROLL, bool CLUSTER, bool DYN>
+__device__ __forceinline__ void reduce_ldg_body(const LocalParams& p) {
+  using R = Reducer<D, O>;
+  using acc_t = typename R::acc_t;
+  using Vec = typename std::conditional<VECW == 8, V32, V16>::type;
+  constexpr unsigned kAlign = 128 / sizeof(Vec);
+
+  pdl_launch_dependents(p);
+  const Vec* __restrict__ vp = (const Vec*)((const char*)p.in + p.head * R::kElemBytes);
+  const uint64_t nstatic = DYN ? p.dyn_first : p.nvec;
+  const uint64_t lo = split_point(nstatic, gridDim.x, blockIdx.x, kAlign);
+  const uint64_t hi = split_point(nstatic, gridDim.x, blockIdx.x + 1, kAlign);
+  if (p.pdl == 1 && p.prefetch_lines) prefetch_l2_range((const char*)(vp + lo), (hi - lo) * sizeof(Vec), p.prefetch_lines);
+  pdl_wait_before_input(p);
+  if (p.trace && threadIdx.x == 0) p.trace[4 * blockIdx.x + 0] = globaltimer_ns();
+
+  typename R::Thread acc;
+  acc.init();
+
+  if (!DYN) {
+    stream_range<R, Vec, VECW, UNROLL>(acc, vp, lo, hi);
+    add_edges<R>(acc, p, p.nvec * (sizeof(Vec) / R::kElemBytes));
+    if (p.trace && threadIdx.x == 0) p.trace[4 * blockIdx.x + 1] = globaltimer_ns();
+    finish_block<R, CLUSTER>(acc.collapse(), p);
+    return;
+  }
+
+  __shared__ acc_t s_scratch[32];
+  __shared__ unsigned s_next[2];
+  const unsigned G = gridDim.x, ntiles = p.dyn_ntiles;
+  // claim the first tile now: the answer is needed only after the static slice
+  if (threadIdx.x == 0) s_next[0] = atomicAdd(p.tile_ctr, 1u);
+  stream_range<R, Vec, VECW, UNROLL>(acc, vp, lo, hi);
+  add_edges<R>(acc, p, p.nvec * (sizeof(Vec) / R::kElemBytes));
+  acc_t* partials = (acc_t*)p.partials;
+  if (!R::kIsInt) {
+    const acc_t v = block_reduce<R>(acc.collapse(), s_scratch);
+    if (threadIdx.x == 0) partials[blockIdx.x] = v;
+    acc.init();
+  }
+  __syncthreads();  // publishes s_next[0]
+  unsigned tile = s_next[0];
+  int buf = 1;
+  while (tile < ntiles) {
+    if (threadIdx.x == 0) s_next[buf] = atomicAdd(p.tile_ctr, 1u);
+    const uint64_t tlo = p.dyn_first + (uint64_t)tile * p.dyn_tile_vecs;
+    const uint64_t thi = tile + 1 == ntiles ? p.nvec : tlo + (uint64_t)p.dyn_tile_vecs;  // the last tile takes the alignment slack
+    stream_range<R, Vec, VECW, UNROLL>(acc, vp, tlo, thi);
+    if (!R::kIsInt) {
+      const acc_t v = block_reduce<R>(acc.collapse(), s_scratch);
+      if (threadIdx.x == 0) partials[G + tile] = v;
+      acc.init();
+    }
+    __syncthreads();
+    tile = s_next[buf];
+    buf ^= 1;
+  }
+  if (p.trace && threadIdx.x == 0) p.trace[4 * blockIdx.x + 1] = globaltimer_ns();
+  unsigned nparts = G + ntiles;
+  if (R::kIsInt) {
+    const acc_t v = block_reduce<R>(acc.collapse(), s_scratch);
+    if (p.trace && threadIdx.x == 0) p.trace[4 * blockIdx.x + 2] = globaltimer_ns();
+    if constexpr (R::kPackedSum) {
+      if (p.acc64) {
+        finish_grid_packed<R>(p, G, (int)v);
+        return;
+      }
+    }
+    if (threadIdx.x == 0) partials[blockIdx.x] = v;
+    nparts = G;
+  } else if (p.trace && threadIdx.x == 0) {
+    p.trace[4 * blockIdx.x + 2] = globaltimer_ns();
+  }
+  finish_grid<R>(p, nparts, G, s_scratch);
 }
 
 template <int D, int O, int VECW, int UNROLL, bool CLUSTER>
 __global__ void __launch_bounds__(512) reduce_ldg_kernel(const __grid_constant__ LocalParams p) {
-  reduce_ldg_body<D, O, VECW, UNROLL, CLUSTER>(p);
+  reduce_ldg_body<D, O, VECW, UNROLL, CLUSTER, false>(p);
+}
+
+// The same streaming loop with the dynamically scheduled tail (plain stream order, no cluster).
+template <int D, int O, int VECW, int UNROLL>
+__global__ void __launch_bounds__(512) reduce_ldg_dyn_kernel(const __grid_constant__ LocalParams p) {
+  reduce_ldg_body<D, O, VECW, UNROLL, false, true>(p);
 }
 
 // Loopback flavour: gridDim.y virtual ranks in ONE (cooperative) launch, blockIdx.y picks the rank's parameters, so the
@@ -270,7 +413,7 @@ struct MultiLocalParams {
 };
 template <int D, int O>
 __global__ void __launch_bounds__(512) reduce_ldg_multi_kernel(const __grid_constant__ MultiLocalParams mp) {
-  reduce_ldg_body<D, O, 4, 4, false>(mp.p[blockIdx.y]);
+  reduce_ldg_body<D, O, 4, 4, false, false>(mp.p[blockIdx.y]);
 }
 
 // ------------------------------------------------------------------------------------------------ TMA (bulk-copy) variant
@@ -283,6 +426,7 @@ __global__ void __launch_bounds__(512) reduce_tma_kernel(const __grid_constant__
   extern __shared__ __align__(128) unsigned char smem[];
 
   pdl_launch_dependents(p);
+  pdl_wait_before_input(p);
   if (p.trace && threadIdx.x == 0) p.trace[4 * blockIdx.x + 0] = globaltimer_ns();
 
   const int stages = p.stages;
@@ -366,7 +510,8 @@ struct LaunchGeom {
   int cluster;   // >= 1
   int unroll;    // 4 or 8
   int smem_bytes;
-  int pdl;
+  int pdl;       // 0 plain, 1 programmatic launch (wait before input), 2 programmatic launch with early streaming
+  int dyn_pct;   // share of the body (percent) scheduled dynamically at the end; 0 = static split only
 };
 
 template <int D>

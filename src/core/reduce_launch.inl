@@ -29,9 +29,21 @@ KernelFn pick_kernel(const LaunchGeom& g) {
   return nullptr;
 }
 
+// the dynamically scheduled tail exists for the register-streaming variants without clusters
+template <int D, int O>
+KernelFn pick_dyn_kernel(const LaunchGeom& g) {
+  switch (g.variant) {
+    case B2R_VARIANT_LDG128:
+      return g.unroll == 8 ? (KernelFn)reduce_ldg_dyn_kernel<D, O, 4, 8> : (KernelFn)reduce_ldg_dyn_kernel<D, O, 4, 4>;
+    case B2R_VARIANT_LDG256:
+      return (KernelFn)reduce_ldg_dyn_kernel<D, O, 8, 4>;
+  }
+  return nullptr;
+}
+
 template <int D, int O>
 b2r_status_t launch_op(const LaunchGeom& g, const LocalParams& p, cudaStream_t stream) {
-  KernelFn k = g.cluster > 1 ? pick_kernel<D, O, true>(g) : pick_kernel<D, O, false>(g);
+  KernelFn k = g.dyn_pct > 0 ? pick_dyn_kernel<D, O>(g) : (g.cluster > 1 ? pick_kernel<D, O, true>(g) : pick_kernel<D, O, false>(g));
   if (!k) return fail(B2R_ERR_INVALID, "launch_local: bad variant %d", g.variant);
   if (g.smem_bytes > 48 * 1024) {
     // opt in to large dynamic shared memory once per (kernel, device)

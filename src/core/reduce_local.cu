@@ -22,7 +22,7 @@ namespace b2r {
 namespace {
 
 struct Tuned {
-  int variant, threads, ctas_per_sm, cluster, unroll, stages, tile_bytes;
+  int variant, threads, ctas_per_sm, cluster, unroll, stages, tile_bytes, dyn_pct;
 };
 
 // Defaults measured on B200 (profiles/local_sweep.md); every field can be overridden per call through
@@ -33,13 +33,19 @@ struct Tuned {
 //  * smaller inputs are dominated by launch/ramp/tail (~7 us fixed): plain stream order likes many resident
 //    threads (512 x 4 per SM); with programmatic dependent launch ONE CTA per SM is best, because the next
 //    kernel's CTAs can become resident while this one drains (9.25 us vs 16.4 us per 64 MiB launch).
-Tuned tuned_defaults(b2r_dtype_t dtype, b2r_op_t op, uint64_t bytes, int pdl) {
+//  * `early` = programmatic launch with early streaming (cfg.pdl = 2); the safe flavour (wait before the first load) does
+//    not overlap the streaming of consecutive kernels, so it takes the plain-order geometry.
+//  * plain order at 8 MiB - 256 MiB: the last quarter of the input is claimed tile by tile (reduce_ldg_body<DYN>), which
+//    removes the tail skew between CTAs (profiles/single_gpu.md, "dynamic tail").
+Tuned tuned_defaults(b2r_dtype_t dtype, b2r_op_t op, uint64_t bytes, int early) {
   (void)op;
   (void)dtype;
+  const int pdl = early;
   Tuned t;
   t.cluster = 1;
   t.unroll = 4;
   t.tile_bytes = 0;
+  t.dyn_pct = 0;
   if (bytes >= (256ull << 20)) {
     t.variant = B2R_VARIANT_TMA;
     t.threads = 160;
@@ -55,6 +61,7 @@ Tuned tuned_defaults(b2r_dtype_t dtype, b2r_op_t op, uint64_t bytes, int pdl) {
     t.threads = 512;
     t.ctas_per_sm = 4;
     t.stages = 4;
+    if (bytes >= (8ull << 20)) t.dyn_pct = 25;
   }
   return t;
 }
@@ -64,13 +71,18 @@ Tuned tuned_defaults(b2r_dtype_t dtype, b2r_op_t op, uint64_t bytes, int pdl) {
 b2r_status_t plan_local(uint64_t count, b2r_dtype_t dtype, b2r_op_t op, int sm_count, const b2r_launch_cfg_t* hint,
                         LaunchGeom* g, int* stages, int* tile_vecs) {
   const uint64_t bytes = count * b2r_dtype_size(dtype);
-  int pdl = B2R_ENV_INT("B2R_PDL", 0);  // cached: see util/env.h
-  if (hint && hint->pdl) pdl = hint->pdl > 0;
-  Tuned t = tuned_defaults(dtype, op, bytes, pdl);
+  // PDL flavour: the environment can only ask for the safe one (wait before the first load); early streaming is a promise
+  // about the input that only the caller can make, per call (b2r_launch_cfg_t.pdl = B2R_PDL_INPUT_READY)
+  // The safe flavour is the DEFAULT (B2R_PDL=0 switches it off): it is correct after any producer, and back-to-back launches
+  // stop paying the full kernel boundary (64 MiB int32 SUM: 16.4 us per launch without it, 13.8 with it).
+  int pdl = B2R_ENV_INT("B2R_PDL", 1) > 0 ? B2R_PDL_SAFE : 0;  // cached: see util/env.h
+  if (hint && hint->pdl) pdl = hint->pdl < 0 ? 0 : (hint->pdl >= B2R_PDL_INPUT_READY ? B2R_PDL_INPUT_READY : B2R_PDL_SAFE);
+  const int early = pdl == B2R_PDL_INPUT_READY;
+  Tuned t = tuned_defaults(dtype, op, bytes, early);
   if (hint && hint->variant && hint->variant != t.variant) {
     // a forced variant keeps its own sensible geometry
-    if (hint->variant == B2R_VARIANT_TMA) { t.threads = pdl ? 288 : 160; t.ctas_per_sm = pdl ? 1 : 3; t.stages = 4; }
-    else { t.threads = 512; t.ctas_per_sm = pdl ? 1 : 4; }
+    if (hint->variant == B2R_VARIANT_TMA) { t.threads = early ? 288 : 160; t.ctas_per_sm = early ? 1 : 3; t.stages = 4; t.dyn_pct = 0; }
+    else { t.threads = 512; t.ctas_per_sm = early ? 1 : 4; }
   }
   t.variant = B2R_ENV_INT("B2R_VARIANT", t.variant);
   t.threads = B2R_ENV_INT("B2R_THREADS", t.threads);
@@ -78,11 +90,13 @@ b2r_status_t plan_local(uint64_t count, b2r_dtype_t dtype, b2r_op_t op, int sm_c
   t.cluster = B2R_ENV_INT("B2R_CLUSTER", t.cluster);
   t.unroll = B2R_ENV_INT("B2R_UNROLL", t.unroll);
   t.stages = B2R_ENV_INT("B2R_STAGES", t.stages);
+  t.dyn_pct = B2R_ENV_INT("B2R_DYN_PCT", t.dyn_pct);
 
   int variant = t.variant, threads = t.threads, cluster = t.cluster, unroll = t.unroll;
-  int st = t.stages, tile_bytes = t.tile_bytes;
+  int st = t.stages, tile_bytes = t.tile_bytes, dyn_pct = t.dyn_pct;
   int ctas = 0;
   if (hint) {
+    if (hint->dyn_pct) dyn_pct = hint->dyn_pct;
     if (hint->variant) variant = hint->variant;
     if (hint->threads) threads = hint->threads;
     if (hint->cluster) cluster = hint->cluster;
@@ -132,7 +146,11 @@ b2r_status_t plan_local(uint64_t count, b2r_dtype_t dtype, b2r_op_t op, int sm_c
   g->ctas = ctas;
   g->cluster = cluster;
   g->unroll = unroll;
-  g->pdl = pdl ? 1 : 0;
+  g->pdl = pdl;
+  // the dynamic tail: register-streaming variants, no clusters, several CTAs, and never under early streaming (the tile
+  // counter lives in the workspace, which an overlapped launch may not touch before its griddepcontrol.wait)
+  if (dyn_pct < 0 || variant == B2R_VARIANT_TMA || cluster > 1 || ctas < 2 || early) dyn_pct = 0;
+  g->dyn_pct = std::min(dyn_pct, 90);
   if (variant == B2R_VARIANT_TMA) {
     // the single-CTA path above may have lowered `threads`: the tile MUST follow (every consumer thread owns exactly
     // kTmaVecsPerThread vectors of a full tile; a stale, larger tile would leave part of each full tile unread)
@@ -189,6 +207,28 @@ b2r_status_t prepare_local(const void* in, void* out, uint64_t count, b2r_dtype_
   p.stages = stages;
   p.tile_vecs = tile_vecs;
   p.out_as_acc = out_as_acc;
+  p.acc64 = ws->d_acc64;
+  p.prefetch_lines = g->pdl == B2R_PDL_SAFE ? (unsigned)std::max(0, std::min(64, B2R_ENV_INT("B2R_PREFETCH_LINES", 2))) : 0u;
+  p.dyn_first = p.nvec;
+  if (g->dyn_pct > 0) {
+    // tiles of one load round of the CTA (threads x unroll vectors: 32 KiB for 512 x 4 x 16 B), grown when the per-tile partials
+    // of a floating-point launch would not fit the workspace; a body too small for one tile per CTA stays static
+    const uint64_t round_vecs = (uint64_t)g->threads * g->unroll;
+    const uint64_t want = p.nvec / 100 * g->dyn_pct + (p.nvec % 100) * g->dyn_pct / 100;
+    const uint64_t max_tiles = (uint64_t)std::max(1, ws->max_partials - g->ctas);
+    uint64_t tile_vecs = std::max<uint64_t>(1, (uint64_t)std::max(1, B2R_ENV_INT("B2R_DYN_TILE_ROUNDS", 1))) * round_vecs;
+    while ((want + tile_vecs - 1) / tile_vecs > max_tiles) tile_vecs += round_vecs;
+    const uint64_t ntiles = want / tile_vecs;
+    if (ntiles >= (uint64_t)g->ctas && ws->d_tile_ctr != nullptr && tile_vecs <= 0xffffffffull) {
+      p.tile_ctr = ws->d_tile_ctr;
+      p.dyn_tile_vecs = (unsigned)tile_vecs;
+      p.dyn_ntiles = (unsigned)ntiles;
+      p.dyn_first = p.nvec - ntiles * tile_vecs;
+      p.dyn_first -= p.dyn_first % (128 / (g->variant == B2R_VARIANT_LDG256 ? 32u : 16u));  // 128-byte aligned tiles; the last one absorbs the slack
+    } else {
+      g->dyn_pct = 0;
+    }
+  }
   // never overlap with the previous launch if this input could be that launch's output scalar
   if (g->pdl && ws->last_out) {
     const char* lo = (const char*)in;
@@ -203,6 +243,7 @@ b2r_status_t prepare_local(const void* in, void* out, uint64_t count, b2r_dtype_
   ws->last_geom[1] = g->threads;
   ws->last_geom[2] = g->ctas;
   ws->last_geom[3] = g->cluster;
+  ws->last_dyn_tiles = (int)p.dyn_ntiles;
   return B2R_OK;
 }
 
@@ -259,6 +300,9 @@ b2r_status_t b2r_workspace_create(b2r_workspace_t* out, int device) {
   if (e == cudaSuccess) e = cudaMalloc(&ws->d_partials, (size_t)kMaxCtas * 8);
   if (e == cudaSuccess) e = cudaMalloc((void**)&ws->d_ticket, 256);
   if (e == cudaSuccess) e = cudaMemset(ws->d_ticket, 0, 256);
+  if (e == cudaSuccess) ws->d_tile_ctr = ws->d_ticket + 32;  // its own 128-byte line of the same allocation
+  if (e == cudaSuccess) ws->d_acc64 = (unsigned long long*)(ws->d_ticket + 16);  // int32 SUM: packed arrivals + sum
+  ws->max_partials = kMaxCtas;
   if (e == cudaSuccess) e = cudaMalloc((void**)&ws->d_trace, (size_t)kMaxCtas * 4 * sizeof(unsigned long long));
   if (e == cudaSuccess) e = cudaMemset(ws->d_trace, 0, (size_t)kMaxCtas * 4 * sizeof(unsigned long long));
   if (e == cudaSuccess) e = cudaDeviceSynchronize();
@@ -327,6 +371,7 @@ b2r_status_t b2r_plan_local(uint64_t count, b2r_dtype_t dtype, b2r_op_t op, int 
   chosen->stages = stages;
   chosen->tile_bytes = tile_vecs * 16;
   chosen->pdl = g.pdl;
+  chosen->dyn_pct = g.dyn_pct;
   return B2R_OK;
 }
 

@@ -89,7 +89,11 @@ extern "C" b2r_status_t b2r_reduce_local_noalloc(const void* in, void* out, uint
   if (c.variant == B2R_VARIANT_AUTO) c.variant = B2R_VARIANT_LDG128;
   B2R_REQUIRE(c.variant == B2R_VARIANT_LDG128 || c.variant == B2R_VARIANT_LDG256,
               "b2r_reduce_local_noalloc: only the ldg128 / ldg256 variants are available without a workspace (got variant %d)", c.variant);
-  c.pdl = 0;  // consecutive calls share the scratch; they must not overlap
+  // Consecutive calls share the scratch, so they must not overlap: programmatic dependent launch is forced OFF here
+  // (a negative value is the one the planner honours as "off"; 0 would mean "whatever B2R_PDL says"), and so is the
+  // dynamically scheduled tail (its per-tile partials could outgrow the 1024 entries of the static array).
+  c.pdl = B2R_PDL_OFF;
+  c.dyn_pct = -1;
 
   // a workspace view over the static array: nothing is allocated, nothing outlives this call
   b2r_workspace view;
@@ -97,6 +101,9 @@ extern "C" b2r_status_t b2r_reduce_local_noalloc(const void* in, void* out, uint
   view.sm_count = d->sm_count;
   view.d_partials = d->scratch;
   view.d_ticket = (unsigned*)(d->scratch + kTicketOffset);
+  view.d_tile_ctr = nullptr;
+  view.d_acc64 = nullptr;
+  view.max_partials = B2R_NOALLOC_MAX_PARTIALS;
   view.d_trace = nullptr;
   view.trace_enabled = false;
 

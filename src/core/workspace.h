@@ -15,10 +15,14 @@ struct b2r_workspace {
   int sm_count = 0;
   void* d_partials = nullptr;             // kMaxCtas x 8 bytes
   unsigned* d_ticket = nullptr;           // arrival counter, zero between launches
+  unsigned* d_tile_ctr = nullptr;         // dynamic tail: next unclaimed tile, zero between launches (nullptr: no dynamic tail)
+  unsigned long long* d_acc64 = nullptr;  // int32 SUM: packed {arrivals, running sum}, zero between launches (nullptr: not offered)
+  int max_partials = 0;                   // capacity of d_partials in 8-byte entries
   unsigned long long* d_trace = nullptr;  // kMaxCtas x 4 stamps
   bool trace_enabled = false;
   int last_ctas = 0;
   int last_geom[4] = {0, 0, 0, 0};
+  int last_dyn_tiles = 0;
   const void* last_out = nullptr;         // output pointer of the previous launch (PDL overlap guard)
   // b2r_reduce_from_host
   cudaStream_t copy_stream = nullptr;

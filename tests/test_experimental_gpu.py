@@ -30,10 +30,7 @@ def _reread_environment_afterwards():
     b2r.refresh_env()
 
 
-pytestmark = [
-    pytest.mark.gpu,
-    pytest.mark.skipif(os.environ.get("B2R_TEST_EXPERIMENTAL", "0") in ("", "0"), reason="experimental path: set B2R_TEST_EXPERIMENTAL=1"),
-]
+pytestmark = [pytest.mark.gpu]
 
 DTYPES = [torch.int32, torch.float32, torch.float64, torch.bfloat16]
 

@@ -33,7 +33,8 @@ hint_sets = st.fixed_dictionaries(
         "cluster": st.sampled_from([1, 2, 3, 4, 8, 16]),
         "stages": st.sampled_from([1, 2, 3, 4, 6, 8, 16, 32, 33]),
         "unroll": st.sampled_from([4, 8, 5]),
-        "pdl": st.sampled_from([0, 1]),
+        "pdl": st.sampled_from([-1, 0, 1, 2]),
+        "dyn_pct": st.sampled_from([-1, 0, 10, 50, 90, 200]),
     },
 )
 
@@ -59,9 +60,13 @@ def test_planner_output_always_satisfies_the_kernel_invariants(n, dtype, op, cfg
         assert 1 <= p["stages"] <= 32
         assert p["stages"] * p["tile_bytes"] + 16 * p["stages"] <= 220 * 1024
     # hints that were accepted are honoured
-    for key in ("variant", "stages", "pdl"):
+    for key in ("variant", "stages"):
         if key in cfg and (key != "stages" or p["variant"] == "tma"):
             assert p[key] == cfg[key], (key, cfg, p)
+    assert p["pdl"] == {-1: 0, 0: 1, 1: 1, 2: 2}[cfg.get("pdl", 0)]  # 0 = default = the safe flavour
+    assert 0 <= p["dyn_pct"] <= 90
+    if p["dyn_pct"]:
+        assert p["variant"] != "tma" and p["cluster"] == 1 and p["pdl"] != 2 and p["ctas"] >= 2
     if "ctas" in cfg:
         assert p["ctas"] in (cfg["ctas"], cfg["ctas"] - cfg["ctas"] % p["cluster"])
         if "threads" in cfg:

@@ -199,7 +199,7 @@ def test_cuda_graph_capture_and_pdl():
     outs = [torch.zeros((), dtype=torch.int32, device="cuda") for _ in range(4)]
     want = [b2r.reduce_oracle(x.cpu(), "sum").item() for x in xs]
     ws = b2r.Workspace()
-    cfg = b2r.launch_config(pdl=1)
+    cfg = b2r.launch_config(pdl=b2r.PDL_INPUT_READY)
     s = torch.cuda.Stream()
     with torch.cuda.stream(s):
         for x, o in zip(xs, outs):
@@ -220,7 +220,7 @@ def test_cuda_graph_capture_and_pdl():
 def test_pdl_back_to_back_is_correct():
     xs = [b2r.fill_device(n, torch.float64, seed=n, mode="signed") for n in (1 << 22, (1 << 23) + 5, 12345, 1 << 24)]
     want = [b2r.reduce(x, "sum").item() for x in xs]
-    cfg = b2r.launch_config(pdl=1)
+    cfg = b2r.launch_config(pdl=b2r.PDL_INPUT_READY)
     ws = b2r.Workspace()
     outs = [torch.zeros((), dtype=torch.float64, device="cuda") for _ in range(400)]
     for i in range(400):
@@ -235,7 +235,7 @@ def test_pdl_back_to_back_is_correct():
 
 def test_reduce_on_non_current_device_pointer_guard():
     # in == previous out: the overlap guard must drop PDL for that launch and still be right
-    cfg = b2r.launch_config(pdl=1)
+    cfg = b2r.launch_config(pdl=b2r.PDL_INPUT_READY)
     ws = b2r.Workspace()
     x = b2r.fill_device(1 << 20, torch.float32, seed=3, mode="sdk")
     o1 = torch.zeros(1, dtype=torch.float32, device="cuda")
@@ -254,4 +254,67 @@ def test_tma_single_cta_tile_follows_thread_count(dtype):
         x = b2r.fill_host(n, dtype, seed=nbytes, mode="signed")
         for op in OPS:
             check(b2r.reduce(x.cuda(), op, cfg={"variant": "tma"}), x, op)
+            check(b2r.reduce(x.cuda(), op, cfg={"variant": "tma", "pdl": 2}), x, op)
             check(b2r.reduce(x.cuda(), op, cfg={"variant": "tma", "pdl": 1}), x, op)
+
+
+def test_safe_pdl_reads_an_input_written_by_the_preceding_kernel(monkeypatch):
+    """with B2R_PDL=1 in the environment EVERY call site gets programmatic launches, including those whose
+    input was written by the kernel right before them. The environment flavour therefore waits for that kernel before its
+    first load. Producer -> reduce, many times, alternating two values so a stale read cannot pass by luck."""
+    monkeypatch.setenv("B2R_PDL", "1")
+    b2r.refresh_env()
+    try:
+        n = 1 << 24
+        x = torch.empty(n, dtype=torch.int32, device="cuda")
+        ws = b2r.Workspace()
+        outs = [torch.zeros((), dtype=torch.int32, device="cuda") for _ in range(60)]
+        assert b2r.plan(n, torch.int32)["pdl"] == 1
+        for i in range(60):
+            x.fill_(1 + (i % 2))  # the producer: a plain torch kernel, it never triggers programmatic completion
+            b2r.reduce(x, "sum", out=outs[i], workspace=ws)
+        torch.cuda.synchronize()
+        for i, o in enumerate(outs):
+            assert o.item() == n * (1 + (i % 2)), i
+        # the same through dot -> reduce (dot's output scalar is the next input)
+        a = torch.full((1 << 20,), 3.0, dtype=torch.float32, device="cuda")
+        for i in range(20):
+            d = b2r.dot(a, a, workspace=ws)
+            r = b2r.reduce(d.reshape(1), "sum", workspace=ws)
+            assert r.item() == 9.0 * (1 << 20)
+    finally:
+        monkeypatch.delenv("B2R_PDL")
+        b2r.refresh_env()
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
+def test_dynamic_tail_matches_oracle_and_is_reproducible(dtype):
+    """The dynamically scheduled tail (tiles claimed with an atomic counter): right answers for every size class around the
+    tile boundaries, misaligned bases included, and floating-point sums that do not depend on which CTA claimed which tile
+    (per-tile partials folded in index order)."""
+    esz = torch.empty((), dtype=dtype).element_size()
+    ws = b2r.Workspace()
+    for nbytes, cfg in (((8 << 20) + 48, {"dyn_pct": 25}), ((32 << 20) - 16, {"dyn_pct": 50, "threads": 256}), ((3 << 20) + 4 * esz, {"dyn_pct": 90, "ctas": 37, "threads": 128}),
+                        ((16 << 20), {"dyn_pct": 25, "variant": "ldg256"}), ((16 << 20) + 1024, {"dyn_pct": 10, "unroll": 8})):
+        n = nbytes // esz
+        x = b2r.fill_host(n + 3, dtype, seed=nbytes, mode="signed")
+        for off in (0, 3):
+            xd = x.cuda()[off:off + n]
+            for op in OPS:
+                got = b2r.reduce(xd, op, workspace=ws, cfg=cfg)
+                check(got, x[off:off + n], op)
+            if dtype != torch.int32:
+                first = b2r.reduce(xd, "sum", workspace=ws, cfg=cfg).cpu().reshape(1).view(torch.uint8)
+                for _ in range(20):
+                    again = b2r.reduce(xd, "sum", workspace=ws, cfg=cfg).cpu().reshape(1).view(torch.uint8)
+                    assert torch.equal(first, again), (dtype, nbytes, cfg)
+
+
+def test_dynamic_tail_is_what_the_default_plain_launch_runs():
+    n = 1 << 24
+    x = b2r.fill_device(n, torch.int32, seed=5, mode="sdk")
+    assert b2r.plan(n, torch.int32, device=0)["dyn_pct"] > 0
+    want = b2r.reduce_oracle(x.cpu(), "sum").item()
+    ws = b2r.Workspace()
+    for _ in range(30):  # the tile counter must be re-armed by every launch
+        assert b2r.reduce(x, "sum", workspace=ws).item() == want

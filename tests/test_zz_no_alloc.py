@@ -28,7 +28,7 @@ MAX_PARTIALS = 1024  # B2R_NOALLOC_MAX_PARTIALS in include/b2r.h
 
 
 class LaunchCfg(C.Structure):
-    _fields_ = [(n, C.c_int) for n in ("variant", "threads", "ctas", "cluster", "stages", "tile_bytes", "unroll", "pdl")]
+    _fields_ = [(n, C.c_int) for n in ("variant", "threads", "ctas", "cluster", "stages", "tile_bytes", "unroll", "pdl", "dyn_pct")]
 
 
 @pytest.fixture(scope="module")
@@ -39,6 +39,9 @@ def lib():
     lib.b2r_reduce_local_noalloc.restype = i
     lib.b2r_reduce_local.argtypes = [vp, vp, u64, i, i, vp, vp]
     lib.b2r_reduce_local.restype = i
+    lib.b2r_reduce_local_ex.argtypes = [vp, vp, u64, i, i, vp, vp, C.POINTER(LaunchCfg)]
+    lib.b2r_reduce_local_ex.restype = i
+    lib.b2r_refresh_env.restype = None
     lib.b2r_workspace_create.argtypes = [C.POINTER(vp), i]
     lib.b2r_workspace_create.restype = i
     lib.b2r_workspace_destroy.argtypes = [vp]
@@ -129,3 +132,54 @@ def test_noalloc_rejects_geometries_beyond_the_static_scratch(lib):
     cfg.ctas = 0
     cfg.variant = 3  # the TMA variant is not offered without a workspace
     assert lib.b2r_reduce_local_noalloc(x.data_ptr(), out.data_ptr(), x.numel(), INT32, SUM, stream, C.byref(cfg)) == 1
+
+
+def test_noalloc_never_uses_programmatic_launch_even_with_B2R_PDL_set(lib, monkeypatch):
+    """Calls share one scratch array, so they must not overlap: with B2R_PDL=1 exported (the documented way to turn
+    programmatic dependent launch on for the whole process) the no-alloc launches still run in plain stream order and agree
+    bit for bit with the workspace entry point given the same static geometry."""
+    torch.cuda.set_device(0)
+    stream = torch.cuda.current_stream().cuda_stream
+    monkeypatch.setenv("B2R_PDL", "1")
+    lib.b2r_refresh_env()
+    ws = C.c_void_p()
+    assert lib.b2r_workspace_create(C.byref(ws), 0) == 0
+    try:
+        same = LaunchCfg()
+        same.variant, same.pdl, same.dyn_pct = 1, -1, -1  # ldg128, plain order, static split: what the no-alloc path launches
+        for dtype in DTYPES:
+            outs = []
+            for n, seed in (((1 << 23) + 5, 11), ((1 << 23) + 5, 12), (123_457, 13)):
+                x = make_input(n, dtype, seed)
+                want = torch.zeros((), dtype=dtype, device="cuda")
+                got = torch.zeros((), dtype=dtype, device="cuda")
+                assert lib.b2r_reduce_local_ex(x.data_ptr(), want.data_ptr(), n, DTYPES[dtype], SUM, ws, stream, C.byref(same)) == 0
+                # two no-alloc calls back to back, no synchronisation in between
+                assert lib.b2r_reduce_local_noalloc(x.data_ptr(), got.data_ptr(), n, DTYPES[dtype], SUM, stream, None) == 0
+                got2 = torch.zeros((), dtype=dtype, device="cuda")
+                assert lib.b2r_reduce_local_noalloc(x.data_ptr(), got2.data_ptr(), n, DTYPES[dtype], SUM, stream, None) == 0
+                outs.append((x, want, got, got2))
+            torch.cuda.synchronize()
+            for x, want, got, got2 in outs:
+                wb, gb, g2 = (t.cpu().reshape(1).view(torch.uint8) for t in (want, got, got2))
+                assert torch.equal(wb, gb) and torch.equal(wb, g2), (dtype, want.item(), got.item(), got2.item())
+    finally:
+        lib.b2r_workspace_destroy(ws)
+        monkeypatch.delenv("B2R_PDL")
+        lib.b2r_refresh_env()
+
+
+@pytest.mark.multigpu
+def test_noalloc_on_a_second_device(lib):
+    """Every device has its own copy of the static array and its own one-time set-up."""
+    for dev in (1, 0, 1):
+        torch.cuda.set_device(dev)
+        stream = torch.cuda.current_stream().cuda_stream
+        x = make_input((1 << 21) + 7, torch.int32, 20 + dev).to(f"cuda:{dev}")
+        out = torch.zeros((), dtype=torch.int32, device=f"cuda:{dev}")
+        st = lib.b2r_reduce_local_noalloc(x.data_ptr(), out.data_ptr(), x.numel(), INT32, SUM, stream, None)
+        assert st == 0, lib.b2r_last_error_string().decode()
+        torch.cuda.synchronize()
+        want = int(x.sum(dtype=torch.int64).item())
+        assert out.item() == (want + 2**31) % 2**32 - 2**31
+    torch.cuda.set_device(0)
