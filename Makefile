@@ -61,7 +61,7 @@ bins: $(BENCHES)
 $(BINDIR)/%: bench/%.cu $(LIB) $(HDRS) $(wildcard bench/*.h)
 	@mkdir -p $(BINDIR)
 	@echo "NVCC $<"
-	$(Q)$(NVCC) $(NVCCFLAGS) -o $@ $< -L$(LIBDIR) -lb2r -Xlinker -rpath,'$$ORIGIN/../$(LIBDIR)'
+	$(Q)$(NVCC) $(NVCCFLAGS) -o $@ $< -L$(LIBDIR) -lb2r -ldl -Xlinker -rpath,'$$ORIGIN/../$(LIBDIR)'
 
 minimpi:
 	$(Q)$(MAKE) -C minimpi $(if $(Q),-s,)

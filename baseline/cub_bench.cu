@@ -26,6 +26,7 @@ double time_cub(b2r_op_t op, InIt* ins, int copies, OutT* d_out, size_t n, int i
   BENCH_CUDA(cudaMalloc(&tmp, std::max<size_t>(tmp_bytes, 16)));
   for (int i = 0; i < 3; ++i) BENCH_CUDA(call(ins[i % copies]));
   BENCH_CUDA(cudaDeviceSynchronize());
+  ClockLog::Window clocks_window;
   EventTimer et;
   et.start(nullptr);
   for (int i = 0; i < iters; ++i) call(ins[i % copies]);
@@ -45,6 +46,7 @@ int main(int argc, char** argv) {
   const int iters = (int)f.i64("iters", 50);
   FILE* csv = f.has("csv") ? fopen(f.str("csv").c_str(), "a") : nullptr;
   BENCH_CUDA(cudaSetDevice((int)f.i64("device", 0)));
+  ClockLog::get().start(1);
   printf("# cub::DeviceReduce %s %s\n# %12s %10s %10s\n", b2r_dtype_name(dt), b2r_op_name(op), "elements", "us", "GB/s");
   for (uint64_t n = nmin; n <= nmax; n *= 4) {
     const size_t bytes = n * b2r_dtype_size(dt);
@@ -80,5 +82,6 @@ int main(int argc, char** argv) {
     cudaFree(d_out);
   }
   if (csv) fclose(csv);
-  return 0;
+  ClockLog::get().stop();
+  return ClockLog::get().print(stdout) ? 0 : 1;
 }

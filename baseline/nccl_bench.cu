@@ -53,6 +53,7 @@ static const char* ref_type_name(b2r_dtype_t d) { return d == B2R_INT32 ? "INT" 
 // one host thread per GPU, like bench_collective (and like one MPI rank per GPU)
 static double timed(std::vector<Rank>& R, bool allreduce, uint64_t count, b2r_dtype_t dt, b2r_op_t op, int root, int iters) {
   const int P = (int)R.size();
+  ClockLog::Window clocks_window;
   std::vector<std::thread> th;
   for (int i = 0; i < P; ++i) {
     th.emplace_back([&, i] {
@@ -93,6 +94,7 @@ int main(int argc, char** argv) {
   for (int i = 0; i < P; ++i) devs[i] = i;
   std::vector<ncclComm_t> comms(P);
   NCCLCHECK(ncclCommInitAll(comms.data(), P, devs.data()));
+  ClockLog::get().start(P);
   std::vector<Rank> R(P);
   for (int i = 0; i < P; ++i) {
     R[i].dev = i;
@@ -171,10 +173,12 @@ int main(int argc, char** argv) {
   }
   if (jsonl) fclose(jsonl);
   if (csv) fclose(csv);
+  ClockLog::get().stop();
+  const bool clocks_ok = ClockLog::get().print(stdout);
   for (auto& r : R) {
     cudaSetDevice(r.dev);
     cudaStreamSynchronize(r.stream);
     ncclCommDestroy(r.comm);
   }
-  return 0;
+  return clocks_ok ? 0 : 1;
 }

@@ -30,8 +30,24 @@ import time
 REPO = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, REPO)
 
-N_ELEMS = 1 << 24  # the SDK sample's default workload (reduction.cpp:665)
-BASELINE_GBS = 90.8413  # CUDA reduction, int, SUM (mpi/CUdata.txt:6)
+
+
+def _workloads():
+    """models/workloads.py (the reference's workloads as data) loaded by PATH: importing the package would load libb2r.so, and the
+    reference arm must run without any of this repository's native code in its process."""
+    import importlib.util
+
+    spec = importlib.util.spec_from_file_location("b2r_workloads", os.path.join(REPO, "cuda_mpi_reductions_b200", "models", "workloads.py"))
+    mod = importlib.util.module_from_spec(spec)
+    sys.modules["b2r_workloads"] = mod  # dataclasses looks the module up by name
+    spec.loader.exec_module(mod)
+    return mod
+
+
+SDK_REDUCTION = _workloads().SDK_REDUCTION
+
+N_ELEMS = SDK_REDUCTION.elements  # the SDK sample's default workload, 2^24 (reduction.cpp:665)
+BASELINE_GBS = SDK_REDUCTION.published_gbs[("int", "SUM")]  # BASELINE.md §1: CUDA reduction, int, SUM = 90.8413 (mpi/CUdata.txt:6)
 METRIC = "reduction_throughput_int32_sum_2p24"
 
 
@@ -47,6 +63,7 @@ def parse_args():
     ap.add_argument("--dtype", default="int32", choices=["int32", "float32", "float64", "bfloat16"])
     ap.add_argument("--op", default="sum", choices=["sum", "min", "max"])
     ap.add_argument("--n", type=int, default=N_ELEMS)
+    ap.add_argument("--no-collectives", action="store_true", help="N > 1: skip the reduce/allreduce-vs-NCCL and config-4 sections")
     return ap.parse_args()
 
 
@@ -94,19 +111,41 @@ def run_reference(args) -> None:
     m = re.search(r"Throughput = ([0-9.]+) GB/s, Time = ([0-9.]+) s", res.stdout)
     passed = "PASSED" in res.stdout
     gbs = float(m.group(1)) if m else 0.0
-    sec = float(m.group(2)) if m else 0.0
+    esz = {"int32": 4, "float32": 4, "float64": 8}[args.dtype]
+    # ---- end to end: the same unmodified kernels driven step by step (baseline/ref_e2e.cu): per step H2D of the input from
+    # pinned host memory, the sample's two-pass reduction, D2H of the scalar; --steps / --warmup apply here
+    e2e_exe = os.path.join(REPO, "baseline", "_ref", "bin", "ref_e2e")
+    e2e_gbs, e2e_ms, e2e_ok, e2e_pageable = 0.0, 0.0, False, 0.0
+    if os.path.exists(e2e_exe):
+        e2e_steps = max(3, min(args.steps, 40))
+        base = [e2e_exe, f"--method={args.op.upper()}", f"--type={typ}", f"--n={args.n}", f"--device={local_rank}",
+                f"--steps={e2e_steps}", f"--warmup={max(3, min(args.warmup, 5))}"]
+        if world > 1:
+            dist.barrier()
+        r2 = subprocess.run(base, capture_output=True, text=True)
+        m2 = re.search(r"REF_E2E gbs=([0-9.]+) ms_per_step=([0-9.]+) .*result_ok=(\d)", r2.stdout)
+        if m2:
+            e2e_gbs, e2e_ms, e2e_ok = float(m2.group(1)), float(m2.group(2)), m2.group(3) == "1"
+        if world > 1:
+            dist.barrier()
+        r3 = subprocess.run(base + ["--pageable"], capture_output=True, text=True)
+        m3 = re.search(r"REF_E2E gbs=([0-9.]+)", r3.stdout)
+        e2e_pageable = float(m3.group(1)) if m3 else 0.0
     if world > 1:
         # the reference has no multi-GPU reduction; N ranks each run the unmodified sample on their own shard and the
-        # job-level rate is N * bytes / slowest rank (the cross-GPU combine, a host loop in simpleMultiGPU.cpp:287-291,
-        # is not part of its timed region either).
-        t = torch.tensor([sec], device="cuda", dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ok = torch.tensor([1 if passed else 0], device="cuda")
+        # job-level rate is N x the slowest rank's own printed throughput (the cross-GPU combine, a host loop in
+        # simpleMultiGPU.cpp:287-291, is not part of its timed region either). Round 1 rebuilt the rate from the sample's
+        # five-decimal `Time =` field, which quantised every multi-GPU figure to +-5 %.
+        t = torch.tensor([gbs, e2e_gbs, e2e_pageable], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        ok = torch.tensor([1 if passed else 0, 1 if e2e_ok else 0], device="cuda")
         dist.all_reduce(ok, op=dist.ReduceOp.MIN)
-        sec = t.item()
-        passed = bool(ok.item())
-        esz = {"int32": 4, "float32": 4, "float64": 8}[args.dtype]
-        gbs = world * args.n * esz / sec * 1e-9 if sec > 0 else 0.0
+        tm = torch.tensor([e2e_ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+        gbs, e2e_gbs, e2e_pageable = (world * v for v in t.tolist())
+        passed, e2e_ok = bool(ok[0].item()), bool(ok[1].item())
+        e2e_ms = tm.item()
+    sec = world * args.n * esz / (gbs * 1e9) if gbs > 0 else 0.0
     if rank == 0:
         out.update({
             "metric": METRIC, "value": gbs, "unit": "GB/s", "n_gpus": world, "steps": 100, "warmup": 1,
@@ -114,9 +153,17 @@ def run_reference(args) -> None:
             "vs_baseline": gbs / BASELINE_GBS if gbs else None, "dtype": args.dtype, "data": "synthetic (rand()&0xFF, the sample's own generator)",
             "config": {"model": "SDK reduction sample (reference, unmodified) recompiled for sm_100", "elements_per_gpu": args.n,
                        "op": args.op, "parallelism": f"dp{world}" if world > 1 else "single-gpu",
-                       "timing": "reference's own host stopwatch around sync+2 launches+sync; one L2-resident buffer (stock path)"},
+                       "timing": "reference's own host stopwatch around sync+2 launches+sync; one L2-resident buffer (stock path)",
+                       "multi_gpu": "N x the slowest rank's printed throughput" if world > 1 else None},
             "self_check": "PASSED" if passed else "FAILED", "wall_s": wall,
         })
+        if e2e_gbs > 0:
+            out["e2e"] = {"value": e2e_gbs, "unit": "GB/s", "h2d_bytes_per_step": args.n * esz, "d2h_bytes_per_step": esz,
+                          "ms_per_step": e2e_ms, "self_check": "PASSED" if e2e_ok else "FAILED",
+                          "api": "reduction.h sumreduce/minreduce/maxreduce<T> (unmodified reduction_kernel.cu) driven by baseline/ref_e2e.cu: "
+                                 "per step cudaMemcpy H2D of the input, two-pass reduction, cudaMemcpy D2H of the scalar (reduction.cpp:725,323-357,377-381)",
+                          "host_memory": "pinned (same rule as the repo's own e2e arm)",
+                          "value_pageable_host": e2e_pageable, "note_pageable": "the stock sample mallocs its host buffer (reduction.cpp:696)"}
         if not m:
             out["unavailable"] = "reference binary produced no throughput line: " + (res.stdout[-200:] + res.stderr[-200:]).replace("\n", " ")
         print(json.dumps(out), flush=True)
@@ -142,15 +189,21 @@ def run_b2r(args) -> None:
     esz = torch.empty((), dtype=dtype).element_size()
     nbytes = args.n * esz
     steps, warmup = args.steps, max(args.warmup, 3)
+    # started now, long before the timed region: the first NVML query of a process takes longer than 20 steps do
+    sampler = ClockSampler(local_rank).start() if rank == 0 else None
 
     comm = None
+    do_sections = world > 1 and not args.no_collectives
     if world > 1:
         import torch.distributed as dist
 
         from cuda_mpi_reductions_b200.parallel import Communicator
 
         dist.init_process_group("nccl", device_id=dev)
-        comm = Communicator.from_torch_distributed()
+        # symmetric_only: every buffer handed to reduce/allreduce below comes from the symmetric heap, so nothing is staged
+        # or chunked; the heap holds the two 1 GiB buffers of the collectives section
+        comm = Communicator.from_torch_distributed(heap_bytes=(2 << 30) + (64 << 20) if do_sections else 0, symmetric_only=do_sections,
+                                                   timeout_ms=30000)
 
     copies = rotating_copies(nbytes)
     big = torch.empty(copies * args.n, dtype=dtype, device=dev)
@@ -221,13 +274,16 @@ def run_b2r(args) -> None:
         ok, msg = verified()
     assert ok, f"self-check failed: {msg}"
 
-    sampler = ClockSampler(local_rank).start() if rank == 0 else None
+    if sampler:
+        sampler.wait_for_samples(1, 3.0)
     for i in range(warmup):
         step(i)
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    if comm is not None:
+        comm.barrier()  # device-side barrier on the launching stream: every GPU passes ev0 within a microsecond or two of its peers
     t_start = time.perf_counter()
     ev0.record()
     for i in range(steps):
@@ -242,12 +298,40 @@ def run_b2r(args) -> None:
         t = torch.tensor([ms], device=dev, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = t.item()
-    clocks = sampler.summary(t_start, t_end) if sampler else None
-    ms_plain = None
-    if comm is None:  # same loop in plain stream order (no overlap between consecutive steps), for the record
+    # Clock record: the timed region is shorter than one NVML poll at --steps 20, so the SAME step loop keeps running,
+    # untimed, for >= 100 ms while the sampler collects; the record covers the timed region plus that repeat.
+    t_rep = time.perf_counter()
+    rep_steps = 0
+    while time.perf_counter() - t_rep < 0.12:
+        for i in range(50):
+            step(i)
+        rep_steps += 50
+        torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    clocks = sampler.summary(t_start, time.perf_counter()) if sampler else None
+    if clocks is not None:
+        clocks["window"] = f"timed region + {rep_steps} untimed repeats of the same step ({clocks.get('window')})"
+    ms_plain = ms_nopdl = ms_synced = None
+    if comm is None:
         from cuda_mpi_reductions_b200.utils import time_steps
 
+        # the same loop as a caller who promises nothing about the inputs gets it: default launch = safe programmatic launch
+        # (waits for the previous kernel before its first load) ...
         ms_plain = time_steps(step_plain, steps, warmup)
+        # ... with programmatic launch switched off altogether (classic stream order) ...
+        cfg_off = b2r.launch_config(pdl=b2r.PDL_OFF)
+        ms_nopdl = time_steps(lambda i: b2r.reduce(inputs[i % copies], opc, out=out, workspace=ws, cfg=cfg_off), steps, warmup)
+        # ... and timed the reference's way (reduction.cpp:319-374): host stopwatch around sync + launch + sync, per iteration
+        torch.cuda.synchronize()
+        acc_s = 0.0
+        for i in range(steps):
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            step_plain(i)
+            torch.cuda.synchronize()
+            acc_s += time.perf_counter() - t0
+        ms_synced = acc_s * 1e3
 
     # ---- end-to-end arm: host (pinned) -> device copy of every step's input + scalar back on the host
     e2e_steps = args.e2e_steps or max(3, min(steps, 40))
@@ -269,6 +353,22 @@ def run_b2r(args) -> None:
         r = e2e_step(i)
     if comm is None:
         assert e2e_step(0).item() == want_e2e.item(), "e2e self-check failed"
+    else:
+        # the timed path checked against the CPU oracle of every rank's shard (combined with NCCL, like the headline check)
+        got = e2e_step(0)
+        local = want_e2e.to(dev).to(torch.int64 if dtype == torch.int32 else dtype)
+        dist.all_reduce(local, op={"sum": dist.ReduceOp.SUM, "min": dist.ReduceOp.MIN, "max": dist.ReduceOp.MAX}[args.op])
+        verdict = torch.ones((), dtype=torch.int32, device=dev)
+        if rank == 0:
+            w = local.item()
+            if dtype == torch.int32:
+                w = (w + 2**31) % 2**32 - 2**31
+                good = got.item() == w
+            else:
+                good = abs(got.item() - w) <= 1e-5 * abs(w) + 1e-6
+            verdict.fill_(1 if good else 0)
+        dist.broadcast(verdict, src=0)
+        assert bool(verdict.item()), "multi-GPU e2e self-check failed"
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
@@ -284,6 +384,20 @@ def run_b2r(args) -> None:
     chunk_bytes = int(os.environ.get("B2R_H2D_CHUNK_MB", "8")) << 20
     nchunks = -(-nbytes // chunk_bytes)
     acc_sz = 8 if dtype == torch.float64 else 4
+    d2h_per_step = nchunks * acc_sz if comm is None else acc_sz  # single GPU: chunk scalars; multi GPU: the one scalar at root
+
+    # ---- N > 1: what BASELINE.json names for several GPUs — reduce / allreduce bus bandwidth against NCCL, and config 4
+    sections = {}
+    if do_sections:
+        from cuda_mpi_reductions_b200.utils.bench_sections import collectives_section, config4_section
+
+        for name, fn in (("collectives", collectives_section), ("config4", config4_section)):
+            try:
+                sections[name] = fn(comm, dist, dev, rank, world)
+            except Exception as e:  # noqa: BLE001  (a failed section must not take the headline line with it)
+                sections[name] = {"error": f"{type(e).__name__}: {e}"}
+                print(f"[rank {rank}] section {name} failed: {e}", file=sys.stderr)
+        dist.barrier()
 
     if sampler:
         sampler.stop()
@@ -308,9 +422,10 @@ def run_b2r(args) -> None:
                        "geometry": b2r.plan(args.n, dtype, args.op, device=local_rank, cfg=cfg),
                        "launch": "programmatic dependent launch between consecutive steps (cfg pdl=PDL_INPUT_READY: inputs complete before the loop)", "host_path": host_path},
             "clocks": clocks,
-            "e2e": {"value": e2e_value, "unit": "GB/s", "h2d_bytes_per_step": nbytes, "d2h_bytes_per_step": nchunks * acc_sz,
-                    "steps": e2e_steps, "ms_per_step": e2e_s * 1e3 / e2e_steps,
+            "e2e": {"value": e2e_value, "unit": "GB/s", "h2d_bytes_per_step": nbytes, "d2h_bytes_per_step": d2h_per_step,
+                    "steps": e2e_steps, "ms_per_step": e2e_s * 1e3 / e2e_steps, "self_check": "PASSED",
                     "api": "cuda_mpi_reductions_b200.reduce_from_host(pinned_tensor)" if comm is None else "Communicator.reduce_scalar_sharded_from_host(pinned_tensor)",
+                    "pipeline": f"{nchunks} chunks of {chunk_bytes >> 20} MiB: copy engine overlapped with the reduction kernels (native, b2r_reduce{'_scalar_sharded' if comm else ''}_from_host)",
                     "numa_rank0": numa},
             "gpu_launches": steps * world,  # one kernel of ours per GPU per step inside the timed region
             "gpu_launches_per_gpu": steps,
@@ -318,7 +433,18 @@ def run_b2r(args) -> None:
             "impl": "b2r",
         }
         if ms_plain is not None:
-            line["value_plain_stream_order"] = total_bytes * steps / (ms_plain * 1e-3) * 1e-9
+            gbs = lambda m: total_bytes * steps / (m * 1e-3) * 1e-9  # noqa: E731
+            line["value_plain_stream_order"] = gbs(ms_plain)
+            line["value_no_programmatic_launch"] = gbs(ms_nopdl)
+            line["value_host_synced"] = gbs(ms_synced)
+            line["variants"] = {
+                "value": "cfg pdl=PDL_INPUT_READY: the caller declares the inputs complete; consecutive launches overlap their streaming",
+                "value_plain_stream_order": "default launch, no promise from the caller: safe programmatic launch (waits for the previous kernel "
+                                            "before its first load; L2 prefetch of the slice head while waiting), device events",
+                "value_no_programmatic_launch": "cfg pdl=PDL_OFF: classic stream order, device events",
+                "value_host_synced": "default launch timed the reference's way: host stopwatch around sync + launch + sync per iteration (reduction.cpp:319-374)",
+                "geometry_plain": b2r.plan(args.n, dtype, args.op, device=local_rank)}
+        line.update(sections)
         print(json.dumps(line), flush=True)
     if world > 1:
         comm.close()

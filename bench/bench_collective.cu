@@ -71,6 +71,7 @@ b2r_algo_t parse_algo(const std::string& s) {
 // single thread driving P devices does not masquerade as collective latency.
 double timed(std::vector<Rank>& R, bool allreduce, uint64_t count, b2r_dtype_t dt, b2r_op_t op, int root, b2r_algo_t algo, int iters) {
   const int P = (int)R.size();
+  ClockLog::Window clocks_window;  // clock samples taken from here to the end of the call count as "during a timed region"
   std::vector<int> failed(P, 0);
   std::vector<std::thread> th;
   for (int i = 0; i < P; ++i) {
@@ -166,6 +167,8 @@ int main(int argc, char** argv) {
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { fprintf(stderr, "no CUDA device\n"); return 2; }
   const int P = (int)f.i64("gpus", ndev);
   if (P < 1 || P > ndev) { fprintf(stderr, "--gpus=%d but %d devices are visible\n", P, ndev); return 1; }
+  ClockLog::get().start(P);
+  const bool nvlink = f.has("nvlink");  // --nvlink: measured NVLink payload bytes per call (NVML counters) next to every sweep row
   const bool tune = f.has("tune");
   const bool sweep = f.has("sweep") || tune;
   const uint64_t total_bytes = (uint64_t)f.i64("total-mib", 2048) << 20;
@@ -322,13 +325,29 @@ int main(int argc, char** argv) {
               if (f.has("check") && bytes <= (256ull << 20)) all_ok = verify(R, allreduce, count, dt, op, root, algo) && all_ok;
               const int it = bytes >= (1ull << 30) ? std::max(3, iters / 4) : (bytes >= (64ull << 20) ? std::max(5, iters / 2) : iters * 5);
               if (timed(R, allreduce, count, dt, op, root, algo, 3) < 0) return 3;
+              std::vector<unsigned long long> tx0(P, 0), rx0(P, 0), tx1(P, 0), rx1(P, 0);
+              bool have_nvl = nvlink;
+              for (int r = 0; r < P && have_nvl; ++r) have_nvl = ClockLog::get().nvlink_bytes(r, &tx0[r], &rx0[r]);
               const double ms = timed(R, allreduce, count, dt, op, root, algo, it);
               if (ms < 0) return 3;
+              if (have_nvl) std::this_thread::sleep_for(std::chrono::milliseconds(30));  // the counters are published with a delay
+              for (int r = 0; r < P && have_nvl; ++r) have_nvl = ClockLog::get().nvlink_bytes(r, &tx1[r], &rx1[r]);
               const double algbw = bytes / ms * 1e-6;
               const double busbw = allreduce ? algbw * 2.0 * (P - 1) / P : algbw;  // nccl-tests convention
               const b2r_algo_t used = algo == B2R_ALGO_AUTO ? b2r_select_algo(allreduce, bytes, dt, op, P, has_mc) : algo;
-              printf("  %-9s %-6s %-4s %-8s %14llu %10.2f %10.2f %10.2f\n", coll.c_str(), ref_type_name(dt), b2r_op_name(op), b2r_algo_name(used),
+              printf("  %-9s %-6s %-4s %-8s %14llu %10.2f %10.2f %10.2f", coll.c_str(), ref_type_name(dt), b2r_op_name(op), b2r_algo_name(used),
                      (unsigned long long)bytes, ms * 1e3, algbw, busbw);
+              if (have_nvl) {
+                // per call, busiest GPU in each direction, as a multiple of the message size (root ingress of an ideal reduce = 1.0)
+                double txm = 0, rxm = 0;
+                for (int r = 0; r < P; ++r) {
+                  txm = std::max(txm, (double)(tx1[r] - tx0[r]) / it);
+                  rxm = std::max(rxm, (double)(rx1[r] - rx0[r]) / it);
+                }
+                printf("   nvlink tx %.3fx rx %.3fx of the message (busiest GPU; root rx %.3fx)", txm / bytes, rxm / bytes,
+                       (double)(rx1[root] - rx0[root]) / it / bytes);
+              }
+              printf("\n");
               fflush(stdout);
               if (csv)
                 fprintf(csv, "b2r,%s,%s,%s,%s,%d,%llu,%.3f,%.3f,%.3f\n", coll.c_str(), ref_type_name(dt), b2r_op_name(op), b2r_algo_name(used), P,
@@ -347,6 +366,8 @@ int main(int argc, char** argv) {
   if (jsonl) fclose(jsonl);
   if (csv) fclose(csv);
   if (raw) fclose(raw);
+  ClockLog::get().stop();
+  if (!ClockLog::get().print(stdout)) all_ok = false;  // a slowdown during a timed region invalidates the run
   for (auto& r : R) {
     cudaSetDevice(r.dev);
     cudaStreamSynchronize(r.stream);

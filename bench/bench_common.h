@@ -7,6 +7,8 @@
 //                    "[name] starting..." / PASSED|FAILED|WAIVED sentinel with exit code (shrQATest.h:83-229)
 #pragma once
 #include <cuda_runtime.h>
+#include <dlfcn.h>
+#include <nvml.h>
 #include <strings.h>
 
 #include <chrono>
@@ -14,8 +16,12 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <algorithm>
+#include <atomic>
 #include <map>
+#include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "b2r.h"
@@ -127,6 +133,149 @@ class Log {
   }
   FILE* f_ = nullptr;
   FILE* m_ = nullptr;
+};
+
+// ---------------------------------------------------------------- clocks + NVLink byte counters (NVML through dlopen)
+// Every number a harness prints is accompanied by a clocks record taken DURING its timed regions (B200_PROFILING.md:
+// a number measured under hw_slowdown / thermal slowdown, or with SM clocks stuck low for no reason, is rejected). A
+// background thread polls SM clock + clock-event reasons of every visible GPU about once per millisecond; the harness
+// brackets its timed loops with ClockLog::Window, and print() emits one line per GPU:
+//   # clocks gpu0: sm_mhz median 1965 min 1965 (max 1965), samples 412, reasons [none]
+// libnvidia-ml.so.1 is loaded with dlopen so the binaries still start on a machine without the driver library.
+// The same handle reads the per-GPU NVLink data counters (NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_TX/RX, KiB, all links): the
+// measured bytes a collective really moved over NVLink, to set against its algorithmic bytes — what ncu cannot give for a
+// kernel that waits on its peers (a replayed launch would deadlock).
+class ClockLog {
+ public:
+  static ClockLog& get() {
+    static ClockLog c;
+    return c;
+  }
+  struct Window {  // RAII: samples taken while at least one Window is alive count
+    Window() { ClockLog::get().active_.fetch_add(1); }
+    ~Window() { ClockLog::get().active_.fetch_sub(1); }
+  };
+  bool ok() const { return ok_; }
+  void start(int ndev) {
+    if (started_ || !load()) return;
+    ndev_ = std::min(ndev, 16);
+    for (int i = 0; i < ndev_; ++i) {
+      // CUDA ordinal -> NVML handle by PCI bus id (CUDA_VISIBLE_DEVICES may renumber)
+      char bus[32] = {0};
+      if (cudaDeviceGetPCIBusId(bus, sizeof(bus), i) != cudaSuccess || by_bus_(bus, &dev_[i]) != NVML_SUCCESS) {
+        if (by_index_((unsigned)i, &dev_[i]) != NVML_SUCCESS) { ndev_ = i; break; }
+      }
+      unsigned mx = 0;
+      if (max_clock_(dev_[i], NVML_CLOCK_SM, &mx) == NVML_SUCCESS) max_mhz_[i] = mx;
+    }
+    started_ = true;
+    stop_ = false;
+    th_ = std::thread([this] { run(); });
+  }
+  void stop() {
+    if (!started_) return;
+    stop_ = true;
+    if (th_.joinable()) th_.join();
+    started_ = false;
+  }
+  ~ClockLog() { stop(); }
+  // One line per GPU with the samples taken inside windows so far. Returns false if any bad reason was seen.
+  bool print(FILE* f = stdout) {
+    if (!ok_) {
+      fprintf(f, "# clocks: unavailable (%s)\n", err_.c_str());
+      return true;
+    }
+    std::lock_guard<std::mutex> lk(mu_);
+    bool good = true;
+    for (int i = 0; i < ndev_; ++i) {
+      std::vector<unsigned> v = mhz_[i];
+      if (v.empty()) {
+        fprintf(f, "# clocks gpu%d: no samples inside a timed region (max %u MHz)\n", i, max_mhz_[i]);
+        continue;
+      }
+      std::sort(v.begin(), v.end());
+      const unsigned long long r = reasons_[i];
+      std::string names;
+      auto add = [&](unsigned long long bit, const char* n) { if (r & bit) names += std::string(names.empty() ? "" : ",") + n; };
+      add(nvmlClocksEventReasonSwPowerCap, "sw_power_cap");
+      add(nvmlClocksThrottleReasonHwSlowdown, "hw_slowdown");
+      add(nvmlClocksEventReasonSwThermalSlowdown, "sw_thermal_slowdown");
+      add(nvmlClocksThrottleReasonHwThermalSlowdown, "hw_thermal_slowdown");
+      add(nvmlClocksThrottleReasonHwPowerBrakeSlowdown, "hw_power_brake_slowdown");
+      add(nvmlClocksEventReasonApplicationsClocksSetting, "applications_clocks_setting");
+      const bool bad = r & (nvmlClocksThrottleReasonHwSlowdown | nvmlClocksEventReasonSwThermalSlowdown | nvmlClocksThrottleReasonHwThermalSlowdown);
+      good = good && !bad;
+      fprintf(f, "# clocks gpu%d: sm_mhz median %u min %u (max %u), samples %zu, reasons [%s]%s\n", i, v[v.size() / 2], v.front(), max_mhz_[i],
+              v.size(), names.empty() ? "none" : names.c_str(), bad ? "  REJECT: slowdown seen during a timed region" : "");
+    }
+    return good;
+  }
+  // Cumulative NVLink payload bytes (all links) sent / received by device i; false if the counters cannot be read.
+  bool nvlink_bytes(int i, unsigned long long* tx, unsigned long long* rx) {
+    if (!ok_ || i >= ndev_ || !field_values_) return false;
+    nvmlFieldValue_t fv[2];
+    memset(fv, 0, sizeof(fv));
+    fv[0].fieldId = NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_TX;
+    fv[1].fieldId = NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_RX;
+    fv[0].scopeId = fv[1].scopeId = 0xffffffffu;  // all links
+    if (field_values_(dev_[i], 2, fv) != NVML_SUCCESS || fv[0].nvmlReturn != NVML_SUCCESS || fv[1].nvmlReturn != NVML_SUCCESS) return false;
+    *tx = fv[0].value.ullVal * 1024ull;
+    *rx = fv[1].value.ullVal * 1024ull;
+    return true;
+  }
+
+ private:
+  bool load() {
+    void* h = dlopen("libnvidia-ml.so.1", RTLD_NOW | RTLD_LOCAL);
+    if (!h) { err_ = "libnvidia-ml.so.1 not found"; return false; }
+    auto sym = [&](const char* n) { return dlsym(h, n); };
+    auto init = (nvmlReturn_t(*)())sym("nvmlInit_v2");
+    by_index_ = (nvmlReturn_t(*)(unsigned, nvmlDevice_t*))sym("nvmlDeviceGetHandleByIndex_v2");
+    by_bus_ = (nvmlReturn_t(*)(const char*, nvmlDevice_t*))sym("nvmlDeviceGetHandleByPciBusId_v2");
+    clock_ = (nvmlReturn_t(*)(nvmlDevice_t, nvmlClockType_t, unsigned*))sym("nvmlDeviceGetClockInfo");
+    max_clock_ = (nvmlReturn_t(*)(nvmlDevice_t, nvmlClockType_t, unsigned*))sym("nvmlDeviceGetMaxClockInfo");
+    reasons_fn_ = (nvmlReturn_t(*)(nvmlDevice_t, unsigned long long*))sym("nvmlDeviceGetCurrentClocksEventReasons");
+    if (!reasons_fn_) reasons_fn_ = (nvmlReturn_t(*)(nvmlDevice_t, unsigned long long*))sym("nvmlDeviceGetCurrentClocksThrottleReasons");
+    field_values_ = (nvmlReturn_t(*)(nvmlDevice_t, int, nvmlFieldValue_t*))sym("nvmlDeviceGetFieldValues");
+    if (!init || !by_index_ || !by_bus_ || !clock_ || !max_clock_ || !reasons_fn_) { err_ = "NVML symbols missing"; return false; }
+    const nvmlReturn_t r = init();
+    if (r != NVML_SUCCESS) { err_ = "nvmlInit_v2 failed with " + std::to_string((int)r); return false; }
+    ok_ = true;
+    return true;
+  }
+  void run() {
+    while (!stop_) {
+      if (active_.load() > 0) {
+        for (int i = 0; i < ndev_; ++i) {
+          unsigned mhz = 0;
+          unsigned long long r = 0;
+          if (clock_(dev_[i], NVML_CLOCK_SM, &mhz) != NVML_SUCCESS) continue;
+          reasons_fn_(dev_[i], &r);
+          std::lock_guard<std::mutex> lk(mu_);
+          mhz_[i].push_back(mhz);
+          reasons_[i] |= r;
+        }
+      }
+      std::this_thread::sleep_for(std::chrono::microseconds(active_.load() > 0 ? 500 : 200));
+    }
+  }
+  bool ok_ = false, started_ = false;
+  std::atomic<bool> stop_{false};
+  std::atomic<int> active_{0};
+  std::string err_;
+  int ndev_ = 0;
+  nvmlDevice_t dev_[16];
+  unsigned max_mhz_[16] = {0};
+  std::vector<unsigned> mhz_[16];
+  unsigned long long reasons_[16] = {0};
+  std::mutex mu_;
+  std::thread th_;
+  nvmlReturn_t (*by_index_)(unsigned, nvmlDevice_t*) = nullptr;
+  nvmlReturn_t (*by_bus_)(const char*, nvmlDevice_t*) = nullptr;
+  nvmlReturn_t (*clock_)(nvmlDevice_t, nvmlClockType_t, unsigned*) = nullptr;
+  nvmlReturn_t (*max_clock_)(nvmlDevice_t, nvmlClockType_t, unsigned*) = nullptr;
+  nvmlReturn_t (*reasons_fn_)(nvmlDevice_t, unsigned long long*) = nullptr;
+  nvmlReturn_t (*field_values_)(nvmlDevice_t, int, nvmlFieldValue_t*) = nullptr;
 };
 
 enum QAStatus { QA_FAILED = 0, QA_PASSED = 1, QA_WAIVED = 2 };

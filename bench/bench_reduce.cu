@@ -112,6 +112,7 @@ Result run_one(const Options& o, b2r_workspace_t ws, Log* log) {
   for (int i = 0; i < o.warmup; ++i) reduce_once(d_in + (size_t)(i % copies) * bytes);
   BENCH_CUDA(cudaDeviceSynchronize());
 
+  ClockLog::Window clocks_window;  // clock samples from here on count as "during a timed region"
   // (a) the reference's measurement: host stopwatch, device sync on both sides of every iteration
   HostTimer ht;
   for (int i = 0; i < o.iters; ++i) {
@@ -210,6 +211,7 @@ int main(int argc, char** argv) {
   }
   b2r_workspace_t ws;
   BENCH_B2R(b2r_workspace_create(&ws, dev));
+  ClockLog::get().start(ndev);
 
   FILE* csv = f.has("csv") ? fopen(f.str("csv").c_str(), "a") : nullptr;
   FILE* jsonl = f.has("jsonl") ? fopen(f.str("jsonl").c_str(), "a") : nullptr;
@@ -276,6 +278,8 @@ int main(int argc, char** argv) {
   if (csv) fclose(csv);
   if (jsonl) fclose(jsonl);
   b2r_workspace_destroy(ws);
+  ClockLog::get().stop();
+  if (!ClockLog::get().print(stdout)) all_ok = false;  // a slowdown during the timed region invalidates the number
   cudaDeviceReset();
   return qa.finish(all_ok ? QA_PASSED : QA_FAILED);
 }

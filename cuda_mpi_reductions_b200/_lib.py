@@ -82,6 +82,7 @@ def _declare(lib: C.CDLL) -> None:
     sig("b2r_plan_local", [u64, i, i, i, C.POINTER(LaunchCfg), C.POINTER(LaunchCfg)])
     sig("b2r_workspace_trace_enable", [vp, i])
     sig("b2r_workspace_trace_read", [vp, C.POINTER(u64), i, C.POINTER(i)])
+    sig("b2r_workspace_trace_read_at", [vp, i, C.POINTER(u64), i, C.POINTER(i)])
     sig("b2r_reduce_from_host", [vp, vp, u64, i, i, vp, vp])
     for name, args in (
         ("b2r_comm_init_all", [C.POINTER(vp), i, C.POINTER(i), C.POINTER(CommConfig)]),
@@ -92,6 +93,7 @@ def _declare(lib: C.CDLL) -> None:
         ("b2r_comm_size", [vp, C.POINTER(i)]),
         ("b2r_comm_device", [vp, C.POINTER(i)]),
         ("b2r_comm_has_multicast", [vp, C.POINTER(i)]),
+        ("b2r_comm_workspace", [vp, C.POINTER(vp)]),
         ("b2r_symm_alloc", [vp, u64, C.POINTER(vp)]),
         ("b2r_symm_free_all", [vp]),
         ("b2r_symm_peer_ptr", [vp, vp, i, C.POINTER(vp)]),
@@ -102,6 +104,7 @@ def _declare(lib: C.CDLL) -> None:
         ("b2r_allreduce_ex", [vp, vp, u64, i, i, vp, vp, i]),
         ("b2r_reduce_scalar_sharded", [vp, vp, u64, i, i, i, i, vp, vp]),
         ("b2r_reduce_scalar_sharded_ex", [vp, vp, u64, i, i, i, i, vp, vp, C.POINTER(LaunchCfg)]),
+        ("b2r_reduce_scalar_sharded_from_host", [vp, vp, u64, i, i, i, i, vp, vp]),
         ("b2r_barrier", [vp, vp]),
         ("b2r_select_algo", [i, u64, i, i, i, i]),
         ("b2r_host_reduce_threads", [C.POINTER(vp), vp, u64, i, i, i, i, i]),

@@ -162,9 +162,11 @@ def plan(n: int, dtype: torch.dtype, op="sum", device: int = -1, cfg=None) -> di
             "unroll": chosen.unroll, "stages": chosen.stages, "tile_bytes": chosen.tile_bytes, "pdl": chosen.pdl, "dyn_pct": chosen.dyn_pct}
 
 
-def trace_last(workspace: Workspace, max_ctas: int = 4096) -> torch.Tensor:
-    """Phase stamps (ns, %globaltimer) of the last traced launch: tensor [ctas, 4] = start, streamed, combined, exit."""
+def trace_last(workspace, max_ctas: int = 4096, back: int = 0) -> torch.Tensor:
+    """Phase stamps (ns, %globaltimer) of a traced launch: tensor [ctas, 4] = start, streamed, combined, exit. `back` = how many
+    traced launches ago (0 = the last; the library keeps a ring of 8). `workspace` is a Workspace or a raw handle."""
     buf = (C.c_uint64 * (4 * max_ctas))()
     n = C.c_int()
-    _lib.check(_lib.LIB.b2r_workspace_trace_read(workspace.handle, buf, max_ctas, C.byref(n)), "b2r_workspace_trace_read")
+    h = workspace.handle if hasattr(workspace, "handle") else workspace
+    _lib.check(_lib.LIB.b2r_workspace_trace_read_at(h, back, buf, max_ctas, C.byref(n)), "b2r_workspace_trace_read_at")
     return torch.tensor(list(buf[: 4 * n.value]), dtype=torch.int64).reshape(n.value, 4)

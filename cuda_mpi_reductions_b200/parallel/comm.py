@@ -196,20 +196,19 @@ class Communicator:
         return start, out
 
     def reduce_scalar_sharded_from_host(self, x: torch.Tensor, op="sum", root: int = 0, all: bool = False):
-        """End-to-end flavour: `x` is this rank's shard in (pinned) HOST memory; it is copied to the GPU, reduced across
-        ranks, and the scalar is read back to the host on the ranks that own it (None elsewhere). Synchronous."""
+        """End-to-end flavour: `x` is this rank's shard in (pinned) HOST memory. The native pipeline streams it to the GPU in
+        chunks (copy engine overlapped with the reduction kernels), folds the chunk scalars and combines them across ranks over
+        NVLink in one more fused launch, and reads the scalar back on the ranks that own it (None elsewhere). Synchronous."""
         assert not x.is_cuda
-        key = (x.numel(), x.dtype)
-        buf = getattr(self, "_e2e_buf", None)
-        if buf is None or self._e2e_key != key:
-            buf = torch.empty(x.numel(), dtype=x.dtype, device=self.device)
-            self._e2e_buf, self._e2e_key = buf, key
-        buf.copy_(x.reshape(-1), non_blocking=True)
-        out = self.reduce_scalar_sharded(buf, op, root=root, all=all)
-        if out is None:
-            torch.cuda.current_stream(self.device).synchronize()
-            return None
-        return out.cpu()
+        x = x.contiguous()
+        gets = all or self.rank == root
+        out = torch.empty((), dtype=x.dtype) if gets else None
+        n = x.numel()
+        st = _lib.LIB.b2r_reduce_scalar_sharded_from_host(C.c_void_p(x.data_ptr() if n else 0), C.c_void_p(out.data_ptr() if gets else 0), n,
+                                                          b2r_dtype(x.dtype), op_code(op), root, 1 if all else 0, self._h,
+                                                          C.c_void_p(_raw_stream(self.device_index)))
+        _lib.check(st, "b2r_reduce_scalar_sharded_from_host")
+        return out
 
     def barrier(self) -> None:
         self._finish(_lib.LIB.b2r_barrier(self._h, self._stream()), "b2r_barrier")

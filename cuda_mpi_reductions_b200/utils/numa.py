@@ -49,6 +49,31 @@ def gpu_numa_node(pci_addr: str, sysfs_root: str = "/sys") -> int | None:
     return node if node >= 0 else None  # -1: the platform does not say
 
 
+def nvml_cpu_affinity(device_index: int) -> set[int]:
+    """The CPUs NVML calls 'ideal' for the device (what `nvidia-smi topo -m` prints as CPU Affinity). Used when sysfs has
+    no numa_node for the PCI function, which is the case in the containers this library is benchmarked in."""
+    try:
+        import pynvml
+
+        pynvml.nvmlInit()
+        import torch
+
+        uuid = str(torch.cuda.get_device_properties(device_index).uuid)
+        try:
+            h = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + uuid).encode())
+        except Exception:
+            h = pynvml.nvmlDeviceGetHandleByIndex(device_index)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+        cpus = set()
+        for w, mask in enumerate(words):
+            for b in range(64):
+                if int(mask) >> b & 1:
+                    cpus.add(64 * w + b)
+        return cpus
+    except Exception:
+        return set()
+
+
 def node_cpus(node: int, sysfs_root: str = "/sys") -> set[int]:
     try:
         with open(os.path.join(sysfs_root, f"devices/system/node/node{node}/cpulist")) as f:
@@ -71,15 +96,20 @@ def bind_to_gpu_node(device_index: int, sysfs_root: str = "/sys", pci_addr: str 
         return info
     node = gpu_numa_node(addr, sysfs_root)
     info["node"] = node
-    if node is None:
-        info["why"] = "the platform reports no NUMA node for the device"
-        return info
     try:
         allowed = os.sched_getaffinity(0)
     except (AttributeError, OSError):
         info["why"] = "sched_getaffinity unavailable"
         return info
-    cpus = node_cpus(node, sysfs_root) & allowed
+    if node is None:
+        # sysfs is silent (containers): ask NVML for the device's CPU affinity, the column `nvidia-smi topo -m` prints
+        cpus = nvml_cpu_affinity(device_index) & allowed if sysfs_root == "/sys" else set()
+        info["source"] = "nvml cpu affinity"
+        if not cpus:
+            info["why"] = "neither sysfs nor NVML reports a NUMA placement for the device"
+            return info
+    else:
+        cpus = node_cpus(node, sysfs_root) & allowed
     info["cpus"] = len(cpus)
     if not cpus:
         info["why"] = "none of the node's CPUs are in this process's cpuset"

@@ -172,6 +172,9 @@ void b2r_refresh_env(void);
 b2r_status_t b2r_workspace_trace_enable(b2r_workspace_t ws, int enable);
 /* Copies stamps of the last launch: stamps[4*cta + phase] in ns; returns number of CTAs in *n_ctas. */
 b2r_status_t b2r_workspace_trace_read(b2r_workspace_t ws, uint64_t* stamps, int max_ctas, int* n_ctas);
+/* The stamps of the launch `launches_back` traced launches ago (0 = the last one; a ring of 8 launches is kept), so the
+ * period between consecutive launches and the overlap of one launch with the next can be read off, not only one launch. */
+b2r_status_t b2r_workspace_trace_read_at(b2r_workspace_t ws, int launches_back, uint64_t* stamps, int max_ctas, int* n_ctas);
 
 /* Pipelined host->device + reduce: `host_in` is (ideally pinned) host memory; it is streamed to the GPU in
  * chunks that are reduced while the next chunk is in flight; out_host receives the scalar. Synchronous. */
@@ -212,6 +215,8 @@ b2r_status_t b2r_comm_rank(b2r_comm_t comm, int* rank);
 b2r_status_t b2r_comm_size(b2r_comm_t comm, int* nranks);
 b2r_status_t b2r_comm_device(b2r_comm_t comm, int* device);
 b2r_status_t b2r_comm_has_multicast(b2r_comm_t comm, int* yes);
+/* The workspace the communicator's scalar-sharded reductions run on (owned by the communicator; for tracing). */
+b2r_status_t b2r_comm_workspace(b2r_comm_t comm, b2r_workspace_t* ws);
 
 /* Symmetric allocation: every rank must call with the same size in the same order. Buffers obtained here are
  * addressable by every peer (zero-copy collectives); other device pointers are staged through the heap. */
@@ -249,6 +254,13 @@ b2r_status_t b2r_reduce_scalar_sharded(const void* in, void* out, uint64_t count
 /* Same with an explicit launch configuration for the local streaming part (variant, threads, ctas, pdl, ...). */
 b2r_status_t b2r_reduce_scalar_sharded_ex(const void* in, void* out, uint64_t count, b2r_dtype_t dtype, b2r_op_t op,
                                           int root, int all, b2r_comm_t comm, void* stream, const b2r_launch_cfg_t* cfg);
+
+/* End-to-end flavour (vendored simpleMultiGPU's H2D + kernel + D2H + host loop, simpleMultiGPU.cpp:227-293, without the host
+ * loop): this rank's shard is `count` elements of (pinned) HOST memory. It is copied to the GPU in chunks by the copy engine
+ * while earlier chunks are reduced; one more fused launch folds the chunk scalars and combines them across the GPUs over
+ * NVLink; the scalar is written to out_host (an element of `dtype`) on root, or on every rank with `all`. Synchronous. */
+b2r_status_t b2r_reduce_scalar_sharded_from_host(const void* host_in, void* out_host, uint64_t count, b2r_dtype_t dtype, b2r_op_t op,
+                                                 int root, int all, b2r_comm_t comm, void* stream);
 
 b2r_status_t b2r_barrier(b2r_comm_t comm, void* stream);
 

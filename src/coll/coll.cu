@@ -351,6 +351,11 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
         L.a[n == 1 ? 0 : rc[i].c->rank].sub_blocks = subs;
       }
     }
+    if (kind == kCollNvls && !is_all) {
+      // reduce: share of the message (in 64ths) that the root pulls through the switch itself; 0 = equal slices for all ranks
+      const int share = std::max(0, std::min(64, B2R_ENV_INT("B2R_NVLS_ROOT_SHARE", 0)));
+      for (int i = 0; i < n; ++i) L.a[n == 1 ? 0 : rc[i].c->rank].sub_blocks = share;
+    }
     if (kind == kCollPush) {
       // staging ring in the work region: depth x P sources x ctas blocks of (threads x 4) vectors; at least 2 deep
       const uint64_t block_bytes = (uint64_t)threads * 4 * 16;
@@ -550,6 +555,43 @@ b2r_status_t b2r_reduce_scalar_sharded(const void* in, void* out, uint64_t count
                                        b2r_comm_t comm, void* stream) {
   return b2r_reduce_scalar_sharded_ex(in, out, count, dtype, op, root, all, comm, stream, nullptr);
 }
+// End-to-end flavour of the sharded scalar reduce (what the vendored simpleMultiGPU does with cudaMemcpyAsync + a host loop,
+// simpleMultiGPU.cpp:227-293): this rank's shard lives in (pinned) HOST memory. It is streamed to the GPU in chunks by the copy
+// engine while earlier chunks are being reduced; the per-chunk scalars are then folded, and combined across the GPUs over
+// NVLink, by ONE more launch of the fused kernel; the ranks that own the result read it back. Synchronous on `stream`.
+b2r_status_t b2r_reduce_scalar_sharded_from_host(const void* host_in, void* out_host, uint64_t count, b2r_dtype_t dtype, b2r_op_t op, int root,
+                                                 int all, b2r_comm_t comm, void* stream_) {
+  NvtxRange nvtx("b2r_reduce_scalar_sharded_from_host");
+  B2R_REQUIRE(comm != nullptr, "b2r_reduce_scalar_sharded_from_host: communicator is NULL");
+  B2R_REQUIRE(!(comm->mode == kModeLoopback && comm->nranks > 1), "b2r_reduce_scalar_sharded_from_host: not available on loopback groups");
+  B2R_REQUIRE(root >= 0 && root < comm->nranks, "b2r_reduce_scalar_sharded_from_host: root %d out of range [0,%d)", root, comm->nranks);
+  const bool gets = all || comm->rank == root;
+  B2R_REQUIRE(!gets || out_host != nullptr, "b2r_reduce_scalar_sharded_from_host: out_host is NULL on a rank that receives the result");
+  cudaStream_t stream = (cudaStream_t)stream_;
+  b2r_workspace* ws = comm->ws;
+  int prev = 0;
+  B2R_CUDA_CHECK(cudaGetDevice(&prev));
+  B2R_CUDA_CHECK(cudaSetDevice(comm->device));
+  struct Restore { int d; ~Restore() { cudaSetDevice(d); } } restore{prev};
+  uint64_t nchunks = 0;
+  B2R_CHECK(stream_chunks_from_host(host_in, count, dtype, op, ws, stream, &nchunks));
+  // fold the chunk scalars (accumulator precision, chunk order) and combine across ranks in the same launch
+  const b2r_dtype_t acc_dtype = dtype == B2R_BFLOAT16 ? B2R_FLOAT32 : dtype;
+  const size_t acc_sz = dtype == B2R_FLOAT64 ? 8 : 4;
+  char* d_final = (char*)ws->d_chunk_out + (size_t)kMaxChunks * 8;
+  PendingCall pc{kCallScalar, ws->d_chunk_out, d_final, nchunks, acc_dtype, op, root, all ? 1 : 0, B2R_ALGO_AUTO, stream};
+  pc.has_cfg = false;
+  B2R_CHECK(submit(comm, pc));
+  unsigned char acc[8] = {0};
+  if (gets) B2R_CUDA_CHECK(cudaMemcpyAsync(ws->h_chunk_out, d_final, acc_sz, cudaMemcpyDeviceToHost, stream));
+  B2R_CUDA_CHECK(cudaStreamSynchronize(stream));
+  if (gets) {
+    memcpy(acc, ws->h_chunk_out, acc_sz);
+    acc_to_dtype(acc, dtype, out_host);
+  }
+  return B2R_OK;
+}
+
 b2r_status_t b2r_barrier(b2r_comm_t comm, void* stream) {
   PendingCall pc{kCallBarrier, nullptr, nullptr, 0, B2R_INT32, B2R_SUM, -1, 0, B2R_ALGO_AUTO, (cudaStream_t)stream};
   return submit(comm, pc);

@@ -745,7 +745,20 @@ __device__ void nvls_body(const CollArgs& A) {
     // goes back out through the multicast address (multimem.st reaches all P copies). reduce: the result is stored
     // straight into the ROOT's recv buffer over NVLink — issuing the multimem loads from all P GPUs instead of from the
     // root alone keeps every GPU's request stream short (a root-only variant tops out near 385 GB/s).
-    const unsigned long long lo = nunit * (unsigned long long)c.rank / P, hi = nunit * (unsigned long long)(c.rank + 1) / P;
+    unsigned long long lo = nunit * (unsigned long long)c.rank / P, hi = nunit * (unsigned long long)(c.rank + 1) / P;
+    if (A.root >= 0 && A.sub_blocks > 0) {
+      // reduce with an uneven split: the root pulls the first sub_blocks/64 of the message itself (its result needs no second
+      // hop: egress of the other GPUs drops from 1 + 1/P towards 1 message), the other ranks share the rest equally
+      const unsigned long long cut = nunit / 64 * (unsigned)A.sub_blocks;
+      if (c.rank == A.root) {
+        lo = 0;
+        hi = cut;
+      } else {
+        const unsigned long long w = (unsigned long long)(c.rank < A.root ? c.rank : c.rank - 1);
+        lo = cut + (nunit - cut) * w / (P - 1);
+        hi = cut + (nunit - cut) * (w + 1) / (P - 1);
+      }
+    }
     {
       const char* msrc = c.mc + A.send_off;
       char* mdst = c.mc + A.recv_off;

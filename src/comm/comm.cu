@@ -484,6 +484,12 @@ b2r_status_t b2r_comm_has_multicast(b2r_comm_t c, int* yes) {
   return B2R_OK;
 }
 
+b2r_status_t b2r_comm_workspace(b2r_comm_t c, b2r_workspace_t* ws) {
+  B2R_REQUIRE(c && ws, "NULL argument");
+  *ws = c->ws;
+  return B2R_OK;
+}
+
 b2r_status_t b2r_symm_alloc(b2r_comm_t c, uint64_t bytes, void** ptr) {
   B2R_REQUIRE(c && ptr, "b2r_symm_alloc: NULL argument");
   const size_t need = round_up((size_t)std::max<uint64_t>(bytes, 1), 256);

@@ -20,6 +20,9 @@ b2r_status_t prepare_local(const void* in, void* out, uint64_t count, b2r_dtype_
                            const b2r_launch_cfg_t* cfg, int out_as_acc, LaunchGeom* g, LocalParams* p);
 b2r_status_t reduce_local_impl(const void* in, void* out, uint64_t count, b2r_dtype_t dtype, b2r_op_t op, b2r_workspace* ws,
                                cudaStream_t stream, const b2r_launch_cfg_t* cfg, int out_as_acc, const XgCall* xg);
+b2r_status_t stream_chunks_from_host(const void* host_in, uint64_t count, b2r_dtype_t dtype, b2r_op_t op, b2r_workspace* ws, cudaStream_t stream,
+                                     uint64_t* nchunks);
+void acc_to_dtype(const void* acc, b2r_dtype_t dtype, void* out);
 b2r_status_t launch_any(b2r_dtype_t dtype, int op, const LaunchGeom& g, const LocalParams& p, cudaStream_t stream);
 b2r_status_t launch_multi_any(b2r_dtype_t dtype, int op, int nranks, int ctas, int threads, const MultiLocalParams& mp, cudaStream_t stream);
 

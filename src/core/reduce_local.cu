@@ -57,9 +57,11 @@ Tuned tuned_defaults(b2r_dtype_t dtype, b2r_op_t op, uint64_t bytes, int early) 
     t.ctas_per_sm = 1;
     t.stages = 4;
   } else {
+    // plain order / safe programmatic launch. 256 threads x 8 CTAs per SM + one prefetched line per thread measured best at
+    // 64 MiB (10.8 us per launch; 512 x 4 with two lines: 11.4; no prefetch: 12.2; no programmatic launch at all: 16.4)
     t.variant = B2R_VARIANT_LDG128;
-    t.threads = 512;
-    t.ctas_per_sm = 4;
+    t.threads = 256;
+    t.ctas_per_sm = 8;
     t.stages = 4;
     if (bytes >= (8ull << 20)) t.dyn_pct = 25;
   }
@@ -82,7 +84,7 @@ b2r_status_t plan_local(uint64_t count, b2r_dtype_t dtype, b2r_op_t op, int sm_c
   if (hint && hint->variant && hint->variant != t.variant) {
     // a forced variant keeps its own sensible geometry
     if (hint->variant == B2R_VARIANT_TMA) { t.threads = early ? 288 : 160; t.ctas_per_sm = early ? 1 : 3; t.stages = 4; t.dyn_pct = 0; }
-    else { t.threads = 512; t.ctas_per_sm = early ? 1 : 4; }
+    else { t.threads = early ? 512 : 256; t.ctas_per_sm = early ? 1 : 8; }
   }
   t.variant = B2R_ENV_INT("B2R_VARIANT", t.variant);
   t.threads = B2R_ENV_INT("B2R_THREADS", t.threads);
@@ -203,12 +205,19 @@ b2r_status_t prepare_local(const void* in, void* out, uint64_t count, b2r_dtype_
   split_edges(in, count, esz, g->variant == B2R_VARIANT_LDG256 ? 32u : 16u, &p);
   p.partials = ws->d_partials;
   p.ticket = ws->d_ticket;
-  p.trace = ws->trace_enabled ? ws->d_trace : nullptr;
+  p.trace = nullptr;
+  if (ws->trace_enabled && ws->d_trace) {  // the next slot of the trace ring
+    const unsigned slot = ws->trace_seq++ % kTraceRing;
+    p.trace = ws->d_trace + (size_t)slot * kMaxCtas * 4;
+    ws->trace_ctas[slot] = g->ctas;
+  }
   p.stages = stages;
   p.tile_vecs = tile_vecs;
   p.out_as_acc = out_as_acc;
-  p.acc64 = ws->d_acc64;
-  p.prefetch_lines = g->pdl == B2R_PDL_SAFE ? (unsigned)std::max(0, std::min(64, B2R_ENV_INT("B2R_PREFETCH_LINES", 2))) : 0u;
+  p.acc64 = B2R_ENV_INT("B2R_PACKED_SUM", 1) ? ws->d_acc64 : nullptr;  // int32 SUM: grid stage in one atomic (finish_grid_packed)
+  // safe programmatic launch: lines per thread pulled into L2 while the previous kernel finishes (one line x 256 threads = 32 KiB
+  // per CTA; more than that competes with the streaming loop of the kernel that is still running and costs more than it saves)
+  p.prefetch_lines = g->pdl == B2R_PDL_SAFE ? (unsigned)std::max(0, std::min(64, B2R_ENV_INT("B2R_PREFETCH_LINES", 1))) : 0u;
   p.dyn_first = p.nvec;
   if (g->dyn_pct > 0) {
     // tiles of one load round of the CTA (threads x unroll vectors: 32 KiB for 512 x 4 x 16 B), grown when the per-tile partials
@@ -283,6 +292,72 @@ b2r_status_t launch_multi_any(b2r_dtype_t dtype, int op, int nranks, int ctas, i
   return fail(B2R_ERR_INVALID, "bad dtype %d", (int)dtype);
 }
 
+// Accumulator-precision scalar (fp32 for bf16) -> one element of `dtype` (bf16: round to nearest even, NaN kept quiet).
+void acc_to_dtype(const void* acc, b2r_dtype_t dtype, void* out) {
+  if (dtype == B2R_BFLOAT16) {
+    uint32_t u;
+    memcpy(&u, acc, 4);
+    uint16_t b;
+    if ((u & 0x7fffffffu) > 0x7f800000u) b = (uint16_t)((u >> 16) | 0x40u);
+    else b = (uint16_t)((u + 0x7fffu + ((u >> 16) & 1u)) >> 16);
+    memcpy(out, &b, 2);
+  } else {
+    memcpy(out, acc, b2r_dtype_size(dtype));
+  }
+}
+
+// The streaming half of the host -> device pipelines (b2r_reduce_from_host, b2r_reduce_scalar_sharded_from_host): on return
+// the per-chunk scalars of the host array, in accumulator precision, are being written to ws->d_chunk_out[0, nchunks) by
+// work queued on `stream`; nothing has been synchronised. The caller's current device must be ws->device.
+b2r_status_t stream_chunks_from_host(const void* host_in, uint64_t count, b2r_dtype_t dtype, b2r_op_t op, b2r_workspace* ws,
+                                     cudaStream_t stream, uint64_t* nchunks_out) {
+  B2R_REQUIRE(host_in != nullptr || count == 0, "reduce from host: host_in is NULL");
+  B2R_REQUIRE(dtype >= B2R_INT32 && dtype <= B2R_BFLOAT16, "bad dtype %d", (int)dtype);
+  B2R_REQUIRE(op >= B2R_SUM && op <= B2R_MAX, "bad op %d", (int)op);
+  const size_t esz = b2r_dtype_size(dtype);
+  const size_t acc_sz = dtype == B2R_FLOAT64 ? 8 : 4;
+  const uint64_t chunk_bytes = (uint64_t)std::max(1, B2R_ENV_INT("B2R_H2D_CHUNK_MB", 8)) << 20;
+  const uint64_t chunk_elems = chunk_bytes / esz;
+  const uint64_t nchunks = count == 0 ? 0 : (count + chunk_elems - 1) / chunk_elems;
+  B2R_REQUIRE(nchunks <= kMaxChunks, "reduce from host: %llu chunks > %d; raise B2R_H2D_CHUNK_MB", (unsigned long long)nchunks, kMaxChunks);
+
+  if (!ws->copy_stream) {
+    B2R_CUDA_CHECK(cudaStreamCreateWithFlags(&ws->copy_stream, cudaStreamNonBlocking));
+    B2R_CUDA_CHECK(cudaMalloc(&ws->d_chunk_out, (size_t)(kMaxChunks + 2) * 8));  // + the final scalar of the sharded flavour
+    B2R_CUDA_CHECK(cudaMallocHost(&ws->h_chunk_out, (size_t)(kMaxChunks + 2) * 8));
+    for (int i = 0; i < kStageBufs; ++i) {
+      B2R_CUDA_CHECK(cudaEventCreateWithFlags(&ws->ev_copied[i], cudaEventDisableTiming));
+      B2R_CUDA_CHECK(cudaEventCreateWithFlags(&ws->ev_consumed[i], cudaEventDisableTiming));
+    }
+  }
+  if (ws->stage_bytes < chunk_bytes) {
+    for (int i = 0; i < kStageBufs; ++i) {
+      if (ws->d_stage[i]) B2R_CUDA_CHECK(cudaFree(ws->d_stage[i]));
+      ws->d_stage[i] = nullptr;
+      B2R_CUDA_CHECK(cudaMalloc(&ws->d_stage[i], chunk_bytes));
+    }
+    ws->stage_bytes = chunk_bytes;
+  }
+
+  // the copy stream must not run ahead of work already queued on `stream` that may still use the staging buffers
+  B2R_CUDA_CHECK(cudaEventRecord(ws->ev_consumed[0], stream));
+  B2R_CUDA_CHECK(cudaStreamWaitEvent(ws->copy_stream, ws->ev_consumed[0], 0));
+  for (uint64_t c = 0; c < nchunks; ++c) {
+    const int b = (int)(c % kStageBufs);
+    const uint64_t first = c * chunk_elems;
+    const uint64_t n = std::min(chunk_elems, count - first);
+    if (c >= (uint64_t)kStageBufs) B2R_CUDA_CHECK(cudaStreamWaitEvent(ws->copy_stream, ws->ev_consumed[b], 0));
+    B2R_CUDA_CHECK(cudaMemcpyAsync(ws->d_stage[b], (const char*)host_in + first * esz, n * esz, cudaMemcpyHostToDevice,
+                                   ws->copy_stream));
+    B2R_CUDA_CHECK(cudaEventRecord(ws->ev_copied[b], ws->copy_stream));
+    B2R_CUDA_CHECK(cudaStreamWaitEvent(stream, ws->ev_copied[b], 0));
+    B2R_CHECK(reduce_local_impl(ws->d_stage[b], (char*)ws->d_chunk_out + c * acc_sz, n, dtype, op, ws, stream, nullptr, 1, nullptr));
+    B2R_CUDA_CHECK(cudaEventRecord(ws->ev_consumed[b], stream));
+  }
+  *nchunks_out = nchunks;
+  return B2R_OK;
+}
+
 }  // namespace b2r
 
 using namespace b2r;
@@ -303,8 +378,8 @@ b2r_status_t b2r_workspace_create(b2r_workspace_t* out, int device) {
   if (e == cudaSuccess) ws->d_tile_ctr = ws->d_ticket + 32;  // its own 128-byte line of the same allocation
   if (e == cudaSuccess) ws->d_acc64 = (unsigned long long*)(ws->d_ticket + 16);  // int32 SUM: packed arrivals + sum
   ws->max_partials = kMaxCtas;
-  if (e == cudaSuccess) e = cudaMalloc((void**)&ws->d_trace, (size_t)kMaxCtas * 4 * sizeof(unsigned long long));
-  if (e == cudaSuccess) e = cudaMemset(ws->d_trace, 0, (size_t)kMaxCtas * 4 * sizeof(unsigned long long));
+  if (e == cudaSuccess) e = cudaMalloc((void**)&ws->d_trace, (size_t)kTraceRing * kMaxCtas * 4 * sizeof(unsigned long long));
+  if (e == cudaSuccess) e = cudaMemset(ws->d_trace, 0, (size_t)kTraceRing * kMaxCtas * 4 * sizeof(unsigned long long));
   if (e == cudaSuccess) e = cudaDeviceSynchronize();
   cudaSetDevice(prev);
   if (e != cudaSuccess) {
@@ -381,17 +456,24 @@ b2r_status_t b2r_workspace_trace_enable(b2r_workspace_t ws, int enable) {
   return B2R_OK;
 }
 
-b2r_status_t b2r_workspace_trace_read(b2r_workspace_t ws, uint64_t* stamps, int max_ctas, int* n_ctas) {
+b2r_status_t b2r_workspace_trace_read_at(b2r_workspace_t ws, int launches_back, uint64_t* stamps, int max_ctas, int* n_ctas) {
   B2R_REQUIRE(ws != nullptr && stamps != nullptr && n_ctas != nullptr, "b2r_workspace_trace_read: NULL argument");
-  int n = std::min(ws->last_ctas, max_ctas);
+  B2R_REQUIRE(launches_back >= 0 && launches_back < kTraceRing && (unsigned)launches_back < ws->trace_seq,
+              "b2r_workspace_trace_read: launch %d back is not in the ring (%u traced launches, ring of %d)", launches_back, ws->trace_seq, kTraceRing);
+  const unsigned slot = (ws->trace_seq - 1u - (unsigned)launches_back) % kTraceRing;
+  int n = std::min(ws->trace_ctas[slot], max_ctas);
   int prev = 0;
   B2R_CUDA_CHECK(cudaGetDevice(&prev));
   B2R_CUDA_CHECK(cudaSetDevice(ws->device));
-  cudaError_t e = cudaMemcpy(stamps, ws->d_trace, (size_t)n * 4 * sizeof(uint64_t), cudaMemcpyDeviceToHost);
+  cudaError_t e = cudaMemcpy(stamps, ws->d_trace + (size_t)slot * kMaxCtas * 4, (size_t)n * 4 * sizeof(uint64_t), cudaMemcpyDeviceToHost);
   cudaSetDevice(prev);
   if (e != cudaSuccess) return fail(B2R_ERR_CUDA, "trace_read: %s", cudaGetErrorString(e));
   *n_ctas = n;
   return B2R_OK;
+}
+
+b2r_status_t b2r_workspace_trace_read(b2r_workspace_t ws, uint64_t* stamps, int max_ctas, int* n_ctas) {
+  return b2r_workspace_trace_read_at(ws, 0, stamps, max_ctas, n_ctas);
 }
 
 // Pipelined host -> device + reduce. The host array is cut into chunks; chunk i is copied by the copy engine on a
@@ -401,57 +483,15 @@ b2r_status_t b2r_reduce_from_host(const void* host_in, void* out_host, uint64_t 
                                   b2r_workspace_t ws, void* stream_) {
   NvtxRange nvtx("b2r_reduce_from_host");
   B2R_REQUIRE(ws != nullptr && out_host != nullptr, "b2r_reduce_from_host: NULL argument");
-  B2R_REQUIRE(host_in != nullptr || count == 0, "b2r_reduce_from_host: host_in is NULL");
-  B2R_REQUIRE(dtype >= B2R_INT32 && dtype <= B2R_BFLOAT16, "bad dtype %d", (int)dtype);
-  B2R_REQUIRE(op >= B2R_SUM && op <= B2R_MAX, "bad op %d", (int)op);
   cudaStream_t stream = (cudaStream_t)stream_;
-  const size_t esz = b2r_dtype_size(dtype);
-  const size_t acc_sz = dtype == B2R_FLOAT64 ? 8 : 4;
-  const b2r_dtype_t acc_dtype = dtype == B2R_BFLOAT16 ? B2R_FLOAT32 : dtype;
   int prev = 0;
   B2R_CUDA_CHECK(cudaGetDevice(&prev));
   B2R_CUDA_CHECK(cudaSetDevice(ws->device));
   struct Restore { int d; ~Restore() { cudaSetDevice(d); } } restore{prev};
-
-  const uint64_t chunk_bytes = (uint64_t)std::max(1, B2R_ENV_INT("B2R_H2D_CHUNK_MB", 8)) << 20;
-  const uint64_t chunk_elems = chunk_bytes / esz;
-  const uint64_t nchunks = count == 0 ? 0 : (count + chunk_elems - 1) / chunk_elems;
-  B2R_REQUIRE(nchunks <= kMaxChunks, "b2r_reduce_from_host: %llu chunks > %d; raise B2R_H2D_CHUNK_MB",
-              (unsigned long long)nchunks, kMaxChunks);
-
-  if (!ws->copy_stream) {
-    B2R_CUDA_CHECK(cudaStreamCreateWithFlags(&ws->copy_stream, cudaStreamNonBlocking));
-    B2R_CUDA_CHECK(cudaMalloc(&ws->d_chunk_out, (size_t)kMaxChunks * 8));
-    B2R_CUDA_CHECK(cudaMallocHost(&ws->h_chunk_out, (size_t)kMaxChunks * 8));
-    for (int i = 0; i < kStageBufs; ++i) {
-      B2R_CUDA_CHECK(cudaEventCreateWithFlags(&ws->ev_copied[i], cudaEventDisableTiming));
-      B2R_CUDA_CHECK(cudaEventCreateWithFlags(&ws->ev_consumed[i], cudaEventDisableTiming));
-    }
-  }
-  if (ws->stage_bytes < chunk_bytes) {
-    for (int i = 0; i < kStageBufs; ++i) {
-      if (ws->d_stage[i]) B2R_CUDA_CHECK(cudaFree(ws->d_stage[i]));
-      ws->d_stage[i] = nullptr;
-      B2R_CUDA_CHECK(cudaMalloc(&ws->d_stage[i], chunk_bytes));
-    }
-    ws->stage_bytes = chunk_bytes;
-  }
-
-  // the copy stream must not run ahead of work already queued on `stream` that may still use the staging buffers
-  B2R_CUDA_CHECK(cudaEventRecord(ws->ev_consumed[0], stream));
-  B2R_CUDA_CHECK(cudaStreamWaitEvent(ws->copy_stream, ws->ev_consumed[0], 0));
-  for (uint64_t c = 0; c < nchunks; ++c) {
-    const int b = (int)(c % kStageBufs);
-    const uint64_t first = c * chunk_elems;
-    const uint64_t n = std::min(chunk_elems, count - first);
-    if (c >= (uint64_t)kStageBufs) B2R_CUDA_CHECK(cudaStreamWaitEvent(ws->copy_stream, ws->ev_consumed[b], 0));
-    B2R_CUDA_CHECK(cudaMemcpyAsync(ws->d_stage[b], (const char*)host_in + first * esz, n * esz, cudaMemcpyHostToDevice,
-                                   ws->copy_stream));
-    B2R_CUDA_CHECK(cudaEventRecord(ws->ev_copied[b], ws->copy_stream));
-    B2R_CUDA_CHECK(cudaStreamWaitEvent(stream, ws->ev_copied[b], 0));
-    B2R_CHECK(reduce_local_impl(ws->d_stage[b], (char*)ws->d_chunk_out + c * acc_sz, n, dtype, op, ws, stream, nullptr, 1, nullptr));
-    B2R_CUDA_CHECK(cudaEventRecord(ws->ev_consumed[b], stream));
-  }
+  uint64_t nchunks = 0;
+  B2R_CHECK(stream_chunks_from_host(host_in, count, dtype, op, ws, stream, &nchunks));
+  const size_t acc_sz = dtype == B2R_FLOAT64 ? 8 : 4;
+  const b2r_dtype_t acc_dtype = dtype == B2R_BFLOAT16 ? B2R_FLOAT32 : dtype;
   if (nchunks) {
     B2R_CUDA_CHECK(cudaMemcpyAsync(ws->h_chunk_out, ws->d_chunk_out, nchunks * acc_sz, cudaMemcpyDeviceToHost, stream));
   }
@@ -459,18 +499,7 @@ b2r_status_t b2r_reduce_from_host(const void* host_in, void* out_host, uint64_t 
   // combine chunk scalars in chunk order (accumulator precision), then round once
   unsigned char acc[8];
   b2r_reduce_host(ws->h_chunk_out, acc, nchunks, acc_dtype, op);
-  if (dtype == B2R_BFLOAT16) {
-    float f;
-    memcpy(&f, acc, 4);
-    uint32_t u;
-    memcpy(&u, &f, 4);
-    uint16_t b;
-    if ((u & 0x7fffffffu) > 0x7f800000u) b = (uint16_t)((u >> 16) | 0x40u);
-    else b = (uint16_t)((u + 0x7fffu + ((u >> 16) & 1u)) >> 16);
-    memcpy(out_host, &b, 2);
-  } else {
-    memcpy(out_host, acc, esz);
-  }
+  acc_to_dtype(acc, dtype, out_host);
   return B2R_OK;
 }
 

@@ -8,6 +8,7 @@ namespace b2r {
 constexpr int kMaxCtas = 4096;    // upper bound on partials (CTAs or clusters) of one launch
 constexpr int kStageBufs = 3;     // staging ring of b2r_reduce_from_host
 constexpr int kMaxChunks = 4096;  // chunks per b2r_reduce_from_host call
+constexpr int kTraceRing = 8;     // traced launches kept (a ring: the stamps of the last kTraceRing launches can be read back)
 }  // namespace b2r
 
 struct b2r_workspace {
@@ -18,7 +19,9 @@ struct b2r_workspace {
   unsigned* d_tile_ctr = nullptr;         // dynamic tail: next unclaimed tile, zero between launches (nullptr: no dynamic tail)
   unsigned long long* d_acc64 = nullptr;  // int32 SUM: packed {arrivals, running sum}, zero between launches (nullptr: not offered)
   int max_partials = 0;                   // capacity of d_partials in 8-byte entries
-  unsigned long long* d_trace = nullptr;  // kMaxCtas x 4 stamps
+  unsigned long long* d_trace = nullptr;  // kTraceRing x kMaxCtas x 4 stamps
+  unsigned trace_seq = 0;                 // traced launches so far (slot = trace_seq % kTraceRing)
+  int trace_ctas[b2r::kTraceRing] = {0};  // CTAs of the launch in each slot
   bool trace_enabled = false;
   int last_ctas = 0;
   int last_geom[4] = {0, 0, 0, 0};

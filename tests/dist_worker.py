@@ -78,6 +78,43 @@ def main():
                         if abs(g.double().item() - want.double().item()) > tol * max(1.0, abs(want.double().item())):
                             fails += 1
                             print(f"[rank {rank}] scalar MISMATCH dtype={dtype} count={count} op={op} got={g.item()} want={want.item()}", flush=True)
+    # end-to-end flavour: shards in pinned host memory, native chunked pipeline + cross-GPU combine, every root, both flavours
+    for dtype in (torch.int32, torch.float64, torch.bfloat16):
+        for count in (1, 3_000_001, (5 << 20) + 7):
+            h = b2r.fill_host(count, dtype, seed=300 + rank, mode="sdk", pin_memory=True)
+            d = h.cuda()
+            gathered = [torch.empty_like(d) for _ in range(world)]
+            dist.all_gather(gathered, d)
+            whole = torch.cat([g.cpu() for g in gathered])
+            for op in ("sum", "min"):
+                want = b2r.reduce_oracle(whole, op)
+                for root, allflag in ((0, False), (world - 1, False), (0, True)):
+                    o = comm.reduce_scalar_sharded_from_host(h, op, root=root, all=allflag)
+                    comm.check()
+                    if (o is None) != (not allflag and rank != root):
+                        fails += 1
+                        print(f"[rank {rank}] from_host returned a result on the wrong ranks", flush=True)
+                    if o is not None:
+                        tol = {torch.int32: 0, torch.float64: 1e-12, torch.bfloat16: 2.0**-7}[dtype]
+                        if abs(o.double().item() - want.double().item()) > tol * max(1.0, abs(want.double().item())):
+                            fails += 1
+                            print(f"[rank {rank}] from_host MISMATCH dtype={dtype} count={count} op={op} got={o.item()} want={want.item()}", flush=True)
+    # the experimental-no-more paths on real NVLink: LL (small), ring allreduce, pipelined ring
+    for dtype in (torch.int32, torch.float32):
+        for count in (5, 1000, comm.ll_max_bytes // 4):
+            x = b2r.fill_device(count, dtype, seed=400 + rank, mode="signed")
+            gathered = [torch.empty_like(x) for _ in range(world)]
+            dist.all_gather(gathered, x)
+            want = gathered[0].cpu().clone()
+            for g in gathered[1:]:
+                b2r.combine_oracle(want, g.cpu(), "sum")
+            for i in range(6):
+                out = comm.allreduce(x, "sum", algo="ll")
+                red = comm.reduce(x, "sum", root=i % world, algo="ll")
+                comm.check()
+                if not torch.equal(out.cpu(), want) or (rank == i % world and not torch.equal(red.cpu(), want)):
+                    fails += 1
+                    print(f"[rank {rank}] LL MISMATCH dtype={dtype} count={count}", flush=True)
     # symmetric zero-copy + in place + stress of small back-to-back collectives
     s = comm.symm_empty(1 << 20, torch.float32)
     s.fill_(float(rank + 1))

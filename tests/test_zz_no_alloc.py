@@ -57,14 +57,17 @@ def make_input(n, dtype, seed):
     return (torch.rand(n, generator=g, dtype=torch.float64) * 2 - 1).to(dtype).cuda()
 
 
-def agree(a: torch.Tensor, b: torch.Tensor, dtype, op, n):
-    """Same tolerance as tests/test_reduce_local_gpu.py: integers and min/max exact, fp sums within the accumulation
-    bound (both entry points use the same kernels, so they normally agree to the bit)."""
+def agree(a: torch.Tensor, b: torch.Tensor, dtype, op, n, mag):
+    """Same tolerance as tests/test_reduce_local_gpu.py: integers and min/max exact; floating-point sums within the
+    accumulation bound, which scales with the sum of magnitudes `mag` (the two entry points may use different launch
+    geometries — static split here, dynamically scheduled tail there — so their partial sums associate differently)."""
     x, y = a.cpu().double().item(), b.cpu().double().item()
     if dtype == torch.int32 or op != SUM:
         return x == y or (math.isnan(x) and math.isnan(y))
-    rel = {torch.float32: 6e-8, torch.float64: 1e-15, torch.bfloat16: 2.0**-8}[dtype]
-    return abs(x - y) <= rel * max(1.0, math.log2(max(n, 2))) * max(abs(x), abs(y), 1e-30) * 8
+    if dtype == torch.bfloat16:  # fp32 accumulation, one rounding to bf16 at the end
+        return abs(x - y) <= 2.0**-7 * max(abs(x), abs(y)) + 6e-8 * mag * math.log2(max(n, 2))
+    rel = {torch.float32: 6e-8, torch.float64: 1e-15}[dtype]
+    return abs(x - y) <= 2 * rel * max(mag, 1e-30) * max(1.0, math.log2(max(n, 2)))
 
 
 @pytest.mark.parametrize("dtype", list(DTYPES))
@@ -84,7 +87,8 @@ def test_noalloc_matches_workspace_entry_point_twice_in_a_row(lib, dtype):
                 st = lib.b2r_reduce_local_noalloc(x.data_ptr(), got.data_ptr(), n, DTYPES[dtype], op, stream, None)
                 assert st == 0, lib.b2r_last_error_string().decode()
                 torch.cuda.synchronize()
-                assert agree(got, want, dtype, op, n), (dtype, op, n, got.item(), want.item())
+                mag = x.double().abs().sum().item()
+                assert agree(got, want, dtype, op, n, mag), (dtype, op, n, got.item(), want.item())
     finally:
         lib.b2r_workspace_destroy(ws)
 
