@@ -172,7 +172,8 @@ int main(int argc, char** argv) {
   const bool tune = f.has("tune");
   const bool sweep = f.has("sweep") || tune;
   const uint64_t total_bytes = (uint64_t)f.i64("total-mib", 2048) << 20;
-  const uint64_t max_bytes = tune ? (uint64_t)f.i64("bytes", 256ll << 20) : (sweep ? (uint64_t)f.i64("max-bytes", 1ll << 32) : total_bytes / P);
+  const uint64_t max_bytes = tune ? (uint64_t)f.i64("bytes", 256ll << 20)
+                             : ((sweep || f.has("plan")) ? (uint64_t)f.i64("max-bytes", 1ll << 32) : total_bytes / P);
   const int root = (int)f.i64("root", 0);
 
   b2r_comm_config_t cfg;
@@ -213,7 +214,83 @@ int main(int argc, char** argv) {
   }
   bool all_ok = true;
 
-  if (tune) {
+  if (f.has("plan")) {
+    // --plan=<file>: an explicit list of measurements run in ONE process (communicator set-up is the expensive part at 8
+    // GPUs). One measurement per line, '#' starts a comment:
+    //     <label> <reduce|allreduce> <type> <op> <algo> <bytes> [B2R_KNOB=value ...]
+    // The knobs are exported for that line only (the library re-reads them: b2r_refresh_env). Output: one row per line in
+    // the sweep format, prefixed by the label. --check verifies every row of at most --check-max bytes against the oracle.
+    FILE* pf = fopen(f.str("plan").c_str(), "r");
+    if (!pf) { fprintf(stderr, "cannot open plan %s\n", f.str("plan").c_str()); return 1; }
+    const int iters = (int)f.i64("iters", 20);
+    const uint64_t check_max = (uint64_t)f.i64("check-max", 64ll << 20);
+    printf("# %-22s %-9s %-6s %-4s %-8s %14s %10s %10s %10s  knobs\n", "label", "coll", "dtype", "op", "algo", "bytes", "us", "algbw GB/s", "busbw GB/s");
+    char linebuf[1024];
+    while (fgets(linebuf, sizeof(linebuf), pf)) {
+      std::string line(linebuf);
+      const size_t hash = line.find('#');
+      if (hash != std::string::npos) line = line.substr(0, hash);
+      std::stringstream ss(line);
+      std::vector<std::string> tok;
+      std::string t;
+      while (ss >> t) tok.push_back(t);
+      if (tok.size() < 6) continue;
+      const bool allreduce = tok[1] == "allreduce";
+      b2r_dtype_t dt;
+      b2r_op_t op;
+      if (!parse_dtype(tok[2], &dt) || !parse_op(tok[3], &op)) { fprintf(stderr, "bad plan line: %s", linebuf); continue; }
+      const b2r_algo_t algo = parse_algo(tok[4]);
+      const uint64_t bytes = strtoull(tok[5].c_str(), nullptr, 0);
+      if (bytes == 0 || bytes > max_bytes) { fprintf(stderr, "plan line skipped (bytes %llu outside (0, %llu]): %s", (unsigned long long)bytes, (unsigned long long)max_bytes, linebuf); continue; }
+      std::vector<std::string> names;
+      std::string knobs;
+      for (size_t k = 6; k < tok.size(); ++k) {
+        const size_t eq = tok[k].find('=');
+        if (eq == std::string::npos) continue;
+        names.push_back(tok[k].substr(0, eq));
+        setenv(names.back().c_str(), tok[k].substr(eq + 1).c_str(), 1);
+        knobs += tok[k] + " ";
+      }
+      b2r_refresh_env();
+      const uint64_t count = bytes / b2r_dtype_size(dt);
+      bool row_ok = true;
+      if (algo == B2R_ALGO_LL) {
+        uint64_t ll_max = 0;
+        b2r_comm_ll_max_bytes(R[0].comm, &ll_max);
+        if (bytes > ll_max) row_ok = false;
+      }
+      if (algo == B2R_ALGO_NVLS && (!has_mc || ((dt == B2R_FLOAT32 || dt == B2R_FLOAT64) && op != B2R_SUM))) row_ok = false;
+      double ms = -1;
+      if (row_ok) {
+        if (f.has("check") && bytes <= check_max && !verify(R, allreduce, count, dt, op, root, algo)) {
+          all_ok = false;
+          printf("  %-22s VERIFY FAILED\n", tok[0].c_str());
+        }
+        const int it = bytes >= (1ull << 30) ? std::max(3, iters / 4) : (bytes >= (64ull << 20) ? std::max(5, iters / 2) : (bytes >= (4ull << 20) ? iters * 2 : iters * 5));
+        if (timed(R, allreduce, count, dt, op, root, algo, 3) >= 0) ms = timed(R, allreduce, count, dt, op, root, algo, it);
+      }
+      if (ms > 0) {
+        const double algbw = bytes / ms * 1e-6;
+        const double busbw = allreduce ? algbw * 2.0 * (P - 1) / P : algbw;
+        const b2r_algo_t used = algo == B2R_ALGO_AUTO ? b2r_select_algo(allreduce, bytes, dt, op, P, has_mc) : algo;
+        printf("  %-22s %-9s %-6s %-4s %-8s %14llu %10.2f %10.2f %10.2f  %s\n", tok[0].c_str(), allreduce ? "allreduce" : "reduce", ref_type_name(dt),
+               b2r_op_name(op), b2r_algo_name(used), (unsigned long long)bytes, ms * 1e3, algbw, busbw, knobs.c_str());
+        if (csv)
+          fprintf(csv, "b2r,%s,%s,%s,%s,%d,%llu,%.3f,%.3f,%.3f,%s,%s\n", allreduce ? "allreduce" : "reduce", ref_type_name(dt), b2r_op_name(op),
+                  b2r_algo_name(used), P, (unsigned long long)bytes, ms * 1e3, algbw, busbw, tok[0].c_str(), knobs.c_str());
+      } else {
+        printf("  %-22s %-9s %-6s %-4s %-8s %14llu  skipped or failed  %s\n", tok[0].c_str(), allreduce ? "allreduce" : "reduce", ref_type_name(dt),
+               b2r_op_name(op), tok[4].c_str(), (unsigned long long)bytes, knobs.c_str());
+        if (ms < 0 && row_ok) {  // a failed collective leaves the error word set: clear it so the next rows can run
+          for (auto& r : R) { cudaSetDevice(r.dev); b2r_comm_check(r.comm, r.stream); }
+        }
+      }
+      fflush(stdout);
+      for (auto& nme : names) unsetenv(nme.c_str());
+      b2r_refresh_env();
+    }
+    fclose(pf);
+  } else if (tune) {
     // In-process launch-shape sweep: the library reads its B2R_* knobs from the environment at every call, so one process
     // (one communicator set-up, the expensive part at 8 GPUs) can walk a whole grid. --tune=ring|push|nvls|twoshot
     //   [--coll=reduce|allreduce] [--bytes=268435456] [--type=FLOAT] [--iters=10]

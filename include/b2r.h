@@ -142,7 +142,8 @@ b2r_status_t b2r_reduce_local_ex(const void* in, void* out, uint64_t count, b2r_
  * b2r_workspace the kernel's scratch (block partials + ticket) is a static 8448-byte __device__ array inside libb2r.so,
  * resident on every GPU that loads the library until the process exits.
  *  - Limit: at most B2R_NOALLOC_MAX_PARTIALS block partials fit; a geometry that needs more (cfg->ctas / cluster above
- *    it) returns B2R_ERR_INVALID. The default geometry stays below the limit for every count.
+ *    it) returns B2R_ERR_INVALID. With cfg->ctas = 0 (or cfg = NULL) the library's own choice is capped at the limit, so
+ *    every count is served.
  *  - This call makes no cudaMalloc / cudaFree / allocating library call. It enqueues a 4-byte memset of the ticket (the
  *    only scratch word that must start at zero; the array otherwise keeps the previous call's contents) and the kernel.
  *  - All calls on one GPU share the array: calls that overlap on the GPU race. Keep them on one stream.

@@ -99,7 +99,9 @@ Shape coll_shape(const b2r_comm* c, int kind, uint64_t bytes, int nvirtual) {
     per_cta = 65536;
   } else {
     s.threads = 512;
-    s.unroll = bytes >= (8u << 20) ? 8 : 4;
+    // eight vectors in flight per thread pay for the two-shot / tree pulls at >= 8 MiB; the one-shot loop (P sources double-
+    // buffered) spills with them — int32 at 2 GPUs: 417 GB/s with 8, 619 with 4 — so it always takes four
+    s.unroll = (bytes >= (8u << 20) && kind != kCollOneshot) ? 8 : 4;
     cap = 128;
     per_cta = 65536;
   }

@@ -74,6 +74,8 @@ struct XgMailbox {
   XgPacket val[kXgSlots][B2R_MAX_RANKS];  // [call % kXgSlots][source rank]: partial scalar in accumulator precision
   XgPacket result[kXgSlots];              // [call % kXgSlots]: final scalar pushed by the root (scalar allreduce)
   unsigned int ack;                       // last call number the root has finished reading (flow control, monotonic)
+  unsigned int calls;                     // scalar-sharded calls this rank has made (written by this rank's own kernels only):
+                                          // the call number lives on the device, so a captured CUDA graph of calls can be replayed
 };
 static_assert(sizeof(XgMailbox) <= kOffError - kOffMailbox, "XgMailbox outgrew its slice of the control region");
 
@@ -118,6 +120,37 @@ __device__ __forceinline__ bool wait_flag_ge(const unsigned int* flag, unsigned 
   unsigned int spins = 0;
   bool slow = false;
   while ((int)(ld_acquire_sys(flag) - want) < 0) {
+    if (++spins >= 32 || slow) {
+      spins = 0;
+      if (ld_volatile_u32(err)) return false;
+      const unsigned long long now = coll_globaltimer();
+      if (t0 == 0) t0 = now;
+      else if (c.timeout_ns && now - t0 > c.timeout_ns) {
+        atomicExch(err, 1u);
+        return false;
+      }
+      if (now - t0 > 10000ull) {
+        slow = true;
+        __nanosleep(100);
+      }
+    }
+  }
+  return true;
+}
+
+// The same wait with relaxed polls (no acquire fence): for counters that only gate the REUSE of a buffer the waiter is about to
+// overwrite — nothing is read on the strength of the value, so there is nothing to acquire.
+__device__ __forceinline__ unsigned int ld_relaxed_sys_u32(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ bool wait_flag_ge_relaxed(const unsigned int* flag, unsigned int want, const CollCtx& c) {
+  unsigned int* err = (unsigned int*)(c.heap[c.rank] + kOffError);
+  unsigned long long t0 = 0;
+  unsigned int spins = 0;
+  bool slow = false;
+  while ((int)(ld_relaxed_sys_u32(flag) - want) < 0) {
     if (++spins >= 32 || slow) {
       spins = 0;
       if (ld_volatile_u32(err)) return false;

@@ -38,7 +38,7 @@ struct LocalParams {
   const CollCtx* xg_ctx;      // nullable: scalar-sharded reduce across GPUs (device copy of the communicator context)
   int xg_root;                //   root rank
   int xg_all;                 //   1 = every rank receives the scalar
-  unsigned xg_seq;            //   call number (1, 2, ...), same on every rank
+  unsigned xg_seq;            //   host-side call count (diagnostics only: the kernels number their calls on the device, see xgpu_finish)
   int stages;                 // TMA ring depth
   int tile_vecs;              // TMA tile size in 16-byte vectors
   int out_as_acc;             // store the scalar as acc_t (fp32 for bf16) instead of the input dtype
@@ -99,10 +99,20 @@ __device__ __forceinline__ void xgpu_finish(const LocalParams& p, typename R::ac
   __shared__ unsigned long long s_vals[B2R_MAX_RANKS];
   __shared__ unsigned long long s_res;
   __shared__ int s_fail;
+  __shared__ unsigned s_seq;
   const CollCtx& c = *p.xg_ctx;
-  const unsigned seq = p.xg_seq, slot = seq % (unsigned)kXgSlots;
   const int P = c.nranks, me = c.rank, root = p.xg_root;
   XgMailbox* my_mb = (XgMailbox*)(c.heap[me] + kOffMailbox);
+  // The call number is kept in this rank's own mailbox and advanced here, by the one thread of the one CTA that finishes the
+  // rank's launch; launches of one communicator are stream-ordered, and every rank makes the same sequence of calls, so the
+  // numbers agree across ranks without any host state — a captured graph of calls replays correctly.
+  unsigned seq = 0;
+  if (threadIdx.x == 0) {
+    seq = my_mb->calls + 1u;
+    my_mb->calls = seq;
+    s_seq = seq;
+  }
+  unsigned slot = seq % (unsigned)kXgSlots;
   auto to_bits = [](acc_t v) -> unsigned long long {
     if (sizeof(acc_t) == 8) return (unsigned long long)__double_as_longlong((double)v);
     if (R::kIsInt) return (unsigned long long)(unsigned int)(int)v;
@@ -117,7 +127,8 @@ __device__ __forceinline__ void xgpu_finish(const LocalParams& p, typename R::ac
     s_fail = 0;
     fault_delay(c);
     // the slot was last used by call seq - kXgSlots: the root must have read it
-    if (seq > (unsigned)kXgSlots && !wait_flag_ge(&my_mb->ack, seq - (unsigned)kXgSlots, c)) s_fail = 1;
+    // (relaxed poll: the value only says the slot may be overwritten; an acquire fence at system scope costs microseconds)
+    if (seq > (unsigned)kXgSlots && !wait_flag_ge_relaxed(&my_mb->ack, seq - (unsigned)kXgSlots, c)) s_fail = 1;
     else if (!c.fault_skip_signal) {
       XgMailbox* root_mb = (XgMailbox*)(c.heap[root] + kOffMailbox);
       xg_post(&root_mb->val[slot][me], to_bits(a), seq);
@@ -126,6 +137,8 @@ __device__ __forceinline__ void xgpu_finish(const LocalParams& p, typename R::ac
   if (me != root && !p.xg_all) return;
   __syncthreads();
   if (s_fail) return;
+  seq = s_seq;
+  slot = seq % (unsigned)kXgSlots;
   if (me == root) {
     if (threadIdx.x < (unsigned)P) {
       unsigned long long bits = 0;
@@ -144,8 +157,11 @@ __device__ __forceinline__ void xgpu_finish(const LocalParams& p, typename R::ac
     if (threadIdx.x < (unsigned)P) {
       XgMailbox* mb = (XgMailbox*)(c.heap[threadIdx.x] + kOffMailbox);
       if (p.xg_all) xg_post(&mb->result[slot], s_res, seq);
-      // release: this thread's read of the slot (program order, then bar.sync) is complete before the slot may be reused
-      st_release_sys(&mb->ack, seq);
+      // The acknowledgement only allows rank r to OVERWRITE its slot kXgSlots calls from now. The reads of the slots were
+      // performed before the two bar.syncs above (a polling loop cannot leave before its load has returned), so a plain
+      // system-scope store is enough; a release here is a MEMBAR.SYS on the exit path of every root launch (measured: the
+      // root's last CTA spent 4-9 us between its combine and its exit with it, see profiles/multi_gpu.md).
+      st_relaxed_sys_u32(&mb->ack, seq);
     }
   } else if (threadIdx.x == 0) {
     unsigned long long bits = 0;

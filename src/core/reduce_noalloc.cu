@@ -11,8 +11,8 @@
 //
 // Rules that follow from sharing ONE array per device:
 //   * Limit: the array holds B2R_NOALLOC_MAX_PARTIALS (1024) block partials of 8 bytes plus the ticket. A launch
-//     geometry that needs more partials (cfg->ctas / cluster > 1024) is rejected with B2R_ERR_INVALID; the default planner
-//     never asks for more than 592 on a B200, so every element count is served.
+//     geometry that needs more partials (cfg->ctas / cluster > 1024) is rejected with B2R_ERR_INVALID; when the caller leaves
+//     cfg->ctas at 0 the planner's choice is capped at 1024, so every element count is served.
 //   * The array keeps whatever the previous call left in it. The only word that must start at zero is the ticket; it is
 //     cleared with a 4-byte cudaMemsetAsync on the caller's stream before every launch (partials are fully overwritten
 //     before they are read).
@@ -109,6 +109,14 @@ extern "C" b2r_status_t b2r_reduce_local_noalloc(const void* in, void* out, uint
 
   LaunchGeom g;
   LocalParams p;
+  if (c.ctas == 0) {
+    // the planner's own choice may exceed what the static array holds (up to 8 CTAs per SM on a B200 = 1184 partials):
+    // cap it here; only a geometry the CALLER asked for is rejected below
+    int stages = 0, tile_vecs = 0;
+    B2R_CHECK(plan_local(count, dtype, op, view.sm_count, &c, &g, &stages, &tile_vecs));
+    const int cl = g.cluster > 0 ? g.cluster : 1;
+    if (g.ctas / cl > B2R_NOALLOC_MAX_PARTIALS) c.ctas = B2R_NOALLOC_MAX_PARTIALS * cl;
+  }
   B2R_CHECK(prepare_local(in, out, count, dtype, op, &view, &c, 0, &g, &p));
   const int partials = g.ctas / (g.cluster > 0 ? g.cluster : 1);
   if (partials > B2R_NOALLOC_MAX_PARTIALS)

@@ -99,6 +99,33 @@ def main():
                         if abs(o.double().item() - want.double().item()) > tol * max(1.0, abs(want.double().item())):
                             fails += 1
                             print(f"[rank {rank}] from_host MISMATCH dtype={dtype} count={count} op={op} got={o.item()} want={want.item()}", flush=True)
+    # the call number of the scalar-sharded reduce lives on the device: a captured graph of calls can be replayed
+    xs = [b2r.fill_device(1 << 20, torch.int32, seed=500 + 10 * rank + k, mode="sdk") for k in range(4)]
+    wants = []
+    for x in xs:
+        t = x.sum(dtype=torch.int64)
+        dist.all_reduce(t)
+        wants.append(int(t.item()))
+    outs = [torch.zeros((), dtype=torch.int32, device=dev) for _ in xs]
+    side = torch.cuda.Stream(dev)
+    with torch.cuda.stream(side):
+        cfg = b2r.launch_config(pdl=b2r.PDL_INPUT_READY)
+        for x, o in zip(xs, outs):
+            comm.reduce_scalar_sharded(x, "sum", root=0, out=o, cfg=cfg)  # warm-up outside the capture
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=side):
+            for x, o in zip(xs, outs):
+                comm.reduce_scalar_sharded(x, "sum", root=0, out=o, cfg=cfg)
+        for rep in range(6):  # 24 calls: beyond the 16 mailbox slots, so slot reuse and the acknowledgements are exercised
+            for o in outs:
+                o.zero_()
+            g.replay()
+            torch.cuda.synchronize()
+            if rank == 0 and [o.item() for o in outs] != wants:
+                fails += 1
+                print(f"[rank 0] graph replay {rep} MISMATCH {[o.item() for o in outs]} vs {wants}", flush=True)
+    comm.check()
     # the experimental-no-more paths on real NVLink: LL (small), ring allreduce, pipelined ring
     for dtype in (torch.int32, torch.float32):
         for count in (5, 1000, comm.ll_max_bytes // 4):

@@ -150,7 +150,10 @@ def test_noalloc_never_uses_programmatic_launch_even_with_B2R_PDL_set(lib, monke
     assert lib.b2r_workspace_create(C.byref(ws), 0) == 0
     try:
         same = LaunchCfg()
-        same.variant, same.pdl, same.dyn_pct = 1, -1, -1  # ldg128, plain order, static split: what the no-alloc path launches
+        # ldg128, plain order, static split, and an explicit grid below the 1024-partial limit: what the no-alloc path launches
+        same.variant, same.pdl, same.dyn_pct, same.ctas, same.threads = 1, -1, -1, 592, 512
+        asked = LaunchCfg()
+        asked.ctas, asked.threads = 592, 512  # pdl left at 0 on purpose: "whatever B2R_PDL says" must still mean OFF here
         for dtype in DTYPES:
             outs = []
             for n, seed in (((1 << 23) + 5, 11), ((1 << 23) + 5, 12), (123_457, 13)):
@@ -159,9 +162,9 @@ def test_noalloc_never_uses_programmatic_launch_even_with_B2R_PDL_set(lib, monke
                 got = torch.zeros((), dtype=dtype, device="cuda")
                 assert lib.b2r_reduce_local_ex(x.data_ptr(), want.data_ptr(), n, DTYPES[dtype], SUM, ws, stream, C.byref(same)) == 0
                 # two no-alloc calls back to back, no synchronisation in between
-                assert lib.b2r_reduce_local_noalloc(x.data_ptr(), got.data_ptr(), n, DTYPES[dtype], SUM, stream, None) == 0
+                assert lib.b2r_reduce_local_noalloc(x.data_ptr(), got.data_ptr(), n, DTYPES[dtype], SUM, stream, C.byref(asked)) == 0
                 got2 = torch.zeros((), dtype=dtype, device="cuda")
-                assert lib.b2r_reduce_local_noalloc(x.data_ptr(), got2.data_ptr(), n, DTYPES[dtype], SUM, stream, None) == 0
+                assert lib.b2r_reduce_local_noalloc(x.data_ptr(), got2.data_ptr(), n, DTYPES[dtype], SUM, stream, C.byref(asked)) == 0
                 outs.append((x, want, got, got2))
             torch.cuda.synchronize()
             for x, want, got, got2 in outs:
