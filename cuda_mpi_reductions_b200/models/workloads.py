@@ -3,8 +3,9 @@
   SDK_REDUCTION   the modified NVIDIA SDK `reduction` sample: one array -> one scalar, defaults from reduction.cpp:665-670.
   MPI_REDUCE      mpi/reduce.c: a fixed 2 GiB problem per datatype sharded over P ranks, element-wise reduce to root 0,
                   constants from mpi/constants.h:1-5 and the loop at reduce.c:71-99.
-bench.py, the native harnesses and the tests take their sizes from here so that the numbers quoted against BASELINE.md are
-always measured on the reference's own configuration.
+bench.py takes its sizes and the published baseline from here (loaded by path, so that the reference arm never imports the
+package); the native harnesses are C++ and carry the same constants as flag defaults, which tests/test_results_pipeline.py
+checks against this table — so the numbers quoted against BASELINE.md are always measured on the reference's own configuration.
 """
 from __future__ import annotations
 

@@ -8,7 +8,11 @@
              CUdata.txt; here they are read from a bench_reduce JSONL or passed explicitly). gnuplot itself is not on the
              image: the script + data are the deliverable.
 
-CLI:  python -m cuda_mpi_reductions_b200.utils.results aggregate --collected results/collected.txt --out results
+  figures    the same two figures rendered directly as SVG by a small pure-Python writer (int.svg, double.svg), for machines like
+             this image that have neither gnuplot nor matplotlib.
+
+CLI:  python -m cuda_mpi_reductions_b200.utils.results figures --results results --single-gpu results/single_gpu_plain.jsonl
+      python -m cuda_mpi_reductions_b200.utils.results aggregate --collected results/collected.txt --out results
       python -m cuda_mpi_reductions_b200.utils.results plot --results results --single-gpu results/single_gpu.jsonl
 """
 from __future__ import annotations
@@ -113,6 +117,106 @@ def write_gnuplot(results_dir: str, out_path: str, single_gpu: dict | None = Non
     return out_path
 
 
+def read_result_file(path: str):
+    """[(ranks, value)] from a results/<DTYPE>_<OP>.txt file."""
+    pts = []
+    try:
+        with open(path) as f:
+            for _dt, _op, nodes, val in parse_rows(f):
+                pts.append((nodes, float(val)))
+    except OSError:
+        pass
+    return sorted(pts)
+
+
+def write_svg(series: dict, out_path: str, title: str, xlabel: str = "GPUs (ranks)", ylabel: str = "bandwidth of the whole problem [GiB/s]",
+              hlines: dict | None = None, logy: bool = True, width: int = 900, height: int = 560) -> str:
+    """The reference's figures (mpi/makePlots.gp:21-39 -> int.eps / double.eps) rendered without gnuplot or matplotlib, neither
+    of which is on the image: a self-contained SVG line chart. `series` = {label: [(x, y), ...]} drawn as lines with markers
+    over a categorical x axis (the distinct x values, like the reference's 64 / 256 / 1024 ranks); `hlines` = {label: y} drawn
+    as dashed horizontal lines (the single-GPU throughputs the reference pasted in from CUdata.txt)."""
+    import math
+
+    hlines = hlines or {}
+    xs = sorted({x for pts in series.values() for x, _ in pts})
+    ys = [y for pts in series.values() for _, y in pts if y > 0] + [y for y in hlines.values() if y > 0]
+    if not xs or not ys:
+        raise ValueError("nothing to plot")
+    palette = ["#2ca02c", "#1f77b4", "#d62728", "#9467bd", "#ff7f0e", "#8c564b", "#17becf", "#7f7f7f", "#bcbd22", "#e377c2"]
+    ml, mr, mt, mb = 80, 250, 50, 60
+    pw, ph = width - ml - mr, height - mt - mb
+    lo, hi = min(ys), max(ys)
+    if logy:
+        lo, hi = 10 ** math.floor(math.log10(lo)), 10 ** math.ceil(math.log10(hi))
+        if lo == hi:
+            hi = lo * 10
+        fy = lambda v: mt + ph * (1 - (math.log10(max(v, lo)) - math.log10(lo)) / (math.log10(hi) - math.log10(lo)))  # noqa: E731
+        ticks = [10 ** e for e in range(int(math.log10(lo)), int(math.log10(hi)) + 1)]
+    else:
+        lo, hi = 0.0, hi * 1.08
+        fy = lambda v: mt + ph * (1 - (v - lo) / (hi - lo))  # noqa: E731
+        ticks = [hi * k / 5 for k in range(6)]
+    fx = lambda x: ml + pw * ((xs.index(x) + 0.5) / len(xs))  # noqa: E731
+    esc = lambda t: str(t).replace("&", "&amp;").replace("<", "&lt;").replace(">", "&gt;")  # noqa: E731
+    o = [f'<svg xmlns="http://www.w3.org/2000/svg" width="{width}" height="{height}" viewBox="0 0 {width} {height}" font-family="Helvetica,Arial,sans-serif" font-size="13">',
+         f'<rect width="{width}" height="{height}" fill="white"/>',
+         f'<text x="{ml + pw / 2}" y="24" text-anchor="middle" font-size="15">{esc(title)}</text>',
+         f'<rect x="{ml}" y="{mt}" width="{pw}" height="{ph}" fill="none" stroke="#333"/>']
+    for t in ticks:
+        y = fy(t)
+        o.append(f'<line x1="{ml}" y1="{y:.1f}" x2="{ml + pw}" y2="{y:.1f}" stroke="#ddd"/>')
+        o.append(f'<text x="{ml - 8}" y="{y + 4:.1f}" text-anchor="end">{t:g}</text>')
+    for x in xs:
+        o.append(f'<text x="{fx(x):.1f}" y="{mt + ph + 20}" text-anchor="middle">{esc(x)}</text>')
+    o.append(f'<text x="{ml + pw / 2}" y="{height - 14}" text-anchor="middle">{esc(xlabel)}</text>')
+    o.append(f'<text transform="translate(18,{mt + ph / 2}) rotate(-90)" text-anchor="middle">{esc(ylabel)}</text>')
+    ly = mt + 10
+    for k, (label, pts) in enumerate(series.items()):
+        c = palette[k % len(palette)]
+        pts = [(x, y) for x, y in sorted(pts) if y > 0]
+        if not pts:
+            continue
+        path = " ".join(f"{'M' if i == 0 else 'L'}{fx(x):.1f},{fy(y):.1f}" for i, (x, y) in enumerate(pts))
+        o.append(f'<path d="{path}" fill="none" stroke="{c}" stroke-width="2"/>')
+        for x, y in pts:
+            o.append(f'<circle cx="{fx(x):.1f}" cy="{fy(y):.1f}" r="4" fill="{c}"><title>{esc(label)}: {x} -> {y:.3f}</title></circle>')
+        o.append(f'<line x1="{ml + pw + 12}" y1="{ly}" x2="{ml + pw + 40}" y2="{ly}" stroke="{c}" stroke-width="2"/><circle cx="{ml + pw + 26}" cy="{ly}" r="4" fill="{c}"/>')
+        o.append(f'<text x="{ml + pw + 46}" y="{ly + 4}">{esc(label)}</text>')
+        ly += 20
+    for k, (label, y) in enumerate(hlines.items()):
+        c = palette[(k + len(series)) % len(palette)]
+        o.append(f'<line x1="{ml}" y1="{fy(y):.1f}" x2="{ml + pw}" y2="{fy(y):.1f}" stroke="{c}" stroke-width="2" stroke-dasharray="7,5"/>')
+        o.append(f'<line x1="{ml + pw + 12}" y1="{ly}" x2="{ml + pw + 40}" y2="{ly}" stroke="{c}" stroke-width="2" stroke-dasharray="7,5"/>')
+        o.append(f'<text x="{ml + pw + 46}" y="{ly + 4}">{esc(label)}</text>')
+        ly += 20
+    o.append("</svg>")
+    with open(out_path, "w") as f:
+        f.write("\n".join(o))
+    return out_path
+
+
+def write_figures(results_dir: str, single_gpu: dict | None = None, dtypes=("INT", "DOUBLE"), families=(("", "b2r"), ("nccl", "NCCL"), ("tree", "custom tree"))) -> list:
+    """int.svg / double.svg — the reference's two figures (writeup.tex:21-29): per datatype, the element-wise reduce-to-root
+    bandwidth over the number of ranks for every operation and every implementation family found under results/
+    (<results>/<DT>_<OP>.txt = this library, <results>/nccl/ = NCCL, <results>/tree/ = the hand-written tree), plus the
+    single-GPU scalar reduction as horizontal lines."""
+    single_gpu = single_gpu or {}
+    written = []
+    for dt in dtypes:
+        series = {}
+        for sub, name in families:
+            for op in OPS:
+                pts = read_result_file(os.path.join(results_dir, sub, f"{dt}_{op}.txt"))
+                if pts:
+                    series[f"{name} reduce {op}"] = pts
+        if not series:
+            continue
+        h = {f"one GPU {op} (scalar)": single_gpu[(dt, op)] / 1.073741824 for op in OPS if (dt, op) in single_gpu}
+        written.append(write_svg(series, os.path.join(results_dir, f"{dt.lower()}.svg"),
+                                 f"{dt}: reduce to root of a 2 GiB problem over NVLink vs the one-GPU scalar reduction", hlines=h))
+    return written
+
+
 def main(argv=None):
     ap = argparse.ArgumentParser(description=__doc__, formatter_class=argparse.RawDescriptionHelpFormatter)
     sub = ap.add_subparsers(dest="cmd", required=True)
@@ -123,10 +227,17 @@ def main(argv=None):
     p.add_argument("--results", default="results")
     p.add_argument("--single-gpu", default=None, help="bench_reduce --jsonl file with the single-GPU numbers")
     p.add_argument("--out", default=None)
+    g = sub.add_parser("figures", help="int.svg / double.svg rendered in pure Python (no gnuplot needed)")
+    g.add_argument("--results", default="results")
+    g.add_argument("--single-gpu", default=None)
     args = ap.parse_args(argv)
     if args.cmd == "aggregate":
         for (dt, op), path in aggregate(args.collected, args.out).items():
             print(f"{dt} {op} -> {path}")
+    elif args.cmd == "figures":
+        sg = single_gpu_lines(args.single_gpu) if args.single_gpu else {}
+        for path in write_figures(args.results, sg):
+            print(path)
     else:
         sg = single_gpu_lines(args.single_gpu) if args.single_gpu else {}
         print(write_gnuplot(args.results, args.out or os.path.join(args.results, "plots.gp"), sg))

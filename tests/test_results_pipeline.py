@@ -98,3 +98,44 @@ def test_compare_sweeps_tool(tmp_path):
     out = res.stdout
     assert "1 KiB: ll (>= 1.38x NCCL)" in out and "1 MiB: nvls" in out and "256 MiB: ring (>= 1.04x NCCL)" in out
     assert md.read_text().count("\n") == 5  # header, rule, three sizes
+
+
+def test_svg_figures_are_written_without_gnuplot(tmp_path):
+    """The reference's two figures (mpi/makePlots.gp:21-39) as self-contained SVG: three rank counts per curve like
+    mpi/results/INT_SUM.txt:2-4, implementation families side by side, single-GPU throughput as dashed lines."""
+    import xml.dom.minidom
+
+    from cuda_mpi_reductions_b200.utils import results as R
+
+    for sub in ("", "nccl", "tree"):
+        d = tmp_path / sub
+        d.mkdir(exist_ok=True)
+        for dt in ("INT", "DOUBLE"):
+            for k, op in enumerate(R.OPS):
+                (d / f"{dt}_{op}.txt").write_text("\n" + "".join(f"{dt} {op} {p} {100.0 * p * (k + 1) + len(sub):.5f}\n" for p in (2, 4, 8)))
+    written = R.write_figures(str(tmp_path), {("INT", "SUM"): 6000.0, ("DOUBLE", "MAX"): 5000.0})
+    assert [os.path.basename(w) for w in written] == ["int.svg", "double.svg"]
+    for w in written:
+        doc = xml.dom.minidom.parse(w)
+        assert len(doc.getElementsByTagName("path")) == 9          # 3 families x 3 ops
+        assert len(doc.getElementsByTagName("circle")) >= 27       # three rank counts per curve (+ legend markers)
+    assert "one GPU SUM" in open(written[0]).read() and "stroke-dasharray" in open(written[0]).read()
+    with pytest.raises(ValueError):
+        R.write_svg({}, str(tmp_path / "empty.svg"), "nothing")
+
+
+def test_native_harness_defaults_are_the_reference_workloads():
+    """models/workloads.py is the single table of the reference's workload constants; the C++ harnesses cannot import it, so
+    their flag defaults are checked against it here (and bench.py loads it by path)."""
+    import re
+
+    src_c = open(os.path.join(REPO, "bench", "bench_collective.cu")).read()
+    src_r = open(os.path.join(REPO, "bench", "bench_reduce.cu")).read()
+    total_mib = int(re.search(r'i64\("total-mib", (\d+)\)', src_c).group(1))
+    retries = int(re.search(r'i64\("retries", (\d+)\)', src_c).group(1))
+    assert total_mib << 20 == MPI_REDUCE.total_ints * 4 == MPI_REDUCE.total_doubles * 8
+    assert retries == MPI_REDUCE.retries
+    n_default = re.search(r'i64\("n", ([^)]+)\)', src_r).group(1)
+    assert eval(n_default.replace("ll", "")) == SDK_REDUCTION.elements  # noqa: S307 (a literal like 1 << 24)
+    bench_py = open(os.path.join(REPO, "bench.py")).read()
+    assert "SDK_REDUCTION.elements" in bench_py and "SDK_REDUCTION.published_gbs" in bench_py
