@@ -316,6 +316,10 @@ def run_b2r(args) -> None:
                 step(i)
 
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    short_region = steps <= 500
+    if sampler and short_region:
+        sampler.pause(True)  # no NVML call may sit between ev0 and the launches (see ClockSampler.pause)
+        time.sleep(0.003)
     if comm is not None:
         comm.barrier()  # device-side barrier on the launching stream: every GPU passes ev0 within a microsecond or two of its peers
     t_start = time.perf_counter()
@@ -324,6 +328,8 @@ def run_b2r(args) -> None:
     ev1.record()
     torch.cuda.synchronize()
     t_end = time.perf_counter()
+    if sampler:
+        sampler.pause(False)
     if world > 1:
         dist.barrier()
     ms = ev0.elapsed_time(ev1)

@@ -88,6 +88,8 @@ def _declare(lib: C.CDLL) -> None:
         ("b2r_comm_init_all", [C.POINTER(vp), i, C.POINTER(i), C.POINTER(CommConfig)]),
         ("b2r_comm_init_rank", [C.POINTER(vp), i, i, i, cp, C.POINTER(CommConfig)]),
         ("b2r_comm_init_loopback", [C.POINTER(vp), i, i, C.POINTER(CommConfig)]),
+        ("b2r_guard_alloc", [u64, i, i, C.POINTER(vp)]),
+        ("b2r_guard_free", [vp]),
         ("b2r_comm_destroy", [vp]),
         ("b2r_comm_rank", [vp, C.POINTER(i)]),
         ("b2r_comm_size", [vp, C.POINTER(i)]),

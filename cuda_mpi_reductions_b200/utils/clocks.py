@@ -28,6 +28,7 @@ class ClockSampler:
         self._nvml = None
         self._handle = None
         self.backend = "none"
+        self.paused = False  # while True the thread sleeps without touching NVML (see pause())
         self.first_error: str | None = None  # the first exception a poll raised (round 1 swallowed them all and reported nothing)
         self.polls = 0
 
@@ -51,6 +52,9 @@ class ClockSampler:
     def _run_nvml(self) -> None:
         n = self._nvml
         while not self._stop.is_set():
+            if self.paused:
+                time.sleep(self.period_s)
+                continue
             try:
                 mhz = int(n.nvmlDeviceGetClockInfo(self._handle, n.NVML_CLOCK_SM))
                 try:
@@ -84,6 +88,12 @@ class ClockSampler:
                     continue
         finally:
             p.kill()
+
+    def pause(self, on: bool = True) -> None:
+        """NVML queries take driver-wide locks; a query in flight can hold up a kernel or graph launch of the same process for
+        tens of microseconds. A timed region that is only a few hundred microseconds long is therefore measured with the sampler
+        paused, and its clock record comes from the samples right before it and from an untimed repeat of the same work."""
+        self.paused = on
 
     def wait_for_samples(self, n: int = 1, timeout_s: float = 2.0) -> bool:
         """Blocks until at least `n` samples exist (the first NVML query of a process can take milliseconds — longer than a

@@ -182,6 +182,14 @@ b2r_status_t b2r_workspace_trace_read_at(b2r_workspace_t ws, int launches_back, 
 b2r_status_t b2r_reduce_from_host(const void* host_in, void* out_host, uint64_t count, b2r_dtype_t dtype, b2r_op_t op,
                                   b2r_workspace_t ws, void* stream);
 
+/* ------------------------------------------------------------------ guard-page buffers (out-of-bounds detector)
+ * The reference's only memory checker is cutil's emulation-mode bank checker (bank_checker.h:25-60); where compute-sanitizer
+ * cannot be used, the MMU can: b2r_guard_alloc returns `bytes` of device memory placed so that the byte right after the
+ * buffer (at_end = 1) or right before it (at_end = 0) is reserved, UNMAPPED address space. A kernel that strays past that
+ * edge faults (cudaErrorIllegalAddress) instead of quietly touching a neighbour. Needs the VMM driver API. */
+b2r_status_t b2r_guard_alloc(uint64_t bytes, int device, int at_end, void** ptr);
+b2r_status_t b2r_guard_free(void* ptr);
+
 /* ------------------------------------------------------------------ communicator */
 
 typedef struct b2r_comm* b2r_comm_t;

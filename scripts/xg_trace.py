@@ -28,6 +28,8 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--n", type=int, default=1 << 24)
 ap.add_argument("--steps", type=int, default=200)
 ap.add_argument("--pdl", type=int, default=2)
+ap.add_argument("--graph", action="store_true", help="capture the timed steps in one CUDA graph and replay it")
+ap.add_argument("--notrace", action="store_true")
 a = ap.parse_args()
 rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
 torch.cuda.set_device(local)
@@ -59,19 +61,44 @@ else:
     def step(i):
         b2r.reduce(inputs[i % copies], 0, out=out, workspace=ws, cfg=cfg)
 
+side = torch.cuda.Stream(dev)
+torch.cuda.synchronize()
+torch.cuda.set_stream(side)
+if comm is not None:  # the prepared call bound the stream that was current when it was made: make it again on this one
+    step, _ = comm.prepare_reduce_scalar_sharded(inputs, "sum", root=0, out=out, cfg=cfg)
+if a.notrace:
+    _lib.check(_lib.LIB.b2r_workspace_trace_enable(ws_handle.handle if hasattr(ws_handle, "handle") else ws_handle, 0), "trace off")
 for i in range(20):
     step(i)
 torch.cuda.synchronize()
+graph = None
+if a.graph:
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph, stream=side):
+        for i in range(a.steps):
+            step(i)
+    graph.replay()
+    torch.cuda.synchronize()
 if comm is not None:
     dist.barrier()
     comm.barrier()
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 e0.record()
-for i in range(a.steps):
-    step(i)
+if graph is not None:
+    graph.replay()
+else:
+    for i in range(a.steps):
+        step(i)
 e1.record()
 torch.cuda.synchronize()
 us_per_step = e0.elapsed_time(e1) * 1e3 / a.steps
+if a.notrace:
+    print(f"rank {rank}/{world}: {us_per_step:.2f} us per step over {a.steps} steps (pdl={a.pdl}, graph={bool(graph)}, no trace)", flush=True)
+    if comm is not None:
+        dist.barrier()
+        comm.close()
+        dist.destroy_process_group()
+    sys.exit(0)
 rows = []
 for back in range(7, -1, -1):
     t = b2r.trace_last(ws_handle, back=back).double()
