@@ -13,3 +13,5 @@ timeout 400 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --mast
 timeout 200 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29572 scripts/xg_trace.py --steps 200 > $O/trace_n8.txt 2>&1; grep "us per step" $O/trace_n8.txt
 for i in 1 2; do timeout 100 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 2958$i scripts/xg_trace.py --steps 20 2>&1 | grep "us per step" | head -3; done
 grep -c FAILED $O/plan_*.txt; grep -h "FAILED\|skipped or failed" $O/plan_*.txt | head -20
+B2R_BENCH_GRAPH=0 timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29573 bench.py --gpus 8 --steps 20 --warmup 5 --no-collectives 2>/dev/null | grep '^{' | cut -c1-260
+timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29574 bench.py --gpus 8 --steps 20 --warmup 5 --no-collectives 2>/dev/null | grep '^{' | cut -c1-260
