@@ -50,8 +50,6 @@ CollKernel pick_kind(int kind) {
     case kCollPush: return coll_kernel<D, O, kCollPush, 4>;
     case kCollRing: return coll_kernel<D, O, kCollRing, 4>;
     case kCollLL: return coll_kernel<D, O, kCollLL, 4>;
-    case kCollRingAll: return coll_kernel<D, O, kCollRingAll, 4>;
-    case kCollRing2: return coll_kernel<D, O, kCollRing2, 4>;
   }
   return nullptr;
 }
@@ -92,16 +90,17 @@ Shape coll_shape(const b2r_comm* c, int kind, uint64_t bytes, int nvirtual) {
     s.unroll = bytes >= (8u << 20) ? 8 : 4;
     cap = 32;
     per_cta = 32768;
-  } else if (kind == kCollPush || kind == kCollRing || kind == kCollRingAll || kind == kCollRing2) {
+  } else if (kind == kCollPush || kind == kCollRing) {
     s.threads = 512;
     s.unroll = 4;
     cap = 128;
     per_cta = 65536;
   } else {
     s.threads = 512;
-    // eight vectors in flight per thread pay for the two-shot / tree pulls at >= 8 MiB; the one-shot loop (P sources double-
-    // buffered) spills with them — int32 at 2 GPUs: 417 GB/s with 8, 619 with 4 — so it always takes four
-    s.unroll = (bytes >= (8u << 20) && kind != kCollOneshot) ? 8 : 4;
+    // four vectors in flight per thread: with eight the source-double-buffered loops spill (one-shot int32 at 2 GPUs: 417 GB/s
+    // with 8, 619 with 4)
+    (void)bytes;
+    s.unroll = 4;  // two-shot reduce at 8 GPUs: 62.7 / 208 / 685 us with four against 71.6 / 301 / 760 with eight (16 / 64 / 256 MiB)
     cap = 128;
     per_cta = 65536;
   }
@@ -131,31 +130,35 @@ uint64_t ll_limit(const b2r_comm* c) {
   return std::max(small, big);
 }
 
-// What AUTO resolves to, on cached environment values (the public b2r_select_algo below refreshes them first).
+// What AUTO resolves to, on cached environment values (the public b2r_select_algo below refreshes them first). The crossovers
+// were read off one 8-GPU measurement of every candidate against NCCL (profiles/collectives_8gpu.md, raw rows in
+// profiles/raw/r2_8gpu/) and a 2-GPU one (profiles/multi_gpu.md):
+//   * <= 8 KiB: the LL path (flag-in-data packets, no barrier at either end) — reduce 8.3 us where the barrier-framed kernels
+//     need 14 (NVLS) to 21 (one-shot) and NCCL 8.2; allreduce 10.3 us against NCCL's 25. Beyond 8 KiB its single CTA is the limit.
+//   * from 4 GPUs up, every (dtype, op) with a multimem form goes through the switch (NVLS) at every larger size — including
+//     int32, whose 4-byte multimem ops were assumed too slow in round 1 and measure the same as the 16-byte fp32 form
+//     (allreduce 256 MiB: 576 us either way, two-shot 891, NCCL 727).
+//   * what has no multimem form (fp32 / fp64 min and max) stays on peer loads: one-shot while the whole message is small,
+//     two-shot beyond; and on stores (push) from B2R_AUTO_PUSH_MIN_MB up.
+//   * 2 GPUs: reduce = the root pulls the peer's message (one-shot, 630 GB/s at 64 MiB vs NCCL 580); allreduce = two-shot.
 b2r_algo_t select_algo_cached(int is_allreduce, uint64_t bytes, b2r_dtype_t dtype, b2r_op_t op, int nranks, int has_multicast, uint64_t ll_max) {
   if (nranks <= 1) return B2R_ALGO_ONESHOT;
   const int forced = B2R_ENV_INT("B2R_ALGO", 0);
-  // the experimental LL path only ever runs when asked for, and only for messages that fit its slots (and are staged-free:
-  // run_collective checks the 16-byte alignment); everything else falls through to the normal choice
+  // a forced LL only applies to messages that fit its slots; everything else falls through to the normal choice
   if (forced == B2R_ALGO_LL && nranks <= B2R_MAX_RANKS && bytes <= ll_max) return B2R_ALGO_LL;
   if (forced >= B2R_ALGO_ONESHOT && forced <= B2R_ALGO_PUSH) return (b2r_algo_t)forced;
   if (forced == B2R_ALGO_RING && !is_allreduce) return B2R_ALGO_RING;
-  // Switches for the paths that have not been measured at 8 GPUs yet; both are off unless the variable is set, so that the
-  // crossovers found by `scripts/run_round2_reduce.sh` can be tried (and then made the default) without a rebuild:
-  //   B2R_AUTO_LL_MAX_BYTES=n   messages of at most n bytes take the LL path (capped by what its slots hold)
-  //   B2R_AUTO_RING_MIN_MB=m    reduce-to-root of at least m MiB takes the store-forwarding ring
-  const uint64_t auto_ll = (uint64_t)std::max(0, B2R_ENV_INT("B2R_AUTO_LL_MAX_BYTES", 0));
+  const uint64_t auto_ll = (uint64_t)std::max(0, B2R_ENV_INT("B2R_AUTO_LL_MAX_BYTES", 8192));
   if (auto_ll && nranks <= B2R_MAX_RANKS && bytes <= std::min<uint64_t>(auto_ll, ll_max)) return B2R_ALGO_LL;
   const uint64_t auto_ring = (uint64_t)std::max(0, B2R_ENV_INT("B2R_AUTO_RING_MIN_MB", 0));
   if (auto_ring && !is_allreduce && nranks > 2 && bytes >= (auto_ring << 20)) return B2R_ALGO_RING;
-  // NVLS moves (1 + 1/P) messages per GPU against two-shot's 2(P-1)/P and needs one switch round trip for any size:
-  // from 4 GPUs up it wins at EVERY size for the types with 8/16-byte multimem forms (fp32 add, bf16, fp64 add);
-  // at 2 GPUs it loses to the P2P paths (measured). 32-bit integer multimem ops move 4 bytes per instruction and
-  // fp32/fp64 min/max have no multimem form: those stay on P2P.
-  const bool nvls_ok = has_multicast && nranks >= 4 && nvls_supported(dtype, op) && dtype != B2R_INT32 && !B2R_ENV_INT("B2R_DISABLE_NVLS", 0);
+  const bool nvls_ok = has_multicast && nranks >= 4 && nvls_supported(dtype, op) && !B2R_ENV_INT("B2R_DISABLE_NVLS", 0);
+  // push: B2R_AUTO_PUSH_MIN_MB = m sends messages of at least m MiB through the store-only algorithm; B2R_AUTO_PUSH_NVLS_TOO=1
+  // extends that to the types NVLS serves (reduce-to-root is where the switch's ~520 GB/s ceiling loses to NCCL's ring)
+  const uint64_t auto_push = (uint64_t)std::max(0, B2R_ENV_INT("B2R_AUTO_PUSH_MIN_MB", 0));
+  if (auto_push && nranks > 2 && bytes >= (auto_push << 20) && (!nvls_ok || (!is_allreduce && B2R_ENV_INT("B2R_AUTO_PUSH_NVLS_TOO", 0))))
+    return B2R_ALGO_PUSH;
   if (nvls_ok) return B2R_ALGO_NVLS;
-  // Two GPUs, reduce: the root simply pulls the peer's message — one message of ingress, 632 GB/s at 64 MiB, better than
-  // two-shot (481) and the ring (567) there.
   if (!is_allreduce && nranks == 2) return B2R_ALGO_ONESHOT;
   // One-shot reads the WHOLE message from every peer: fine for two GPUs or tiny messages, hopeless beyond.
   const uint64_t oneshot_max = (uint64_t)std::max(0, B2R_ENV_INT("B2R_ONESHOT_MAX_KB", nranks <= 2 ? 512 : 16)) << 10;
@@ -222,13 +225,7 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
   }
   int kind = algo == B2R_ALGO_ONESHOT ? kCollOneshot : algo == B2R_ALGO_TWOSHOT ? kCollTwoshot : algo == B2R_ALGO_TREE ? kCollTree
              : algo == B2R_ALGO_PUSH ? kCollPush : algo == B2R_ALGO_RING ? kCollRing : algo == B2R_ALGO_LL ? kCollLL : kCollNvls;
-  if (kind == kCollRing && is_all) {
-    // the ring allreduce (P chains + all-gather by stores) exists but has not run on hardware yet: opt-in only
-    if (!B2R_ENV_INT("B2R_EXPERIMENTAL", 0)) return fail(B2R_ERR_UNSUPPORTED, "the ring algorithm implements reduce-to-root only");
-    kind = kCollRingAll;
-  }
-  // the pipelined ring (waiter / data / signal warps) replaces ring_body only when asked for: not yet run on hardware
-  if (kind == kCollRing && B2R_ENV_INT("B2R_RING_V2", 0)) kind = kCollRing2;
+  if (kind == kCollRing && is_all) return fail(B2R_ERR_UNSUPPORTED, "the ring algorithm implements reduce-to-root only");
   if (kind == kCollLL) {
     // LL never touches a peer's send/recv buffer: any device pointer works, nothing is chunked, and only a buffer that is not
     // 16-byte aligned is bounced through this rank's own staging (a purely local decision: ranks need not agree on it)
@@ -242,8 +239,15 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
   // unless the communicator was created with symmetric_only (then nothing is ever staged and one launch does it all).
   const uint64_t stage_elems = (c0->stage_bytes / 16) * 16 / esz;
   const uint64_t chunk_elems = c0->symmetric_only ? count : std::min<uint64_t>(count, stage_elems);
-  // the tree keeps its running partial in the work region: it can never exceed one staging region per launch
-  const uint64_t chunk = (kind == kCollTree) ? std::min<uint64_t>(chunk_elems, stage_elems) : chunk_elems;
+  // the tree keeps its running partial in the work region, and push stages P whole slices there: both are bounded per launch
+  const uint64_t work_elems = (c0->work_bytes / 16) * 16 / esz;
+  uint64_t chunk = chunk_elems;
+  if (kind == kCollTree) chunk = std::min<uint64_t>(chunk_elems, work_elems);
+  if (kind == kCollPush) {
+    const uint64_t W = is_all ? P : P - 1;
+    const uint64_t slice_bytes = std::min<uint64_t>(c0->work_bytes / P - 64, (uint64_t)kPushChunkCap * 512 * 4 * 16 - 64);
+    chunk = std::min<uint64_t>(chunk_elems, (slice_bytes / 16) * 16 * W / esz);
+  }
 
   for (uint64_t first = 0; first < count; first += chunk) {
     const uint64_t cnt = std::min<uint64_t>(chunk, count - first);
@@ -314,7 +318,7 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
       A.epoch = c->epoch;
       A.root = is_all ? -1 : root;
       c->epoch += 8;  // start + end + up to 4 tree rounds, rounded up; same increment on every rank
-      if (kind == kCollPush || kind == kCollRing || kind == kCollRingAll || kind == kCollRing2) A.seq = ++c->push_seq;
+      if (kind == kCollPush || kind == kCollRing) A.seq = ++c->push_seq;
     }
     const Shape shape = coll_shape(c0, kind, bytes, n);
     int ctas = shape.ctas;
@@ -329,25 +333,18 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
         threads = kLLThreads;
       }
     }
-    if (kind == kCollRing || kind == kCollRingAll || kind == kCollRing2) {
+    if (kind == kCollRing) {
       // staging ring in the work region: depth x ctas steps of sub_blocks x (threads x 8) vectors; at least 2 deep.
       // Large messages use big steps (default 8 sub-blocks = 512 KiB with 512 threads) to amortise the per-step fence.
-      if (kind == kCollRing2) threads = std::max(threads, 96);  // waiter warp + signal warp + at least one data warp
-      const uint64_t sub_bytes = (uint64_t)(kind == kCollRing2 ? threads - 64 : threads) * 8 * 16;
+      const uint64_t sub_bytes = (uint64_t)threads * 8 * 16;
       int subs = std::max(1, B2R_ENV_INT("B2R_RING_SUBBLOCKS", 8));
       int cap = std::max(1, B2R_ENV_INT("B2R_RING_CTAS", 32));
       if (n > 1) cap = std::max(1, std::min(cap, c0->sm_count / n));
       while (subs > 1 && bytes < (uint64_t)cap * sub_bytes * subs * 2) subs /= 2;  // small message: keep all CTAs busy
       const uint64_t step_bytes = sub_bytes * subs;
       ctas = (int)std::max<uint64_t>(1, std::min<uint64_t>((bytes + step_bytes - 1) / step_bytes, (uint64_t)cap));
-      ctas = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)ctas, c0->stage_bytes / (2ull * step_bytes)));
-      if (kind == kCollRingAll) {  // one chain per rank: a multiple of P CTAs, at least one channel per chain
-        ctas = std::max(P, ctas - ctas % P);
-        B2R_REQUIRE((uint64_t)ctas * step_bytes * 2 <= c0->stage_bytes && ctas <= kCollMaxCtas && (n == 1 || ctas * n <= c0->sm_count),
-                    "ring allreduce: %d CTAs x %llu-byte steps do not fit (staging %zu bytes, %d SMs)", ctas, (unsigned long long)step_bytes,
-                    c0->stage_bytes, c0->sm_count);
-      }
-      const int depth = (int)std::min<uint64_t>(8, c0->stage_bytes / ((uint64_t)ctas * step_bytes));
+      ctas = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)ctas, c0->work_bytes / (2ull * step_bytes)));
+      const int depth = (int)std::min<uint64_t>(8, c0->work_bytes / ((uint64_t)ctas * step_bytes));
       for (int i = 0; i < n; ++i) {
         L.a[n == 1 ? 0 : rc[i].c->rank].ring_depth = depth;
         L.a[n == 1 ? 0 : rc[i].c->rank].sub_blocks = subs;
@@ -359,12 +356,23 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
       for (int i = 0; i < n; ++i) L.a[n == 1 ? 0 : rc[i].c->rank].sub_blocks = share;
     }
     if (kind == kCollPush) {
-      // staging ring in the work region: depth x P sources x ctas blocks of (threads x 4) vectors; at least 2 deep
-      const uint64_t block_bytes = (uint64_t)threads * 4 * 16;
-      ctas = std::min(ctas, std::max(1, B2R_ENV_INT("B2R_PUSH_CTAS", 128)));
-      ctas = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)ctas, c0->stage_bytes / (2ull * P * block_bytes)));
-      const int depth = (int)std::min<uint64_t>(8, c0->stage_bytes / ((uint64_t)P * ctas * block_bytes));
-      for (int i = 0; i < n; ++i) L.a[n == 1 ? 0 : rc[i].c->rank].ring_depth = depth;
+      // whole-slice staging in the work region: P sources x slice_cap vectors (coll_push.cuh). The chunk = threads x 4 vectors:
+      // small slices take small chunks so that enough CTAs get work; the flag table names at most kPushChunkCap chunks per slice.
+      const int W = is_all ? P : P - 1;
+      const uint64_t nvec = bytes / 16, slice_cap = (nvec + W - 1) / W + 1;
+      threads = 512;
+      while (threads > 128 && slice_cap / ((uint64_t)threads * 4) < 96) threads /= 2;
+      const int et = B2R_ENV_INT("B2R_COLL_THREADS", 0);
+      if (et >= 64 && et <= 512) threads = et - et % 32;
+      while (threads < 512 && (slice_cap + (uint64_t)threads * 4 - 1) / ((uint64_t)threads * 4) > kPushChunkCap) threads *= 2;
+      const uint64_t nchunks = (slice_cap + (uint64_t)threads * 4 - 1) / ((uint64_t)threads * 4);
+      B2R_REQUIRE(nchunks <= kPushChunkCap && (uint64_t)P * slice_cap * 16 <= c0->work_bytes,
+                  "push: a piece of %llu bytes does not fit the work region (%zu bytes) / flag table", (unsigned long long)bytes, c0->work_bytes);
+      int cap = std::max(1, B2R_ENV_INT("B2R_PUSH_CTAS", 128));
+      if (c0->max_ctas > 0) cap = std::min(cap, c0->max_ctas);
+      cap = std::min(cap, kCollMaxCtas);
+      if (n > 1) cap = std::max(1, std::min(cap, c0->sm_count / n));
+      ctas = (int)std::max<uint64_t>(1, std::min<uint64_t>(nchunks, (uint64_t)cap));
     }
     CollKernel kernel = pick_kernel(dtype, (int)op, kind, shape.unroll);
     if (n == 1) {

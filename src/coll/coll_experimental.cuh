@@ -1,268 +1,15 @@
-// coll_experimental.cuh — collective kernels that exist but have NOT run on hardware yet (written after the GPU budget of
-// round 1 was spent). Nothing here is reachable unless asked for: algo=LL, algo=ring on an allreduce with
-// B2R_EXPERIMENTAL=1, B2R_RING_V2=1. Included by coll_kernels.cuh (needs its helpers: VecOps, ld_peer / st_peer, barriers);
-// tests/test_experimental_gpu.py (opt-in) and tests/test_ll_protocol_model.py (CPU) cover them. The kernels of
-// coll_kernels.cuh proper are the ones the GPU suite has passed on; scripts/sass_compare.py shows they are unaffected.
+// coll_experimental.cuh — the LL ("low latency") small-message path. Included by coll_kernels.cuh (needs its helpers: VecOps,
+// ld_peer / st_peer, barriers); tests/test_experimental_gpu.py (loopback), tests/dist_worker.py (real NVLink) and
+// tests/test_ll_protocol_model.py (CPU model of the slot / acknowledgement protocol) cover it.
+// History: this file also held a pipelined ring (waiter / data / signal warps) and a ring allreduce (P chains + all-gather by
+// stores). Both were measured on 8 B200s in round 2 and removed: the pipelined ring was slower than the plain ring at every
+// size (884 vs 669 us at 256 MiB) and failed its bf16 check on hardware; the ring allreduce lost to NVLS and to two-shot at
+// every size (802 vs 576 / 891 us at 256 MiB int32). profiles/raw/r2_8gpu/ has the rows.
 #pragma once
 
 namespace b2r {
 
-// ------------------------------------------------------------------------------------------------ pipelined ring (reduce to root)  [EXPERIMENTAL]
-// ring_body runs every step as wait -> move -> __syncthreads -> release fence -> signal, so each step pays the fence
-// (one NVLink round trip) and the flag hop serially: ~8 us of latency per step, fitted on the 2-GPU runs. To keep the link
-// busy the steps must then be large (bytes per round >= link rate x latency ~ 6.5 MB), which leaves few steps per channel
-// — and an 8-long chain loses (P-2) step times to pipeline fill (13% at 256 MiB). Here the three jobs run concurrently in
-// one CTA and are coupled only by two shared-memory counters:
-//   waiter warp : polls the data flag (from the predecessor) and the slot-reuse ack (from the successor) for step i, then
-//                 publishes ready = i+1;
-//   data warps  : wait for ready > i, move their part of step i (load own + staged partial, combine, store downstream) and
-//                 publish their own progress word (steps finished); no block-wide barrier, they start step i+1 at once;
-//   signal warp : lane w watches data warp w's progress word; once EVERY data warp has finished step i it acks the step
-//                 upstream and release-stores the data flag downstream. (A single shared counter is not enough: a fast warp's
-//                 step i+1 would be counted towards step i while a slow warp is still moving it — seen as a wrong fp64 MIN at
-//                 8 ranks x 6 data warps on the first hardware run.)
-// The fence now overlaps the next steps' traffic; it only delays when the successor SEES a step, not how fast steps are
-// produced, so steps can be small and many. Same chain order, same staging slots and flag words as ring_body (results are
-// bit-identical to it and to the host restatement). Ordering: data stores -> __syncwarp -> red.release.cta(done) ->
-// ld.acquire.cta by the signal warp -> __syncwarp -> st.release.sys(flag) is one causality chain, and the mirror image on the way in.
-__device__ __forceinline__ void st_release_cta_shared(uint32_t addr, unsigned int v) {
-  asm volatile("st.release.cta.shared.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
-}
-__device__ __forceinline__ unsigned int ld_acquire_cta_shared(uint32_t addr) {
-  unsigned int v;
-  asm volatile("ld.acquire.cta.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
-  return v;
-}
-__device__ __forceinline__ void red_release_cta_shared_add(uint32_t addr, unsigned int v) {
-  asm volatile("red.release.cta.shared.add.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
-}
-
-template <int D, int O, int UNR>
-__device__ void ring2_body(const CollArgs& A) {
-  using V = VecOps<D, O>;
-  const CollCtx& c = A.ctx;
-  constexpr int E = V::kElem;
-  constexpr int VPT = 8;
-  const int P = c.nranks, r = c.rank, root = A.root, G = (int)gridDim.x, b = (int)blockIdx.x;
-  const int pos = (r - root + P) % P;
-  const int pred = pos + 1 < P ? (root + pos + 1) % P : -1;
-  const int succ = pos > 0 ? (root + pos - 1) % P : -1;
-  const unsigned int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const unsigned int ndw = (blockDim.x >> 5) - 2;  // data warps; then the waiter warp, then the signal warp
-  const unsigned int ndata = ndw * 32;
-  const unsigned long long nvec = A.count * E / 16;
-  const unsigned int Sv = ndata * VPT;
-  const unsigned int Cv = Sv * (unsigned int)max(1, A.sub_blocks);
-  const unsigned long long nblocks = (nvec + Cv - 1) / Cv;
-  const unsigned long long steps = (unsigned long long)b < nblocks ? (nblocks - b + G - 1) / G : 0;
-  const int depth = A.ring_depth;
-  const unsigned int base_val = A.seq << 16;
-
-  __shared__ PeerOffsets po;
-  __shared__ unsigned int s_ready, s_prog[16];  // s_prog[w]: steps data warp w has finished (blockDim <= 512: at most 14 data warps)
-  if (threadIdx.x == 0) s_ready = 0;
-  if (threadIdx.x < 16) s_prog[threadIdx.x] = 0;
-  start_barrier(A, &po);  // contains __syncthreads on both sides: the counters are visible to everybody
-  const uint32_t a_ready = smem_u32(&s_ready), a_prog = smem_u32(s_prog);
-  const char* send = c.heap[r] + A.send_off;
-  auto slot = [&](int rank, unsigned long long step) {
-    return c.heap[rank] + A.work_off + (((step % depth) * G + b) * (unsigned long long)Cv) * 16ull;
-  };
-
-  if (warp == ndw) {
-    // ---- waiter: a timed-out wait still publishes the step (the error word is set; everything touched is valid memory)
-    for (unsigned long long i = 0; i < steps; ++i) {
-      if (lane == 0 && pred >= 0) {
-        const unsigned int* flag = (const unsigned int*)(c.heap[r] + kOffPushData) + (size_t)b * B2R_MAX_RANKS + pred;
-        wait_flag_ge(flag, base_val + (unsigned int)(i + 1), c);
-      }
-      if (lane == 1 && succ >= 0 && i >= (unsigned long long)depth) {
-        const unsigned int* ack = (const unsigned int*)(c.heap[r] + kOffPushAck) + (size_t)b * B2R_MAX_RANKS + succ;
-        wait_flag_ge(ack, base_val + (unsigned int)(i - depth + 1), c);
-      }
-      __syncwarp();
-      if (lane == 0) st_release_cta_shared(a_ready, (unsigned int)(i + 1));
-    }
-  } else if (warp == ndw + 1) {
-    // ---- signaller
-    for (unsigned long long i = 0; i < steps; ++i) {
-      if (lane < ndw)
-        while (ld_acquire_cta_shared(a_prog + 4u * lane) < (unsigned int)(i + 1)) __nanosleep(20);
-      __syncwarp();
-      if (lane == 0) {
-        if (!c.fault_skip_signal) {
-          if (pred >= 0) {  // the staged partial of step i has been read: its slot may be refilled
-            unsigned int* ack = (unsigned int*)(c.heap[pred] + kOffPushAck) + (size_t)b * B2R_MAX_RANKS + r;
-            st_relaxed_sys_u32(ack, base_val + (unsigned int)(i + 1));
-          }
-          if (succ >= 0) {  // release: every data warp's stores of step i are visible before the flag is
-            unsigned int* flag = (unsigned int*)(c.heap[succ] + kOffPushData) + (size_t)b * B2R_MAX_RANKS + r;
-            st_release_sys(flag, base_val + (unsigned int)(i + 1));
-          }
-        }
-      }
-      __syncwarp();
-    }
-  } else {
-    // ---- data warps
-    const unsigned int dt = threadIdx.x;  // 0 .. ndata-1
-    for (unsigned long long i = 0; i < steps; ++i) {
-      const unsigned long long lo = (b + i * G) * (unsigned long long)Cv;
-      const unsigned int len = (unsigned int)min((unsigned long long)Cv, nvec - lo);
-      if (lane == 0)
-        while (ld_acquire_cta_shared(a_ready) < (unsigned int)(i + 1)) __nanosleep(20);
-      __syncwarp();
-      char* dst = succ >= 0 ? slot(succ, i) : c.heap[r] + A.recv_off + lo * 16;
-      const char* in = slot(r, i);
-      for (unsigned int sb = 0; sb < len; sb += Sv) {
-        V16 own[VPT], got[VPT];
-#pragma unroll
-        for (int u = 0; u < VPT; ++u) {
-          const unsigned int j = sb + dt + u * ndata;
-          if (j < len) {
-            own[u] = ld_peer(send + (lo + j) * 16);
-            if (pred >= 0) got[u] = ld_peer(in + (unsigned long long)j * 16);
-          }
-        }
-#pragma unroll
-        for (int u = 0; u < VPT; ++u) {
-          const unsigned int j = sb + dt + u * ndata;
-          if (j < len) {
-            if (pred >= 0) {
-              typename V::Acc acc = V::unpack(got[u]);
-              V::combine(acc, own[u]);
-              st_peer(dst + (unsigned long long)j * 16, V::pack(acc));
-            } else {
-              st_peer(dst + (unsigned long long)j * 16, own[u]);
-            }
-          }
-        }
-      }
-      __syncwarp();
-      if (lane == 0) st_release_cta_shared(a_prog + 4u * warp, (unsigned int)(i + 1));
-    }
-  }
-  __syncthreads();
-  // the (< 16 byte) tail: exactly as in ring_body
-  if (pos == 0 && nvec * (16 / E) < A.count && blockIdx.x == 0) {
-    for (unsigned long long e = nvec * (16 / E) + threadIdx.x; e < A.count; e += blockDim.x) {
-      typename TailAcc<D>::type acc = tail_load<D>(c.heap[(root + P - 1) % P] + po.send[(root + P - 1) % P] + e * E);
-      for (int q = 1; q < P; ++q) {
-        const int rank_q = (root + (P - 1 - q)) % P;
-        acc = tail_apply<D, O>(acc, tail_load<D>(c.heap[rank_q] + po.send[rank_q] + e * E));
-        if constexpr (D == B2R_BFLOAT16) acc = __bfloat162float(__float2bfloat16_rn(acc));
-      }
-      tail_store<D>(c.heap[r] + A.recv_off + e * E, acc);
-    }
-  }
-  cta_barrier(A, A.epoch + 2);
-}
-
-// ------------------------------------------------------------------------------------------------ ring allreduce  [EXPERIMENTAL]
-// P chains at once, each exactly the reduce ring above: chain c ends at rank c and reduces slice c of the message, and the
-// chain root, instead of keeping the result, stores it into EVERY rank's recv buffer (all-gather by stores). CTA b works
-// for chain b % P as its channel b / P (the host launches a multiple of P CTAs), with its own staging slots and flag row, so
-// the chains never share anything. Per GPU: (P-1)/P of a message forwarded to ONE neighbour per chain plus (P-1)/P of a
-// message of result stores — no remote loads anywhere, which is what the pull two-shot (0.83x NCCL for int32 / min / max at
-// >= 256 MiB) pays for. Every rank sits on every chain, so a block of the send buffer has been consumed by its owner before
-// the chain root can overwrite it: in place is safe. Folding order = chain order per slice; host_algos.h restates it.
-template <int D, int O, int UNR>
-__device__ void ringall_body(const CollArgs& A) {
-  using V = VecOps<D, O>;
-  const CollCtx& c = A.ctx;
-  constexpr int E = V::kElem;
-  constexpr int VPT = 8;
-  const int P = c.nranks, r = c.rank, G = (int)gridDim.x, b = (int)blockIdx.x;
-  const int chain = b % P, ch = b / P, Gc = G / P;  // G is a multiple of P (host)
-  const int pos = (r - chain + P) % P;
-  const int pred = pos + 1 < P ? (chain + pos + 1) % P : -1;  // sends to me
-  const int succ = pos > 0 ? (chain + pos - 1) % P : -1;      // I send to it; -1: I am this chain's root
-  const unsigned long long nvec = A.count * E / 16;
-  const unsigned long long s_lo = nvec * (unsigned long long)chain / P, s_hi = nvec * (unsigned long long)(chain + 1) / P;
-  const unsigned int Sv = blockDim.x * VPT;
-  const unsigned int Cv = Sv * (unsigned int)max(1, A.sub_blocks);
-  const unsigned long long nblocks = (s_hi - s_lo + Cv - 1) / Cv;
-  const unsigned long long steps = (unsigned long long)ch < nblocks ? (nblocks - ch + Gc - 1) / Gc : 0;
-  const int depth = A.ring_depth;
-  const unsigned int base_val = A.seq << 16;
-
-  __shared__ PeerOffsets po;
-  __shared__ char* rdst[B2R_MAX_RANKS];
-  start_barrier(A, &po);
-  if (threadIdx.x < (unsigned)P) rdst[threadIdx.x] = c.heap[threadIdx.x] + po.recv[threadIdx.x];
-  __syncthreads();
-  const char* send = c.heap[r] + A.send_off;
-  auto slot = [&](int rank, unsigned long long step) {
-    return c.heap[rank] + A.work_off + (((step % depth) * G + b) * (unsigned long long)Cv) * 16ull;
-  };
-  for (unsigned long long i = 0; i < steps; ++i) {
-    const unsigned long long lo = s_lo + (ch + i * Gc) * (unsigned long long)Cv;
-    const unsigned int len = (unsigned int)min((unsigned long long)Cv, s_hi - lo);
-    if (threadIdx.x == 0 && pred >= 0) {
-      const unsigned int* flag = (const unsigned int*)(c.heap[r] + kOffPushData) + (size_t)b * B2R_MAX_RANKS + pred;
-      wait_flag_ge(flag, base_val + (unsigned int)(i + 1), c);
-    }
-    if (threadIdx.x == 32 && succ >= 0 && i >= (unsigned long long)depth) {
-      const unsigned int* ack = (const unsigned int*)(c.heap[r] + kOffPushAck) + (size_t)b * B2R_MAX_RANKS + succ;
-      wait_flag_ge(ack, base_val + (unsigned int)(i - depth + 1), c);
-    }
-    __syncthreads();
-    char* fwd = succ >= 0 ? slot(succ, i) : nullptr;
-    const char* in = slot(r, i);
-    for (unsigned int sb = 0; sb < len; sb += Sv) {
-      V16 own[VPT], got[VPT];
-#pragma unroll
-      for (int u = 0; u < VPT; ++u) {
-        const unsigned int j = sb + threadIdx.x + u * blockDim.x;
-        if (j < len) {
-          own[u] = ld_peer(send + (lo + j) * 16);
-          if (pred >= 0) got[u] = ld_peer(in + (unsigned long long)j * 16);
-        }
-      }
-#pragma unroll
-      for (int u = 0; u < VPT; ++u) {
-        const unsigned int j = sb + threadIdx.x + u * blockDim.x;
-        if (j < len) {
-          V16 res = own[u];
-          if (pred >= 0) {
-            typename V::Acc acc = V::unpack(got[u]);
-            V::combine(acc, own[u]);
-            res = V::pack(acc);
-          }
-          if (fwd) st_peer(fwd + (unsigned long long)j * 16, res);
-          else
-            for (int p = 0; p < P; ++p) st_peer(rdst[p] + (lo + j) * 16, res);
-        }
-      }
-    }
-    __syncthreads();
-    if (threadIdx.x == 0 && succ >= 0 && !c.fault_skip_signal) {
-      unsigned int* flag = (unsigned int*)(c.heap[succ] + kOffPushData) + (size_t)b * B2R_MAX_RANKS + r;
-      st_release_sys(flag, base_val + (unsigned int)(i + 1));
-    }
-    if (threadIdx.x == 32 && pred >= 0 && !c.fault_skip_signal) {
-      unsigned int* ack = (unsigned int*)(c.heap[pred] + kOffPushAck) + (size_t)b * B2R_MAX_RANKS + r;
-      st_release_sys(ack, base_val + (unsigned int)(i + 1));
-    }
-  }
-  // the (< 16 byte) tail rides with the last chain: its root (rank P-1, channel 0) pulls it in chain order, rounding bf16
-  // after every hop like the vector path, and stores it everywhere
-  if (r == P - 1 && b == P - 1 && nvec * (16 / E) < A.count) {
-    for (unsigned long long e = nvec * (16 / E) + threadIdx.x; e < A.count; e += blockDim.x) {
-      const int far = (P - 1 + P - 1) % P;
-      typename TailAcc<D>::type acc = tail_load<D>(c.heap[far] + po.send[far] + e * E);
-      for (int q = 1; q < P; ++q) {
-        const int rank_q = (P - 1 + (P - 1 - q)) % P;
-        acc = tail_apply<D, O>(acc, tail_load<D>(c.heap[rank_q] + po.send[rank_q] + e * E));
-        if constexpr (D == B2R_BFLOAT16) acc = __bfloat162float(__float2bfloat16_rn(acc));
-      }
-      for (int p = 0; p < P; ++p) tail_store<D>(rdst[p] + e * E, acc);
-    }
-  }
-  cta_barrier(A, A.epoch + 2);
-}
-
-// ------------------------------------------------------------------------------------------------ LL (small messages, no barriers)  [EXPERIMENTAL]
+// ------------------------------------------------------------------------------------------------ LL (small messages, no barriers)  
 // The barrier-framed kernels above pay two NVLink round trips (start + end barrier) whatever the size: 12.5-14.5 us for a
 // 1 KiB-256 KiB reduce at 8 GPUs where NCCL's LL protocol needs 8-12. Here the synchronisation rides with the data, as in
 // that protocol: every 16-byte vector is pushed into the consumer's slot as four 8-byte packets {32 data bits, call number};

@@ -390,165 +390,9 @@ __device__ void tree_body(const CollArgs& A) {
   }
 }
 
-// ------------------------------------------------------------------------------------------------ push (scatter by stores, reduce locally, push the result)
-// NVLink carries posted stores better than it carries loads: under an all-to-all load the pull-based two-shot tops out
-// near 410-470 GB/s per direction on 8 B200s, while stores run close to link rate. So here nothing is ever loaded from
-// a peer. The message is cut into one slice per worker (reduce: the P-1 non-root ranks; allreduce: all P ranks); in
-// round i CTA b of every rank
-//   1. stores block (i*G + b) of each worker's slice from its own send buffer into that worker's staging slot
-//      [i % depth][my rank][b]  (flow control: the worker's ack for round i - depth must have arrived),
-//   2. release-stores "round i landed" into that worker's flag row,
-//   3. as a worker, one round behind the pushes: waits for round i-1 from every source, combines its own block with the
-//      P-1 staged blocks in rank order (all local reads), stores the result into the root's (or everybody's) recv
-//      buffer, and acks the round to every source.
-// Per GPU: one message in, one message out, all of it stores. Flags are (call << 16 | round): monotonic, never reset.
-template <int D, int O, int UNR>
-__device__ void push_body(const CollArgs& A) {
-  using V = VecOps<D, O>;
-  const CollCtx& c = A.ctx;
-  constexpr int E = V::kElem;
-  constexpr int VPT = 4;  // vectors per thread per block
-  const int P = c.nranks, r = c.rank, G = (int)gridDim.x, b = (int)blockIdx.x;
-  const int W = A.root < 0 ? P : P - 1;
-  const int my_w = A.root < 0 ? r : (r == A.root ? -1 : (r < A.root ? r : r - 1));
-  const unsigned long long nvec = A.count * E / 16;
-  const unsigned int Cv = blockDim.x * VPT;  // vectors per block
-  const unsigned long long max_len = (nvec + W - 1) / W + 1;
-  const unsigned long long rounds = (max_len + (unsigned long long)G * Cv - 1) / ((unsigned long long)G * Cv);
-  const int depth = A.ring_depth;
-  const unsigned int base_val = A.seq << 16;
-
-  __shared__ PeerOffsets po;
-  start_barrier(A, &po);
-
-  auto worker_rank = [&](int w) { return A.root < 0 ? w : (w < A.root ? w : w + 1); };
-  auto slice_lo = [&](int w) { return nvec * (unsigned long long)w / W; };
-  auto stage_slot = [&](int rank_of_worker, unsigned long long round, int src) {
-    return c.heap[rank_of_worker] + A.work_off + ((((round % depth) * P + src) * G + b) * (unsigned long long)Cv) * 16ull;
-  };
-  const char* send = c.heap[r] + A.send_off;
-
-  for (unsigned long long i = 0; i <= rounds; ++i) {
-    if (i < rounds) {
-      // ---- 1. push my contribution for round i to every worker
-      if (i >= (unsigned long long)depth && threadIdx.x < (unsigned)W) {
-        const int w = (int)threadIdx.x;
-        if (worker_rank(w) != r) {
-          const unsigned int* ack = (const unsigned int*)(c.heap[r] + kOffPushAck) + (size_t)b * B2R_MAX_RANKS + w;
-          wait_flag_ge(ack, base_val + (unsigned int)(i - depth + 1), c);
-        }
-      }
-      if (i >= (unsigned long long)depth) __syncthreads();
-      for (int w = 0; w < W; ++w) {
-        const int wr = worker_rank(w);
-        if (wr == r) continue;
-        const unsigned long long lo = slice_lo(w) + (i * G + b) * Cv, end = slice_lo(w + 1);
-        if (lo >= end) continue;
-        const unsigned int len = (unsigned int)min((unsigned long long)Cv, end - lo);
-        char* dst = stage_slot(wr, i, r);
-        V16 v[VPT];
-#pragma unroll
-        for (int u = 0; u < VPT; ++u) {
-          const unsigned int j = threadIdx.x + u * blockDim.x;
-          if (j < len) v[u] = ld_peer(send + (lo + j) * 16);
-        }
-#pragma unroll
-        for (int u = 0; u < VPT; ++u) {
-          const unsigned int j = threadIdx.x + u * blockDim.x;
-          if (j < len) st_peer(dst + (unsigned long long)j * 16, v[u]);
-        }
-      }
-      __syncthreads();
-      // ---- 2. tell every worker that my round i has landed
-      if (threadIdx.x < (unsigned)W && !c.fault_skip_signal) {
-        const int wr = worker_rank((int)threadIdx.x);
-        if (wr != r) {
-          unsigned int* flag = (unsigned int*)(c.heap[wr] + kOffPushData) + (size_t)b * B2R_MAX_RANKS + r;
-          st_release_sys(flag, base_val + (unsigned int)(i + 1));
-        }
-      }
-    }
-    if (i >= 1 && my_w >= 0) {
-      // ---- 3. worker: combine round i-1 of my slice and push the result
-      const unsigned long long ri = i - 1;
-      if (threadIdx.x < (unsigned)P && (int)threadIdx.x != r) {
-        const unsigned int* flag = (const unsigned int*)(c.heap[r] + kOffPushData) + (size_t)b * B2R_MAX_RANKS + threadIdx.x;
-        wait_flag_ge(flag, base_val + (unsigned int)(ri + 1), c);
-      }
-      __syncthreads();
-      const unsigned long long lo = slice_lo(my_w) + (ri * G + b) * Cv, end = slice_lo(my_w + 1);
-      if (lo < end) {
-        const unsigned int len = (unsigned int)min((unsigned long long)Cv, end - lo);
-        // all VPT vectors of one source are fetched back to back, and source s+1 is in flight while s is combined
-        // (a naive per-vector, per-source loop serialises P*VPT load latencies and runs 2-3x slower)
-        auto src_ptr = [&](int sidx) { return sidx == r ? send + lo * 16 : stage_slot(r, ri, sidx); };
-        typename V::Acc acc[VPT];
-        V16 cur[VPT], nxt[VPT];
-        {
-          const char* sp = src_ptr(0);
-#pragma unroll
-          for (int u = 0; u < VPT; ++u) {
-            const unsigned int j = threadIdx.x + u * blockDim.x;
-            if (j < len) cur[u] = ld_peer(sp + (unsigned long long)j * 16);
-          }
-#pragma unroll
-          for (int u = 0; u < VPT; ++u) acc[u] = V::unpack(cur[u]);
-          sp = src_ptr(1 < P ? 1 : 0);
-#pragma unroll
-          for (int u = 0; u < VPT; ++u) {
-            const unsigned int j = threadIdx.x + u * blockDim.x;
-            if (j < len) cur[u] = ld_peer(sp + (unsigned long long)j * 16);
-          }
-        }
-        for (int sidx = 1; sidx < P; ++sidx) {
-          if (sidx + 1 < P) {
-            const char* sp = src_ptr(sidx + 1);
-#pragma unroll
-            for (int u = 0; u < VPT; ++u) {
-              const unsigned int j = threadIdx.x + u * blockDim.x;
-              if (j < len) nxt[u] = ld_peer(sp + (unsigned long long)j * 16);
-            }
-          }
-#pragma unroll
-          for (int u = 0; u < VPT; ++u) V::combine(acc[u], cur[u]);
-#pragma unroll
-          for (int u = 0; u < VPT; ++u) cur[u] = nxt[u];
-        }
-#pragma unroll
-        for (int u = 0; u < VPT; ++u) {
-          const unsigned int j = threadIdx.x + u * blockDim.x;
-          if (j < len) {
-            const V16 res = V::pack(acc[u]);
-            if (A.root < 0) {
-              for (int p = 0; p < P; ++p) st_peer(c.heap[p] + po.recv[p] + (lo + j) * 16, res);
-            } else {
-              st_peer(c.heap[A.root] + po.recv[A.root] + (lo + j) * 16, res);
-            }
-          }
-        }
-      }
-      __syncthreads();
-      if (threadIdx.x < (unsigned)P && (int)threadIdx.x != r && !c.fault_skip_signal) {
-        unsigned int* ack = (unsigned int*)(c.heap[threadIdx.x] + kOffPushAck) + (size_t)b * B2R_MAX_RANKS + my_w;
-        st_release_sys(ack, base_val + (unsigned int)(ri + 1));
-      }
-    }
-  }
-  // the (< 16 byte) tail: pulled by the last worker
-  if (my_w == W - 1 && nvec * (16 / E) < A.count) {
-    __shared__ const char* src[B2R_MAX_RANKS];
-    __shared__ char* dst[B2R_MAX_RANKS];
-    const int ndst = A.root < 0 ? P : 1;
-    if (threadIdx.x == 0) {
-      for (int p = 0; p < P; ++p) src[p] = c.heap[p] + po.send[p];
-      if (A.root < 0) for (int p = 0; p < P; ++p) dst[p] = c.heap[p] + po.recv[p];
-      else dst[0] = c.heap[A.root] + po.recv[A.root];
-    }
-    __syncthreads();
-    combine_tail<D, O>(nvec * (16 / E), A.count, src, P, dst, ndst);
-  }
-  cta_barrier(A, A.epoch + 2);
-}
+}  // namespace b2r
+#include "coll_push.cuh"  // push: scatter by stores into whole-slice staging, combine locally, store the result
+namespace b2r {
 
 // ------------------------------------------------------------------------------------------------ ring (store-forwarding chain to the root)
 // What NCCL's reduce does, restated for this runtime: the ranks form a chain that ends at the root (position p = distance
@@ -803,7 +647,7 @@ __device__ void nvls_body(const CollArgs& A) {
 }
 
 }  // namespace b2r
-#include "coll_experimental.cuh"  // LL, ring allreduce, pipelined ring: opt-in, not yet run on hardware
+#include "coll_experimental.cuh"  // LL small-message path
 namespace b2r {
 
 // barrier-only kernel body
@@ -812,7 +656,7 @@ __device__ inline void barrier_body(const CollArgs& A) {
   start_barrier(A, &po);
 }
 
-enum CollKind { kCollOneshot = 1, kCollTwoshot = 2, kCollTree = 3, kCollNvls = 4, kCollBarrier = 5, kCollPush = 6, kCollRing = 7, kCollLL = 8, kCollRingAll = 9, kCollRing2 = 10 };
+enum CollKind { kCollOneshot = 1, kCollTwoshot = 2, kCollTree = 3, kCollNvls = 4, kCollBarrier = 5, kCollPush = 6, kCollRing = 7, kCollLL = 8 };
 
 template <int D, int O, int KIND, int UNR>
 __global__ void __launch_bounds__(512) coll_kernel(const __grid_constant__ CollLaunch L) {
@@ -824,8 +668,6 @@ __global__ void __launch_bounds__(512) coll_kernel(const __grid_constant__ CollL
   else if (KIND == kCollPush) push_body<D, O, UNR>(A);
   else if (KIND == kCollRing) ring_body<D, O, UNR>(A);
   else if (KIND == kCollLL) ll_body<D, O>(A);
-  else if (KIND == kCollRingAll) ringall_body<D, O, UNR>(A);
-  else if (KIND == kCollRing2) ring2_body<D, O, UNR>(A);
   else barrier_body(A);
 }
 

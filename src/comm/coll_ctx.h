@@ -19,14 +19,16 @@ constexpr size_t kOffMeta = 64 * 1024;               // PeerMeta meta[kCollMaxCt
 constexpr size_t kOffPushData = 128 * 1024;          // uint32 [kCollMaxCtas][B2R_MAX_RANKS]: push algorithm, "block of round i from rank s has landed"
 constexpr size_t kOffPushAck = 160 * 1024;           // uint32 [kCollMaxCtas][B2R_MAX_RANKS]: push algorithm, "worker w has consumed round i"
 constexpr size_t kOffLLAck = 176 * 1024;             // uint32 [B2R_MAX_RANKS]: LL path, "rank r has finished LL call n" (flow control)
-constexpr size_t kOffLL = 192 * 1024;                // LL path: packet slots [call parity][source rank][ll_slot_bytes(P)], to the end of the region
-constexpr size_t kCtrlBytes = 1 << 20;               // control region size; staging starts here
+constexpr size_t kOffLL = 192 * 1024;                // LL path: packet slots [call parity][source rank][ll_slot_bytes(P)], up to kOffPushFlags
+constexpr size_t kOffPushFlags = 1 << 20;            // push algorithm: uint32 [B2R_MAX_RANKS][kPushChunkCap], "chunk k of source s landed in call n"
+constexpr size_t kPushChunkCap = 16384;              //   chunks per slice the flag table can name (x 16 ranks x 4 bytes = 1 MiB)
+constexpr size_t kCtrlBytes = 2 << 20;               // control region size; staging starts here
 
 // LL ("low latency") small-message path: every 16-byte vector travels as four 8-byte packets {32 data bits, 32-bit call
 // number}, so a slot holds half its size in payload. One CTA of up to kLLThreads threads, kLLVecPerThread vectors each.
 constexpr int kLLThreads = 512;
 constexpr int kLLVecPerThread = 4;
-constexpr size_t ll_slot_bytes(int nranks) { return ((kCtrlBytes - kOffLL) / (2 * (size_t)nranks)) & ~(size_t)255; }
+constexpr size_t ll_slot_bytes(int nranks) { return ((kOffPushFlags - kOffLL) / (2 * (size_t)nranks)) & ~(size_t)255; }
 constexpr size_t ll_max_msg_bytes(int nranks) {
   return ll_slot_bytes(nranks) / 2 < (size_t)kLLThreads * kLLVecPerThread * 16 ? ll_slot_bytes(nranks) / 2 : (size_t)kLLThreads * kLLVecPerThread * 16;
 }

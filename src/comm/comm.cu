@@ -65,24 +65,28 @@ void parse_fault_injection(CollCtx* ctx, int rank) {
 }
 
 struct Sizes {
-  size_t stage_bytes, user_bytes, heap_bytes, ll_big_bytes;
+  size_t stage_bytes, work_bytes, user_bytes, heap_bytes, ll_big_bytes;
 };
 
 Sizes compute_sizes(const b2r_comm_config_t* cfg, size_t granularity) {
   Sizes s;
   s.stage_bytes = (size_t)std::max(1, env_int("B2R_STAGE_MB", 64)) << 20;
+  // the work region (tree partials, ring slots, the push algorithm's whole-slice staging: 8/7 of a message per launch at 8
+  // GPUs) is sized separately: 320 MiB lets a 256 MiB reduce run as one launch. Same on every rank, like B2R_STAGE_MB.
+  s.work_bytes = std::max(s.stage_bytes, (size_t)std::max(1, env_int("B2R_WORK_MB", 320)) << 20);
   s.user_bytes = cfg && cfg->heap_bytes ? (size_t)cfg->heap_bytes : ((size_t)256 << 20);
   s.user_bytes = round_up(s.user_bytes, 256);
   // optional large LL region (experimental, off unless asked for; like B2R_STAGE_MB it must be the same on every rank)
   s.ll_big_bytes = (size_t)std::max(0, env_int("B2R_LL_BIG_MB", 0)) << 20;
-  s.heap_bytes = round_up(kCtrlBytes + 3 * s.stage_bytes + s.user_bytes + s.ll_big_bytes, granularity);
+  s.heap_bytes = round_up(kCtrlBytes + 2 * s.stage_bytes + s.work_bytes + s.user_bytes + s.ll_big_bytes, granularity);
   return s;
 }
 
 void fill_common(b2r_comm* c, const b2r_comm_config_t* cfg, const Sizes& s) {
   c->heap_bytes = s.heap_bytes;
   c->stage_bytes = s.stage_bytes;
-  c->user_off = kCtrlBytes + 3 * s.stage_bytes;
+  c->work_bytes = s.work_bytes;
+  c->user_off = kCtrlBytes + 2 * s.stage_bytes + s.work_bytes;
   c->ll_big_bytes = s.ll_big_bytes;
   c->ll_big_off = s.ll_big_bytes ? c->user_off + s.user_bytes : 0;
   c->user_end = s.ll_big_bytes ? c->ll_big_off : s.heap_bytes;

@@ -46,7 +46,7 @@ struct b2r_comm {
   b2r::CommMode mode = b2r::kModeAll;
   int rank = 0, nranks = 1, device = 0, sm_count = 0;
   b2r::CollCtx ctx;
-  size_t heap_bytes = 0, stage_bytes = 0, user_off = 0, bump = 0;
+  size_t heap_bytes = 0, stage_bytes = 0, work_bytes = 0, user_off = 0, bump = 0;
   size_t user_end = 0;                       // first byte past the user allocations (== heap_bytes without an LL-big region)
   size_t ll_big_off = 0, ll_big_bytes = 0;   // optional large LL region behind the user heap (B2R_LL_BIG_MB at creation)
   uint32_t epoch = 0;   // barrier epoch counter (same sequence on every rank)

@@ -1,10 +1,6 @@
-"""GPU, opt-in: the EXPERIMENTAL collective paths of src/coll/coll_experimental.cuh — the LL small-message path (`algo="ll"`,
-`ll_body`) and the ring allreduce (`algo="ring"` on allreduce with B2R_EXPERIMENTAL=1, `ringall_body`).
-
-Both kernels were written after the round's GPU budget was spent, so they have been compiled and inspected (SASS,
-registers) but not run. Until they have passed on hardware these tests only run when asked for:
-
-    B2R_TEST_EXPERIMENTAL=1 python -m pytest tests/test_experimental_gpu.py -m gpu -x -q
+"""GPU (loopback transport): the collective paths added after round 1 — the LL small-message path (`algo="ll"`, `ll_body` in
+src/coll/coll_experimental.cuh) and the store-only push algorithm (`algo="push"`, src/coll/coll_push.cuh). The pipelined ring
+and the ring allreduce that used to be tested here were measured on 8 GPUs in round 2, lost everywhere, and were removed.
 
 The host-side pieces that do not need a GPU (size limit, selection rule, the CPU restatement) are covered in
 tests/test_plan.py and tests/test_host_collectives.py and always run.
@@ -151,92 +147,71 @@ def test_ll_rejects_what_it_cannot_carry(comms):
         assert int(outs_store[r][:3].abs().sum()) == 0 and int(outs_store[r][35:].abs().sum()) == 0  # nothing written around the view
 
 
-# ------------------------------------------------------------------------------------------------ ring allreduce (B2R_EXPERIMENTAL=1)
-@pytest.fixture()
-def experimental(monkeypatch):
-    monkeypatch.setenv("B2R_EXPERIMENTAL", "1")
-    b2r.refresh_env()  # the library caches its B2R_* lookups
-    yield
-    monkeypatch.delenv("B2R_EXPERIMENTAL")
-    b2r.refresh_env()
-
-
+# ------------------------------------------------------------------------------------------------ push (whole-slice staging, no flow control)
 @pytest.mark.parametrize("dtype", DTYPES)
-def test_ring_allreduce_matches_host_restatement(comms, experimental, dtype):
-    """P chains + all-gather by stores (`ringall_body`): bit-identical to the per-slice chain fold of host_algos.h."""
+def test_push_matches_rank_order_fold(comms, dtype):
+    """`push_body` (coll_push.cuh): every rank stores its slices into the workers' staging, workers fold in rank order and
+    store the result. Bit-identical to the one-shot order, every root and allreduce, sizes around the chunk / slice boundaries
+    (1 element, sub-vector tails, fewer vectors than workers, one chunk, many chunks per CTA), inputs left untouched."""
     P = len(comms)
-    for count in (1, 3, 7, 1000, 4099, 65537, (1 << 21) + 9, (3 << 21) + 5):
-        xs_h = [b2r.fill_host(count, dtype, seed=41 * r + count, mode="signed") for r in range(P)]
+    esz = torch.empty(0, dtype=dtype).element_size()
+    per_vec = 16 // esz
+    for count in (1, per_vec - 1, per_vec * (P - 1), per_vec * P + 1, 4099, 128 * 4 * per_vec * P, 128 * 4 * per_vec * P + per_vec + 1,
+                  (1 << 21) + 9, (6 << 20) // esz * 4 + 3):
+        xs_h = [b2r.fill_host(count, dtype, seed=31 * r + count, mode="signed") for r in range(P)]
         xs = [x.cuda() for x in xs_h]
-        for op in ("sum", "min", "max"):
-            want = host_reduce_threads(xs_h, op, -1, "ring")[0]
-            outs = Communicator.group_allreduce(comms, xs, op, algo="ring")
+        for op in ("sum", "max"):
+            want = host_reduce_threads(xs_h, op, -1, "push")[0]
+            outs = Communicator.group_allreduce(comms, xs, op, algo="push")
             Communicator.group_check(comms)
             for r in range(P):
-                assert torch.equal(bits(outs[r].cpu()), bits(want)), (P, dtype, op, count, r)
+                assert torch.equal(bits(outs[r].cpu()), bits(want)), ("allreduce", P, dtype, op, count, r)
+            for root in sorted({0, P - 1}):
+                outs = Communicator.group_reduce(comms, xs, op, root=root, algo="push")
+                Communicator.group_check(comms)
+                assert torch.equal(bits(outs[root].cpu()), bits(want)), ("reduce", P, dtype, op, count, root)
         for r in range(P):
             assert torch.equal(bits(xs[r].cpu()), bits(xs_h[r]))
 
 
-def test_ring_allreduce_in_place_symmetric_and_back_to_back(comms, experimental):
+def test_push_in_place_symmetric_back_to_back_and_mixed(comms, monkeypatch):
+    """Calls of different sizes and launch shapes back to back (the flag table is reused, values only ever grow), in place on
+    symmetric buffers, interleaved with algorithms that use the same work region (ring, tree)."""
     P = len(comms)
-    count = 300001
     for c in comms:
         c.symm_free_all()
+    count = 700001
     bufs = [c.symm_empty(count, torch.int32) for c in comms]
-    xs_h = [b2r.fill_host(count, torch.int32, seed=77 + r, mode="full") for r in range(P)]
-    want = host_reduce_threads(xs_h, "sum", -1, "ring")[0]
-    for it in range(20):
+    xs_h = [b2r.fill_host(count, torch.int32, seed=91 + r, mode="full") for r in range(P)]
+    want = host_reduce_threads(xs_h, "sum", -1, "push")[0]
+    for it in range(24):
+        n = (count, 1000, 65537, 300000)[it % 4]
         for bf, x in zip(bufs, xs_h):
             bf.copy_(x)
-        algo = "ring" if it % 3 else "twoshot"  # interleave with a barrier-framed algorithm that shares the flag rows
-        Communicator.group_allreduce(comms, bufs, "sum", algo=algo, outs=bufs)
-    Communicator.group_check(comms)
-    for r in range(P):
-        assert torch.equal(bufs[r].cpu(), want)
+        views = [bf[:n] for bf in bufs]
+        algo = ("push", "push", "tree", "push", "twoshot")[it % 5]
+        if it % 7 == 3:
+            monkeypatch.setenv("B2R_COLL_THREADS", "128")
+        else:
+            monkeypatch.delenv("B2R_COLL_THREADS", raising=False)
+        b2r.refresh_env()
+        Communicator.group_allreduce(comms, views, "sum", algo=algo, outs=views)
+        Communicator.group_check(comms)
+        if algo != "tree":
+            for r in range(P):
+                assert torch.equal(bufs[r][:n].cpu(), want[:n]), (it, algo, n, r)
+                assert torch.equal(bufs[r][n:].cpu(), xs_h[r][n:]), "bytes past the message were written"
+    monkeypatch.delenv("B2R_COLL_THREADS", raising=False)
+    b2r.refresh_env()
+    red_in = [x.cuda() for x in xs_h]
+    for it in range(12):  # reduce: root's buffer receives only stores; ring in between shares the call counter
+        root = it % P
+        outs = Communicator.group_reduce(comms, red_in, "sum", root=root, algo=("push", "ring", "push")[it % 3])
+        Communicator.group_check(comms)
+        if it % 3 != 1:
+            assert torch.equal(outs[root].cpu(), want), (it, root)
     for c in comms:
         c.symm_free_all()
-
-
-# ------------------------------------------------------------------------------------------------ pipelined ring (B2R_RING_V2=1)
-@pytest.mark.parametrize("shape", [(512, 8), (256, 1), (96, 2)])
-def test_pipelined_ring_is_bit_identical_to_the_ring(comms, monkeypatch, shape):
-    """`ring2_body` (waiter / data / signal warps, no block-wide barrier per step) against the host chain fold, every root,
-    for launch shapes from one data warp to fourteen and for single- and multi-sub-block steps."""
-    threads, subs = shape
-    monkeypatch.setenv("B2R_RING_V2", "1")
-    monkeypatch.setenv("B2R_COLL_THREADS", str(threads))
-    monkeypatch.setenv("B2R_RING_SUBBLOCKS", str(subs))
-    b2r.refresh_env()
-    P = len(comms)
-    for dtype in (torch.int32, torch.float64, torch.bfloat16):
-        for count in (1, 1000, 65537, (1 << 21) + 9, (5 << 20) + 3):
-            xs_h = [b2r.fill_host(count, dtype, seed=19 * r + count, mode="signed") for r in range(P)]
-            xs = [x.cuda() for x in xs_h]
-            for root in sorted({0, P - 1, P // 2}):
-                for op in ("sum", "min"):
-                    want = host_reduce_threads(xs_h, op, root, "ring")
-                    outs = Communicator.group_reduce(comms, xs, op, root=root, algo="ring")
-                    Communicator.group_check(comms)
-                    assert torch.equal(bits(outs[root].cpu()), bits(want)), (P, shape, dtype, op, count, root)
-
-
-def test_pipelined_ring_back_to_back_with_other_algorithms(comms, monkeypatch):
-    monkeypatch.setenv("B2R_RING_V2", "1")
-    b2r.refresh_env()
-    P = len(comms)
-    count = 200003
-    xs_h = [b2r.fill_host(count, torch.int32, seed=5 + r, mode="full") for r in range(P)]
-    xs = [x.cuda() for x in xs_h]
-    want = host_reduce_threads(xs_h, "sum", 0, "ring")
-    outs = None
-    for it in range(60):
-        algo = ("ring", "twoshot", "ring", "push")[it % 4]  # the push algorithm shares the ring's flag words and call counter
-        outs = Communicator.group_reduce(comms, xs, "sum", root=it % P, algo=algo)
-        if it % P == 0:
-            keep = outs
-    Communicator.group_check(comms)
-    assert torch.equal(keep[0].cpu(), want)
 
 
 # ------------------------------------------------------------------------------------------------ not experimental code, but tests not yet run

@@ -68,18 +68,21 @@ def test_int_sum_wraps_across_ranks():
 
 def test_algo_selection_is_pure_and_sensible():
     sel = _lib.LIB.b2r_select_algo
-    # NVLS whenever the switch can do it (>= 4 GPUs, 8/16-byte multimem forms); otherwise one-shot for tiny messages
-    # and two-shot beyond
-    assert sel(1, 1024, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS
+    # <= 8 KiB: the LL path. Beyond: NVLS whenever the switch can do it (>= 4 GPUs, any dtype/op with a multimem form, int32
+    # included since the 8-GPU measurement of round 2); otherwise one-shot for small messages and two-shot beyond
+    assert sel(1, 1024, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_LL
+    assert sel(0, 8192, _lib.INT32, _lib.MIN, 8, 0) == _lib.ALGO_LL
+    assert sel(1, 8196, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS
     assert sel(1, 1 << 30, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS
     assert sel(1, 1 << 30, _lib.FLOAT32, _lib.SUM, 2, 1) == _lib.ALGO_TWOSHOT  # NVLS loses at 2 GPUs
     assert sel(1, 1 << 30, _lib.FLOAT32, _lib.SUM, 8, 0) == _lib.ALGO_TWOSHOT
-    assert sel(1, 1024, _lib.FLOAT32, _lib.SUM, 8, 0) == _lib.ALGO_ONESHOT
+    assert sel(1, 16384, _lib.FLOAT32, _lib.SUM, 8, 0) == _lib.ALGO_ONESHOT
     assert sel(1, 1 << 30, _lib.FLOAT32, _lib.MIN, 8, 1) == _lib.ALGO_TWOSHOT  # no multimem min for fp32
     assert sel(1, 1 << 30, _lib.FLOAT64, _lib.MAX, 8, 1) == _lib.ALGO_TWOSHOT
     assert sel(1, 1 << 30, _lib.BFLOAT16, _lib.MAX, 8, 1) == _lib.ALGO_NVLS
-    assert sel(0, 1 << 30, _lib.INT32, _lib.SUM, 8, 1) == _lib.ALGO_TWOSHOT  # 4-byte multimem ops: P2P vectors are faster
-    assert sel(0, 64, _lib.FLOAT64, _lib.SUM, 2, 0) == _lib.ALGO_ONESHOT
+    assert sel(0, 1 << 30, _lib.INT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS  # 4-byte multimem ops measure like the 16-byte fp32 form
+    assert sel(1, 1 << 28, _lib.INT32, _lib.MAX, 4, 1) == _lib.ALGO_NVLS
+    assert sel(0, 64, _lib.FLOAT64, _lib.SUM, 2, 0) == _lib.ALGO_LL
     assert sel(0, 1 << 30, _lib.FLOAT64, _lib.SUM, 2, 1) == _lib.ALGO_ONESHOT  # 2-GPU reduce: the root pulls, at any size
     assert sel(0, 1 << 20, _lib.FLOAT64, _lib.SUM, 1, 0) == _lib.ALGO_ONESHOT
 
@@ -97,21 +100,24 @@ def test_ring_reduce_folds_in_chain_order(nranks, dtype):
 
 
 def test_ll_path_limits_and_selection(monkeypatch):
-    """Host-side rules of the experimental LL path: size limit per communicator size, never chosen by AUTO, chosen under
-    B2R_ALGO=7 only for messages that fit, and its CPU restatement is the rank-order fold (== one-shot)."""
+    """Host-side rules of the LL path: size limit per communicator size, chosen by AUTO up to 8 KiB (B2R_AUTO_LL_MAX_BYTES),
+    chosen under B2R_ALGO=7 for every message that fits, and its CPU restatement is the rank-order fold (== one-shot)."""
     lim = _lib.LIB.b2r_ll_max_bytes
     assert [lim(p) for p in (0, 1, 2, 4, 8, 16, 17)] == [0, 0, 32768, 32768, 26624, 13312, 0]
-    for p in (2, 3, 4, 8, 16):  # two parities x P sources x (2 x payload) must fit between kOffLL and the end of the control region
+    for p in (2, 3, 4, 8, 16):  # two parities x P sources x (2 x payload) must fit between kOffLL and the push flag table at 1 MiB
         assert 2 * p * 2 * lim(p) <= (1 << 20) - 192 * 1024 and lim(p) % 16 == 0
     sel = _lib.LIB.b2r_select_algo
     monkeypatch.delenv("B2R_ALGO", raising=False)
-    for nbytes in (4, 1024, 26624):
-        for all_ in (0, 1):
-            assert sel(all_, nbytes, _lib.INT32, _lib.SUM, 8, 1) != _lib.ALGO_LL
+    for all_ in (0, 1):
+        assert sel(all_, 4, _lib.INT32, _lib.SUM, 8, 1) == _lib.ALGO_LL and sel(all_, 8192, _lib.INT32, _lib.SUM, 8, 1) == _lib.ALGO_LL
+        assert sel(all_, 26624, _lib.INT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS  # fits the slots, but one CTA is too slow by then
+    monkeypatch.setenv("B2R_AUTO_LL_MAX_BYTES", "0")
+    assert sel(0, 4, _lib.INT32, _lib.SUM, 8, 0) == _lib.ALGO_ONESHOT
+    monkeypatch.delenv("B2R_AUTO_LL_MAX_BYTES")
     monkeypatch.setenv("B2R_ALGO", str(_lib.ALGO_LL))
     assert sel(0, 26624, _lib.INT32, _lib.SUM, 8, 1) == _lib.ALGO_LL
     assert sel(1, 4, _lib.FLOAT64, _lib.MAX, 2, 0) == _lib.ALGO_LL
-    assert sel(0, 26625, _lib.INT32, _lib.SUM, 8, 1) == _lib.ALGO_TWOSHOT  # too big: the normal choice
+    assert sel(0, 26625, _lib.INT32, _lib.SUM, 8, 0) == _lib.ALGO_TWOSHOT  # too big: the normal choice
     assert sel(1, 1 << 20, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS
     monkeypatch.delenv("B2R_ALGO")
     xs = [b2r.fill_host(1001, torch.bfloat16, seed=9 * r, mode="signed") for r in range(5)]
@@ -145,13 +151,13 @@ def test_ring_allreduce_is_one_chain_per_slice(nranks, dtype):
                 assert torch.equal(rows[r].view(torch.uint8), want.view(torch.uint8)), (nranks, dtype, op, count, r)
 
 
-def test_auto_switches_for_unmeasured_paths_are_off_by_default(monkeypatch):
-    """B2R_AUTO_LL_MAX_BYTES / B2R_AUTO_RING_MIN_MB let the next round try crossovers without a rebuild; unset = old choice."""
+def test_auto_crossover_switches(monkeypatch):
+    """B2R_AUTO_LL_MAX_BYTES (default 8192), B2R_AUTO_RING_MIN_MB and B2R_AUTO_PUSH_MIN_MB (both off by default) move AUTO's
+    crossovers without a rebuild; unsetting them restores the measured defaults."""
     sel = _lib.LIB.b2r_select_algo
-    for var in ("B2R_ALGO", "B2R_AUTO_LL_MAX_BYTES", "B2R_AUTO_RING_MIN_MB"):
+    for var in ("B2R_ALGO", "B2R_AUTO_LL_MAX_BYTES", "B2R_AUTO_RING_MIN_MB", "B2R_AUTO_PUSH_MIN_MB", "B2R_AUTO_PUSH_NVLS_TOO"):
         monkeypatch.delenv(var, raising=False)
     before = [sel(a, n, d, _lib.SUM, p, 1) for a in (0, 1) for n in (64, 8192, 1 << 20, 1 << 28) for d in (_lib.INT32, _lib.FLOAT32) for p in (2, 8)]
-    monkeypatch.setenv("B2R_AUTO_LL_MAX_BYTES", "8192")
     assert sel(0, 8192, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_LL
     assert sel(1, 64, _lib.INT32, _lib.MIN, 2, 0) == _lib.ALGO_LL
     assert sel(0, 8193, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS
@@ -166,6 +172,17 @@ def test_auto_switches_for_unmeasured_paths_are_off_by_default(monkeypatch):
     assert sel(1, 1 << 30, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS  # allreduce: the ring is reduce-only
     assert sel(0, 1 << 30, _lib.FLOAT64, _lib.SUM, 2, 1) == _lib.ALGO_ONESHOT  # two GPUs: the root pulls
     monkeypatch.delenv("B2R_AUTO_RING_MIN_MB")
+    monkeypatch.setenv("B2R_AUTO_PUSH_MIN_MB", "32")
+    assert sel(0, 32 << 20, _lib.FLOAT64, _lib.MIN, 8, 1) == _lib.ALGO_PUSH      # no multimem form: stores instead of pulls
+    assert sel(1, 32 << 20, _lib.FLOAT32, _lib.MAX, 8, 1) == _lib.ALGO_PUSH
+    assert sel(0, (32 << 20) - 8, _lib.FLOAT64, _lib.MIN, 8, 1) == _lib.ALGO_TWOSHOT
+    assert sel(0, 1 << 30, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS       # the switch keeps what it can do ...
+    monkeypatch.setenv("B2R_AUTO_PUSH_NVLS_TOO", "1")
+    assert sel(0, 1 << 30, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_PUSH       # ... unless asked: reduce-to-root only
+    assert sel(1, 1 << 30, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS
+    assert sel(0, 1 << 30, _lib.FLOAT32, _lib.SUM, 2, 1) == _lib.ALGO_ONESHOT
+    monkeypatch.delenv("B2R_AUTO_PUSH_NVLS_TOO")
+    monkeypatch.delenv("B2R_AUTO_PUSH_MIN_MB")
     after = [sel(a, n, d, _lib.SUM, p, 1) for a in (0, 1) for n in (64, 8192, 1 << 20, 1 << 28) for d in (_lib.INT32, _lib.FLOAT32) for p in (2, 8)]
     assert before == after
 
