@@ -139,8 +139,11 @@ uint64_t ll_limit(const b2r_comm* c) {
 //     int32, whose 4-byte multimem ops were assumed too slow in round 1 and measure the same as the 16-byte fp32 form
 //     (allreduce 256 MiB: 576 us either way, two-shot 891, NCCL 727).
 //   * what has no multimem form (fp32 / fp64 min and max) stays on peer loads: one-shot while the whole message is small,
-//     two-shot beyond; and on stores (push) from B2R_AUTO_PUSH_MIN_MB up.
+//     two-shot beyond; and on stores (push) from the crossovers below up.
 //   * 2 GPUs: reduce = the root pulls the peer's message (one-shot, 630 GB/s at 64 MiB vs NCCL 580); allreduce = two-shot.
+// measured crossovers (MiB) of the push algorithm, see above; 0 = AUTO never picks it
+constexpr int kAutoPushReduceMB = 0, kAutoPushAllreduceMB = 0, kAutoPushReduceNvlsMB = 0;
+
 b2r_algo_t select_algo_cached(int is_allreduce, uint64_t bytes, b2r_dtype_t dtype, b2r_op_t op, int nranks, int has_multicast, uint64_t ll_max) {
   if (nranks <= 1) return B2R_ALGO_ONESHOT;
   const int forced = B2R_ENV_INT("B2R_ALGO", 0);
@@ -153,11 +156,16 @@ b2r_algo_t select_algo_cached(int is_allreduce, uint64_t bytes, b2r_dtype_t dtyp
   const uint64_t auto_ring = (uint64_t)std::max(0, B2R_ENV_INT("B2R_AUTO_RING_MIN_MB", 0));
   if (auto_ring && !is_allreduce && nranks > 2 && bytes >= (auto_ring << 20)) return B2R_ALGO_RING;
   const bool nvls_ok = has_multicast && nranks >= 4 && nvls_supported(dtype, op) && !B2R_ENV_INT("B2R_DISABLE_NVLS", 0);
-  // push: B2R_AUTO_PUSH_MIN_MB = m sends messages of at least m MiB through the store-only algorithm; B2R_AUTO_PUSH_NVLS_TOO=1
-  // extends that to the types NVLS serves (reduce-to-root is where the switch's ~520 GB/s ceiling loses to NCCL's ring)
-  const uint64_t auto_push = (uint64_t)std::max(0, B2R_ENV_INT("B2R_AUTO_PUSH_MIN_MB", 0));
-  if (auto_push && nranks > 2 && bytes >= (auto_push << 20) && (!nvls_ok || (!is_allreduce && B2R_ENV_INT("B2R_AUTO_PUSH_NVLS_TOO", 0))))
-    return B2R_ALGO_PUSH;
+  // push (stores only, two hops): from how many MiB on it replaces the pulls / the switch; 0 = never. Three crossovers:
+  //   B2R_AUTO_PUSH_REDUCE_MB        reduce-to-root of a (dtype, op) without a multimem form (fp32 / fp64 min and max)
+  //   B2R_AUTO_PUSH_ALLREDUCE_MB     allreduce of the same
+  //   B2R_AUTO_PUSH_REDUCE_NVLS_MB   reduce-to-root of what NVLS serves (the switch's ~520 GB/s ceiling loses to NCCL's ring)
+  if (nranks > 2) {
+    const uint64_t mb = (uint64_t)std::max(0, nvls_ok ? (is_allreduce ? 0 : B2R_ENV_INT("B2R_AUTO_PUSH_REDUCE_NVLS_MB", kAutoPushReduceNvlsMB))
+                                                      : (is_allreduce ? B2R_ENV_INT("B2R_AUTO_PUSH_ALLREDUCE_MB", kAutoPushAllreduceMB)
+                                                                      : B2R_ENV_INT("B2R_AUTO_PUSH_REDUCE_MB", kAutoPushReduceMB)));
+    if (mb && bytes >= (mb << 20)) return B2R_ALGO_PUSH;
+  }
   if (nvls_ok) return B2R_ALGO_NVLS;
   if (!is_allreduce && nranks == 2) return B2R_ALGO_ONESHOT;
   // One-shot reads the WHOLE message from every peer: fine for two GPUs or tiny messages, hopeless beyond.

@@ -152,10 +152,10 @@ def test_ring_allreduce_is_one_chain_per_slice(nranks, dtype):
 
 
 def test_auto_crossover_switches(monkeypatch):
-    """B2R_AUTO_LL_MAX_BYTES (default 8192), B2R_AUTO_RING_MIN_MB and B2R_AUTO_PUSH_MIN_MB (both off by default) move AUTO's
+    """B2R_AUTO_LL_MAX_BYTES (default 8192), B2R_AUTO_RING_MIN_MB and the three B2R_AUTO_PUSH_*_MB crossovers move AUTO's
     crossovers without a rebuild; unsetting them restores the measured defaults."""
     sel = _lib.LIB.b2r_select_algo
-    for var in ("B2R_ALGO", "B2R_AUTO_LL_MAX_BYTES", "B2R_AUTO_RING_MIN_MB", "B2R_AUTO_PUSH_MIN_MB", "B2R_AUTO_PUSH_NVLS_TOO"):
+    for var in ("B2R_ALGO", "B2R_AUTO_LL_MAX_BYTES", "B2R_AUTO_RING_MIN_MB", "B2R_AUTO_PUSH_REDUCE_MB", "B2R_AUTO_PUSH_ALLREDUCE_MB", "B2R_AUTO_PUSH_REDUCE_NVLS_MB"):
         monkeypatch.delenv(var, raising=False)
     before = [sel(a, n, d, _lib.SUM, p, 1) for a in (0, 1) for n in (64, 8192, 1 << 20, 1 << 28) for d in (_lib.INT32, _lib.FLOAT32) for p in (2, 8)]
     assert sel(0, 8192, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_LL
@@ -172,17 +172,22 @@ def test_auto_crossover_switches(monkeypatch):
     assert sel(1, 1 << 30, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS  # allreduce: the ring is reduce-only
     assert sel(0, 1 << 30, _lib.FLOAT64, _lib.SUM, 2, 1) == _lib.ALGO_ONESHOT  # two GPUs: the root pulls
     monkeypatch.delenv("B2R_AUTO_RING_MIN_MB")
-    monkeypatch.setenv("B2R_AUTO_PUSH_MIN_MB", "32")
+    monkeypatch.setenv("B2R_AUTO_PUSH_REDUCE_MB", "32")
+    monkeypatch.setenv("B2R_AUTO_PUSH_ALLREDUCE_MB", "128")
+    monkeypatch.setenv("B2R_AUTO_PUSH_REDUCE_NVLS_MB", "0")
     assert sel(0, 32 << 20, _lib.FLOAT64, _lib.MIN, 8, 1) == _lib.ALGO_PUSH      # no multimem form: stores instead of pulls
-    assert sel(1, 32 << 20, _lib.FLOAT32, _lib.MAX, 8, 1) == _lib.ALGO_PUSH
     assert sel(0, (32 << 20) - 8, _lib.FLOAT64, _lib.MIN, 8, 1) == _lib.ALGO_TWOSHOT
+    assert sel(1, 32 << 20, _lib.FLOAT32, _lib.MAX, 8, 1) == _lib.ALGO_TWOSHOT   # allreduce has its own crossover
+    assert sel(1, 128 << 20, _lib.FLOAT32, _lib.MAX, 8, 1) == _lib.ALGO_PUSH
     assert sel(0, 1 << 30, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS       # the switch keeps what it can do ...
-    monkeypatch.setenv("B2R_AUTO_PUSH_NVLS_TOO", "1")
-    assert sel(0, 1 << 30, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_PUSH       # ... unless asked: reduce-to-root only
+    monkeypatch.setenv("B2R_AUTO_PUSH_REDUCE_NVLS_MB", "64")
+    assert sel(0, 1 << 30, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_PUSH       # ... unless told otherwise: reduce-to-root only
+    assert sel(0, 1 << 30, _lib.INT32, _lib.MAX, 8, 1) == _lib.ALGO_PUSH
+    assert sel(0, 1 << 20, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS
     assert sel(1, 1 << 30, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS
-    assert sel(0, 1 << 30, _lib.FLOAT32, _lib.SUM, 2, 1) == _lib.ALGO_ONESHOT
-    monkeypatch.delenv("B2R_AUTO_PUSH_NVLS_TOO")
-    monkeypatch.delenv("B2R_AUTO_PUSH_MIN_MB")
+    assert sel(0, 1 << 30, _lib.FLOAT32, _lib.SUM, 2, 1) == _lib.ALGO_ONESHOT    # two GPUs: one worker would do all the work
+    for var in ("B2R_AUTO_PUSH_REDUCE_MB", "B2R_AUTO_PUSH_ALLREDUCE_MB", "B2R_AUTO_PUSH_REDUCE_NVLS_MB"):
+        monkeypatch.delenv(var)
     after = [sel(a, n, d, _lib.SUM, p, 1) for a in (0, 1) for n in (64, 8192, 1 << 20, 1 << 28) for d in (_lib.INT32, _lib.FLOAT32) for p in (2, 8)]
     assert before == after
 
