@@ -130,6 +130,13 @@ uint64_t ll_limit(const b2r_comm* c) {
   return std::max(small, big);
 }
 
+// Which LL instance carries a message: the one-CTA instance in the control region up to kLLSmallMaxBytes (or whenever there is
+// no large region), the 64-CTA instance behind the user heap beyond.
+bool ll_use_small(const b2r_comm* c, uint64_t bytes) {
+  if (!c->ll_big_bytes || bytes > ll_big_max_msg_bytes(c->ll_big_bytes, c->nranks)) return true;
+  return bytes <= kLLSmallMaxBytes && bytes <= ll_max_msg_bytes(c->nranks);
+}
+
 // What AUTO resolves to, on cached environment values (the public b2r_select_algo below refreshes them first). The crossovers
 // were read off one 8-GPU measurement of every candidate against NCCL (profiles/collectives_8gpu.md, raw rows in
 // profiles/raw/r2_8gpu/) and a 2-GPU one (profiles/multi_gpu.md):
@@ -143,6 +150,7 @@ uint64_t ll_limit(const b2r_comm* c) {
 //   * 2 GPUs: reduce = the root pulls the peer's message (one-shot, 630 GB/s at 64 MiB vs NCCL 580); allreduce = two-shot.
 // measured crossovers (MiB) of the push algorithm, see above; 0 = AUTO never picks it
 constexpr int kAutoPushReduceMB = 0, kAutoPushAllreduceMB = 0, kAutoPushReduceNvlsMB = 0;
+constexpr int kAutoLLAllreduceBytes = 8192, kAutoLLReduceBytes = 8192;
 
 b2r_algo_t select_algo_cached(int is_allreduce, uint64_t bytes, b2r_dtype_t dtype, b2r_op_t op, int nranks, int has_multicast, uint64_t ll_max) {
   if (nranks <= 1) return B2R_ALGO_ONESHOT;
@@ -151,7 +159,10 @@ b2r_algo_t select_algo_cached(int is_allreduce, uint64_t bytes, b2r_dtype_t dtyp
   if (forced == B2R_ALGO_LL && nranks <= B2R_MAX_RANKS && bytes <= ll_max) return B2R_ALGO_LL;
   if (forced >= B2R_ALGO_ONESHOT && forced <= B2R_ALGO_PUSH) return (b2r_algo_t)forced;
   if (forced == B2R_ALGO_RING && !is_allreduce) return B2R_ALGO_RING;
-  const uint64_t auto_ll = (uint64_t)std::max(0, B2R_ENV_INT("B2R_AUTO_LL_MAX_BYTES", 8192));
+  // LL crossovers: allreduce B2R_AUTO_LL_MAX_BYTES, reduce-to-root B2R_AUTO_LL_REDUCE_MAX_BYTES (only the root consumes, so the
+  // 64-CTA instance stays ahead of the barrier-framed kernels for longer); both capped by what the communicator's slots hold
+  const uint64_t auto_ll = (uint64_t)std::max(0, is_allreduce ? B2R_ENV_INT("B2R_AUTO_LL_MAX_BYTES", kAutoLLAllreduceBytes)
+                                                             : B2R_ENV_INT("B2R_AUTO_LL_REDUCE_MAX_BYTES", kAutoLLReduceBytes));
   if (auto_ll && nranks <= B2R_MAX_RANKS && bytes <= std::min<uint64_t>(auto_ll, ll_max)) return B2R_ALGO_LL;
   const uint64_t auto_ring = (uint64_t)std::max(0, B2R_ENV_INT("B2R_AUTO_RING_MIN_MB", 0));
   if (auto_ring && !is_allreduce && nranks > 2 && bytes >= (auto_ring << 20)) return B2R_ALGO_RING;
@@ -287,7 +298,7 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
         // small instance (control region, one CTA) when the message fits it, else the large one; each has its own slots,
         // acknowledgement words and consecutive call numbering (the slot parity and the n-2 rule depend on it)
         LLLayout lay;
-        if (bytes <= ll_max_msg_bytes(P)) {
+        if (ll_use_small(c, bytes)) {
           lay.region_off = kOffLL;
           lay.ack_off = kOffLLAck;
           lay.slot_bytes = (unsigned int)ll_slot_bytes(P);
@@ -332,13 +343,13 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
     int ctas = shape.ctas;
     int threads = shape.threads;
     if (kind == kCollLL) {
-      if (bytes <= ll_max_msg_bytes(P)) {  // one CTA; just enough threads for one vector each, up to kLLThreads x kLLVecPerThread vectors
+      if (ll_use_small(c0, bytes)) {  // one CTA; just enough threads for one vector each, up to kLLThreads x kLLVecPerThread vectors
         const uint64_t nvec = (bytes + 15) / 16;
         ctas = 1;
         threads = nvec <= 128 ? 128 : nvec <= 256 ? 256 : kLLThreads;
       } else {  // the large instance: always the same grid, whatever the length (fixed partition, see ll_body)
         ctas = kLLBigCtas;
-        threads = kLLThreads;
+        threads = kLLBigThreads;
       }
     }
     if (kind == kCollRing) {
@@ -356,6 +367,7 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
       for (int i = 0; i < n; ++i) {
         L.a[n == 1 ? 0 : rc[i].c->rank].ring_depth = depth;
         L.a[n == 1 ? 0 : rc[i].c->rank].sub_blocks = subs;
+        L.a[n == 1 ? 0 : rc[i].c->rank].stagger_ns = (unsigned int)std::max(0, B2R_ENV_INT("B2R_RING_STAGGER_US", 0)) * 1000u;
       }
     }
     if (kind == kCollNvls && !is_all) {

@@ -26,6 +26,7 @@ struct CollArgs {
   unsigned int seq;                                 // push / ring: call number (flag values are seq<<16 | round)
   int ring_depth;                                   // push / ring: staging slots per (source, CTA)
   int sub_blocks;                                   // ring: sub-blocks of (threads x 8) vectors moved per flag/fence
+  unsigned int stagger_ns;                          // ring: delay of the odd channels at the head of the chain (0 = none)
   const char* send_ptr;                             // LL: this rank's buffers as plain device pointers (peers never touch them,
   char* recv_ptr;                                   //     so they need not live in the heap); 16-byte aligned
 };
@@ -430,6 +431,15 @@ __device__ void ring_body(const CollArgs& A) {
   auto slot = [&](int rank, unsigned long long step) {
     return c.heap[rank] + A.work_off + (((step % depth) * G + b) * (unsigned long long)Cv) * 16ull;
   };
+  // All channels of a rank run the same step at the same time — stream, then sit in the release fence while the link drains,
+  // then wait one hop for the next flag — so the link idles in the latency part of every step (measured: 30 us per 512 KiB step,
+  // 21 of them link time). Delaying the ODD channels by about half a step at the head of the chain (the delay then travels down
+  // the chain with the flags) makes one half stream while the other half waits.
+  if (A.stagger_ns && (b & 1) && pred < 0 && threadIdx.x == 0) {
+    const unsigned long long t0 = coll_globaltimer();
+    while (coll_globaltimer() - t0 < (unsigned long long)A.stagger_ns) __nanosleep(500);
+  }
+  if (A.stagger_ns && (b & 1) && pred < 0) __syncthreads();
   for (unsigned long long i = 0; i < steps; ++i) {
     const unsigned long long lo = (b + i * G) * (unsigned long long)Cv;
     const unsigned int len = (unsigned int)min((unsigned long long)Cv, nvec - lo);

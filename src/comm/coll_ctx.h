@@ -34,8 +34,13 @@ constexpr size_t ll_max_msg_bytes(int nranks) {
 }
 // The optional large instance of the same layout (communicators created with B2R_LL_BIG_MB=n get n MiB behind the user heap):
 // kLLBigCtas CTAs own kLLBigVecPerCta vectors each, the acknowledgement words sit at the end of the region.
-constexpr int kLLBigCtas = 16;
-constexpr int kLLBigVecPerCta = 1024;  // 16 KiB of payload per CTA, two vectors per thread
+// Round 2, measured on 8 GPUs: with 16 CTAs x 16 KiB a 16-64 KiB message kept ONE to FOUR CTAs busy and needed 12.3-12.6 us
+// (NCCL: 10.8-11.5); the partition is now 64 CTAs x 4 KiB (one vector per thread of a 256-thread CTA), so a 16 KiB message
+// already spreads over four SMs. Messages of at most kLLSmallMaxBytes stay on the one-CTA instance in the control region.
+constexpr int kLLBigCtas = 64;
+constexpr int kLLBigVecPerCta = 256;   // 4 KiB of payload per CTA
+constexpr int kLLBigThreads = 256;
+constexpr size_t kLLSmallMaxBytes = 8192;
 constexpr size_t kLLBigAckBytes = (size_t)kLLBigCtas * B2R_MAX_RANKS * sizeof(unsigned int);
 constexpr size_t ll_big_slot_bytes(size_t region_bytes, int nranks) {
   return region_bytes <= kLLBigAckBytes ? 0 : ((region_bytes - kLLBigAckBytes) / (2 * (size_t)nranks)) & ~(size_t)255;

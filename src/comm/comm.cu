@@ -76,8 +76,9 @@ Sizes compute_sizes(const b2r_comm_config_t* cfg, size_t granularity) {
   s.work_bytes = std::max(s.stage_bytes, (size_t)std::max(1, env_int("B2R_WORK_MB", 320)) << 20);
   s.user_bytes = cfg && cfg->heap_bytes ? (size_t)cfg->heap_bytes : ((size_t)256 << 20);
   s.user_bytes = round_up(s.user_bytes, 256);
-  // optional large LL region (experimental, off unless asked for; like B2R_STAGE_MB it must be the same on every rank)
-  s.ll_big_bytes = (size_t)std::max(0, env_int("B2R_LL_BIG_MB", 0)) << 20;
+  // the large LL region (64 CTAs x 4 KiB per rank and parity; 16 MiB covers 256 KiB messages on up to 16 ranks; 0 = none).
+  // Like B2R_STAGE_MB it must be the same on every rank.
+  s.ll_big_bytes = (size_t)std::max(0, env_int("B2R_LL_BIG_MB", 16)) << 20;
   s.heap_bytes = round_up(kCtrlBytes + 2 * s.stage_bytes + s.work_bytes + s.user_bytes + s.ll_big_bytes, granularity);
   return s;
 }

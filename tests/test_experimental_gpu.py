@@ -261,8 +261,16 @@ def big_comms(request):
 
 def test_ll_big_limits(big_comms, comms):
     P = len(big_comms)
-    assert big_comms[0].ll_max_bytes == 256 << 10  # 16 CTAs x 1024 vectors; the 16 MiB region would hold more
-    assert comms[0].ll_max_bytes == _lib.LIB.b2r_ll_max_bytes(len(comms))  # no big region: the small instance only
+    assert big_comms[0].ll_max_bytes == 256 << 10  # 64 CTAs x 256 vectors; the 16 MiB region would hold more
+    assert comms[0].ll_max_bytes == 256 << 10      # the large region is part of every communicator by default
+    os.environ["B2R_LL_BIG_MB"] = "0"
+    try:
+        plain = Communicator.loopback(2, device=0, heap_bytes=16 << 20)
+    finally:
+        del os.environ["B2R_LL_BIG_MB"]
+    assert plain[0].ll_max_bytes == _lib.LIB.b2r_ll_max_bytes(2)  # no large region: the one-CTA instance only
+    for c in plain:
+        c.close()
     x = [torch.zeros((256 << 10) // 4 + 4, dtype=torch.int32, device="cuda") for _ in range(P)]
     with pytest.raises(b2r.B2RError, match="LL path carries at most"):
         Communicator.group_allreduce(big_comms, x, "sum", algo="ll")
@@ -270,14 +278,14 @@ def test_ll_big_limits(big_comms, comms):
 
 @pytest.mark.parametrize("dtype", [torch.int32, torch.float64, torch.bfloat16])
 def test_ll_big_reduce_and_allreduce(big_comms, dtype):
-    """Sizes on both sides of the small/large switch, around CTA boundaries of the fixed partition (1024 vectors per CTA),
+    """Sizes on both sides of the small/large switch, around CTA boundaries of the fixed partition (256 vectors per CTA),
     the largest message, and long mixed sequences (the two instances keep separate call counters and acknowledgements)."""
     P = len(big_comms)
     esz = torch.empty(0, dtype=dtype).element_size()
     per_vec = 16 // esz
     small_max = _lib.LIB.b2r_ll_max_bytes(P) // esz
-    counts = sorted({small_max, small_max + 1, 1024 * per_vec - 1, 1024 * per_vec, 1024 * per_vec + 1, 3 * 1024 * per_vec + 5,
-                     15 * 1024 * per_vec + 7, (256 << 10) // esz - 1, (256 << 10) // esz})
+    counts = sorted({small_max, small_max + 1, 8192 // esz, 8192 // esz + 1, 256 * per_vec - 1, 256 * per_vec, 256 * per_vec + 1, 3 * 256 * per_vec + 5,
+                     1024 * per_vec + 1, 63 * 256 * per_vec + 7, (256 << 10) // esz - 1, (256 << 10) // esz})
     for count in counts:
         xs_h = [b2r.fill_host(count, dtype, seed=23 * r + count, mode="signed") for r in range(P)]
         xs = [x.cuda() for x in xs_h]

@@ -111,9 +111,11 @@ def test_ll_path_limits_and_selection(monkeypatch):
     for all_ in (0, 1):
         assert sel(all_, 4, _lib.INT32, _lib.SUM, 8, 1) == _lib.ALGO_LL and sel(all_, 8192, _lib.INT32, _lib.SUM, 8, 1) == _lib.ALGO_LL
         assert sel(all_, 26624, _lib.INT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS  # fits the slots, but one CTA is too slow by then
-    monkeypatch.setenv("B2R_AUTO_LL_MAX_BYTES", "0")
-    assert sel(0, 4, _lib.INT32, _lib.SUM, 8, 0) == _lib.ALGO_ONESHOT
+    monkeypatch.setenv("B2R_AUTO_LL_MAX_BYTES", "0")          # allreduce crossover
+    monkeypatch.setenv("B2R_AUTO_LL_REDUCE_MAX_BYTES", "0")   # reduce-to-root crossover
+    assert sel(0, 4, _lib.INT32, _lib.SUM, 8, 0) == _lib.ALGO_ONESHOT and sel(1, 4, _lib.INT32, _lib.SUM, 8, 0) == _lib.ALGO_ONESHOT
     monkeypatch.delenv("B2R_AUTO_LL_MAX_BYTES")
+    monkeypatch.delenv("B2R_AUTO_LL_REDUCE_MAX_BYTES")
     monkeypatch.setenv("B2R_ALGO", str(_lib.ALGO_LL))
     assert sel(0, 26624, _lib.INT32, _lib.SUM, 8, 1) == _lib.ALGO_LL
     assert sel(1, 4, _lib.FLOAT64, _lib.MAX, 2, 0) == _lib.ALGO_LL
@@ -155,16 +157,17 @@ def test_auto_crossover_switches(monkeypatch):
     """B2R_AUTO_LL_MAX_BYTES (default 8192), B2R_AUTO_RING_MIN_MB and the three B2R_AUTO_PUSH_*_MB crossovers move AUTO's
     crossovers without a rebuild; unsetting them restores the measured defaults."""
     sel = _lib.LIB.b2r_select_algo
-    for var in ("B2R_ALGO", "B2R_AUTO_LL_MAX_BYTES", "B2R_AUTO_RING_MIN_MB", "B2R_AUTO_PUSH_REDUCE_MB", "B2R_AUTO_PUSH_ALLREDUCE_MB", "B2R_AUTO_PUSH_REDUCE_NVLS_MB"):
+    for var in ("B2R_ALGO", "B2R_AUTO_LL_MAX_BYTES", "B2R_AUTO_LL_REDUCE_MAX_BYTES", "B2R_AUTO_RING_MIN_MB", "B2R_AUTO_PUSH_REDUCE_MB", "B2R_AUTO_PUSH_ALLREDUCE_MB", "B2R_AUTO_PUSH_REDUCE_NVLS_MB"):
         monkeypatch.delenv(var, raising=False)
     before = [sel(a, n, d, _lib.SUM, p, 1) for a in (0, 1) for n in (64, 8192, 1 << 20, 1 << 28) for d in (_lib.INT32, _lib.FLOAT32) for p in (2, 8)]
     assert sel(0, 8192, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_LL
     assert sel(1, 64, _lib.INT32, _lib.MIN, 2, 0) == _lib.ALGO_LL
     assert sel(0, 8193, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS
-    monkeypatch.setenv("B2R_AUTO_LL_MAX_BYTES", str(1 << 30))  # capped by what the slots hold
+    monkeypatch.setenv("B2R_AUTO_LL_REDUCE_MAX_BYTES", str(1 << 30))  # capped by what the slots hold
     assert sel(0, 26624, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_LL
     assert sel(0, 26628, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS
-    monkeypatch.delenv("B2R_AUTO_LL_MAX_BYTES")
+    assert sel(1, 26624, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS  # the allreduce crossover is a separate knob
+    monkeypatch.delenv("B2R_AUTO_LL_REDUCE_MAX_BYTES")
     monkeypatch.setenv("B2R_AUTO_RING_MIN_MB", "64")
     assert sel(0, 64 << 20, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_RING
     assert sel(0, 64 << 20, _lib.INT32, _lib.MAX, 4, 0) == _lib.ALGO_RING
@@ -193,11 +196,11 @@ def test_auto_crossover_switches(monkeypatch):
 
 
 def test_ll_big_region_arithmetic():
-    """Sizes of the optional large LL instance (coll_ctx.h), restated: 16 CTAs x 1024 vectors, acknowledgement words at the
+    """Sizes of the large LL instance (coll_ctx.h), restated: 64 CTAs x 256 vectors, acknowledgement words at the
     end of the region, two parities x P sources x slot, payload = half a slot."""
-    ack = 16 * 16 * 4
+    ack = 64 * 16 * 4
     for region_mb, P, want in ((16, 8, 256 << 10), (16, 16, 262016), (16, 2, 256 << 10), (4, 8, 130944), (1, 16, 16256)):
         region = region_mb << 20
         slot = ((region - ack) // (2 * P)) & ~255
-        assert min(slot // 2, 16 * 1024 * 16) == want, (region_mb, P)
+        assert min(slot // 2, 64 * 256 * 16) == want, (region_mb, P)
         assert 2 * P * slot + ack <= region
