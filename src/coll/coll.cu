@@ -81,7 +81,7 @@ CollKernel pick_kernel(b2r_dtype_t dtype, int op, int kind, int unroll) {
 struct Shape {
   int ctas, threads, unroll;
 };
-Shape coll_shape(const b2r_comm* c, int kind, uint64_t bytes, int nvirtual) {
+Shape coll_shape(const b2r_comm* c, int kind, uint64_t bytes, int nvirtual, int unit_bytes = 16) {
   Shape s;
   int cap;
   uint64_t per_cta;
@@ -90,6 +90,14 @@ Shape coll_shape(const b2r_comm* c, int kind, uint64_t bytes, int nvirtual) {
     s.unroll = bytes >= (8u << 20) ? 8 : 4;
     cap = 32;
     per_cta = 32768;
+    // The switch wants a certain number of BYTES in flight, and a multimem instruction moves 16 (fp32 x4, bf16 x8), 8 (fp64) or 4
+    // (32-bit integers) of them: the narrow forms get proportionally more CTAs and always eight requests per thread. int32 at 4
+    // GPUs, 1 GiB: 32 x 256 x 4 -> 198 GB/s, 32 x 256 x 8 -> 342, 128 x 256 x 8 -> 558 (= the fp32 form); at 8 GPUs each rank
+    // owns half as much of the message and 32 x 256 x 8 was already enough up to 256 MiB, not beyond (profiles/raw/r2_4gpu, r2_8gpu_b).
+    if (unit_bytes < 16) {
+      cap = std::min(128, 32 * 16 / std::max(4, unit_bytes));
+      if (bytes >= (1u << 20)) s.unroll = 8;
+    }
   } else if (kind == kCollPush || kind == kCollRing) {
     s.threads = 512;
     s.unroll = 4;
@@ -150,7 +158,9 @@ bool ll_use_small(const b2r_comm* c, uint64_t bytes) {
 //   * 2 GPUs: reduce = the root pulls the peer's message (one-shot, 630 GB/s at 64 MiB vs NCCL 580); allreduce = two-shot.
 // measured crossovers (MiB) of the push algorithm, see above; 0 = AUTO never picks it
 constexpr int kAutoPushReduceMB = 0, kAutoPushAllreduceMB = 0, kAutoPushReduceNvlsMB = 0;
-constexpr int kAutoLLAllreduceBytes = 8192, kAutoLLReduceBytes = 8192;
+// LL: 4 GPUs, 64-CTA instance: reduce 8.2-10.5 us up to 256 KiB (NCCL 7.8-11.0, NVLS 12.5-15.7); allreduce ahead of NVLS up to
+// 128 KiB at 4 GPUs — every consumer receives (P-1) x 2 x the message, so the crossover is set lower for all sizes of P
+constexpr int kAutoLLAllreduceBytes = 65536, kAutoLLReduceBytes = 262144;
 
 b2r_algo_t select_algo_cached(int is_allreduce, uint64_t bytes, b2r_dtype_t dtype, b2r_op_t op, int nranks, int has_multicast, uint64_t ll_max) {
   if (nranks <= 1) return B2R_ALGO_ONESHOT;
@@ -339,7 +349,7 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
       c->epoch += 8;  // start + end + up to 4 tree rounds, rounded up; same increment on every rank
       if (kind == kCollPush || kind == kCollRing) A.seq = ++c->push_seq;
     }
-    const Shape shape = coll_shape(c0, kind, bytes, n);
+    const Shape shape = coll_shape(c0, kind, bytes, n, dtype == B2R_INT32 ? 4 : (dtype == B2R_FLOAT64 ? 8 : 16));
     int ctas = shape.ctas;
     int threads = shape.threads;
     if (kind == kCollLL) {
@@ -554,7 +564,11 @@ uint64_t b2r_ll_max_bytes(int nranks) { return (nranks >= 2 && nranks <= B2R_MAX
 // Public, for tests and harnesses: looks at the environment as it is now (the launch path uses cached values, util/env.h).
 b2r_algo_t b2r_select_algo(int is_allreduce, uint64_t bytes, b2r_dtype_t dtype, b2r_op_t op, int nranks, int has_multicast) {
   env_refresh();
-  return select_algo_cached(is_allreduce, bytes, dtype, op, nranks, has_multicast, nranks <= B2R_MAX_RANKS ? ll_max_msg_bytes(std::max(nranks, 1)) : 0);
+  // the LL limit of a communicator created with the default large LL region (B2R_LL_BIG_MB unset = 16)
+  const uint64_t ll_max = nranks <= B2R_MAX_RANKS
+                              ? std::max<uint64_t>(ll_max_msg_bytes(std::max(nranks, 1)), ll_big_max_msg_bytes((size_t)16 << 20, std::max(nranks, 1)))
+                              : 0;
+  return select_algo_cached(is_allreduce, bytes, dtype, op, nranks, has_multicast, ll_max);
 }
 
 b2r_status_t b2r_reduce_ex(const void* sendbuf, void* recvbuf, uint64_t count, b2r_dtype_t dtype, b2r_op_t op, int root, b2r_comm_t comm,

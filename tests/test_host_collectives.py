@@ -68,15 +68,19 @@ def test_int_sum_wraps_across_ranks():
 
 def test_algo_selection_is_pure_and_sensible():
     sel = _lib.LIB.b2r_select_algo
-    # <= 8 KiB: the LL path. Beyond: NVLS whenever the switch can do it (>= 4 GPUs, any dtype/op with a multimem form, int32
+    # small messages: the LL path (allreduce up to 64 KiB, reduce-to-root up to 256 KiB). Beyond: NVLS whenever the switch can do it (>= 4 GPUs, any dtype/op with a multimem form, int32
     # included since the 8-GPU measurement of round 2); otherwise one-shot for small messages and two-shot beyond
     assert sel(1, 1024, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_LL
     assert sel(0, 8192, _lib.INT32, _lib.MIN, 8, 0) == _lib.ALGO_LL
-    assert sel(1, 8196, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS
+    assert sel(1, 65536, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_LL
+    assert sel(1, 65540, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS
+    assert sel(0, 262144, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_LL
+    assert sel(0, 262148, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS
     assert sel(1, 1 << 30, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS
     assert sel(1, 1 << 30, _lib.FLOAT32, _lib.SUM, 2, 1) == _lib.ALGO_TWOSHOT  # NVLS loses at 2 GPUs
     assert sel(1, 1 << 30, _lib.FLOAT32, _lib.SUM, 8, 0) == _lib.ALGO_TWOSHOT
-    assert sel(1, 16384, _lib.FLOAT32, _lib.SUM, 8, 0) == _lib.ALGO_ONESHOT
+    assert sel(1, 65540, _lib.FLOAT32, _lib.SUM, 8, 0) == _lib.ALGO_TWOSHOT
+    assert sel(1, 65540, _lib.FLOAT32, _lib.SUM, 2, 0) == _lib.ALGO_ONESHOT
     assert sel(1, 1 << 30, _lib.FLOAT32, _lib.MIN, 8, 1) == _lib.ALGO_TWOSHOT  # no multimem min for fp32
     assert sel(1, 1 << 30, _lib.FLOAT64, _lib.MAX, 8, 1) == _lib.ALGO_TWOSHOT
     assert sel(1, 1 << 30, _lib.BFLOAT16, _lib.MAX, 8, 1) == _lib.ALGO_NVLS
@@ -109,17 +113,18 @@ def test_ll_path_limits_and_selection(monkeypatch):
     sel = _lib.LIB.b2r_select_algo
     monkeypatch.delenv("B2R_ALGO", raising=False)
     for all_ in (0, 1):
-        assert sel(all_, 4, _lib.INT32, _lib.SUM, 8, 1) == _lib.ALGO_LL and sel(all_, 8192, _lib.INT32, _lib.SUM, 8, 1) == _lib.ALGO_LL
-        assert sel(all_, 26624, _lib.INT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS  # fits the slots, but one CTA is too slow by then
+        assert sel(all_, 4, _lib.INT32, _lib.SUM, 8, 1) == _lib.ALGO_LL and sel(all_, 65536, _lib.INT32, _lib.SUM, 8, 1) == _lib.ALGO_LL
+        assert sel(all_, 262148, _lib.INT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS
     monkeypatch.setenv("B2R_AUTO_LL_MAX_BYTES", "0")          # allreduce crossover
     monkeypatch.setenv("B2R_AUTO_LL_REDUCE_MAX_BYTES", "0")   # reduce-to-root crossover
     assert sel(0, 4, _lib.INT32, _lib.SUM, 8, 0) == _lib.ALGO_ONESHOT and sel(1, 4, _lib.INT32, _lib.SUM, 8, 0) == _lib.ALGO_ONESHOT
     monkeypatch.delenv("B2R_AUTO_LL_MAX_BYTES")
     monkeypatch.delenv("B2R_AUTO_LL_REDUCE_MAX_BYTES")
     monkeypatch.setenv("B2R_ALGO", str(_lib.ALGO_LL))
-    assert sel(0, 26624, _lib.INT32, _lib.SUM, 8, 1) == _lib.ALGO_LL
+    assert sel(0, 262144, _lib.INT32, _lib.SUM, 8, 1) == _lib.ALGO_LL
+    assert sel(1, 262144, _lib.INT32, _lib.SUM, 8, 1) == _lib.ALGO_LL      # forced: every message that fits, allreduce too
     assert sel(1, 4, _lib.FLOAT64, _lib.MAX, 2, 0) == _lib.ALGO_LL
-    assert sel(0, 26625, _lib.INT32, _lib.SUM, 8, 0) == _lib.ALGO_TWOSHOT  # too big: the normal choice
+    assert sel(0, 262148, _lib.INT32, _lib.SUM, 8, 0) == _lib.ALGO_TWOSHOT  # too big: the normal choice
     assert sel(1, 1 << 20, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS
     monkeypatch.delenv("B2R_ALGO")
     xs = [b2r.fill_host(1001, torch.bfloat16, seed=9 * r, mode="signed") for r in range(5)]
@@ -162,11 +167,12 @@ def test_auto_crossover_switches(monkeypatch):
     before = [sel(a, n, d, _lib.SUM, p, 1) for a in (0, 1) for n in (64, 8192, 1 << 20, 1 << 28) for d in (_lib.INT32, _lib.FLOAT32) for p in (2, 8)]
     assert sel(0, 8192, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_LL
     assert sel(1, 64, _lib.INT32, _lib.MIN, 2, 0) == _lib.ALGO_LL
+    monkeypatch.setenv("B2R_AUTO_LL_REDUCE_MAX_BYTES", "8192")
     assert sel(0, 8193, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS
-    monkeypatch.setenv("B2R_AUTO_LL_REDUCE_MAX_BYTES", str(1 << 30))  # capped by what the slots hold
-    assert sel(0, 26624, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_LL
-    assert sel(0, 26628, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS
-    assert sel(1, 26624, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS  # the allreduce crossover is a separate knob
+    assert sel(1, 8193, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_LL     # the allreduce crossover is a separate knob
+    monkeypatch.setenv("B2R_AUTO_LL_REDUCE_MAX_BYTES", str(1 << 30))  # capped by what the slots hold (256 KiB)
+    assert sel(0, 262144, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_LL
+    assert sel(0, 262148, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS
     monkeypatch.delenv("B2R_AUTO_LL_REDUCE_MAX_BYTES")
     monkeypatch.setenv("B2R_AUTO_RING_MIN_MB", "64")
     assert sel(0, 64 << 20, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_RING
