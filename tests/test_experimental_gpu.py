@@ -130,7 +130,7 @@ def test_ll_back_to_back_mixed_sequence(comms):
 
 def test_ll_rejects_what_it_cannot_carry(comms):
     P = len(comms)
-    too_big = _lib.LIB.b2r_ll_max_bytes(P) // 4 + 1
+    too_big = comms[0].ll_max_bytes // 4 + 1  # the communicator's own limit (large region included: 256 KiB by default)
     xs = [torch.zeros(too_big, dtype=torch.int32, device="cuda") for _ in range(P)]
     with pytest.raises(b2r.B2RError, match="LL path carries at most"):
         Communicator.group_allreduce(comms, xs, "sum", algo="ll")
