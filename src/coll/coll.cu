@@ -359,7 +359,9 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
         threads = nvec <= 128 ? 128 : nvec <= 256 ? 256 : kLLThreads;
       } else {  // the large instance: always the same grid, whatever the length (fixed partition, see ll_body)
         ctas = kLLBigCtas;
-        threads = kLLBigThreads;
+        // loopback: all virtual ranks' CTAs must be co-resident in ONE cooperative launch (8 x 64 CTAs): half-size CTAs, two
+        // vectors per thread, same partition
+        threads = n > 1 ? kLLBigThreads / 2 : kLLBigThreads;
       }
     }
     if (kind == kCollRing) {
