@@ -187,6 +187,9 @@ b2r_algo_t select_algo_cached(int is_allreduce, uint64_t bytes, b2r_dtype_t dtyp
                                                                       : B2R_ENV_INT("B2R_AUTO_PUSH_REDUCE_MB", kAutoPushReduceMB)));
     if (mb && bytes >= (mb << 20)) return B2R_ALGO_PUSH;
   }
+  // 32-bit integers through the switch collapse for reduce-to-root at >= 1 GiB on 8 GPUs (2.1-4.8 ms at 1 GiB where fp32 needs 2.0 and
+  // 256 MiB is on par: 4-byte multimem loads AND 4-byte stores to the root); the store-forwarding ring is steady there (2.04 ms)
+  if (nvls_ok && !is_allreduce && dtype == B2R_INT32 && bytes >= (512ull << 20)) return B2R_ALGO_RING;
   if (nvls_ok) return B2R_ALGO_NVLS;
   if (!is_allreduce && nranks == 2) return B2R_ALGO_ONESHOT;
   // One-shot reads the WHOLE message from every peer: fine for two GPUs or tiny messages, hopeless beyond.

@@ -84,7 +84,9 @@ def test_algo_selection_is_pure_and_sensible():
     assert sel(1, 1 << 30, _lib.FLOAT32, _lib.MIN, 8, 1) == _lib.ALGO_TWOSHOT  # no multimem min for fp32
     assert sel(1, 1 << 30, _lib.FLOAT64, _lib.MAX, 8, 1) == _lib.ALGO_TWOSHOT
     assert sel(1, 1 << 30, _lib.BFLOAT16, _lib.MAX, 8, 1) == _lib.ALGO_NVLS
-    assert sel(0, 1 << 30, _lib.INT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS  # 4-byte multimem ops measure like the 16-byte fp32 form
+    assert sel(0, 1 << 28, _lib.INT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS  # 4-byte multimem ops measure like the 16-byte fp32 form ...
+    assert sel(0, 1 << 30, _lib.INT32, _lib.SUM, 8, 1) == _lib.ALGO_RING  # ... except for reduce-to-root from 512 MiB up
+    assert sel(1, 1 << 30, _lib.INT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS
     assert sel(1, 1 << 28, _lib.INT32, _lib.MAX, 4, 1) == _lib.ALGO_NVLS
     assert sel(0, 64, _lib.FLOAT64, _lib.SUM, 2, 0) == _lib.ALGO_LL
     assert sel(0, 1 << 30, _lib.FLOAT64, _lib.SUM, 2, 1) == _lib.ALGO_ONESHOT  # 2-GPU reduce: the root pulls, at any size
@@ -191,7 +193,7 @@ def test_auto_crossover_switches(monkeypatch):
     assert sel(0, 1 << 30, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS       # the switch keeps what it can do ...
     monkeypatch.setenv("B2R_AUTO_PUSH_REDUCE_NVLS_MB", "64")
     assert sel(0, 1 << 30, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_PUSH       # ... unless told otherwise: reduce-to-root only
-    assert sel(0, 1 << 30, _lib.INT32, _lib.MAX, 8, 1) == _lib.ALGO_PUSH
+    assert sel(0, 1 << 28, _lib.INT32, _lib.MAX, 8, 1) == _lib.ALGO_PUSH
     assert sel(0, 1 << 20, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS
     assert sel(1, 1 << 30, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS
     assert sel(0, 1 << 30, _lib.FLOAT32, _lib.SUM, 2, 1) == _lib.ALGO_ONESHOT    # two GPUs: one worker would do all the work
