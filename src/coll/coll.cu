@@ -173,7 +173,9 @@ b2r_algo_t select_algo_cached(int is_allreduce, uint64_t bytes, b2r_dtype_t dtyp
   // 64-CTA instance stays ahead of the barrier-framed kernels for longer); both capped by what the communicator's slots hold
   const uint64_t auto_ll = (uint64_t)std::max(0, is_allreduce ? B2R_ENV_INT("B2R_AUTO_LL_MAX_BYTES", kAutoLLAllreduceBytes)
                                                              : B2R_ENV_INT("B2R_AUTO_LL_REDUCE_MAX_BYTES", kAutoLLReduceBytes));
-  if (auto_ll && nranks <= B2R_MAX_RANKS && bytes <= std::min<uint64_t>(auto_ll, ll_max)) return B2R_ALGO_LL;
+  // two GPUs: a consumer receives from ONE peer, so LL stays ahead of the barrier-framed one-shot (16.6 us at 256 KiB) for as long as its slots reach
+  const uint64_t ll_cut = (is_allreduce && nranks == 2 && auto_ll) ? std::max<uint64_t>(auto_ll, 262144) : auto_ll;
+  if (ll_cut && nranks <= B2R_MAX_RANKS && bytes <= std::min<uint64_t>(ll_cut, ll_max)) return B2R_ALGO_LL;
   const uint64_t auto_ring = (uint64_t)std::max(0, B2R_ENV_INT("B2R_AUTO_RING_MIN_MB", 0));
   if (auto_ring && !is_allreduce && nranks > 2 && bytes >= (auto_ring << 20)) return B2R_ALGO_RING;
   const bool nvls_ok = has_multicast && nranks >= 4 && nvls_supported(dtype, op) && !B2R_ENV_INT("B2R_DISABLE_NVLS", 0);

@@ -80,7 +80,8 @@ def test_algo_selection_is_pure_and_sensible():
     assert sel(1, 1 << 30, _lib.FLOAT32, _lib.SUM, 2, 1) == _lib.ALGO_TWOSHOT  # NVLS loses at 2 GPUs
     assert sel(1, 1 << 30, _lib.FLOAT32, _lib.SUM, 8, 0) == _lib.ALGO_TWOSHOT
     assert sel(1, 65540, _lib.FLOAT32, _lib.SUM, 8, 0) == _lib.ALGO_TWOSHOT
-    assert sel(1, 65540, _lib.FLOAT32, _lib.SUM, 2, 0) == _lib.ALGO_ONESHOT
+    assert sel(1, 65540, _lib.FLOAT32, _lib.SUM, 2, 0) == _lib.ALGO_LL       # two GPUs: one peer per consumer, LL up to 256 KiB
+    assert sel(1, 262148, _lib.FLOAT32, _lib.SUM, 2, 0) == _lib.ALGO_ONESHOT
     assert sel(1, 1 << 30, _lib.FLOAT32, _lib.MIN, 8, 1) == _lib.ALGO_TWOSHOT  # no multimem min for fp32
     assert sel(1, 1 << 30, _lib.FLOAT64, _lib.MAX, 8, 1) == _lib.ALGO_TWOSHOT
     assert sel(1, 1 << 30, _lib.BFLOAT16, _lib.MAX, 8, 1) == _lib.ALGO_NVLS
