@@ -63,7 +63,6 @@ b2r_algo_t parse_algo(const std::string& s) {
   if (s == "push") return B2R_ALGO_PUSH;
   if (s == "ring") return B2R_ALGO_RING;
   if (s == "ll") return B2R_ALGO_LL;
-  if (s == "hybrid") return B2R_ALGO_HYBRID;
   return B2R_ALGO_AUTO;
 }
 

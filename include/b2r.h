@@ -58,11 +58,8 @@ typedef enum {
   B2R_ALGO_NVLS = 4,    /* multimem.ld_reduce / multimem.st through the NVSwitch (needs multicast) */
   B2R_ALGO_PUSH = 5,    /* scatter by P2P stores into the owners' staging, reduce locally, push the result: no remote loads */
   B2R_ALGO_RING = 6,    /* reduce only: store-forwarding chain that ends at the root (one neighbour per GPU, no remote loads) */
-  B2R_ALGO_LL = 7,      /* small-message path (see b2r_ll_max_bytes): flag-in-data packets pushed into the consumers' slots, no
-                           barrier at either end; AUTO's choice up to 64 KiB (allreduce) / 256 KiB (reduce) */
-  B2R_ALGO_HYBRID = 8   /* reduce only, needs multicast: the head of the message through the switch (NVLS) and the tail down the
-                           store-forwarding ring in ONE launch — the switch's reduction rate and the ring's latency are different
-                           bottlenecks */
+  B2R_ALGO_LL = 7       /* EXPERIMENTAL small-message path (see b2r_ll_max_bytes): flag-in-data packets pushed into the consumers'
+                           slots, no barrier at either end; never chosen by AUTO, not yet validated on hardware */
 } b2r_algo_t;
 
 typedef struct {

@@ -50,7 +50,6 @@ CollKernel pick_kind(int kind) {
     case kCollPush: return coll_kernel<D, O, kCollPush, 4>;
     case kCollRing: return coll_kernel<D, O, kCollRing, 4>;
     case kCollLL: return coll_kernel<D, O, kCollLL, 4>;
-    case kCollHybrid: return Nvls<D, O>::kSupported ? coll_kernel<D, O, kCollHybrid, UNR> : nullptr;
   }
   return nullptr;
 }
@@ -99,7 +98,7 @@ Shape coll_shape(const b2r_comm* c, int kind, uint64_t bytes, int nvirtual, int 
       cap = std::min(128, 32 * 16 / std::max(4, unit_bytes));
       if (bytes >= (1u << 20)) s.unroll = 8;
     }
-  } else if (kind == kCollPush || kind == kCollRing || kind == kCollHybrid) {
+  } else if (kind == kCollPush || kind == kCollRing) {
     s.threads = 512;
     s.unroll = 4;
     cap = 128;
@@ -254,14 +253,12 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
 
   const uint64_t total_bytes = count * esz;
   if (algo == B2R_ALGO_AUTO) algo = select_algo_cached(is_all ? 1 : 0, total_bytes, dtype, op, P, c0->has_mc ? 1 : 0, ll_limit(c0));
-  if (algo == B2R_ALGO_HYBRID && is_all) return fail(B2R_ERR_UNSUPPORTED, "the hybrid algorithm implements reduce-to-root only");
-  if (algo == B2R_ALGO_NVLS || algo == B2R_ALGO_HYBRID) {
+  if (algo == B2R_ALGO_NVLS) {
     if (!c0->has_mc) return fail(B2R_ERR_UNSUPPORTED, "NVLS requested but this communicator has no multicast mapping");
     if (!nvls_supported(dtype, op)) return fail(B2R_ERR_UNSUPPORTED, "NVLS has no %s %s instruction", b2r_dtype_name(dtype), b2r_op_name(op));
   }
   int kind = algo == B2R_ALGO_ONESHOT ? kCollOneshot : algo == B2R_ALGO_TWOSHOT ? kCollTwoshot : algo == B2R_ALGO_TREE ? kCollTree
-             : algo == B2R_ALGO_PUSH ? kCollPush : algo == B2R_ALGO_RING ? kCollRing : algo == B2R_ALGO_LL ? kCollLL
-             : algo == B2R_ALGO_HYBRID ? kCollHybrid : kCollNvls;
+             : algo == B2R_ALGO_PUSH ? kCollPush : algo == B2R_ALGO_RING ? kCollRing : algo == B2R_ALGO_LL ? kCollLL : kCollNvls;
   if (kind == kCollRing && is_all) return fail(B2R_ERR_UNSUPPORTED, "the ring algorithm implements reduce-to-root only");
   if (kind == kCollLL) {
     // LL never touches a peer's send/recv buffer: any device pointer works, nothing is chunked, and only a buffer that is not
@@ -355,7 +352,7 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
       A.epoch = c->epoch;
       A.root = is_all ? -1 : root;
       c->epoch += 8;  // start + end + up to 4 tree rounds, rounded up; same increment on every rank
-      if (kind == kCollPush || kind == kCollRing || kind == kCollHybrid) A.seq = ++c->push_seq;
+      if (kind == kCollPush || kind == kCollRing) A.seq = ++c->push_seq;
     }
     const Shape shape = coll_shape(c0, kind, bytes, n, dtype == B2R_INT32 ? 4 : (dtype == B2R_FLOAT64 ? 8 : 16));
     int ctas = shape.ctas;
@@ -388,36 +385,6 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
         L.a[n == 1 ? 0 : rc[i].c->rank].ring_depth = depth;
         L.a[n == 1 ? 0 : rc[i].c->rank].sub_blocks = subs;
         L.a[n == 1 ? 0 : rc[i].c->rank].stagger_ns = (unsigned int)std::max(0, B2R_ENV_INT("B2R_RING_STAGGER_US", 0)) * 1000u;
-      }
-    }
-    if (kind == kCollHybrid) {
-      // CTAs [0, Gn) take elements [0, split) through the switch, CTAs [Gn, Gn + Gr) send the rest down the ring (512 KiB steps)
-      threads = 512;
-      int Gn = std::max(1, B2R_ENV_INT("B2R_HYBRID_NVLS_CTAS", 32)), Gr = std::max(1, B2R_ENV_INT("B2R_HYBRID_RING_CTAS", 64));
-      if (n > 1) {  // loopback: everything co-resident in one cooperative launch
-        const int cap = std::max(2, c0->sm_count / n);
-        Gn = std::max(1, cap / 3);
-        Gr = std::max(1, cap - Gn);
-      }
-      const int share = std::max(1, std::min(63, B2R_ENV_INT("B2R_HYBRID_NVLS_SHARE", 32)));
-      const uint64_t split = (cnt / 64 * (uint64_t)share) / 128 * 128;
-      const uint64_t ring_bytes = (cnt - split) * esz;
-      const uint64_t sub_bytes = (uint64_t)threads * 8 * 16;
-      int subs = std::max(1, B2R_ENV_INT("B2R_RING_SUBBLOCKS", 8));
-      while (subs > 1 && ring_bytes < (uint64_t)Gr * sub_bytes * subs * 2) subs /= 2;
-      const uint64_t step_bytes = sub_bytes * subs;
-      Gr = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)Gr, std::max<uint64_t>(1, (ring_bytes + step_bytes - 1) / step_bytes)));
-      Gr = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)Gr, c0->work_bytes / (2ull * step_bytes)));
-      const int depth = (int)std::min<uint64_t>(8, c0->work_bytes / ((uint64_t)Gr * step_bytes));
-      ctas = Gn + Gr;
-      B2R_REQUIRE(ctas <= kCollMaxCtas, "hybrid: %d CTAs exceed the flag table", ctas);
-      for (int i = 0; i < n; ++i) {
-        CollArgs& H = L.a[n == 1 ? 0 : rc[i].c->rank];
-        H.ring_depth = depth;
-        H.sub_blocks = subs;
-        H.stagger_ns = 0;
-        H.hy_nvls_ctas = Gn;
-        H.hy_split = split;
       }
     }
     if (kind == kCollNvls && !is_all) {

@@ -27,10 +27,6 @@ struct CollArgs {
   int ring_depth;                                   // push / ring: staging slots per (source, CTA)
   int sub_blocks;                                   // ring: sub-blocks of (threads x 8) vectors moved per flag/fence
   unsigned int stagger_ns;                          // ring: delay of the odd channels at the head of the chain (0 = none)
-  int hy_nvls_ctas;                                 // hybrid: CTAs [0, hy_nvls_ctas) take the switch, the rest run the ring
-  unsigned long long hy_split;                      // hybrid: elements [0, hy_split) go through the switch, the rest down the ring
-  int cta_base, cta_count;                          // hybrid: this body runs on CTAs [cta_base, cta_base + cta_count) of the launch
-                                                    //   (cta_count == 0: the whole grid). Barrier rows stay indexed by blockIdx.x.
   const char* send_ptr;                             // LL: this rank's buffers as plain device pointers (peers never touch them,
   char* recv_ptr;                                   //     so they need not live in the heap); 16-byte aligned
 };
@@ -276,9 +272,9 @@ __device__ __forceinline__ void combine_range(unsigned long long lo, unsigned lo
 // the tail elements after the last full 16-byte vector, done by one thread per element in CTA 0
 template <int D, int O>
 __device__ __forceinline__ void combine_tail(unsigned long long first_elem, unsigned long long count, const char* const* src, int nsrc,
-                                             char* const* dst, int ndst, bool first_cta = (blockIdx.x == 0)) {
+                                             char* const* dst, int ndst) {
   constexpr int E = VecOps<D, O>::kElem;
-  if (!first_cta) return;
+  if (blockIdx.x != 0) return;
   for (unsigned long long e = first_elem + threadIdx.x; e < count; e += blockDim.x) {
     typename TailAcc<D>::type acc = tail_load<D>(src[0] + e * E);
     for (int s = 1; s < nsrc; ++s) acc = tail_apply<D, O>(acc, tail_load<D>(src[s] + e * E));
@@ -414,8 +410,7 @@ __device__ void ring_body(const CollArgs& A) {
   const CollCtx& c = A.ctx;
   constexpr int E = V::kElem;
   constexpr int VPT = 8;  // vectors per thread per sub-block
-  const int P = c.nranks, r = c.rank, root = A.root;
-  const int G = A.cta_count ? A.cta_count : (int)gridDim.x, b = (int)blockIdx.x - A.cta_base;
+  const int P = c.nranks, r = c.rank, root = A.root, G = (int)gridDim.x, b = (int)blockIdx.x;
   const int pos = (r - root + P) % P;
   const int pred = pos + 1 < P ? (root + pos + 1) % P : -1;  // sends to me
   const int succ = pos > 0 ? (root + pos - 1) % P : -1;      // I send to it
@@ -495,7 +490,7 @@ __device__ void ring_body(const CollArgs& A) {
   }
   // the (< 16 byte) tail: the root pulls it, folding in chain order and — like the vector path, whose partials travel as
   // bf16 — rounding bf16 after every hop
-  if (pos == 0 && nvec * (16 / E) < A.count && b == 0) {
+  if (pos == 0 && nvec * (16 / E) < A.count && blockIdx.x == 0) {
     for (unsigned long long e = nvec * (16 / E) + threadIdx.x; e < A.count; e += blockDim.x) {
       typename TailAcc<D>::type acc = tail_load<D>(c.heap[(root + P - 1) % P] + po.send[(root + P - 1) % P] + e * E);
       for (int q = 1; q < P; ++q) {
@@ -623,10 +618,9 @@ __device__ void nvls_body(const CollArgs& A) {
       char* mdst = c.mc + A.recv_off;
       char* rdst = A.root < 0 ? nullptr : c.heap[A.root] + po.recv[A.root];
       char* ldst = c.heap[c.rank] + A.recv_off;
-      const unsigned int Gn = A.cta_count ? (unsigned int)A.cta_count : gridDim.x, bn = blockIdx.x - (unsigned int)A.cta_base;
-      const unsigned long long stride = (unsigned long long)Gn * blockDim.x;
+      const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
       constexpr int U = UNR;
-      for (unsigned long long base = lo + (unsigned long long)bn * blockDim.x + threadIdx.x; base < hi; base += stride * U) {
+      for (unsigned long long base = lo + (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; base < hi; base += stride * U) {
         uint32_t w[U][4];
 #pragma unroll
         for (int u = 0; u < U; ++u) {
@@ -655,7 +649,7 @@ __device__ void nvls_body(const CollArgs& A) {
           else dst[0] = ldst;
         }
         __syncthreads();
-        combine_tail<D, O>(nunit * B / E, A.count, src, P, dst, ndst, blockIdx.x == (unsigned int)A.cta_base);
+        combine_tail<D, O>(nunit * B / E, A.count, src, P, dst, ndst);
       }
     }
   }
@@ -666,41 +660,13 @@ __device__ void nvls_body(const CollArgs& A) {
 #include "coll_experimental.cuh"  // LL small-message path
 namespace b2r {
 
-// ------------------------------------------------------------------------------------------------ hybrid: switch + ring at once (reduce to root)
-// Two ceilings were measured on 8 GPUs for reduce-to-root: the switch's in-network reduction delivers ~520 GB/s of reduced output
-// whatever the launch shape (every GPU's egress is then 1.125 x 520 = 585 GB/s of a ~770 GB/s port), and the store-forwarding ring
-// is bound by its per-step latency, not by the port. They use different resources, so one launch runs BOTH: the first CTAs take the
-// head of the message through the switch (nvls_body), the others send the tail down the chain (ring_body). Each role sees its own
-// sub-message (offsets and count adjusted), its own CTA numbering (cta_base / cta_count) and, because barrier rows are indexed by the
-// absolute CTA, its own flags. Reduce only; the sub-vector tail rides with the ring part.
-template <int D, int O, int UNR>
-__device__ void hybrid_body(const CollArgs& A) {
-  constexpr int E = VecOps<D, O>::kElem;
-  CollArgs B = A;
-  if ((int)blockIdx.x < A.hy_nvls_ctas) {
-    B.count = A.hy_split;
-    B.cta_base = 0;
-    B.cta_count = A.hy_nvls_ctas;
-    B.sub_blocks = 0;  // equal slices for all ranks
-    nvls_body<D, O, UNR>(B);
-  } else {
-    const unsigned long long off = A.hy_split * (unsigned long long)E;
-    B.send_off += off;
-    B.recv_off += off;
-    B.count = A.count - A.hy_split;
-    B.cta_base = A.hy_nvls_ctas;
-    B.cta_count = (int)gridDim.x - A.hy_nvls_ctas;
-    ring_body<D, O, UNR>(B);
-  }
-}
-
 // barrier-only kernel body
 __device__ inline void barrier_body(const CollArgs& A) {
   __shared__ PeerOffsets po;
   start_barrier(A, &po);
 }
 
-enum CollKind { kCollOneshot = 1, kCollTwoshot = 2, kCollTree = 3, kCollNvls = 4, kCollBarrier = 5, kCollPush = 6, kCollRing = 7, kCollLL = 8, kCollHybrid = 9 };
+enum CollKind { kCollOneshot = 1, kCollTwoshot = 2, kCollTree = 3, kCollNvls = 4, kCollBarrier = 5, kCollPush = 6, kCollRing = 7, kCollLL = 8 };
 
 template <int D, int O, int KIND, int UNR>
 __global__ void __launch_bounds__(512) coll_kernel(const __grid_constant__ CollLaunch L) {
@@ -712,7 +678,6 @@ __global__ void __launch_bounds__(512) coll_kernel(const __grid_constant__ CollL
   else if (KIND == kCollPush) push_body<D, O, UNR>(A);
   else if (KIND == kCollRing) ring_body<D, O, UNR>(A);
   else if (KIND == kCollLL) ll_body<D, O>(A);
-  else if (KIND == kCollHybrid) hybrid_body<D, O, UNR>(A);
   else barrier_body(A);
 }
 

@@ -55,7 +55,7 @@ def main():
                         fails += 1
                         print(f"[rank {rank}] allreduce MISMATCH dtype={dtype} count={count} op={op} algo={algo}", flush=True)
                     root = (count + rank * 0) % world
-                    for ralgo in ([algo, "ring"] if algo == "twoshot" else ([algo, "hybrid"] if algo == "nvls" else [algo])):
+                    for ralgo in ([algo, "ring"] if algo == "twoshot" else [algo]):
                         red = comm.reduce(x, op, root=root, algo=ralgo)
                         comm.check()
                         if rank == root:
