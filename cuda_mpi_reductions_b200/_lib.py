@@ -20,11 +20,11 @@ OK, ERR_INVALID, ERR_CUDA, ERR_UNSUPPORTED, ERR_TIMEOUT, ERR_NOMEM, ERR_SYSTEM, 
 INT32, FLOAT32, FLOAT64, BFLOAT16 = range(4)
 SUM, MIN, MAX = range(3)
 VARIANT_AUTO, VARIANT_LDG128, VARIANT_LDG256, VARIANT_TMA = range(4)
-ALGO_AUTO, ALGO_ONESHOT, ALGO_TWOSHOT, ALGO_TREE, ALGO_NVLS, ALGO_PUSH, ALGO_RING, ALGO_LL = range(8)
+ALGO_AUTO, ALGO_ONESHOT, ALGO_TWOSHOT, ALGO_TREE, ALGO_NVLS, ALGO_PUSH, ALGO_RING, ALGO_LL, ALGO_POSTED = range(9)
 
 OPS = {"sum": SUM, "min": MIN, "max": MAX, "SUM": SUM, "MIN": MIN, "MAX": MAX}
 ALGOS = {"auto": ALGO_AUTO, "oneshot": ALGO_ONESHOT, "twoshot": ALGO_TWOSHOT, "tree": ALGO_TREE, "nvls": ALGO_NVLS, "push": ALGO_PUSH, "ring": ALGO_RING,
-         "ll": ALGO_LL}  # "ll": experimental small-message path, never chosen by "auto"
+         "ll": ALGO_LL, "posted": ALGO_POSTED}  # "ll": small messages; "posted": mid-size reduce-to-root (stage locally, root reduces via the switch)
 VARIANTS = {"auto": VARIANT_AUTO, "ldg128": VARIANT_LDG128, "ldg256": VARIANT_LDG256, "tma": VARIANT_TMA}
 DTYPE_SIZE = {INT32: 4, FLOAT32: 4, FLOAT64: 8, BFLOAT16: 2}
 
@@ -117,6 +117,7 @@ def _declare(lib: C.CDLL) -> None:
         sig("b2r_ll_max_bytes", [i], u64)
     if hasattr(lib, "b2r_comm_ll_max_bytes"):
         sig("b2r_comm_ll_max_bytes", [vp, C.POINTER(C.c_uint64)])
+    sig("b2r_comm_posted_max_bytes", [vp, C.POINTER(C.c_uint64)])
     if hasattr(lib, "b2r_refresh_env"):
         sig("b2r_refresh_env", [], None)
 

@@ -219,9 +219,16 @@ class Communicator:
 
     @property
     def ll_max_bytes(self) -> int:
-        """Largest message (bytes per rank) the experimental LL path accepts on this communicator."""
+        """Largest message (bytes per rank) the LL path accepts on this communicator."""
         n = C.c_uint64()
         _lib.check(_lib.LIB.b2r_comm_ll_max_bytes(self._h, C.byref(n)), "b2r_comm_ll_max_bytes")
+        return int(n.value)
+
+    @property
+    def posted_max_bytes(self) -> int:
+        """Largest message (bytes per rank) algo="posted" accepts on this communicator (half the work region, at most 64 MiB)."""
+        n = C.c_uint64()
+        _lib.check(_lib.LIB.b2r_comm_posted_max_bytes(self._h, C.byref(n)), "b2r_comm_posted_max_bytes")
         return int(n.value)
 
     def select_algo(self, nbytes: int, dtype: torch.dtype, op="sum", allreduce: bool = True) -> str:

@@ -58,8 +58,11 @@ typedef enum {
   B2R_ALGO_NVLS = 4,    /* multimem.ld_reduce / multimem.st through the NVSwitch (needs multicast) */
   B2R_ALGO_PUSH = 5,    /* scatter by P2P stores into the owners' staging, reduce locally, push the result: no remote loads */
   B2R_ALGO_RING = 6,    /* reduce only: store-forwarding chain that ends at the root (one neighbour per GPU, no remote loads) */
-  B2R_ALGO_LL = 7       /* EXPERIMENTAL small-message path (see b2r_ll_max_bytes): flag-in-data packets pushed into the consumers'
-                           slots, no barrier at either end; never chosen by AUTO, not yet validated on hardware */
+  B2R_ALGO_LL = 7,      /* small messages (see b2r_comm_ll_max_bytes): flag-in-data packets pushed into the consumers' slots, no
+                           barrier at either end; AUTO's choice up to 64 KiB (allreduce) / 256 KiB (reduce) */
+  B2R_ALGO_POSTED = 8   /* reduce only, mid-size messages (see b2r_comm_posted_max_bytes): every rank stages its contribution in
+                           its own heap and returns, the root reduces the staged copies through the switch; no barrier at either end,
+                           fp min/max travel as order-preserving integer keys */
 } b2r_algo_t;
 
 typedef struct {
@@ -275,9 +278,12 @@ b2r_status_t b2r_barrier(b2r_comm_t comm, void* stream);
 
 /* Largest message (bytes per rank) the LL path accepts on a communicator of `nranks` ranks; 0 if nranks is out of range. */
 uint64_t b2r_ll_max_bytes(int nranks);
-/* The same for an existing communicator: larger when it was created with B2R_LL_BIG_MB=n (n MiB of extra LL slots behind
- * the user heap, 16 CTAs, up to 256 KiB per rank; experimental like the rest of the LL path). */
+/* The same for an existing communicator: larger with the 64-CTA LL region behind the user heap (B2R_LL_BIG_MB at creation,
+ * default 16 MiB; 0 = none). */
 b2r_status_t b2r_comm_ll_max_bytes(b2r_comm_t comm, uint64_t* bytes);
+/* Largest message (bytes per rank) B2R_ALGO_POSTED accepts on this communicator: half the work region (B2R_WORK_MB at
+ * creation), at most 64 MiB. */
+b2r_status_t b2r_comm_posted_max_bytes(b2r_comm_t comm, uint64_t* bytes);
 
 /* Which algorithm AUTO resolves to (pure function; used by tests and the harness). */
 b2r_algo_t b2r_select_algo(int is_allreduce, uint64_t bytes, b2r_dtype_t dtype, b2r_op_t op, int nranks,

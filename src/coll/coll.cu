@@ -50,6 +50,7 @@ CollKernel pick_kind(int kind) {
     case kCollPush: return coll_kernel<D, O, kCollPush, 4>;
     case kCollRing: return coll_kernel<D, O, kCollRing, 4>;
     case kCollLL: return coll_kernel<D, O, kCollLL, 4>;
+    case kCollPosted: return coll_kernel<D, O, kCollPosted, 4>;
   }
   return nullptr;
 }
@@ -138,6 +139,10 @@ uint64_t ll_limit(const b2r_comm* c) {
   return std::max(small, big);
 }
 
+// Posted reduce: one staging slot per call parity at the start of the work region; a message must fit one slot.
+uint64_t posted_slot_bytes(const b2r_comm* c) { return std::min<uint64_t>(c->work_bytes / 2, kPostedMaxSlotBytes) & ~(uint64_t)255; }
+int posted_ctas(const b2r_comm* c) { return std::max(1, c->max_ctas > 0 ? std::min(c->max_ctas, kPostedCtas) : kPostedCtas); }
+
 // Which LL instance carries a message: the one-CTA instance in the control region up to kLLSmallMaxBytes (or whenever there is
 // no large region), the 64-CTA instance behind the user heap beyond.
 bool ll_use_small(const b2r_comm* c, uint64_t bytes) {
@@ -161,14 +166,20 @@ constexpr int kAutoPushReduceMB = 0, kAutoPushAllreduceMB = 0, kAutoPushReduceNv
 // LL: 4 GPUs, 64-CTA instance: reduce 8.2-10.5 us up to 256 KiB (NCCL 7.8-11.0, NVLS 12.5-15.7); allreduce ahead of NVLS up to
 // 128 KiB at 4 GPUs — every consumer receives (P-1) x 2 x the message, so the crossover is set lower for all sizes of P
 constexpr int kAutoLLAllreduceBytes = 65536, kAutoLLReduceBytes = 262144;
+// posted reduce (stage locally, return; the root reduces the staged copies through the switch): from the LL crossover up to
+// these sizes. Two limits: pairs the switch reduces natively (the alternative is the barrier-framed NVLS kernel), and fp32 / fp64
+// min and max, which travel as integer keys (the alternative is two-shot by peer loads).
+constexpr int kAutoPostedMaxBytes = 8 << 20, kAutoPostedKeyMaxBytes = 64 << 20;
 
-b2r_algo_t select_algo_cached(int is_allreduce, uint64_t bytes, b2r_dtype_t dtype, b2r_op_t op, int nranks, int has_multicast, uint64_t ll_max) {
+b2r_algo_t select_algo_cached(int is_allreduce, uint64_t bytes, b2r_dtype_t dtype, b2r_op_t op, int nranks, int has_multicast, uint64_t ll_max,
+                              uint64_t posted_max) {
   if (nranks <= 1) return B2R_ALGO_ONESHOT;
   const int forced = B2R_ENV_INT("B2R_ALGO", 0);
   // a forced LL only applies to messages that fit its slots; everything else falls through to the normal choice
   if (forced == B2R_ALGO_LL && nranks <= B2R_MAX_RANKS && bytes <= ll_max) return B2R_ALGO_LL;
   if (forced >= B2R_ALGO_ONESHOT && forced <= B2R_ALGO_PUSH) return (b2r_algo_t)forced;
   if (forced == B2R_ALGO_RING && !is_allreduce) return B2R_ALGO_RING;
+  if (forced == B2R_ALGO_POSTED && !is_allreduce && bytes <= posted_max) return B2R_ALGO_POSTED;
   // LL crossovers: allreduce B2R_AUTO_LL_MAX_BYTES, reduce-to-root B2R_AUTO_LL_REDUCE_MAX_BYTES (only the root consumes, so the
   // 64-CTA instance stays ahead of the barrier-framed kernels for longer); both capped by what the communicator's slots hold
   const uint64_t auto_ll = (uint64_t)std::max(0, is_allreduce ? B2R_ENV_INT("B2R_AUTO_LL_MAX_BYTES", kAutoLLAllreduceBytes)
@@ -178,7 +189,8 @@ b2r_algo_t select_algo_cached(int is_allreduce, uint64_t bytes, b2r_dtype_t dtyp
   if (ll_cut && nranks <= B2R_MAX_RANKS && bytes <= std::min<uint64_t>(ll_cut, ll_max)) return B2R_ALGO_LL;
   const uint64_t auto_ring = (uint64_t)std::max(0, B2R_ENV_INT("B2R_AUTO_RING_MIN_MB", 0));
   if (auto_ring && !is_allreduce && nranks > 2 && bytes >= (auto_ring << 20)) return B2R_ALGO_RING;
-  const bool nvls_ok = has_multicast && nranks >= 4 && nvls_supported(dtype, op) && !B2R_ENV_INT("B2R_DISABLE_NVLS", 0);
+  const bool switch_ok = has_multicast && nranks >= 4 && !B2R_ENV_INT("B2R_DISABLE_NVLS", 0);
+  const bool nvls_ok = switch_ok && nvls_supported(dtype, op);
   // push (stores only, two hops): from how many MiB on it replaces the pulls / the switch; 0 = never. Three crossovers:
   //   B2R_AUTO_PUSH_REDUCE_MB        reduce-to-root of a (dtype, op) without a multimem form (fp32 / fp64 min and max)
   //   B2R_AUTO_PUSH_ALLREDUCE_MB     allreduce of the same
@@ -188,6 +200,12 @@ b2r_algo_t select_algo_cached(int is_allreduce, uint64_t bytes, b2r_dtype_t dtyp
                                                       : (is_allreduce ? B2R_ENV_INT("B2R_AUTO_PUSH_ALLREDUCE_MB", kAutoPushAllreduceMB)
                                                                       : B2R_ENV_INT("B2R_AUTO_PUSH_REDUCE_MB", kAutoPushReduceMB)));
     if (mb && bytes >= (mb << 20)) return B2R_ALGO_PUSH;
+  }
+  // posted: mid-size reduce-to-root wherever the switch can do the reading (natively, or on integer keys for fp min / max)
+  if (switch_ok && !is_allreduce) {
+    const uint64_t cut = (uint64_t)std::max(0, nvls_ok ? B2R_ENV_INT("B2R_AUTO_POSTED_MAX_BYTES", kAutoPostedMaxBytes)
+                                                       : B2R_ENV_INT("B2R_AUTO_POSTED_KEY_MAX_BYTES", kAutoPostedKeyMaxBytes));
+    if (bytes <= std::min(cut, posted_max)) return B2R_ALGO_POSTED;
   }
   // 32-bit integers through the switch collapse for reduce-to-root at >= 1 GiB on 8 GPUs (2.1-4.8 ms at 1 GiB where fp32 needs 2.0 and
   // 256 MiB is on par: 4-byte multimem loads AND 4-byte stores to the root); the store-forwarding ring is steady there (2.04 ms)
@@ -252,14 +270,21 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
   B2R_CHECK(apply_data_flavour(c0->device));
 
   const uint64_t total_bytes = count * esz;
-  if (algo == B2R_ALGO_AUTO) algo = select_algo_cached(is_all ? 1 : 0, total_bytes, dtype, op, P, c0->has_mc ? 1 : 0, ll_limit(c0));
+  if (algo == B2R_ALGO_AUTO) algo = select_algo_cached(is_all ? 1 : 0, total_bytes, dtype, op, P, c0->has_mc ? 1 : 0, ll_limit(c0), posted_slot_bytes(c0));
   if (algo == B2R_ALGO_NVLS) {
     if (!c0->has_mc) return fail(B2R_ERR_UNSUPPORTED, "NVLS requested but this communicator has no multicast mapping");
     if (!nvls_supported(dtype, op)) return fail(B2R_ERR_UNSUPPORTED, "NVLS has no %s %s instruction", b2r_dtype_name(dtype), b2r_op_name(op));
   }
   int kind = algo == B2R_ALGO_ONESHOT ? kCollOneshot : algo == B2R_ALGO_TWOSHOT ? kCollTwoshot : algo == B2R_ALGO_TREE ? kCollTree
-             : algo == B2R_ALGO_PUSH ? kCollPush : algo == B2R_ALGO_RING ? kCollRing : algo == B2R_ALGO_LL ? kCollLL : kCollNvls;
+             : algo == B2R_ALGO_PUSH ? kCollPush : algo == B2R_ALGO_RING ? kCollRing : algo == B2R_ALGO_LL ? kCollLL
+             : algo == B2R_ALGO_POSTED ? kCollPosted : kCollNvls;
   if (kind == kCollRing && is_all) return fail(B2R_ERR_UNSUPPORTED, "the ring algorithm implements reduce-to-root only");
+  if (kind == kCollPosted) {
+    if (is_all) return fail(B2R_ERR_UNSUPPORTED, "the posted algorithm implements reduce-to-root only");
+    if (((total_bytes + 15) & ~15ull) > posted_slot_bytes(c0))
+      return fail(B2R_ERR_INVALID, "the posted path carries at most %llu bytes per rank on this communicator (got %llu)",
+                  (unsigned long long)posted_slot_bytes(c0), (unsigned long long)total_bytes);
+  }
   if (kind == kCollLL) {
     // LL never touches a peer's send/recv buffer: any device pointer works, nothing is chunked, and only a buffer that is not
     // 16-byte aligned is bounced through this rank's own staging (a purely local decision: ranks need not agree on it)
@@ -277,6 +302,7 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
   const uint64_t work_elems = (c0->work_bytes / 16) * 16 / esz;
   uint64_t chunk = chunk_elems;
   if (kind == kCollTree) chunk = std::min<uint64_t>(chunk_elems, work_elems);
+  if (kind == kCollPosted) chunk = count;  // like LL: peers' buffers are never touched, nothing is staged per chunk
   if (kind == kCollPush) {
     const uint64_t W = is_all ? P : P - 1;
     const uint64_t slice_bytes = std::min<uint64_t>(c0->work_bytes / P - 64, (uint64_t)kPushChunkCap * 512 * 4 * 16 - 64);
@@ -294,9 +320,12 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
       const bool gets_result = is_all || c->rank == root;
       const char* send = (const char*)rc[i].send + first * esz;
       char* recv = rc[i].recv ? (char*)rc[i].recv + first * esz : nullptr;
-      if (kind == kCollLL) {
+      if (kind == kCollLL || kind == kCollPosted) {
         CollArgs& A = L.a[n == 1 ? 0 : c->rank];
         A.ctx = c->ctx;
+        if (((uintptr_t)send % 16) || (gets_result && ((uintptr_t)recv % 16)))
+          B2R_REQUIRE(bytes <= c->stage_bytes, "rank %d: a buffer that is not 16-byte aligned is bounced through staging (%zu bytes), got %llu",
+                      c->rank, c->stage_bytes, (unsigned long long)bytes);
         if ((uintptr_t)send % 16) {
           B2R_CUDA_CHECK(cudaMemcpyAsync(c->stage_send(), send, bytes, cudaMemcpyDeviceToDevice, rc[i].stream));
           send = c->stage_send();
@@ -310,6 +339,14 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
         A.count = cnt;
         A.epoch = c->epoch;
         A.root = is_all ? -1 : root;
+        if (kind == kCollPosted) {
+          A.seq = ++c->posted_seq;
+          A.work_off = (unsigned long long)(c->stage_work() - c->my_heap());
+          A.recv_off = posted_slot_bytes(c);                 // slot stride (the recv buffer travels as recv_ptr)
+          A.ring_depth = c->posted_root[A.seq & 1u];         // whose acknowledgement frees this parity's slot
+          c->posted_root[A.seq & 1u] = root;
+          continue;
+        }
         // small instance (control region, one CTA) when the message fits it, else the large one; each has its own slots,
         // acknowledgement words and consecutive call numbering (the slot parity and the n-2 rule depend on it)
         LLLayout lay;
@@ -368,6 +405,10 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
         // vectors per thread, same partition
         threads = n > 1 ? kLLBigThreads / 2 : kLLBigThreads;
       }
+    }
+    if (kind == kCollPosted) {  // the same grid in every call (fixed partition, see coll_posted.cuh); loopback: half-size CTAs
+      ctas = posted_ctas(c0);
+      threads = n > 1 ? kPostedThreads / 2 : kPostedThreads;
     }
     if (kind == kCollRing) {
       // staging ring in the work region: depth x ctas steps of sub_blocks x (threads x 8) vectors; at least 2 deep.
@@ -564,6 +605,12 @@ b2r_status_t b2r_comm_ll_max_bytes(b2r_comm_t comm, uint64_t* bytes) {
   return B2R_OK;
 }
 
+b2r_status_t b2r_comm_posted_max_bytes(b2r_comm_t comm, uint64_t* bytes) {
+  B2R_REQUIRE(comm && bytes, "b2r_comm_posted_max_bytes: NULL argument");
+  *bytes = comm->nranks >= 2 ? posted_slot_bytes(comm) : 0;
+  return B2R_OK;
+}
+
 uint64_t b2r_ll_max_bytes(int nranks) { return (nranks >= 2 && nranks <= B2R_MAX_RANKS) ? (uint64_t)ll_max_msg_bytes(nranks) : 0; }
 
 // Size thresholds measured on 8x B200 (profiles/collectives_8gpu.md). One-shot costs one NVLink round trip but every
@@ -575,7 +622,8 @@ b2r_algo_t b2r_select_algo(int is_allreduce, uint64_t bytes, b2r_dtype_t dtype, 
   const uint64_t ll_max = nranks <= B2R_MAX_RANKS
                               ? std::max<uint64_t>(ll_max_msg_bytes(std::max(nranks, 1)), ll_big_max_msg_bytes((size_t)16 << 20, std::max(nranks, 1)))
                               : 0;
-  return select_algo_cached(is_allreduce, bytes, dtype, op, nranks, has_multicast, ll_max);
+  // and with the default work region (B2R_WORK_MB unset = 320): posted slots of 64 MiB
+  return select_algo_cached(is_allreduce, bytes, dtype, op, nranks, has_multicast, ll_max, kPostedMaxSlotBytes);
 }
 
 b2r_status_t b2r_reduce_ex(const void* sendbuf, void* recvbuf, uint64_t count, b2r_dtype_t dtype, b2r_op_t op, int root, b2r_comm_t comm,

@@ -658,6 +658,7 @@ __device__ void nvls_body(const CollArgs& A) {
 
 }  // namespace b2r
 #include "coll_experimental.cuh"  // LL small-message path
+#include "coll_posted.cuh"        // posted reduce-to-root (stage locally, the root reduces through the switch)
 namespace b2r {
 
 // barrier-only kernel body
@@ -666,7 +667,7 @@ __device__ inline void barrier_body(const CollArgs& A) {
   start_barrier(A, &po);
 }
 
-enum CollKind { kCollOneshot = 1, kCollTwoshot = 2, kCollTree = 3, kCollNvls = 4, kCollBarrier = 5, kCollPush = 6, kCollRing = 7, kCollLL = 8 };
+enum CollKind { kCollOneshot = 1, kCollTwoshot = 2, kCollTree = 3, kCollNvls = 4, kCollBarrier = 5, kCollPush = 6, kCollRing = 7, kCollLL = 8, kCollPosted = 9 };
 
 template <int D, int O, int KIND, int UNR>
 __global__ void __launch_bounds__(512) coll_kernel(const __grid_constant__ CollLaunch L) {
@@ -678,6 +679,7 @@ __global__ void __launch_bounds__(512) coll_kernel(const __grid_constant__ CollL
   else if (KIND == kCollPush) push_body<D, O, UNR>(A);
   else if (KIND == kCollRing) ring_body<D, O, UNR>(A);
   else if (KIND == kCollLL) ll_body<D, O>(A);
+  else if (KIND == kCollPosted) posted_body<D, O>(A);
   else barrier_body(A);
 }
 

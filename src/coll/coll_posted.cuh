@@ -1,0 +1,203 @@
+// coll_posted.cuh — "posted" reduce-to-root: every rank stages its contribution in its OWN heap and returns; the root alone
+// reduces the staged copies through the switch.
+//
+// Why it exists. Between 512 KiB and a few MiB the barrier-framed switch reduction (nvls_body) is all overhead: two NVLink
+// round trips frame 2-20 us of data movement, and every call of a back-to-back series pays them again because no rank may
+// leave before the root has read its send buffer (8 GPUs, 1 MiB: 18 us where NCCL's pipelined chain needs 12.6). Here the
+// send buffer is copied (16-byte vectors, local HBM/L2 traffic only) into one of two staging slots of the work region, a
+// per-CTA ready word is released to the root, and the rank is done: its next call — posted or not — can start while the root is
+// still working on this one. The root waits for the ready words (in a series they arrived long ago), issues
+// multimem.ld_reduce over the slot (one instruction fetches and combines all P copies), writes its recv buffer locally and
+// acknowledges. No barrier at either end; the only cross-GPU wait on a non-root rank is for the acknowledgement of the call
+// two back (same slot), which is off the critical path.
+//   partition : FIXED. gridDim.x is the same in every call on every rank; chunk k (kPostedChunkVecs vectors) belongs to CTA
+//               k % gridDim.x. So slot bytes are only ever touched by the same CTA index, and one word per (CTA, source) /
+//               (root, CTA) carries the whole protocol, with call numbers that only grow.
+//   roots     : may change from call to call; the acknowledgement a rank waits for is that of the root of the call two back
+//               (the host passes it in), and words are indexed by the acknowledging rank.
+//   fp min/max: have no multimem form, but signed-integer min/max do, and IEEE floats order like sign-magnitude integers.
+//               Staging maps every value to the two's-complement integer of the same rank (k = b ^ ((b >> 31) & 0x7fff...)), the
+//               switch reduces integers, the root maps back (the map is its own inverse). -0 orders below +0; a NaN orders
+//               beyond the infinity of its sign (the host restatement and the pull kernels use a < b ? a : b).
+//   no switch : (loopback groups, or a (dtype, op) pair without any multimem form) the root folds the staged copies in rank
+//               order with peer loads — same protocol, same bits as the one-shot kernel; this is what the loopback tests
+//               exercise. AUTO only ever picks the algorithm where the switch does the reading.
+#pragma once
+
+namespace b2r {
+
+__device__ __forceinline__ unsigned int* posted_ready(char* heap, int cta, int src) {
+  return (unsigned int*)(heap + kOffPostedReady) + (size_t)cta * B2R_MAX_RANKS + src;
+}
+__device__ __forceinline__ unsigned int* posted_ack(char* heap, int acker, int cta) {
+  return (unsigned int*)(heap + kOffPostedAck) + (size_t)acker * kPostedCtas + cta;
+}
+
+// 64-bit signed min/max through the switch (the keys of fp64 min/max)
+template <int O>
+struct NvlsS64 {
+  __device__ __forceinline__ static void ld_reduce(const char* p, uint32_t* w) {
+    long long d;
+    if (O == B2R_MIN) asm volatile("multimem.ld_reduce.relaxed.sys.global.min.s64 %0, [%1];" : "=l"(d) : "l"(p) : "memory");
+    else asm volatile("multimem.ld_reduce.relaxed.sys.global.max.s64 %0, [%1];" : "=l"(d) : "l"(p) : "memory");
+    w[0] = (uint32_t)((unsigned long long)d & 0xffffffffull);
+    w[1] = (uint32_t)((unsigned long long)d >> 32);
+  }
+};
+
+// How a (dtype, op) pair travels: which multimem form reads the slots, and what staging does to the bits.
+template <int D, int O>
+struct PostedCodec {
+  static constexpr bool kSwitch = Nvls<D, O>::kSupported;
+  static constexpr int kBytes = Nvls<D, O>::kBytes;
+  __device__ __forceinline__ static void ld_reduce(const char* p, uint32_t* w) { Nvls<D, O>::ld_reduce(p, w); }
+  __device__ __forceinline__ static V16 code(const V16& v) { return v; }
+};
+template <int O>
+struct PostedKey32 {
+  static constexpr bool kSwitch = true;
+  static constexpr int kBytes = 4;
+  __device__ __forceinline__ static void ld_reduce(const char* p, uint32_t* w) { Nvls<B2R_INT32, O>::ld_reduce(p, w); }
+  __device__ __forceinline__ static V16 code(const V16& v) {
+    V16 k;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) k.w[j] = v.w[j] ^ ((uint32_t)((int32_t)v.w[j] >> 31) & 0x7fffffffu);
+    return k;
+  }
+};
+template <int O>
+struct PostedKey64 {
+  static constexpr bool kSwitch = true;
+  static constexpr int kBytes = 8;
+  __device__ __forceinline__ static void ld_reduce(const char* p, uint32_t* w) { NvlsS64<O>::ld_reduce(p, w); }
+  __device__ __forceinline__ static V16 code(const V16& v) {  // little endian: w[1], w[3] hold the sign and the high bits
+    V16 k;
+#pragma unroll
+    for (int j = 0; j < 4; j += 2) {
+      const uint32_t m = (uint32_t)((int32_t)v.w[j + 1] >> 31);
+      k.w[j] = v.w[j] ^ m;
+      k.w[j + 1] = v.w[j + 1] ^ (m & 0x7fffffffu);
+    }
+    return k;
+  }
+};
+template <> struct PostedCodec<B2R_FLOAT32, B2R_MIN> : PostedKey32<B2R_MIN> {};
+template <> struct PostedCodec<B2R_FLOAT32, B2R_MAX> : PostedKey32<B2R_MAX> {};
+template <> struct PostedCodec<B2R_FLOAT64, B2R_MIN> : PostedKey64<B2R_MIN> {};
+template <> struct PostedCodec<B2R_FLOAT64, B2R_MAX> : PostedKey64<B2R_MAX> {};
+
+template <int D, int O>
+__device__ void posted_body(const CollArgs& A) {
+  using V = VecOps<D, O>;
+  using C = PostedCodec<D, O>;
+  const CollCtx& c = A.ctx;
+  constexpr int E = V::kElem;
+  constexpr int U = 4;  // vectors in flight per thread
+  const int P = c.nranks, me = c.rank, root = A.root, b = (int)blockIdx.x, G = (int)gridDim.x;
+  const unsigned int seq = A.seq;
+  const int prev_root = A.ring_depth;  // root of posted call seq-2, the last reader of this parity's slots (-1: none yet)
+  const unsigned long long bytes = A.count * E;
+  const unsigned long long nfull = bytes / 16;
+  const unsigned int tail_bytes = (unsigned int)(bytes % 16);
+  const unsigned long long nvec = nfull + (tail_bytes ? 1ull : 0ull);
+  const unsigned long long slot_off = A.work_off + (unsigned long long)(seq & 1u) * A.recv_off;  // recv_off carries the slot stride
+  const bool via_switch = C::kSwitch && c.mc != nullptr;
+  const bool has_work = (unsigned long long)b * kPostedChunkVecs < nvec;
+  char* my_slot = c.heap[me] + slot_off;
+
+  auto load_send = [&](unsigned long long v) -> V16 {
+    return v < nfull ? ld_peer(A.send_ptr + v * 16) : ll_load_tail<E>(A.send_ptr + nfull * 16, tail_bytes);
+  };
+
+  if (threadIdx.x == 0) fault_delay(c);
+  // ---- stage my contribution (a root that pulls reads its own send buffer directly and stages nothing)
+  if (has_work && (me != root || via_switch)) {
+    if (prev_root >= 0 && prev_root != me) {
+      if (threadIdx.x == 0) wait_flag_ge_relaxed(posted_ack(c.heap[me], prev_root, b), seq - 2, c);
+      __syncthreads();
+    }
+    for (unsigned long long k = (unsigned long long)b; k * kPostedChunkVecs < nvec; k += (unsigned long long)G) {
+      const unsigned long long v0 = k * kPostedChunkVecs, vend = min(nvec, v0 + kPostedChunkVecs);
+      for (unsigned long long base = v0 + threadIdx.x; base < vend; base += (unsigned long long)blockDim.x * U) {
+        V16 x[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const unsigned long long v = base + (unsigned long long)u * blockDim.x;
+          if (v < vend) x[u] = load_send(v);
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const unsigned long long v = base + (unsigned long long)u * blockDim.x;
+          if (v < vend) st_peer(my_slot + v * 16, via_switch ? C::code(x[u]) : x[u]);
+        }
+      }
+    }
+    __syncthreads();
+    if (me != root) {
+      if (threadIdx.x == 0 && !c.fault_skip_signal) st_release_sys(posted_ready(c.heap[root], b, me), seq);
+    } else {
+      // my own staged copy is read back through the switch: make it visible at system scope first
+      if (threadIdx.x == 0) __threadfence_system();
+      __syncthreads();
+    }
+  }
+  if (me != root) return;
+
+  // ---- the root: wait for every peer's CTA b, reduce the chunks of CTA b, acknowledge
+  if (has_work) {
+    if (threadIdx.x < (unsigned)P && (int)threadIdx.x != me) wait_flag_ge(posted_ready(c.heap[me], b, (int)threadIdx.x), seq, c);
+    __syncthreads();
+    const char* mslot = via_switch ? c.mc + slot_off : nullptr;
+    for (unsigned long long k = (unsigned long long)b; k * kPostedChunkVecs < nvec; k += (unsigned long long)G) {
+      const unsigned long long v0 = k * kPostedChunkVecs, vend = min(nvec, v0 + kPostedChunkVecs);
+      for (unsigned long long base = v0 + threadIdx.x; base < vend; base += (unsigned long long)blockDim.x * U) {
+        V16 r[U];
+        if (via_switch) {
+#pragma unroll
+          for (int u = 0; u < U; ++u) {
+            const unsigned long long v = base + (unsigned long long)u * blockDim.x;
+            if (v < vend) {
+#pragma unroll
+              for (int j = 0; j < 16 / C::kBytes; ++j) C::ld_reduce(mslot + v * 16 + j * C::kBytes, &r[u].w[j * C::kBytes / 4]);
+            }
+          }
+#pragma unroll
+          for (int u = 0; u < U; ++u) r[u] = C::code(r[u]);
+        } else {
+          typename V::Acc acc[U];
+          for (int p = 0; p < P; ++p) {
+            V16 x[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+              const unsigned long long v = base + (unsigned long long)u * blockDim.x;
+              if (v < vend) x[u] = p == me ? load_send(v) : ld_peer(c.heap[p] + slot_off + v * 16);
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+              if (p == 0) acc[u] = V::unpack(x[u]);
+              else V::combine(acc[u], x[u]);
+            }
+          }
+#pragma unroll
+          for (int u = 0; u < U; ++u) r[u] = V::pack(acc[u]);
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const unsigned long long v = base + (unsigned long long)u * blockDim.x;
+          if (v < vend) {
+            if (v < nfull) st_peer(A.recv_ptr + v * 16, r[u]);
+            else ll_store_tail<E>(A.recv_ptr + nfull * 16, r[u], tail_bytes);
+          }
+        }
+      }
+    }
+  }
+  // Every CTA acknowledges every call, with or without work, so that "ack[root][b] >= n" always means "the root's CTA b is past
+  // call n". Relaxed: the loads above have returned (their values were stored), and a release here would make the root wait
+  // for a system-wide fence on its exit path (measured at 4-9 us for the scalar-sharded kernel's acknowledgement).
+  __syncthreads();
+  if (threadIdx.x < (unsigned)P && (int)threadIdx.x != me && !c.fault_skip_signal)
+    st_relaxed_sys_u32(posted_ack(c.heap[threadIdx.x], me, b), seq);
+}
+
+}  // namespace b2r

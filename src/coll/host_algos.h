@@ -27,7 +27,8 @@ void host_collective_rank(const HostRankView& v, uint64_t count, b2r_dtype_t dty
                           b2r_algo_t algo, Barrier&& barrier) {
   const int P = v.nranks, r = v.rank;
   barrier();  // everybody's send buffer is ready
-  if (algo == B2R_ALGO_ONESHOT || algo == B2R_ALGO_AUTO || algo == B2R_ALGO_NVLS || algo == B2R_ALGO_LL) {  // LL: same rank-order fold
+  if (algo == B2R_ALGO_ONESHOT || algo == B2R_ALGO_AUTO || algo == B2R_ALGO_NVLS || algo == B2R_ALGO_LL ||
+      algo == B2R_ALGO_POSTED) {  // LL, posted: same rank-order fold
     if (root < 0 || root == r) combine_many_host(v.recv[r], v.send, P, 0, count, dtype, op);
     barrier();
   } else if (algo == B2R_ALGO_TWOSHOT || algo == B2R_ALGO_PUSH) {  // same slices, same rank-order combine

@@ -17,6 +17,8 @@ constexpr size_t kOffError = 40 * 1024;              // uint32 error word (devic
 constexpr size_t kOffCtx = 44 * 1024;                // device copy of CollCtx (read by the scalar-sharded kernels)
 constexpr size_t kOffMeta = 64 * 1024;               // PeerMeta meta[kCollMaxCtas][B2R_MAX_RANKS]: per-collective buffer offsets
 constexpr size_t kOffPushData = 128 * 1024;          // uint32 [kCollMaxCtas][B2R_MAX_RANKS]: push algorithm, "block of round i from rank s has landed"
+constexpr size_t kOffPostedReady = 144 * 1024;       // uint32 [kPostedCtas][B2R_MAX_RANKS]: posted reduce, at the root: "CTA b of rank s has staged call n"
+constexpr size_t kOffPostedAck = 148 * 1024;         // uint32 [B2R_MAX_RANKS][kPostedCtas]: posted reduce, "CTA b of root r has consumed call n"
 constexpr size_t kOffPushAck = 160 * 1024;           // uint32 [kCollMaxCtas][B2R_MAX_RANKS]: push algorithm, "worker w has consumed round i"
 constexpr size_t kOffLLAck = 176 * 1024;             // uint32 [B2R_MAX_RANKS]: LL path, "rank r has finished LL call n" (flow control)
 constexpr size_t kOffLL = 192 * 1024;                // LL path: packet slots [call parity][source rank][ll_slot_bytes(P)], up to kOffPushFlags
@@ -49,6 +51,16 @@ constexpr size_t ll_big_max_msg_bytes(size_t region_bytes, int nranks) {
   return ll_big_slot_bytes(region_bytes, nranks) / 2 < (size_t)kLLBigCtas * kLLBigVecPerCta * 16 ? ll_big_slot_bytes(region_bytes, nranks) / 2
                                                                                                    : (size_t)kLLBigCtas * kLLBigVecPerCta * 16;
 }
+
+// Posted reduce (coll_posted.cuh): a FIXED grid of kPostedCtas CTAs per rank; chunk k of kPostedChunkVecs 16-byte vectors belongs to
+// CTA k % grid on every rank in every call, so one ready word per (CTA, source) and one acknowledgement word per (root, CTA) is
+// all the flow control it needs. The two staging slots (call parity) live at the start of the work region.
+constexpr int kPostedCtas = 64;
+constexpr int kPostedThreads = 256;
+constexpr unsigned int kPostedChunkVecs = 1024;  // 16 KiB
+constexpr size_t kPostedMaxSlotBytes = (size_t)64 << 20;
+static_assert(kOffPostedReady + (size_t)kPostedCtas * B2R_MAX_RANKS * 4 <= kOffPostedAck, "posted: ready words overlap the ack words");
+static_assert(kOffPostedAck + (size_t)B2R_MAX_RANKS * kPostedCtas * 4 <= kOffPushAck, "posted: ack words overlap the ring's");
 
 // Where rank r keeps its send/recv buffer for the collective in flight, published to every peer inside the start
 // barrier, so buffers do NOT have to sit at the same heap offset on every rank (only the NVLS path needs that).

@@ -55,7 +55,7 @@ def main():
                         fails += 1
                         print(f"[rank {rank}] allreduce MISMATCH dtype={dtype} count={count} op={op} algo={algo}", flush=True)
                     root = (count + rank * 0) % world
-                    for ralgo in ([algo, "ring"] if algo == "twoshot" else [algo]):
+                    for ralgo in ([algo, "ring", "posted"] if algo == "twoshot" else [algo]):
                         red = comm.reduce(x, op, root=root, algo=ralgo)
                         comm.check()
                         if rank == root:
@@ -142,6 +142,34 @@ def main():
                 if not torch.equal(out.cpu(), want) or (rank == i % world and not torch.equal(red.cpu(), want)):
                     fails += 1
                     print(f"[rank {rank}] LL MISMATCH dtype={dtype} count={count}", flush=True)
+    # posted reduce on real NVLink: a back-to-back series with rotating roots, changing sizes and no host synchronisation (slot
+    # parity, acknowledgements of the root two calls back), interleaved with barrier-framed algorithms that use the same work
+    # region; with a switch the staged copies are read by multimem (fp32 min travels as integer keys: exact)
+    for dtype, op in ((torch.int32, "sum"), (torch.float32, "min"), (torch.float64, "max"), (torch.bfloat16, "max")):
+        sizes = (7, 70_001, (1 << 20) + 5, (3 << 20) + 1)
+        xs, wants = {}, {}
+        for n in sizes:
+            xs[n] = b2r.fill_device(n, dtype, seed=600 + rank + n % 97, mode="signed")
+            gathered = [torch.empty_like(xs[n]) for _ in range(world)]
+            dist.all_gather(gathered, xs[n])
+            w = gathered[0].cpu().clone()
+            for g in gathered[1:]:
+                if dtype == torch.bfloat16:
+                    w = torch.maximum(w.float(), g.cpu().float()).bfloat16()
+                else:
+                    b2r.combine_oracle(w, g.cpu(), op)
+            wants[n] = w
+        pending = []
+        for i in range(60):
+            n = sizes[(i * 3) % len(sizes)]
+            root = (i * 5 + i // 7) % world
+            algo = "posted" if i % 10 != 9 else ("push", "tree", "twoshot")[(i // 10) % 3]
+            pending.append((n, root, comm.reduce(xs[n], op, root=root, algo=algo), algo))
+        comm.check()
+        for n, root, red, algo in pending:
+            if rank == root and not torch.equal(red.cpu(), wants[n]):
+                fails += 1
+                print(f"[rank {rank}] posted series MISMATCH dtype={dtype} op={op} count={n} algo={algo}", flush=True)
     # symmetric zero-copy + in place + stress of small back-to-back collectives
     s = comm.symm_empty(1 << 20, torch.float32)
     s.fill_(float(rank + 1))

@@ -75,7 +75,14 @@ def test_algo_selection_is_pure_and_sensible():
     assert sel(1, 65536, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_LL
     assert sel(1, 65540, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS
     assert sel(0, 262144, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_LL
-    assert sel(0, 262148, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS
+    assert sel(0, 262148, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_POSTED  # mid-size reduce-to-root: stage and return, the root reduces via the switch
+    assert sel(0, 1 << 20, _lib.INT32, _lib.MAX, 4, 1) == _lib.ALGO_POSTED
+    assert sel(0, 1 << 20, _lib.FLOAT32, _lib.MIN, 8, 1) == _lib.ALGO_POSTED   # fp min/max travel as integer keys
+    assert sel(0, 1 << 20, _lib.FLOAT32, _lib.MIN, 8, 0) == _lib.ALGO_TWOSHOT  # no switch, no posted
+    assert sel(0, 1 << 20, _lib.FLOAT32, _lib.SUM, 2, 1) == _lib.ALGO_ONESHOT
+    assert sel(1, 1 << 20, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS     # reduce-to-root only
+    assert sel(0, 1 << 28, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS
+    assert sel(0, 1 << 30, _lib.FLOAT32, _lib.MIN, 8, 1) == _lib.ALGO_TWOSHOT
     assert sel(1, 1 << 30, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS
     assert sel(1, 1 << 30, _lib.FLOAT32, _lib.SUM, 2, 1) == _lib.ALGO_TWOSHOT  # NVLS loses at 2 GPUs
     assert sel(1, 1 << 30, _lib.FLOAT32, _lib.SUM, 8, 0) == _lib.ALGO_TWOSHOT
@@ -117,10 +124,15 @@ def test_ll_path_limits_and_selection(monkeypatch):
     monkeypatch.delenv("B2R_ALGO", raising=False)
     for all_ in (0, 1):
         assert sel(all_, 4, _lib.INT32, _lib.SUM, 8, 1) == _lib.ALGO_LL and sel(all_, 65536, _lib.INT32, _lib.SUM, 8, 1) == _lib.ALGO_LL
-        assert sel(all_, 262148, _lib.INT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS
+        assert sel(all_, 262148, _lib.INT32, _lib.SUM, 8, 1) == (_lib.ALGO_NVLS if all_ else _lib.ALGO_POSTED)
     monkeypatch.setenv("B2R_AUTO_LL_MAX_BYTES", "0")          # allreduce crossover
     monkeypatch.setenv("B2R_AUTO_LL_REDUCE_MAX_BYTES", "0")   # reduce-to-root crossover
     assert sel(0, 4, _lib.INT32, _lib.SUM, 8, 0) == _lib.ALGO_ONESHOT and sel(1, 4, _lib.INT32, _lib.SUM, 8, 0) == _lib.ALGO_ONESHOT
+    monkeypatch.setenv("B2R_AUTO_POSTED_MAX_BYTES", "0")
+    monkeypatch.setenv("B2R_AUTO_POSTED_KEY_MAX_BYTES", "0")
+    assert sel(0, 1 << 20, _lib.INT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS and sel(0, 1 << 20, _lib.FLOAT64, _lib.MAX, 8, 1) == _lib.ALGO_TWOSHOT
+    monkeypatch.delenv("B2R_AUTO_POSTED_MAX_BYTES")
+    monkeypatch.delenv("B2R_AUTO_POSTED_KEY_MAX_BYTES")
     monkeypatch.delenv("B2R_AUTO_LL_MAX_BYTES")
     monkeypatch.delenv("B2R_AUTO_LL_REDUCE_MAX_BYTES")
     monkeypatch.setenv("B2R_ALGO", str(_lib.ALGO_LL))
@@ -165,17 +177,20 @@ def test_auto_crossover_switches(monkeypatch):
     """B2R_AUTO_LL_MAX_BYTES (default 8192), B2R_AUTO_RING_MIN_MB and the three B2R_AUTO_PUSH_*_MB crossovers move AUTO's
     crossovers without a rebuild; unsetting them restores the measured defaults."""
     sel = _lib.LIB.b2r_select_algo
-    for var in ("B2R_ALGO", "B2R_AUTO_LL_MAX_BYTES", "B2R_AUTO_LL_REDUCE_MAX_BYTES", "B2R_AUTO_RING_MIN_MB", "B2R_AUTO_PUSH_REDUCE_MB", "B2R_AUTO_PUSH_ALLREDUCE_MB", "B2R_AUTO_PUSH_REDUCE_NVLS_MB"):
+    for var in ("B2R_ALGO", "B2R_AUTO_POSTED_MAX_BYTES", "B2R_AUTO_POSTED_KEY_MAX_BYTES", "B2R_AUTO_LL_MAX_BYTES", "B2R_AUTO_LL_REDUCE_MAX_BYTES", "B2R_AUTO_RING_MIN_MB", "B2R_AUTO_PUSH_REDUCE_MB", "B2R_AUTO_PUSH_ALLREDUCE_MB", "B2R_AUTO_PUSH_REDUCE_NVLS_MB"):
         monkeypatch.delenv(var, raising=False)
     before = [sel(a, n, d, _lib.SUM, p, 1) for a in (0, 1) for n in (64, 8192, 1 << 20, 1 << 28) for d in (_lib.INT32, _lib.FLOAT32) for p in (2, 8)]
     assert sel(0, 8192, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_LL
     assert sel(1, 64, _lib.INT32, _lib.MIN, 2, 0) == _lib.ALGO_LL
     monkeypatch.setenv("B2R_AUTO_LL_REDUCE_MAX_BYTES", "8192")
-    assert sel(0, 8193, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS
+    assert sel(0, 8193, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_POSTED  # what takes over from LL for reduce-to-root
     assert sel(1, 8193, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_LL     # the allreduce crossover is a separate knob
     monkeypatch.setenv("B2R_AUTO_LL_REDUCE_MAX_BYTES", str(1 << 30))  # capped by what the slots hold (256 KiB)
     assert sel(0, 262144, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_LL
-    assert sel(0, 262148, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS
+    assert sel(0, 262148, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_POSTED
+    monkeypatch.setenv("B2R_AUTO_POSTED_MAX_BYTES", str(1 << 20))
+    assert sel(0, 1 << 20, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_POSTED and sel(0, (1 << 20) + 4, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS
+    monkeypatch.delenv("B2R_AUTO_POSTED_MAX_BYTES")
     monkeypatch.delenv("B2R_AUTO_LL_REDUCE_MAX_BYTES")
     monkeypatch.setenv("B2R_AUTO_RING_MIN_MB", "64")
     assert sel(0, 64 << 20, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_RING
@@ -188,14 +203,15 @@ def test_auto_crossover_switches(monkeypatch):
     monkeypatch.setenv("B2R_AUTO_PUSH_ALLREDUCE_MB", "128")
     monkeypatch.setenv("B2R_AUTO_PUSH_REDUCE_NVLS_MB", "0")
     assert sel(0, 32 << 20, _lib.FLOAT64, _lib.MIN, 8, 1) == _lib.ALGO_PUSH      # no multimem form: stores instead of pulls
-    assert sel(0, (32 << 20) - 8, _lib.FLOAT64, _lib.MIN, 8, 1) == _lib.ALGO_TWOSHOT
+    assert sel(0, (32 << 20) - 8, _lib.FLOAT64, _lib.MIN, 8, 1) == _lib.ALGO_POSTED
+    assert sel(0, (32 << 20) - 8, _lib.FLOAT64, _lib.MIN, 8, 0) == _lib.ALGO_TWOSHOT
     assert sel(1, 32 << 20, _lib.FLOAT32, _lib.MAX, 8, 1) == _lib.ALGO_TWOSHOT   # allreduce has its own crossover
     assert sel(1, 128 << 20, _lib.FLOAT32, _lib.MAX, 8, 1) == _lib.ALGO_PUSH
     assert sel(0, 1 << 30, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS       # the switch keeps what it can do ...
     monkeypatch.setenv("B2R_AUTO_PUSH_REDUCE_NVLS_MB", "64")
     assert sel(0, 1 << 30, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_PUSH       # ... unless told otherwise: reduce-to-root only
     assert sel(0, 1 << 28, _lib.INT32, _lib.MAX, 8, 1) == _lib.ALGO_PUSH
-    assert sel(0, 1 << 20, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS
+    assert sel(0, 1 << 20, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_POSTED
     assert sel(1, 1 << 30, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS
     assert sel(0, 1 << 30, _lib.FLOAT32, _lib.SUM, 2, 1) == _lib.ALGO_ONESHOT    # two GPUs: one worker would do all the work
     for var in ("B2R_AUTO_PUSH_REDUCE_MB", "B2R_AUTO_PUSH_ALLREDUCE_MB", "B2R_AUTO_PUSH_REDUCE_NVLS_MB"):
