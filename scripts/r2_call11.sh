@@ -1,28 +1,10 @@
 #!/bin/bash
-# round 2, call 11 (N GPUs): LL 64-CTA instance and ring stagger vs the rest, then the record sweeps at N GPUs
+# posted reduce on N real GPUs: the multimem path checked (torchrun worker, short form), then posted vs the previous choice vs NCCL
 N=${1:-4}
 O=gpurun_out/r2c11_$N; mkdir -p $O
-timeout 300 python -m pytest tests/test_experimental_gpu.py -m gpu -x -q 2>&1 | tail -3
-C="--gpus=$N --max-bytes=1073741824 --check --check-max=16777216 --timeout-ms=4000 --iters=20"
-timeout 300 bin/bench_collective $C --plan=scripts/plans/plan_ll_ring.txt --csv=$O/plan.csv > $O/plan.txt 2> $O/plan.err; tail -3 $O/plan.txt; grep -c "VERIFY FAILED\|skipped or failed" $O/plan.txt
-timeout 100 bin/nccl_bench --gpus=$N --sweep --types=FLOAT,INT --ops=SUM --colls=reduce,allreduce --min-bytes=1024 --max-bytes=262144 --factor=2 --csv=$O/nccl.csv > $O/nccl_small.txt 2>/dev/null
-timeout 100 bin/nccl_bench --gpus=$N --sweep --types=FLOAT --ops=SUM,MIN --colls=reduce,allreduce --min-bytes=67108864 --max-bytes=1073741824 --factor=4 --csv=$O/nccl.csv > $O/nccl_big.txt 2>/dev/null
-[ "$2" = "plan-only" ] && exit 0
-timeout 200 bin/bench_collective --gpus=$N --check --jsonl=$O/refloop.jsonl --raw=$O/refloop_b2r.txt > $O/refloop_b2r.log 2>&1; tail -3 $O/refloop_b2r.log
-timeout 300 bin/bench_collective --gpus=$N --algo=tree --retries=2 --check --raw=$O/refloop_tree.txt > $O/refloop_tree.log 2>&1; tail -2 $O/refloop_tree.log
-timeout 200 bin/nccl_bench --gpus=$N --jsonl=$O/refloop.jsonl > $O/refloop_nccl.txt 2>/dev/null; tail -2 $O/refloop_nccl.txt
-timeout 400 bin/bench_collective --gpus=$N --sweep --types=INT,DOUBLE,BF16 --colls=reduce,allreduce --algos=auto --min-bytes=1024 --max-bytes=4294967296 --factor=4 --nvlink --check --csv=$O/sweep.csv --jsonl=$O/sweep.jsonl > $O/sweep_b2r.txt 2>&1; tail -3 $O/sweep_b2r.txt
-timeout 400 bin/nccl_bench --gpus=$N --sweep --types=INT,DOUBLE,BF16 --colls=reduce,allreduce --min-bytes=1024 --max-bytes=4294967296 --factor=4 --csv=$O/sweep.csv --jsonl=$O/sweep.jsonl > $O/sweep_nccl.txt 2>/dev/null; tail -2 $O/sweep_nccl.txt
-timeout 200 bin/b2r_mpirun -np $N bin/reduce_gpu_mpi > $O/reduce_gpu_mpi.txt 2>&1; tail -2 $O/reduce_gpu_mpi.txt
 T="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1"
-timeout 500 $T --master-port 29602 bench.py --gpus $N --steps 20 --warmup 5 > $O/bench.json 2> $O/bench.err; tail -c 300 $O/bench.err
-python - <<PY
-import json
-try:
-    d=json.loads([l for l in open('$O/bench.json') if l.startswith('{')][-1])
-    print('value',round(d['value']),'ms/step',d['ms_per_step'],'e2e',round(d['e2e']['value'],1))
-    for r in d.get('collectives',{}).get('rows',[]): print(r['coll'],r['dtype'],r['bytes'],r['algo'],round(r['b2r_busbw_gbs'],1),round(r['nccl_busbw_gbs'],1),round(r['ratio'],3),r['b2r_check'],r['nccl_check'])
-    print(d.get('collectives',{}).get('error'), {k:v for k,v in d.get('config4',{}).items() if k in ('b2r_gbs','library_gbs','ratio','self_check','error')})
-except Exception as e: print('parse failed',e)
-PY
-timeout 400 python -m pytest tests/test_multigpu.py -m gpu -x -q 2>&1 | tail -4
+B2R_DIST_ONLY=posted timeout 200 $T --master-port 29611 tests/dist_worker.py > $O/dist_posted.txt 2>&1; grep -h "DIST_WORKER\|MISMATCH\|multicast" $O/dist_posted.txt | head -n 12
+timeout 300 bin/bench_collective --gpus=$N --plan=scripts/plans/plan_posted.txt --check --iters=10 --csv=$O/plan.csv > $O/plan.txt 2> $O/plan.err; grep -c "Q\." $O/plan.txt; grep -h "FAILED\|clocks" $O/plan.txt | head -n 6
+timeout 200 bin/nccl_bench --gpus=$N --sweep --types=FLOAT,INT,DOUBLE,BF16 --ops=SUM --colls=reduce --min-bytes=524288 --max-bytes=67108864 --factor=2 --csv=$O/nccl.csv > $O/nccl_sum.txt 2>/dev/null
+timeout 200 bin/nccl_bench --gpus=$N --sweep --types=FLOAT,DOUBLE,INT --ops=MIN,MAX --colls=reduce --min-bytes=524288 --max-bytes=67108864 --factor=2 --csv=$O/nccl.csv > $O/nccl_minmax.txt 2>/dev/null
+python scripts/posted_table.py $O/plan.csv $O/nccl.csv

@@ -16,6 +16,49 @@ from cuda_mpi_reductions_b200.parallel import Communicator  # noqa: E402
 ATOL = {torch.int32: 0, torch.float32: 1e-5, torch.float64: 1e-13, torch.bfloat16: 2.0**-7}
 
 
+def check_posted(comm, rank, world, fails):
+    # posted reduce on real NVLink: a back-to-back series with rotating roots, changing sizes and no host synchronisation (slot
+    # parity, acknowledgements of the root two calls back), interleaved with barrier-framed algorithms that use the same work
+    # region; with a switch the staged copies are read by multimem (fp32 min travels as integer keys: exact)
+    for dtype, op in ((torch.int32, "sum"), (torch.float32, "min"), (torch.float64, "max"), (torch.bfloat16, "max")):
+        sizes = (7, 70_001, (1 << 20) + 5, (3 << 20) + 1)
+        xs, wants = {}, {}
+        for n in sizes:
+            xs[n] = b2r.fill_device(n, dtype, seed=600 + rank + n % 97, mode="signed")
+            gathered = [torch.empty_like(xs[n]) for _ in range(world)]
+            dist.all_gather(gathered, xs[n])
+            w = gathered[0].cpu().clone()
+            for g in gathered[1:]:
+                if dtype == torch.bfloat16:
+                    w = torch.maximum(w.float(), g.cpu().float()).bfloat16()
+                else:
+                    b2r.combine_oracle(w, g.cpu(), op)
+            wants[n] = w
+        pending = []
+        for i in range(60):
+            n = sizes[(i * 3) % len(sizes)]
+            root = (i * 5 + i // 7) % world
+            algo = "posted" if i % 10 != 9 else ("push", "tree", "twoshot")[(i // 10) % 3]
+            pending.append((n, root, comm.reduce(xs[n], op, root=root, algo=algo), algo))
+        comm.check()
+        for n, root, red, algo in pending:
+            if rank == root and not torch.equal(red.cpu(), wants[n]):
+                fails[0] += 1
+                print(f"[rank {rank}] posted series MISMATCH dtype={dtype} op={op} count={n} algo={algo}", flush=True)
+
+
+def finish(comm, dev, rank, fails):
+    comm.barrier()
+    comm.check()
+    t = torch.tensor([fails], device=dev)
+    dist.all_reduce(t)
+    comm.close()
+    dist.destroy_process_group()
+    if rank == 0:
+        print("DIST_WORKER " + ("PASSED" if t.item() == 0 else f"FAILED ({t.item()} mismatches)"), flush=True)
+    sys.exit(0 if t.item() == 0 else 1)
+
+
 def main():
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ.get("LOCAL_RANK", os.environ["RANK"]))
     torch.cuda.set_device(local)
@@ -27,6 +70,10 @@ def main():
         print(f"world={world} multicast={comm.has_multicast}", flush=True)
     algos = ["oneshot", "twoshot", "tree", "push"] + (["nvls"] if comm.has_multicast else [])
     fails = 0
+    if os.environ.get("B2R_DIST_ONLY") == "posted":  # the short form used while tuning: only the posted series
+        box = [0]
+        check_posted(comm, rank, world, box)
+        finish(comm, dev, rank, box[0])
     for dtype in (torch.int32, torch.float32, torch.float64, torch.bfloat16):
         for count in (1, 1000, 65537, (1 << 22) + 3):
             x = b2r.fill_device(count, dtype, seed=100 + rank, mode="signed")
@@ -142,34 +189,9 @@ def main():
                 if not torch.equal(out.cpu(), want) or (rank == i % world and not torch.equal(red.cpu(), want)):
                     fails += 1
                     print(f"[rank {rank}] LL MISMATCH dtype={dtype} count={count}", flush=True)
-    # posted reduce on real NVLink: a back-to-back series with rotating roots, changing sizes and no host synchronisation (slot
-    # parity, acknowledgements of the root two calls back), interleaved with barrier-framed algorithms that use the same work
-    # region; with a switch the staged copies are read by multimem (fp32 min travels as integer keys: exact)
-    for dtype, op in ((torch.int32, "sum"), (torch.float32, "min"), (torch.float64, "max"), (torch.bfloat16, "max")):
-        sizes = (7, 70_001, (1 << 20) + 5, (3 << 20) + 1)
-        xs, wants = {}, {}
-        for n in sizes:
-            xs[n] = b2r.fill_device(n, dtype, seed=600 + rank + n % 97, mode="signed")
-            gathered = [torch.empty_like(xs[n]) for _ in range(world)]
-            dist.all_gather(gathered, xs[n])
-            w = gathered[0].cpu().clone()
-            for g in gathered[1:]:
-                if dtype == torch.bfloat16:
-                    w = torch.maximum(w.float(), g.cpu().float()).bfloat16()
-                else:
-                    b2r.combine_oracle(w, g.cpu(), op)
-            wants[n] = w
-        pending = []
-        for i in range(60):
-            n = sizes[(i * 3) % len(sizes)]
-            root = (i * 5 + i // 7) % world
-            algo = "posted" if i % 10 != 9 else ("push", "tree", "twoshot")[(i // 10) % 3]
-            pending.append((n, root, comm.reduce(xs[n], op, root=root, algo=algo), algo))
-        comm.check()
-        for n, root, red, algo in pending:
-            if rank == root and not torch.equal(red.cpu(), wants[n]):
-                fails += 1
-                print(f"[rank {rank}] posted series MISMATCH dtype={dtype} op={op} count={n} algo={algo}", flush=True)
+    fails_box = [0]
+    check_posted(comm, rank, world, fails_box)
+    fails += fails_box[0]
     # symmetric zero-copy + in place + stress of small back-to-back collectives
     s = comm.symm_empty(1 << 20, torch.float32)
     s.fill_(float(rank + 1))
@@ -179,15 +201,7 @@ def main():
     if not bool((s == world).all()):
         fails += 1
         print(f"[rank {rank}] in-place symmetric stress MISMATCH", flush=True)
-    comm.barrier()
-    comm.check()
-    t = torch.tensor([fails], device=dev)
-    dist.all_reduce(t)
-    comm.close()
-    dist.destroy_process_group()
-    if rank == 0:
-        print("DIST_WORKER " + ("PASSED" if t.item() == 0 else f"FAILED ({t.item()} mismatches)"), flush=True)
-    sys.exit(0 if t.item() == 0 else 1)
+    finish(comm, dev, rank, fails)
 
 
 if __name__ == "__main__":
