@@ -141,7 +141,13 @@ uint64_t ll_limit(const b2r_comm* c) {
 
 // Posted reduce: one staging slot per call parity at the start of the work region; a message must fit one slot.
 uint64_t posted_slot_bytes(const b2r_comm* c) { return std::min<uint64_t>(c->work_bytes / 2, kPostedMaxSlotBytes) & ~(uint64_t)255; }
-int posted_ctas(const b2r_comm* c) { return std::max(1, c->max_ctas > 0 ? std::min(c->max_ctas, kPostedCtas) : kPostedCtas); }
+// The grid of the posted path is a property of the communicator (chunk ownership depends on it): kPostedCtas, fewer if the
+// communicator caps CTAs; a loopback group runs all its virtual ranks in one cooperative launch, one CTA per SM in total.
+int posted_ctas(const b2r_comm* c) {
+  int g = c->max_ctas > 0 ? std::min(c->max_ctas, kPostedCtas) : kPostedCtas;
+  if (c->mode == kModeLoopback && c->nranks > 1) g = std::min(g, c->sm_count / c->nranks);
+  return std::max(1, g);
+}
 
 // Which LL instance carries a message: the one-CTA instance in the control region up to kLLSmallMaxBytes (or whenever there is
 // no large region), the 64-CTA instance behind the user heap beyond.

@@ -109,6 +109,15 @@ __device__ void posted_body(const CollArgs& A) {
     return v < nfull ? ld_peer(A.send_ptr + v * 16) : ll_load_tail<E>(A.send_ptr + nfull * 16, tail_bytes);
   };
 
+  // Work of CTA b: chunks b, b+G, b+2G, ...; a thread handles vector j of a chunk (j = threadIdx.x when the CTA has
+  // kPostedChunkVecs threads) and keeps the same vector of U consecutive owned chunks in flight.
+  const unsigned long long nchunks = (nvec + kPostedChunkVecs - 1) / kPostedChunkVecs;
+  auto vec_of = [&](unsigned long long k0, int u, unsigned int j) -> unsigned long long {  // ~0 = nothing there
+    const unsigned long long k = k0 + (unsigned long long)u * G;
+    const unsigned long long v = k * kPostedChunkVecs + j;
+    return (k < nchunks && v < nvec) ? v : ~0ull;
+  };
+
   if (threadIdx.x == 0) fault_delay(c);
   // ---- stage my contribution (a root that pulls reads its own send buffer directly and stages nothing)
   if (has_work && (me != root || via_switch)) {
@@ -116,19 +125,18 @@ __device__ void posted_body(const CollArgs& A) {
       if (threadIdx.x == 0) wait_flag_ge_relaxed(posted_ack(c.heap[me], prev_root, b), seq - 2, c);
       __syncthreads();
     }
-    for (unsigned long long k = (unsigned long long)b; k * kPostedChunkVecs < nvec; k += (unsigned long long)G) {
-      const unsigned long long v0 = k * kPostedChunkVecs, vend = min(nvec, v0 + kPostedChunkVecs);
-      for (unsigned long long base = v0 + threadIdx.x; base < vend; base += (unsigned long long)blockDim.x * U) {
+    for (unsigned long long k0 = (unsigned long long)b; k0 < nchunks; k0 += (unsigned long long)G * U) {
+      for (unsigned int j = threadIdx.x; j < kPostedChunkVecs; j += blockDim.x) {
         V16 x[U];
 #pragma unroll
         for (int u = 0; u < U; ++u) {
-          const unsigned long long v = base + (unsigned long long)u * blockDim.x;
-          if (v < vend) x[u] = load_send(v);
+          const unsigned long long v = vec_of(k0, u, j);
+          if (v != ~0ull) x[u] = load_send(v);
         }
 #pragma unroll
         for (int u = 0; u < U; ++u) {
-          const unsigned long long v = base + (unsigned long long)u * blockDim.x;
-          if (v < vend) st_peer(my_slot + v * 16, via_switch ? C::code(x[u]) : x[u]);
+          const unsigned long long v = vec_of(k0, u, j);
+          if (v != ~0ull) st_peer(my_slot + v * 16, via_switch ? C::code(x[u]) : x[u]);
         }
       }
     }
@@ -148,17 +156,16 @@ __device__ void posted_body(const CollArgs& A) {
     if (threadIdx.x < (unsigned)P && (int)threadIdx.x != me) wait_flag_ge(posted_ready(c.heap[me], b, (int)threadIdx.x), seq, c);
     __syncthreads();
     const char* mslot = via_switch ? c.mc + slot_off : nullptr;
-    for (unsigned long long k = (unsigned long long)b; k * kPostedChunkVecs < nvec; k += (unsigned long long)G) {
-      const unsigned long long v0 = k * kPostedChunkVecs, vend = min(nvec, v0 + kPostedChunkVecs);
-      for (unsigned long long base = v0 + threadIdx.x; base < vend; base += (unsigned long long)blockDim.x * U) {
+    for (unsigned long long k0 = (unsigned long long)b; k0 < nchunks; k0 += (unsigned long long)G * U) {
+      for (unsigned int j = threadIdx.x; j < kPostedChunkVecs; j += blockDim.x) {
         V16 r[U];
         if (via_switch) {
 #pragma unroll
           for (int u = 0; u < U; ++u) {
-            const unsigned long long v = base + (unsigned long long)u * blockDim.x;
-            if (v < vend) {
+            const unsigned long long v = vec_of(k0, u, j);
+            if (v != ~0ull) {
 #pragma unroll
-              for (int j = 0; j < 16 / C::kBytes; ++j) C::ld_reduce(mslot + v * 16 + j * C::kBytes, &r[u].w[j * C::kBytes / 4]);
+              for (int q = 0; q < 16 / C::kBytes; ++q) C::ld_reduce(mslot + v * 16 + q * C::kBytes, &r[u].w[q * C::kBytes / 4]);
             }
           }
 #pragma unroll
@@ -169,8 +176,8 @@ __device__ void posted_body(const CollArgs& A) {
             V16 x[U];
 #pragma unroll
             for (int u = 0; u < U; ++u) {
-              const unsigned long long v = base + (unsigned long long)u * blockDim.x;
-              if (v < vend) x[u] = p == me ? load_send(v) : ld_peer(c.heap[p] + slot_off + v * 16);
+              const unsigned long long v = vec_of(k0, u, j);
+              if (v != ~0ull) x[u] = p == me ? load_send(v) : ld_peer(c.heap[p] + slot_off + v * 16);
             }
 #pragma unroll
             for (int u = 0; u < U; ++u) {
@@ -183,8 +190,8 @@ __device__ void posted_body(const CollArgs& A) {
         }
 #pragma unroll
         for (int u = 0; u < U; ++u) {
-          const unsigned long long v = base + (unsigned long long)u * blockDim.x;
-          if (v < vend) {
+          const unsigned long long v = vec_of(k0, u, j);
+          if (v != ~0ull) {
             if (v < nfull) st_peer(A.recv_ptr + v * 16, r[u]);
             else ll_store_tail<E>(A.recv_ptr + nfull * 16, r[u], tail_bytes);
           }

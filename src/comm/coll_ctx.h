@@ -18,7 +18,7 @@ constexpr size_t kOffCtx = 44 * 1024;                // device copy of CollCtx (
 constexpr size_t kOffMeta = 64 * 1024;               // PeerMeta meta[kCollMaxCtas][B2R_MAX_RANKS]: per-collective buffer offsets
 constexpr size_t kOffPushData = 128 * 1024;          // uint32 [kCollMaxCtas][B2R_MAX_RANKS]: push algorithm, "block of round i from rank s has landed"
 constexpr size_t kOffPostedReady = 144 * 1024;       // uint32 [kPostedCtas][B2R_MAX_RANKS]: posted reduce, at the root: "CTA b of rank s has staged call n"
-constexpr size_t kOffPostedAck = 148 * 1024;         // uint32 [B2R_MAX_RANKS][kPostedCtas]: posted reduce, "CTA b of root r has consumed call n"
+constexpr size_t kOffPostedAck = 152 * 1024;         // uint32 [B2R_MAX_RANKS][kPostedCtas]: posted reduce, "CTA b of root r has consumed call n"
 constexpr size_t kOffPushAck = 160 * 1024;           // uint32 [kCollMaxCtas][B2R_MAX_RANKS]: push algorithm, "worker w has consumed round i"
 constexpr size_t kOffLLAck = 176 * 1024;             // uint32 [B2R_MAX_RANKS]: LL path, "rank r has finished LL call n" (flow control)
 constexpr size_t kOffLL = 192 * 1024;                // LL path: packet slots [call parity][source rank][ll_slot_bytes(P)], up to kOffPushFlags
@@ -55,9 +55,13 @@ constexpr size_t ll_big_max_msg_bytes(size_t region_bytes, int nranks) {
 // Posted reduce (coll_posted.cuh): a FIXED grid of kPostedCtas CTAs per rank; chunk k of kPostedChunkVecs 16-byte vectors belongs to
 // CTA k % grid on every rank in every call, so one ready word per (CTA, source) and one acknowledgement word per (root, CTA) is
 // all the flow control it needs. The two staging slots (call parity) live at the start of the work region.
-constexpr int kPostedCtas = 64;
-constexpr int kPostedThreads = 256;
-constexpr unsigned int kPostedChunkVecs = 1024;  // 16 KiB
+// Geometry, second version. The first (64 CTAs x 256 threads, 16 KiB chunks, four vectors per thread) kept 1 MiB of multimem
+// requests in flight from the root and measured 245 GB/s for the 16-byte forms on 4 GPUs (110 for the 4- and 8-byte forms):
+// latency-bound. Now 128 CTAs x 512 threads; a chunk is one vector per thread (8 KiB), so a 1 MiB message already occupies
+// every CTA, and a thread keeps four chunks in flight.
+constexpr int kPostedCtas = 128;
+constexpr int kPostedThreads = 512;
+constexpr unsigned int kPostedChunkVecs = 512;  // 8 KiB
 constexpr size_t kPostedMaxSlotBytes = (size_t)64 << 20;
 static_assert(kOffPostedReady + (size_t)kPostedCtas * B2R_MAX_RANKS * 4 <= kOffPostedAck, "posted: ready words overlap the ack words");
 static_assert(kOffPostedAck + (size_t)B2R_MAX_RANKS * kPostedCtas * 4 <= kOffPushAck, "posted: ack words overlap the ring's");

@@ -13,8 +13,9 @@ from cuda_mpi_reductions_b200.parallel import Communicator, host_reduce_threads
 pytestmark = [pytest.mark.gpu]
 
 DTYPES = [torch.int32, torch.float32, torch.float64, torch.bfloat16]
-CHUNK_BYTES = 1024 * 16  # kPostedChunkVecs vectors
-GRID = 64                # kPostedCtas
+CHUNK_BYTES = 512 * 16  # kPostedChunkVecs vectors
+GRID = 128              # kPostedCtas on real GPUs; a loopback group of P ranks uses min(128, SMs / P) CTAs per rank, so the
+                        # sizes below cross "every CTA has one chunk" at different points for different P
 
 
 @pytest.fixture(scope="module", params=[2, 3, 8])
