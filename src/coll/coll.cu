@@ -172,10 +172,11 @@ constexpr int kAutoPushReduceMB = 0, kAutoPushAllreduceMB = 0, kAutoPushReduceNv
 // LL: 4 GPUs, 64-CTA instance: reduce 8.2-10.5 us up to 256 KiB (NCCL 7.8-11.0, NVLS 12.5-15.7); allreduce ahead of NVLS up to
 // 128 KiB at 4 GPUs — every consumer receives (P-1) x 2 x the message, so the crossover is set lower for all sizes of P
 constexpr int kAutoLLAllreduceBytes = 65536, kAutoLLReduceBytes = 262144;
-// posted reduce (stage locally, return; the root reduces the staged copies through the switch): from the LL crossover up to
-// these sizes. Two limits: pairs the switch reduces natively (the alternative is the barrier-framed NVLS kernel), and fp32 / fp64
-// min and max, which travel as integer keys (the alternative is two-shot by peer loads).
-constexpr int kAutoPostedMaxBytes = 8 << 20, kAutoPostedKeyMaxBytes = 64 << 20;
+// posted reduce (stage locally, return; the root alone reduces the staged copies through the switch): from the LL crossover up
+// to these sizes. The root's multimem request stream is the limit, so the crossover depends on how many bytes one request moves:
+// 16 (fp32 add, bf16) ~400 GB/s, 8 (fp64 add, fp64 min/max as 64-bit keys) ~215, 4 (int32, fp32 min/max as 32-bit keys) ~120.
+// Measured on 4 GPUs against the barrier-framed NVLS kernel (native forms) and two-shot (keys): profiles/raw/r2_posted/.
+constexpr int kAutoPosted16 = 8 << 20, kAutoPosted8 = 2 << 20, kAutoPosted4 = 1 << 20, kAutoPostedKey8 = 4 << 20, kAutoPostedKey4 = 1 << 20;
 
 b2r_algo_t select_algo_cached(int is_allreduce, uint64_t bytes, b2r_dtype_t dtype, b2r_op_t op, int nranks, int has_multicast, uint64_t ll_max,
                               uint64_t posted_max) {
@@ -209,8 +210,14 @@ b2r_algo_t select_algo_cached(int is_allreduce, uint64_t bytes, b2r_dtype_t dtyp
   }
   // posted: mid-size reduce-to-root wherever the switch can do the reading (natively, or on integer keys for fp min / max)
   if (switch_ok && !is_allreduce) {
-    const uint64_t cut = (uint64_t)std::max(0, nvls_ok ? B2R_ENV_INT("B2R_AUTO_POSTED_MAX_BYTES", kAutoPostedMaxBytes)
-                                                       : B2R_ENV_INT("B2R_AUTO_POSTED_KEY_MAX_BYTES", kAutoPostedKeyMaxBytes));
+    // B2R_AUTO_POSTED_MAX_BYTES / _8 / _4: native forms by bytes per multimem request; B2R_AUTO_POSTED_KEY_MAX_BYTES_8 / _4: fp64 /
+    // fp32 min and max (integer keys); 0 = never
+    int cut_i;
+    if (nvls_ok) cut_i = dtype == B2R_INT32 ? B2R_ENV_INT("B2R_AUTO_POSTED_MAX_BYTES_4", kAutoPosted4)
+                         : dtype == B2R_FLOAT64 ? B2R_ENV_INT("B2R_AUTO_POSTED_MAX_BYTES_8", kAutoPosted8)
+                                                : B2R_ENV_INT("B2R_AUTO_POSTED_MAX_BYTES", kAutoPosted16);
+    else cut_i = dtype == B2R_FLOAT64 ? B2R_ENV_INT("B2R_AUTO_POSTED_KEY_MAX_BYTES_8", kAutoPostedKey8) : B2R_ENV_INT("B2R_AUTO_POSTED_KEY_MAX_BYTES_4", kAutoPostedKey4);
+    const uint64_t cut = (uint64_t)std::max(0, cut_i);
     if (bytes <= std::min(cut, posted_max)) return B2R_ALGO_POSTED;
   }
   // 32-bit integers through the switch collapse for reduce-to-root at >= 1 GiB on 8 GPUs (2.1-4.8 ms at 1 GiB where fp32 needs 2.0 and

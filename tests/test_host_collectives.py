@@ -66,6 +66,10 @@ def test_int_sum_wraps_across_ranks():
     assert (got == want).all()
 
 
+POSTED_KNOBS = ("B2R_AUTO_POSTED_MAX_BYTES", "B2R_AUTO_POSTED_MAX_BYTES_8", "B2R_AUTO_POSTED_MAX_BYTES_4", "B2R_AUTO_POSTED_KEY_MAX_BYTES_8",
+                "B2R_AUTO_POSTED_KEY_MAX_BYTES_4")
+
+
 def test_algo_selection_is_pure_and_sensible():
     sel = _lib.LIB.b2r_select_algo
     # small messages: the LL path (allreduce up to 64 KiB, reduce-to-root up to 256 KiB). Beyond: NVLS whenever the switch can do it (>= 4 GPUs, any dtype/op with a multimem form, int32
@@ -78,6 +82,11 @@ def test_algo_selection_is_pure_and_sensible():
     assert sel(0, 262148, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_POSTED  # mid-size reduce-to-root: stage and return, the root reduces via the switch
     assert sel(0, 1 << 20, _lib.INT32, _lib.MAX, 4, 1) == _lib.ALGO_POSTED
     assert sel(0, 1 << 20, _lib.FLOAT32, _lib.MIN, 8, 1) == _lib.ALGO_POSTED   # fp min/max travel as integer keys
+    # the crossover depends on how many bytes one multimem request moves: 16 (fp32 add, bf16) / 8 (fp64) / 4 (int32, fp32 keys)
+    assert sel(0, 8 << 20, _lib.BFLOAT16, _lib.MAX, 8, 1) == _lib.ALGO_POSTED and sel(0, (8 << 20) + 2, _lib.BFLOAT16, _lib.MAX, 8, 1) == _lib.ALGO_NVLS
+    assert sel(0, 2 << 20, _lib.FLOAT64, _lib.SUM, 8, 1) == _lib.ALGO_POSTED and sel(0, 4 << 20, _lib.FLOAT64, _lib.SUM, 8, 1) == _lib.ALGO_NVLS
+    assert sel(0, 4 << 20, _lib.FLOAT64, _lib.MIN, 8, 1) == _lib.ALGO_POSTED and sel(0, 8 << 20, _lib.FLOAT64, _lib.MIN, 8, 1) == _lib.ALGO_TWOSHOT
+    assert sel(0, 2 << 20, _lib.INT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS and sel(0, 2 << 20, _lib.FLOAT32, _lib.MAX, 8, 1) == _lib.ALGO_TWOSHOT
     assert sel(0, 1 << 20, _lib.FLOAT32, _lib.MIN, 8, 0) == _lib.ALGO_TWOSHOT  # no switch, no posted
     assert sel(0, 1 << 20, _lib.FLOAT32, _lib.SUM, 2, 1) == _lib.ALGO_ONESHOT
     assert sel(1, 1 << 20, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS     # reduce-to-root only
@@ -128,11 +137,12 @@ def test_ll_path_limits_and_selection(monkeypatch):
     monkeypatch.setenv("B2R_AUTO_LL_MAX_BYTES", "0")          # allreduce crossover
     monkeypatch.setenv("B2R_AUTO_LL_REDUCE_MAX_BYTES", "0")   # reduce-to-root crossover
     assert sel(0, 4, _lib.INT32, _lib.SUM, 8, 0) == _lib.ALGO_ONESHOT and sel(1, 4, _lib.INT32, _lib.SUM, 8, 0) == _lib.ALGO_ONESHOT
-    monkeypatch.setenv("B2R_AUTO_POSTED_MAX_BYTES", "0")
-    monkeypatch.setenv("B2R_AUTO_POSTED_KEY_MAX_BYTES", "0")
+    for var in POSTED_KNOBS:
+        monkeypatch.setenv(var, "0")
     assert sel(0, 1 << 20, _lib.INT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS and sel(0, 1 << 20, _lib.FLOAT64, _lib.MAX, 8, 1) == _lib.ALGO_TWOSHOT
-    monkeypatch.delenv("B2R_AUTO_POSTED_MAX_BYTES")
-    monkeypatch.delenv("B2R_AUTO_POSTED_KEY_MAX_BYTES")
+    assert sel(0, 1 << 20, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS and sel(0, 1 << 20, _lib.FLOAT32, _lib.MIN, 8, 1) == _lib.ALGO_TWOSHOT
+    for var in POSTED_KNOBS:
+        monkeypatch.delenv(var)
     monkeypatch.delenv("B2R_AUTO_LL_MAX_BYTES")
     monkeypatch.delenv("B2R_AUTO_LL_REDUCE_MAX_BYTES")
     monkeypatch.setenv("B2R_ALGO", str(_lib.ALGO_LL))
@@ -177,7 +187,7 @@ def test_auto_crossover_switches(monkeypatch):
     """B2R_AUTO_LL_MAX_BYTES (default 8192), B2R_AUTO_RING_MIN_MB and the three B2R_AUTO_PUSH_*_MB crossovers move AUTO's
     crossovers without a rebuild; unsetting them restores the measured defaults."""
     sel = _lib.LIB.b2r_select_algo
-    for var in ("B2R_ALGO", "B2R_AUTO_POSTED_MAX_BYTES", "B2R_AUTO_POSTED_KEY_MAX_BYTES", "B2R_AUTO_LL_MAX_BYTES", "B2R_AUTO_LL_REDUCE_MAX_BYTES", "B2R_AUTO_RING_MIN_MB", "B2R_AUTO_PUSH_REDUCE_MB", "B2R_AUTO_PUSH_ALLREDUCE_MB", "B2R_AUTO_PUSH_REDUCE_NVLS_MB"):
+    for var in POSTED_KNOBS + ("B2R_ALGO", "B2R_AUTO_LL_MAX_BYTES", "B2R_AUTO_LL_REDUCE_MAX_BYTES", "B2R_AUTO_RING_MIN_MB", "B2R_AUTO_PUSH_REDUCE_MB", "B2R_AUTO_PUSH_ALLREDUCE_MB", "B2R_AUTO_PUSH_REDUCE_NVLS_MB"):
         monkeypatch.delenv(var, raising=False)
     before = [sel(a, n, d, _lib.SUM, p, 1) for a in (0, 1) for n in (64, 8192, 1 << 20, 1 << 28) for d in (_lib.INT32, _lib.FLOAT32) for p in (2, 8)]
     assert sel(0, 8192, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_LL
@@ -203,8 +213,7 @@ def test_auto_crossover_switches(monkeypatch):
     monkeypatch.setenv("B2R_AUTO_PUSH_ALLREDUCE_MB", "128")
     monkeypatch.setenv("B2R_AUTO_PUSH_REDUCE_NVLS_MB", "0")
     assert sel(0, 32 << 20, _lib.FLOAT64, _lib.MIN, 8, 1) == _lib.ALGO_PUSH      # no multimem form: stores instead of pulls
-    assert sel(0, (32 << 20) - 8, _lib.FLOAT64, _lib.MIN, 8, 1) == _lib.ALGO_POSTED
-    assert sel(0, (32 << 20) - 8, _lib.FLOAT64, _lib.MIN, 8, 0) == _lib.ALGO_TWOSHOT
+    assert sel(0, (32 << 20) - 8, _lib.FLOAT64, _lib.MIN, 8, 1) == _lib.ALGO_TWOSHOT
     assert sel(1, 32 << 20, _lib.FLOAT32, _lib.MAX, 8, 1) == _lib.ALGO_TWOSHOT   # allreduce has its own crossover
     assert sel(1, 128 << 20, _lib.FLOAT32, _lib.MAX, 8, 1) == _lib.ALGO_PUSH
     assert sel(0, 1 << 30, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS       # the switch keeps what it can do ...
