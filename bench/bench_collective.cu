@@ -10,10 +10,10 @@
 // decimal GB/s and bus bandwidth go to the JSONL/CSV sink, not into the reference-format rows.
 //
 //   bench_collective [--gpus=N] [--total-mib=2048] [--retries=5] [--types=INT,DOUBLE[,BF16,FLOAT]] [--coll=reduce|allreduce]
-//                    [--algo=auto|oneshot|twoshot|tree|nvls|push|ring|ll|posted|assist] [--root=0] [--check] [--jsonl=path] [--raw=path]
+//                    [--algo=auto|oneshot|twoshot|tree|nvls|push|ring|ll|posted] [--root=0] [--check] [--jsonl=path] [--raw=path]
 //   bench_collective --tune=ring|push|nvls|twoshot [--coll=] [--bytes=] [--type=] [--iters=]   (in-process launch-shape grid)
 //   bench_collective --sweep [--min-bytes=1024] [--max-bytes=4294967296] [--types=...] [--colls=reduce,allreduce]
-//                    [--algos=auto,oneshot,twoshot,tree,nvls,push,ring,ll,posted,assist] [--iters=20] [--jsonl=path] [--csv=path]
+//                    [--algos=auto,oneshot,twoshot,tree,nvls,push,ring,ll,posted] [--iters=20] [--jsonl=path] [--csv=path]
 // Runs as ONE process driving all GPUs (b2r_comm_init_all); buffers come from the symmetric heap (zero copy).
 #include <algorithm>
 #include <cmath>
@@ -64,7 +64,6 @@ b2r_algo_t parse_algo(const std::string& s) {
   if (s == "ring") return B2R_ALGO_RING;
   if (s == "ll") return B2R_ALGO_LL;
   if (s == "posted") return B2R_ALGO_POSTED;
-  if (s == "assist") return B2R_ALGO_ASSIST;
   return B2R_ALGO_AUTO;
 }
 
@@ -261,7 +260,7 @@ int main(int argc, char** argv) {
         b2r_comm_ll_max_bytes(R[0].comm, &ll_max);
         if (bytes > ll_max) row_ok = false;
       }
-      if (algo == B2R_ALGO_POSTED || algo == B2R_ALGO_ASSIST) {
+      if (algo == B2R_ALGO_POSTED) {
         uint64_t pmax = 0;
         b2r_comm_posted_max_bytes(R[0].comm, &pmax);
         if (allreduce || bytes > pmax) row_ok = false;
@@ -404,7 +403,7 @@ int main(int argc, char** argv) {
                 b2r_comm_ll_max_bytes(R[0].comm, &ll_max);
                 if (bytes > ll_max) continue;
               }
-              if (algo == B2R_ALGO_POSTED || algo == B2R_ALGO_ASSIST) {
+              if (algo == B2R_ALGO_POSTED) {
                 uint64_t pmax = 0;
                 b2r_comm_posted_max_bytes(R[0].comm, &pmax);
                 if (allreduce || bytes > pmax) continue;

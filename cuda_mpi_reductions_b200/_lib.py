@@ -20,11 +20,11 @@ OK, ERR_INVALID, ERR_CUDA, ERR_UNSUPPORTED, ERR_TIMEOUT, ERR_NOMEM, ERR_SYSTEM, 
 INT32, FLOAT32, FLOAT64, BFLOAT16 = range(4)
 SUM, MIN, MAX = range(3)
 VARIANT_AUTO, VARIANT_LDG128, VARIANT_LDG256, VARIANT_TMA = range(4)
-ALGO_AUTO, ALGO_ONESHOT, ALGO_TWOSHOT, ALGO_TREE, ALGO_NVLS, ALGO_PUSH, ALGO_RING, ALGO_LL, ALGO_POSTED, ALGO_ASSIST = range(10)
+ALGO_AUTO, ALGO_ONESHOT, ALGO_TWOSHOT, ALGO_TREE, ALGO_NVLS, ALGO_PUSH, ALGO_RING, ALGO_LL, ALGO_POSTED = range(9)
 
 OPS = {"sum": SUM, "min": MIN, "max": MAX, "SUM": SUM, "MIN": MIN, "MAX": MAX}
 ALGOS = {"auto": ALGO_AUTO, "oneshot": ALGO_ONESHOT, "twoshot": ALGO_TWOSHOT, "tree": ALGO_TREE, "nvls": ALGO_NVLS, "push": ALGO_PUSH, "ring": ALGO_RING,
-         "ll": ALGO_LL, "posted": ALGO_POSTED, "assist": ALGO_ASSIST}  # "ll": small messages; "posted": mid-size reduce-to-root (stage locally, root reduces via the switch)
+         "ll": ALGO_LL, "posted": ALGO_POSTED}  # "ll": small messages; "posted": mid-size reduce-to-root (stage locally, root reduces via the switch)
 VARIANTS = {"auto": VARIANT_AUTO, "ldg128": VARIANT_LDG128, "ldg256": VARIANT_LDG256, "tma": VARIANT_TMA}
 DTYPE_SIZE = {INT32: 4, FLOAT32: 4, FLOAT64: 8, BFLOAT16: 2}
 

@@ -60,12 +60,9 @@ typedef enum {
   B2R_ALGO_RING = 6,    /* reduce only: store-forwarding chain that ends at the root (one neighbour per GPU, no remote loads) */
   B2R_ALGO_LL = 7,      /* small messages (see b2r_comm_ll_max_bytes): flag-in-data packets pushed into the consumers' slots, no
                            barrier at either end; AUTO's choice up to 64 KiB (allreduce) / 256 KiB (reduce) */
-  B2R_ALGO_POSTED = 8,  /* reduce only, mid-size messages (see b2r_comm_posted_max_bytes): every rank stages its contribution in
+  B2R_ALGO_POSTED = 8   /* reduce only, mid-size messages (see b2r_comm_posted_max_bytes): every rank stages its contribution in
                            its own heap and returns, the root reduces the staged copies through the switch; no barrier at either end,
                            fp min/max travel as order-preserving integer keys */
-  B2R_ALGO_ASSIST = 9   /* reduce only, same size limit: the non-root ranks stage, reduce their shares through the switch (the root's
-                           slot holds the identity) and deliver into a result slot at the root, which adds its own contribution
-                           locally; the root is never on the other ranks' critical path */
 } b2r_algo_t;
 
 typedef struct {

@@ -7,4 +7,3 @@ for dtype, op in (("FLOAT", "SUM"), ("INT", "SUM"), ("DOUBLE", "SUM"), ("BF16", 
     for s in (512 * K, 1 * M, 2 * M, 4 * M, 8 * M, 16 * M, 32 * M, 64 * M):
         print(f"Q.base reduce {dtype} {op} auto {s} {OFF}")
         print(f"Q.posted reduce {dtype} {op} posted {s}")
-        print(f"Q.assist reduce {dtype} {op} assist {s}")

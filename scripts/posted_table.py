@@ -17,9 +17,9 @@ for path in sys.argv[1:]:
             rows[key][label] = float(r[7])
             if label == "Q.base":
                 rows[key]["base_algo"] = r[4]
-print(f"{'dtype':7s}{'op':5s}{'bytes':>10s} {'base':>9s} {'(algo)':>8s} {'posted':>9s} {'assist':>9s} {'nccl':>9s} {'nccl/posted':>12s} {'nccl/assist':>12s} {'nccl/base':>10s}")
+print(f"{'dtype':7s}{'op':5s}{'bytes':>10s} {'base':>9s} {'(algo)':>8s} {'posted':>9s} {'nccl':>9s} {'posted/base':>12s} {'nccl/posted':>12s} {'nccl/base':>10s}")
 for (dt, op, b), v in sorted(rows.items()):
-    base, post, asst, nccl = v.get("Q.base"), v.get("Q.posted"), v.get("Q.assist"), v.get("nccl")
+    base, post, nccl = v.get("Q.base"), v.get("Q.posted"), v.get("nccl")
     f = lambda x: f"{x:9.2f}" if x else "        -"
     g = lambda a, c: f"{a / c:12.2f}" if a and c else "           -"
-    print(f"{dt:7s}{op:5s}{b:10d} {f(base)} {v.get('base_algo', '-'):>8s} {f(post)} {f(asst)} {f(nccl)} {g(nccl, post)} {g(nccl, asst)} {g(nccl, base)[2:]}")
+    print(f"{dt:7s}{op:5s}{b:10d} {f(base)} {v.get('base_algo', '-'):>8s} {f(post)} {f(nccl)} {g(post, base)} {g(nccl, post)} {g(nccl, base)[2:]}")

@@ -51,7 +51,6 @@ CollKernel pick_kind(int kind) {
     case kCollRing: return coll_kernel<D, O, kCollRing, 4>;
     case kCollLL: return coll_kernel<D, O, kCollLL, 4>;
     case kCollPosted: return coll_kernel<D, O, kCollPosted, 4>;
-    case kCollAssist: return coll_kernel<D, O, kCollAssist, 4>;
   }
   return nullptr;
 }
@@ -140,22 +139,8 @@ uint64_t ll_limit(const b2r_comm* c) {
   return std::max(small, big);
 }
 
-// Posted / assisted reduce: four slots at the start of the work region (contributions and results, one of each per call
-// parity); a message must fit one slot.
-uint64_t posted_slot_bytes(const b2r_comm* c) { return std::min<uint64_t>(c->work_bytes / 4, kPostedMaxSlotBytes) & ~(uint64_t)255; }
-// Assisted reduce: what the root's slot has to hold so that a switch reduction over all P slots combines the helpers only
-// (8 bytes of the pattern; fp min / max travel as integer keys, see coll_posted.cuh)
-uint64_t assist_identity(b2r_dtype_t dtype, b2r_op_t op) {
-  if (op == B2R_SUM) return 0;
-  const bool mn = op == B2R_MIN;
-  switch (dtype) {
-    case B2R_INT32:
-    case B2R_FLOAT32: return mn ? 0x7fffffff7fffffffull : 0x8000000080000000ull;
-    case B2R_FLOAT64: return mn ? 0x7fffffffffffffffull : 0x8000000000000000ull;
-    case B2R_BFLOAT16: return mn ? 0x7f807f807f807f80ull : 0xff80ff80ff80ff80ull;  // +inf / -inf
-  }
-  return 0;
-}
+// Posted reduce: one staging slot per call parity at the start of the work region; a message must fit one slot.
+uint64_t posted_slot_bytes(const b2r_comm* c) { return std::min<uint64_t>(c->work_bytes / 2, kPostedMaxSlotBytes) & ~(uint64_t)255; }
 // The grid of the posted path is a property of the communicator (chunk ownership depends on it): kPostedCtas, fewer if the
 // communicator caps CTAs; a loopback group runs all its virtual ranks in one cooperative launch, one CTA per SM in total.
 int posted_ctas(const b2r_comm* c) {
@@ -201,7 +186,7 @@ b2r_algo_t select_algo_cached(int is_allreduce, uint64_t bytes, b2r_dtype_t dtyp
   if (forced == B2R_ALGO_LL && nranks <= B2R_MAX_RANKS && bytes <= ll_max) return B2R_ALGO_LL;
   if (forced >= B2R_ALGO_ONESHOT && forced <= B2R_ALGO_PUSH) return (b2r_algo_t)forced;
   if (forced == B2R_ALGO_RING && !is_allreduce) return B2R_ALGO_RING;
-  if ((forced == B2R_ALGO_POSTED || forced == B2R_ALGO_ASSIST) && !is_allreduce && bytes <= posted_max) return (b2r_algo_t)forced;
+  if (forced == B2R_ALGO_POSTED && !is_allreduce && bytes <= posted_max) return B2R_ALGO_POSTED;
   // LL crossovers: allreduce B2R_AUTO_LL_MAX_BYTES, reduce-to-root B2R_AUTO_LL_REDUCE_MAX_BYTES (only the root consumes, so the
   // 64-CTA instance stays ahead of the barrier-framed kernels for longer); both capped by what the communicator's slots hold
   const uint64_t auto_ll = (uint64_t)std::max(0, is_allreduce ? B2R_ENV_INT("B2R_AUTO_LL_MAX_BYTES", kAutoLLAllreduceBytes)
@@ -305,12 +290,12 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
   }
   int kind = algo == B2R_ALGO_ONESHOT ? kCollOneshot : algo == B2R_ALGO_TWOSHOT ? kCollTwoshot : algo == B2R_ALGO_TREE ? kCollTree
              : algo == B2R_ALGO_PUSH ? kCollPush : algo == B2R_ALGO_RING ? kCollRing : algo == B2R_ALGO_LL ? kCollLL
-             : algo == B2R_ALGO_POSTED ? kCollPosted : algo == B2R_ALGO_ASSIST ? kCollAssist : kCollNvls;
+             : algo == B2R_ALGO_POSTED ? kCollPosted : kCollNvls;
   if (kind == kCollRing && is_all) return fail(B2R_ERR_UNSUPPORTED, "the ring algorithm implements reduce-to-root only");
-  if (kind == kCollPosted || kind == kCollAssist) {
-    if (is_all) return fail(B2R_ERR_UNSUPPORTED, "the posted and assisted algorithms implement reduce-to-root only");
+  if (kind == kCollPosted) {
+    if (is_all) return fail(B2R_ERR_UNSUPPORTED, "the posted algorithm implements reduce-to-root only");
     if (((total_bytes + 15) & ~15ull) > posted_slot_bytes(c0))
-      return fail(B2R_ERR_INVALID, "the posted / assisted path carries at most %llu bytes per rank on this communicator (got %llu)",
+      return fail(B2R_ERR_INVALID, "the posted path carries at most %llu bytes per rank on this communicator (got %llu)",
                   (unsigned long long)posted_slot_bytes(c0), (unsigned long long)total_bytes);
   }
   if (kind == kCollLL) {
@@ -330,7 +315,7 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
   const uint64_t work_elems = (c0->work_bytes / 16) * 16 / esz;
   uint64_t chunk = chunk_elems;
   if (kind == kCollTree) chunk = std::min<uint64_t>(chunk_elems, work_elems);
-  if (kind == kCollPosted || kind == kCollAssist) chunk = count;  // like LL: peers' buffers are never touched, nothing is staged per chunk
+  if (kind == kCollPosted) chunk = count;  // like LL: peers' buffers are never touched, nothing is staged per chunk
   if (kind == kCollPush) {
     const uint64_t W = is_all ? P : P - 1;
     const uint64_t slice_bytes = std::min<uint64_t>(c0->work_bytes / P - 64, (uint64_t)kPushChunkCap * 512 * 4 * 16 - 64);
@@ -348,7 +333,7 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
       const bool gets_result = is_all || c->rank == root;
       const char* send = (const char*)rc[i].send + first * esz;
       char* recv = rc[i].recv ? (char*)rc[i].recv + first * esz : nullptr;
-      if (kind == kCollLL || kind == kCollPosted || kind == kCollAssist) {
+      if (kind == kCollLL || kind == kCollPosted) {
         CollArgs& A = L.a[n == 1 ? 0 : c->rank];
         A.ctx = c->ctx;
         if (((uintptr_t)send % 16) || (gets_result && ((uintptr_t)recv % 16)))
@@ -367,28 +352,12 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
         A.count = cnt;
         A.epoch = c->epoch;
         A.root = is_all ? -1 : root;
-        if (kind == kCollPosted || kind == kCollAssist) {
+        if (kind == kCollPosted) {
           A.seq = ++c->posted_seq;
-          const int par = (int)(A.seq & 1u);
           A.work_off = (unsigned long long)(c->stage_work() - c->my_heap());
-          A.recv_off = posted_slot_bytes(c);             // slot stride (the recv buffer travels as recv_ptr)
-          A.sub_blocks = (int)c->posted_readers[par];    // whose acknowledgements free this parity's slots
-          if (kind == kCollPosted) {
-            c->posted_readers[par] = 1u << root;
-            c->assist_clean_root[par] = -1;              // every rank stages here, the root included
-          } else {
-            const uint64_t pat = assist_identity(dtype, op), b16 = (bytes + 15) & ~15ull;
-            const bool same = c->assist_clean_root[par] == root && c->assist_clean_pat[par] == pat;
-            const bool fast = same && c->assist_clean_bytes[par] >= b16;
-            A.send_off = pat;
-            A.stagger_ns = fast ? 0u : 1u;               // 1: the root rewrites the identity and the helpers wait for it
-            if (!fast) {
-              c->assist_clean_bytes[par] = same ? std::max(c->assist_clean_bytes[par], b16) : b16;
-              c->assist_clean_root[par] = root;
-              c->assist_clean_pat[par] = pat;
-            }
-            c->posted_readers[par] = (1u << P) - 1u;
-          }
+          A.recv_off = posted_slot_bytes(c);                 // slot stride (the recv buffer travels as recv_ptr)
+          A.ring_depth = c->posted_root[A.seq & 1u];         // whose acknowledgement frees this parity's slot
+          c->posted_root[A.seq & 1u] = root;
           continue;
         }
         // small instance (control region, one CTA) when the message fits it, else the large one; each has its own slots,
@@ -434,8 +403,6 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
       A.root = is_all ? -1 : root;
       c->epoch += 8;  // start + end + up to 4 tree rounds, rounded up; same increment on every rank
       if (kind == kCollPush || kind == kCollRing) A.seq = ++c->push_seq;
-      // these write the work region: an identity kept there for the assisted reduce is gone
-      if (kind == kCollPush || kind == kCollRing || kind == kCollTree) c->assist_clean_root[0] = c->assist_clean_root[1] = -1;
     }
     const Shape shape = coll_shape(c0, kind, bytes, n, dtype == B2R_INT32 ? 4 : (dtype == B2R_FLOAT64 ? 8 : 16));
     int ctas = shape.ctas;
@@ -452,7 +419,7 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
         threads = n > 1 ? kLLBigThreads / 2 : kLLBigThreads;
       }
     }
-    if (kind == kCollPosted || kind == kCollAssist) {  // the same grid in every call (fixed partition, see coll_posted.cuh); loopback: half-size CTAs
+    if (kind == kCollPosted) {  // the same grid in every call (fixed partition, see coll_posted.cuh); loopback: half-size CTAs
       ctas = posted_ctas(c0);
       threads = n > 1 ? kPostedThreads / 2 : kPostedThreads;
     }

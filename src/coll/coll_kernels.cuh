@@ -667,7 +667,7 @@ __device__ inline void barrier_body(const CollArgs& A) {
   start_barrier(A, &po);
 }
 
-enum CollKind { kCollOneshot = 1, kCollTwoshot = 2, kCollTree = 3, kCollNvls = 4, kCollBarrier = 5, kCollPush = 6, kCollRing = 7, kCollLL = 8, kCollPosted = 9, kCollAssist = 10 };
+enum CollKind { kCollOneshot = 1, kCollTwoshot = 2, kCollTree = 3, kCollNvls = 4, kCollBarrier = 5, kCollPush = 6, kCollRing = 7, kCollLL = 8, kCollPosted = 9 };
 
 template <int D, int O, int KIND, int UNR>
 __global__ void __launch_bounds__(512) coll_kernel(const __grid_constant__ CollLaunch L) {
@@ -680,7 +680,6 @@ __global__ void __launch_bounds__(512) coll_kernel(const __grid_constant__ CollL
   else if (KIND == kCollRing) ring_body<D, O, UNR>(A);
   else if (KIND == kCollLL) ll_body<D, O>(A);
   else if (KIND == kCollPosted) posted_body<D, O>(A);
-  else if (KIND == kCollAssist) assist_body<D, O>(A);
   else barrier_body(A);
 }
 

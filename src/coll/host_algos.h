@@ -27,20 +27,7 @@ void host_collective_rank(const HostRankView& v, uint64_t count, b2r_dtype_t dty
                           b2r_algo_t algo, Barrier&& barrier) {
   const int P = v.nranks, r = v.rank;
   barrier();  // everybody's send buffer is ready
-  if (algo == B2R_ALGO_ASSIST && root >= 0 && P > 1 && P <= B2R_MAX_RANKS) {
-    // the helpers' contributions in rank order, stored in the buffer's own dtype (bf16: rounded, like the result slot of
-    // assist_body), then the root's own contribution as the last operand
-    if (r == root) {
-      const void* helpers[B2R_MAX_RANKS];
-      int nh = 0;
-      for (int p = 0; p < P; ++p)
-        if (p != root) helpers[nh++] = v.send[p];
-      combine_many_host(v.recv[root], helpers, nh, 0, count, dtype, op);
-      const void* pair[2] = {v.recv[root], v.send[root]};
-      combine_many_host(v.recv[root], pair, 2, 0, count, dtype, op);
-    }
-    barrier();
-  } else if (algo == B2R_ALGO_ONESHOT || algo == B2R_ALGO_ASSIST || algo == B2R_ALGO_AUTO || algo == B2R_ALGO_NVLS || algo == B2R_ALGO_LL ||
+  if (algo == B2R_ALGO_ONESHOT || algo == B2R_ALGO_AUTO || algo == B2R_ALGO_NVLS || algo == B2R_ALGO_LL ||
       algo == B2R_ALGO_POSTED) {  // LL, posted: same rank-order fold
     if (root < 0 || root == r) combine_many_host(v.recv[r], v.send, P, 0, count, dtype, op);
     barrier();

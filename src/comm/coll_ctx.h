@@ -15,7 +15,6 @@ constexpr size_t kOffFlags = 0;                      // uint32 flags[kCollMaxCta
 constexpr size_t kOffMailbox = 32 * 1024;            // XgMailbox (scalar-sharded reduce)
 constexpr size_t kOffError = 40 * 1024;              // uint32 error word (device-side timeouts)
 constexpr size_t kOffCtx = 44 * 1024;                // device copy of CollCtx (read by the scalar-sharded kernels)
-constexpr size_t kOffAssistDone = 48 * 1024;         // uint32 [kPostedCtas][B2R_MAX_RANKS]: assisted reduce, at the root: "CTA b of helper s has delivered call n"
 constexpr size_t kOffMeta = 64 * 1024;               // PeerMeta meta[kCollMaxCtas][B2R_MAX_RANKS]: per-collective buffer offsets
 constexpr size_t kOffPushData = 128 * 1024;          // uint32 [kCollMaxCtas][B2R_MAX_RANKS]: push algorithm, "block of round i from rank s has landed"
 constexpr size_t kOffPostedReady = 144 * 1024;       // uint32 [kPostedCtas][B2R_MAX_RANKS]: posted reduce, at the root: "CTA b of rank s has staged call n"
@@ -64,7 +63,6 @@ constexpr int kPostedCtas = 128;
 constexpr int kPostedThreads = 512;
 constexpr unsigned int kPostedChunkVecs = 512;  // 8 KiB
 constexpr size_t kPostedMaxSlotBytes = (size_t)64 << 20;
-static_assert(kOffAssistDone + (size_t)kPostedCtas * B2R_MAX_RANKS * 4 <= kOffMeta, "assist: done words overlap the buffer offsets");
 static_assert(kOffPostedReady + (size_t)kPostedCtas * B2R_MAX_RANKS * 4 <= kOffPostedAck, "posted: ready words overlap the ack words");
 static_assert(kOffPostedAck + (size_t)B2R_MAX_RANKS * kPostedCtas * 4 <= kOffPushAck, "posted: ack words overlap the ring's");
 

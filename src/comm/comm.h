@@ -54,11 +54,8 @@ struct b2r_comm {
   uint32_t push_seq = 0;  // push-algorithm call counter (flag values are seq << 16 | round)
   uint32_t ll_seq = 0;    // LL path call counter (consecutive: slot parity and the n-2 acknowledgement rule depend on it)
   uint32_t ll_big_seq = 0;  // the same for the large LL region (separate slots and acknowledgements, separate numbering)
-  uint32_t posted_seq = 0;  // posted / assisted reduce: call counter shared by both (slot parity = seq & 1)
-  uint32_t posted_readers[2] = {0, 0};  // bit p: rank p read this parity's slots in the last call that used them (its ack frees them)
-  int assist_clean_root[2] = {-1, -1};  // assisted reduce: the rank whose slot of this parity holds the identity ...
-  uint64_t assist_clean_pat[2] = {0, 0};    // ... which identity (8-byte pattern) ...
-  uint64_t assist_clean_bytes[2] = {0, 0};  // ... and over how many bytes; -1 / anything else = has to be rewritten
+  uint32_t posted_seq = 0;  // posted-reduce call counter (slot parity = seq & 1)
+  int posted_root[2] = {-1, -1};  // root of the last posted call of each parity: whose acknowledgement frees the slot
   b2r_workspace* ws = nullptr;
   int max_ctas = 0, timeout_ms = 0;
   bool has_mc = false;

@@ -174,7 +174,6 @@ const char* b2r_algo_name(b2r_algo_t a) {
     case B2R_ALGO_RING: return "ring";
     case B2R_ALGO_LL: return "ll";
     case B2R_ALGO_POSTED: return "posted";
-    case B2R_ALGO_ASSIST: return "assist";
   }
   return "?";
 }

@@ -17,7 +17,7 @@ ATOL = {torch.int32: 0, torch.float32: 1e-5, torch.float64: 1e-13, torch.bfloat1
 
 
 def check_posted(comm, rank, world, fails):
-    # posted / assisted reduce on real NVLink: a back-to-back series with rotating roots, changing sizes and no host synchronisation (slot
+    # posted reduce on real NVLink: a back-to-back series with rotating roots, changing sizes and no host synchronisation (slot
     # parity, acknowledgements of the root two calls back), interleaved with barrier-framed algorithms that use the same work
     # region; with a switch the staged copies are read by multimem (fp32 min travels as integer keys: exact)
     for dtype, op in ((torch.int32, "sum"), (torch.float32, "min"), (torch.float64, "max"), (torch.bfloat16, "max")):
@@ -37,8 +37,8 @@ def check_posted(comm, rank, world, fails):
         pending = []
         for i in range(60):
             n = sizes[(i * 3) % len(sizes)]
-            root = (i // 4 + i // 25) % world  # roots stay for a few calls (assist's fast path), then move
-            algo = ("assist", "assist", "posted")[(i // 6) % 3] if i % 10 != 9 else ("push", "tree", "twoshot")[(i // 10) % 3]
+            root = (i * 5 + i // 7) % world
+            algo = "posted" if i % 10 != 9 else ("push", "tree", "twoshot")[(i // 10) % 3]
             pending.append((n, root, comm.reduce(xs[n], op, root=root, algo=algo), algo))
         comm.check()
         for n, root, red, algo in pending:
@@ -102,7 +102,7 @@ def main():
                         fails += 1
                         print(f"[rank {rank}] allreduce MISMATCH dtype={dtype} count={count} op={op} algo={algo}", flush=True)
                     root = (count + rank * 0) % world
-                    for ralgo in ([algo, "ring", "posted", "assist"] if algo == "twoshot" else [algo]):
+                    for ralgo in ([algo, "ring", "posted"] if algo == "twoshot" else [algo]):
                         red = comm.reduce(x, op, root=root, algo=ralgo)
                         comm.check()
                         if rank == root:
