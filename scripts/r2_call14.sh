@@ -1,5 +1,6 @@
 #!/bin/bash
-O=gpurun_out/r2c14; mkdir -p $O
-python scripts/ncu_default.py > $O/plain.log 2>&1 && ncu --metrics gpu__time_duration.sum --clock-control none -c 60 --csv --log-file $O/launches.csv python scripts/ncu_default.py > $O/ncu_launches.log 2>&1
-python scripts/ncu_default.py > $O/plain2.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:reduce_ldg -s 5 -c 6 -o $O/reduce_ldg_dyn_int32_sum python scripts/ncu_default.py > $O/ncu_full.log 2>&1
-tail -n 2 $O/ncu_full.log
+# posted reduce with coalesced 4- / 8-byte multimem requests, N GPUs: checked rows only (the other arms were measured in r2_call12)
+N=${1:-8}
+O=gpurun_out/r2c14_$N; mkdir -p $O
+timeout 100 bin/bench_collective --gpus=$N --plan=scripts/plans/plan_posted_narrow.txt --check --iters=10 --csv=$O/plan.csv > $O/plan.txt 2> $O/plan.err
+grep -h "R\.\|FAILED\|clocks gpu0" $O/plan.txt $O/plan.err | cut -c1-110

@@ -19,6 +19,9 @@
 //               Staging maps every value to the two's-complement integer of the same rank (k = b ^ ((b >> 31) & 0x7fff...)), the
 //               switch reduces integers, the root maps back (the map is its own inverse). -0 orders below +0; a NaN orders
 //               beyond the infinity of its sign (the host restatement and the pull kernels use a < b ? a : b).
+//   history   : a variant in which the P-1 non-root ranks did the switch reductions around an identity kept in the root's slot
+//               and delivered into a result slot at the root ("assist") was built and measured on 4 GPUs: correct, and no
+//               faster than this one at any size (profiles/raw/r2_posted/table_4gpu_assist.txt). Removed.
 //   no switch : (loopback groups, or a (dtype, op) pair without any multimem form) the root folds the staged copies in rank
 //               order with peer loads — same protocol, same bits as the one-shot kernel; this is what the loopback tests
 //               exercise. AUTO only ever picks the algorithm where the switch does the reading.
@@ -159,6 +162,37 @@ __device__ void posted_body(const CollArgs& A) {
     for (unsigned long long k0 = (unsigned long long)b; k0 < nchunks; k0 += (unsigned long long)G * U) {
       for (unsigned int j = threadIdx.x; j < kPostedChunkVecs; j += blockDim.x) {
         V16 r[U];
+        if (via_switch && C::kBytes < 16) {
+          // 4- and 8-byte multimem forms: a thread does NOT take the 16 / B units of "its" vector (a warp's instruction would
+          // then touch 32 units 16 bytes apart: four times the transactions, and the first version measured 120 GB/s for int32
+          // against 390 for fp32). Unit m of the thread sits at j + m x (units of a quarter chunk), so every instruction of a
+          // warp covers 32 consecutive units. Messages are whole units (count x element size), so no vector tail here.
+          constexpr int B = C::kBytes, M = 16 / B;
+#pragma unroll
+          for (int u = 0; u < U; ++u) {
+            const unsigned long long k = k0 + (unsigned long long)u * G;
+#pragma unroll
+            for (int m = 0; m < M; ++m) {
+              const unsigned long long off = k * kPostedChunkVecs * 16ull + ((unsigned long long)j + (unsigned long long)m * kPostedChunkVecs) * B;
+              if (k < nchunks && off < bytes) C::ld_reduce(mslot + off, &r[u].w[m * B / 4]);
+            }
+          }
+#pragma unroll
+          for (int u = 0; u < U; ++u) r[u] = C::code(r[u]);  // element-wise (32- or 64-bit), so any unit may sit in any lane
+#pragma unroll
+          for (int u = 0; u < U; ++u) {
+            const unsigned long long k = k0 + (unsigned long long)u * G;
+#pragma unroll
+            for (int m = 0; m < M; ++m) {
+              const unsigned long long off = k * kPostedChunkVecs * 16ull + ((unsigned long long)j + (unsigned long long)m * kPostedChunkVecs) * B;
+              if (k < nchunks && off < bytes) {
+                if (B == 8) asm volatile("st.relaxed.sys.global.v2.b32 [%0], {%1,%2};" ::"l"(A.recv_ptr + off), "r"(r[u].w[2 * m]), "r"(r[u].w[(2 * m + 1) & 3]) : "memory");
+                else asm volatile("st.relaxed.sys.global.b32 [%0], %1;" ::"l"(A.recv_ptr + off), "r"(r[u].w[m]) : "memory");
+              }
+            }
+          }
+          continue;
+        }
         if (via_switch) {
 #pragma unroll
           for (int u = 0; u < U; ++u) {
