@@ -173,10 +173,12 @@ constexpr int kAutoPushReduceMB = 0, kAutoPushAllreduceMB = 0, kAutoPushReduceNv
 // 128 KiB at 4 GPUs — every consumer receives (P-1) x 2 x the message, so the crossover is set lower for all sizes of P
 constexpr int kAutoLLAllreduceBytes = 65536, kAutoLLReduceBytes = 262144;
 // posted reduce (stage locally, return; the root alone reduces the staged copies through the switch): from the LL crossover up
-// to these sizes. The root's multimem request stream is the limit, so the crossover depends on how many bytes one request moves:
-// 16 (fp32 add, bf16) ~400 GB/s, 8 (fp64 add, fp64 min/max as 64-bit keys) ~215, 4 (int32, fp32 min/max as 32-bit keys) ~120.
-// Measured on 4 GPUs against the barrier-framed NVLS kernel (native forms) and two-shot (keys): profiles/raw/r2_posted/.
-constexpr int kAutoPosted16 = 8 << 20, kAutoPosted8 = 2 << 20, kAutoPosted4 = 1 << 20, kAutoPostedKey8 = 4 << 20, kAutoPostedKey4 = 1 << 20;
+// to these sizes. Measured on 8 GPUs (profiles/raw/r2_posted/): one GPU's multimem request stream sustains ~290 GB/s whatever the
+// form (once the 4- and 8-byte requests are coalesced across the warp), and a call costs 12.9 us up to 1 MiB. Against the
+// barrier-framed NVLS kernel (native forms) it is ahead up to 8 MiB (1 MiB: 13 vs 18 us, 4 MiB: 22 vs 25-26, 8 MiB: 34-36 vs
+// 35-36); against two-shot by peer loads (fp32 / fp64 min and max, which travel as 32- / 64-bit integer keys) up to 32 MiB
+// (fp32: 16 MiB 60 vs 63 us) and 8 MiB (fp64: 38 vs 46; 16 MiB 68 vs 64).
+constexpr int kAutoPostedMaxBytes = 8 << 20, kAutoPostedKey4MaxBytes = 32 << 20, kAutoPostedKey8MaxBytes = 8 << 20;
 
 b2r_algo_t select_algo_cached(int is_allreduce, uint64_t bytes, b2r_dtype_t dtype, b2r_op_t op, int nranks, int has_multicast, uint64_t ll_max,
                               uint64_t posted_max) {
@@ -210,13 +212,10 @@ b2r_algo_t select_algo_cached(int is_allreduce, uint64_t bytes, b2r_dtype_t dtyp
   }
   // posted: mid-size reduce-to-root wherever the switch can do the reading (natively, or on integer keys for fp min / max)
   if (switch_ok && !is_allreduce) {
-    // B2R_AUTO_POSTED_MAX_BYTES / _8 / _4: native forms by bytes per multimem request; B2R_AUTO_POSTED_KEY_MAX_BYTES_8 / _4: fp64 /
-    // fp32 min and max (integer keys); 0 = never
-    int cut_i;
-    if (nvls_ok) cut_i = dtype == B2R_INT32 ? B2R_ENV_INT("B2R_AUTO_POSTED_MAX_BYTES_4", kAutoPosted4)
-                         : dtype == B2R_FLOAT64 ? B2R_ENV_INT("B2R_AUTO_POSTED_MAX_BYTES_8", kAutoPosted8)
-                                                : B2R_ENV_INT("B2R_AUTO_POSTED_MAX_BYTES", kAutoPosted16);
-    else cut_i = dtype == B2R_FLOAT64 ? B2R_ENV_INT("B2R_AUTO_POSTED_KEY_MAX_BYTES_8", kAutoPostedKey8) : B2R_ENV_INT("B2R_AUTO_POSTED_KEY_MAX_BYTES_4", kAutoPostedKey4);
+    // B2R_AUTO_POSTED_MAX_BYTES: pairs with a multimem form; B2R_AUTO_POSTED_KEY_MAX_BYTES_4 / _8: fp32 / fp64 min and max; 0 = never
+    const int cut_i = nvls_ok ? B2R_ENV_INT("B2R_AUTO_POSTED_MAX_BYTES", kAutoPostedMaxBytes)
+                              : (dtype == B2R_FLOAT64 ? B2R_ENV_INT("B2R_AUTO_POSTED_KEY_MAX_BYTES_8", kAutoPostedKey8MaxBytes)
+                                                      : B2R_ENV_INT("B2R_AUTO_POSTED_KEY_MAX_BYTES_4", kAutoPostedKey4MaxBytes));
     const uint64_t cut = (uint64_t)std::max(0, cut_i);
     if (bytes <= std::min(cut, posted_max)) return B2R_ALGO_POSTED;
   }

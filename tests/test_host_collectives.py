@@ -66,8 +66,7 @@ def test_int_sum_wraps_across_ranks():
     assert (got == want).all()
 
 
-POSTED_KNOBS = ("B2R_AUTO_POSTED_MAX_BYTES", "B2R_AUTO_POSTED_MAX_BYTES_8", "B2R_AUTO_POSTED_MAX_BYTES_4", "B2R_AUTO_POSTED_KEY_MAX_BYTES_8",
-                "B2R_AUTO_POSTED_KEY_MAX_BYTES_4")
+POSTED_KNOBS = ("B2R_AUTO_POSTED_MAX_BYTES", "B2R_AUTO_POSTED_KEY_MAX_BYTES_8", "B2R_AUTO_POSTED_KEY_MAX_BYTES_4")
 
 
 def test_algo_selection_is_pure_and_sensible():
@@ -82,11 +81,11 @@ def test_algo_selection_is_pure_and_sensible():
     assert sel(0, 262148, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_POSTED  # mid-size reduce-to-root: stage and return, the root reduces via the switch
     assert sel(0, 1 << 20, _lib.INT32, _lib.MAX, 4, 1) == _lib.ALGO_POSTED
     assert sel(0, 1 << 20, _lib.FLOAT32, _lib.MIN, 8, 1) == _lib.ALGO_POSTED   # fp min/max travel as integer keys
-    # the crossover depends on how many bytes one multimem request moves: 16 (fp32 add, bf16) / 8 (fp64) / 4 (int32, fp32 keys)
-    assert sel(0, 8 << 20, _lib.BFLOAT16, _lib.MAX, 8, 1) == _lib.ALGO_POSTED and sel(0, (8 << 20) + 2, _lib.BFLOAT16, _lib.MAX, 8, 1) == _lib.ALGO_NVLS
-    assert sel(0, 2 << 20, _lib.FLOAT64, _lib.SUM, 8, 1) == _lib.ALGO_POSTED and sel(0, 4 << 20, _lib.FLOAT64, _lib.SUM, 8, 1) == _lib.ALGO_NVLS
-    assert sel(0, 4 << 20, _lib.FLOAT64, _lib.MIN, 8, 1) == _lib.ALGO_POSTED and sel(0, 8 << 20, _lib.FLOAT64, _lib.MIN, 8, 1) == _lib.ALGO_TWOSHOT
-    assert sel(0, 2 << 20, _lib.INT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS and sel(0, 2 << 20, _lib.FLOAT32, _lib.MAX, 8, 1) == _lib.ALGO_TWOSHOT
+    # native multimem forms: up to 8 MiB (then the barrier-framed NVLS kernel); keys: fp32 up to 32 MiB, fp64 up to 8 MiB (then two-shot)
+    for dt, op in ((_lib.BFLOAT16, _lib.MAX), (_lib.FLOAT64, _lib.SUM), (_lib.INT32, _lib.SUM), (_lib.INT32, _lib.MIN), (_lib.FLOAT32, _lib.SUM)):
+        assert sel(0, 8 << 20, dt, op, 8, 1) == _lib.ALGO_POSTED and sel(0, (8 << 20) + 8, dt, op, 8, 1) == _lib.ALGO_NVLS
+    assert sel(0, 32 << 20, _lib.FLOAT32, _lib.MAX, 4, 1) == _lib.ALGO_POSTED and sel(0, (32 << 20) + 4, _lib.FLOAT32, _lib.MAX, 4, 1) == _lib.ALGO_TWOSHOT
+    assert sel(0, 8 << 20, _lib.FLOAT64, _lib.MIN, 8, 1) == _lib.ALGO_POSTED and sel(0, 16 << 20, _lib.FLOAT64, _lib.MIN, 8, 1) == _lib.ALGO_TWOSHOT
     assert sel(0, 1 << 20, _lib.FLOAT32, _lib.MIN, 8, 0) == _lib.ALGO_TWOSHOT  # no switch, no posted
     assert sel(0, 1 << 20, _lib.FLOAT32, _lib.SUM, 2, 1) == _lib.ALGO_ONESHOT
     assert sel(1, 1 << 20, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS     # reduce-to-root only
@@ -214,6 +213,7 @@ def test_auto_crossover_switches(monkeypatch):
     monkeypatch.setenv("B2R_AUTO_PUSH_REDUCE_NVLS_MB", "0")
     assert sel(0, 32 << 20, _lib.FLOAT64, _lib.MIN, 8, 1) == _lib.ALGO_PUSH      # no multimem form: stores instead of pulls
     assert sel(0, (32 << 20) - 8, _lib.FLOAT64, _lib.MIN, 8, 1) == _lib.ALGO_TWOSHOT
+    assert sel(0, (32 << 20) - 8, _lib.FLOAT32, _lib.MIN, 8, 1) == _lib.ALGO_POSTED   # below the push crossover: the usual choice
     assert sel(1, 32 << 20, _lib.FLOAT32, _lib.MAX, 8, 1) == _lib.ALGO_TWOSHOT   # allreduce has its own crossover
     assert sel(1, 128 << 20, _lib.FLOAT32, _lib.MAX, 8, 1) == _lib.ALGO_PUSH
     assert sel(0, 1 << 30, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS       # the switch keeps what it can do ...
