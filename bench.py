@@ -245,7 +245,7 @@ def run_b2r(args) -> None:
                 print(f"[rank {rank}] prepared call unavailable ({e}); using the regular method", file=sys.stderr)
                 step = step_regular
 
-    # correctness of what is being timed (cheap: one step per distinct input, against the CPU oracle)
+    # correctness of what is being timed (cheap: one step, on the first of the rotating inputs, against the CPU oracle)
     def verified() -> tuple[bool, str]:
         out.zero_()
         step(0)
