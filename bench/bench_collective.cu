@@ -265,7 +265,7 @@ int main(int argc, char** argv) {
         b2r_comm_posted_max_bytes(R[0].comm, &pmax);
         if (allreduce || bytes > pmax) row_ok = false;
       }
-      if (algo == B2R_ALGO_NVLS && (!has_mc || ((dt == B2R_FLOAT32 || dt == B2R_FLOAT64) && op != B2R_SUM))) row_ok = false;
+      if (algo == B2R_ALGO_NVLS && !has_mc) row_ok = false;  // fp min / max: the keyed form
       double ms = -1;
       if (row_ok) {
         if (f.has("check") && bytes <= check_max && !verify(R, allreduce, count, dt, op, root, algo)) {
@@ -408,7 +408,6 @@ int main(int argc, char** argv) {
                 b2r_comm_posted_max_bytes(R[0].comm, &pmax);
                 if (allreduce || bytes > pmax) continue;
               }
-              if (algo == B2R_ALGO_NVLS && (dt == B2R_FLOAT32 || dt == B2R_FLOAT64) && op != B2R_SUM) continue;
               if ((algo == B2R_ALGO_ONESHOT || algo == B2R_ALGO_TREE) && bytes > (64ull << 20)) continue;  // pointless at this size
               if (f.has("check") && bytes <= (256ull << 20)) all_ok = verify(R, allreduce, count, dt, op, root, algo) && all_ok;
               const int it = bytes >= (1ull << 30) ? std::max(3, iters / 4) : (bytes >= (64ull << 20) ? std::max(5, iters / 2) : iters * 5);

@@ -226,7 +226,7 @@ class Communicator:
 
     @property
     def posted_max_bytes(self) -> int:
-        """Largest message (bytes per rank) algo="posted" accepts on this communicator (half the work region, at most 64 MiB)."""
+        """Largest message (bytes per rank) algo="posted" accepts on this communicator (a quarter of the work region, at most 64 MiB)."""
         n = C.c_uint64()
         _lib.check(_lib.LIB.b2r_comm_posted_max_bytes(self._h, C.byref(n)), "b2r_comm_posted_max_bytes")
         return int(n.value)

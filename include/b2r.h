@@ -55,7 +55,8 @@ typedef enum {
   B2R_ALGO_ONESHOT = 1, /* every rank (or root) loads all peers' vectors, combines in registers */
   B2R_ALGO_TWOSHOT = 2, /* reduce-scatter by P2P loads + gather by P2P stores */
   B2R_ALGO_TREE = 3,    /* hand-written binomial tree, log2(P) rounds of pairwise P2P combine */
-  B2R_ALGO_NVLS = 4,    /* multimem.ld_reduce / multimem.st through the NVSwitch (needs multicast) */
+  B2R_ALGO_NVLS = 4,    /* multimem.ld_reduce / multimem.st through the NVSwitch (needs multicast); fp32 / fp64 min and max
+                           travel as order-preserving integer keys, encoded by one extra local pass */
   B2R_ALGO_PUSH = 5,    /* scatter by P2P stores into the owners' staging, reduce locally, push the result: no remote loads */
   B2R_ALGO_RING = 6,    /* reduce only: store-forwarding chain that ends at the root (one neighbour per GPU, no remote loads) */
   B2R_ALGO_LL = 7,      /* small messages (see b2r_comm_ll_max_bytes): flag-in-data packets pushed into the consumers' slots, no
@@ -281,8 +282,8 @@ uint64_t b2r_ll_max_bytes(int nranks);
 /* The same for an existing communicator: larger with the 64-CTA LL region behind the user heap (B2R_LL_BIG_MB at creation,
  * default 16 MiB; 0 = none). */
 b2r_status_t b2r_comm_ll_max_bytes(b2r_comm_t comm, uint64_t* bytes);
-/* Largest message (bytes per rank) B2R_ALGO_POSTED accepts on this communicator: half the work region (B2R_WORK_MB at
- * creation), at most 64 MiB. */
+/* Largest message (bytes per rank) B2R_ALGO_POSTED accepts on this communicator: a quarter of the work region (B2R_WORK_MB at
+ * creation, default 320), at most 64 MiB. */
 b2r_status_t b2r_comm_posted_max_bytes(b2r_comm_t comm, uint64_t* bytes);
 
 /* Which algorithm AUTO resolves to (pure function; used by tests and the harness). */

@@ -130,6 +130,8 @@ bool nvls_supported(b2r_dtype_t dtype, b2r_op_t op) {
   if (dtype == B2R_FLOAT32 || dtype == B2R_FLOAT64) return op == B2R_SUM;
   return true;  // bf16x2 add/min/max, 32-bit integer add/min/max
 }
+// fp32 / fp64 min and max go through the switch as integer keys: the send buffer is first staged (encoded) into the work region
+bool nvls_keyed(b2r_dtype_t dtype, b2r_op_t op) { return (dtype == B2R_FLOAT32 || dtype == B2R_FLOAT64) && op != B2R_SUM; }
 
 // Largest message the LL path can carry on this communicator: the small instance in the control region, or the large one
 // behind the user heap when the communicator was created with B2R_LL_BIG_MB.
@@ -140,7 +142,12 @@ uint64_t ll_limit(const b2r_comm* c) {
 }
 
 // Posted reduce: one staging slot per call parity at the start of the work region; a message must fit one slot.
-uint64_t posted_slot_bytes(const b2r_comm* c) { return std::min<uint64_t>(c->work_bytes / 2, kPostedMaxSlotBytes) & ~(uint64_t)255; }
+// The two slots take at most the first half of the work region; what lies behind them is the staging area of the keyed NVLS
+// form. (Everything else that uses the work region — tree, push, ring — starts with a cross-GPU barrier, so it cannot overwrite a
+// slot that a lagging root is still reading; the keyed form's encoding pass has no barrier in front of it, hence its own area.)
+uint64_t posted_slot_bytes(const b2r_comm* c) { return std::min<uint64_t>(c->work_bytes / 4, kPostedMaxSlotBytes) & ~(uint64_t)255; }
+uint64_t keyed_off(const b2r_comm* c) { return 2 * posted_slot_bytes(c); }
+uint64_t keyed_bytes(const b2r_comm* c) { return (c->work_bytes - keyed_off(c)) & ~(uint64_t)255; }
 // The grid of the posted path is a property of the communicator (chunk ownership depends on it): kPostedCtas, fewer if the
 // communicator caps CTAs; a loopback group runs all its virtual ranks in one cooperative launch, one CTA per SM in total.
 int posted_ctas(const b2r_comm* c) {
@@ -178,6 +185,7 @@ constexpr int kAutoLLAllreduceBytes = 65536, kAutoLLReduceBytes = 262144;
 // barrier-framed NVLS kernel (native forms) it is ahead up to 8 MiB (1 MiB: 13 vs 18 us, 4 MiB: 22 vs 25-26, 8 MiB: 34-36 vs
 // 35-36); against two-shot by peer loads (fp32 / fp64 min and max, which travel as 32- / 64-bit integer keys) up to 32 MiB
 // (fp32: 16 MiB 60 vs 63 us) and 8 MiB (fp64: 38 vs 46; 16 MiB 68 vs 64).
+constexpr int kAutoNvlsKeys = 0;
 constexpr int kAutoPostedMaxBytes = 8 << 20, kAutoPostedKey4MaxBytes = 32 << 20, kAutoPostedKey8MaxBytes = 8 << 20;
 
 b2r_algo_t select_algo_cached(int is_allreduce, uint64_t bytes, b2r_dtype_t dtype, b2r_op_t op, int nranks, int has_multicast, uint64_t ll_max,
@@ -200,6 +208,8 @@ b2r_algo_t select_algo_cached(int is_allreduce, uint64_t bytes, b2r_dtype_t dtyp
   if (auto_ring && !is_allreduce && nranks > 2 && bytes >= (auto_ring << 20)) return B2R_ALGO_RING;
   const bool switch_ok = has_multicast && nranks >= 4 && !B2R_ENV_INT("B2R_DISABLE_NVLS", 0);
   const bool nvls_ok = switch_ok && nvls_supported(dtype, op);
+  // fp32 / fp64 min and max through the switch as integer keys (one extra local pass to encode): B2R_AUTO_NVLS_KEYS=0 keeps them on peer loads
+  const bool keyed_ok = switch_ok && nvls_keyed(dtype, op) && B2R_ENV_INT("B2R_AUTO_NVLS_KEYS", kAutoNvlsKeys);
   // push (stores only, two hops): from how many MiB on it replaces the pulls / the switch; 0 = never. Three crossovers:
   //   B2R_AUTO_PUSH_REDUCE_MB        reduce-to-root of a (dtype, op) without a multimem form (fp32 / fp64 min and max)
   //   B2R_AUTO_PUSH_ALLREDUCE_MB     allreduce of the same
@@ -222,7 +232,7 @@ b2r_algo_t select_algo_cached(int is_allreduce, uint64_t bytes, b2r_dtype_t dtyp
   // 32-bit integers through the switch collapse for reduce-to-root at >= 1 GiB on 8 GPUs (2.1-4.8 ms at 1 GiB where fp32 needs 2.0 and
   // 256 MiB is on par: 4-byte multimem loads AND 4-byte stores to the root); the store-forwarding ring is steady there (2.04 ms)
   if (nvls_ok && !is_allreduce && dtype == B2R_INT32 && bytes >= (512ull << 20)) return B2R_ALGO_RING;
-  if (nvls_ok) return B2R_ALGO_NVLS;
+  if (nvls_ok || keyed_ok) return B2R_ALGO_NVLS;
   if (!is_allreduce && nranks == 2) return B2R_ALGO_ONESHOT;
   // One-shot reads the WHOLE message from every peer: fine for two GPUs or tiny messages, hopeless beyond.
   const uint64_t oneshot_max = (uint64_t)std::max(0, B2R_ENV_INT("B2R_ONESHOT_MAX_KB", nranks <= 2 ? 512 : 16)) << 10;
@@ -285,7 +295,8 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
   if (algo == B2R_ALGO_AUTO) algo = select_algo_cached(is_all ? 1 : 0, total_bytes, dtype, op, P, c0->has_mc ? 1 : 0, ll_limit(c0), posted_slot_bytes(c0));
   if (algo == B2R_ALGO_NVLS) {
     if (!c0->has_mc) return fail(B2R_ERR_UNSUPPORTED, "NVLS requested but this communicator has no multicast mapping");
-    if (!nvls_supported(dtype, op)) return fail(B2R_ERR_UNSUPPORTED, "NVLS has no %s %s instruction", b2r_dtype_name(dtype), b2r_op_name(op));
+    if (!nvls_supported(dtype, op) && !nvls_keyed(dtype, op))
+      return fail(B2R_ERR_UNSUPPORTED, "NVLS has no %s %s instruction", b2r_dtype_name(dtype), b2r_op_name(op));
   }
   int kind = algo == B2R_ALGO_ONESHOT ? kCollOneshot : algo == B2R_ALGO_TWOSHOT ? kCollTwoshot : algo == B2R_ALGO_TREE ? kCollTree
              : algo == B2R_ALGO_PUSH ? kCollPush : algo == B2R_ALGO_RING ? kCollRing : algo == B2R_ALGO_LL ? kCollLL
@@ -314,6 +325,8 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
   const uint64_t work_elems = (c0->work_bytes / 16) * 16 / esz;
   uint64_t chunk = chunk_elems;
   if (kind == kCollTree) chunk = std::min<uint64_t>(chunk_elems, work_elems);
+  const bool keyed = kind == kCollNvls && nvls_keyed(dtype, op);  // the encoded copy of a piece lives in the work region
+  if (keyed) chunk = std::min<uint64_t>(chunk_elems, keyed_bytes(c0) / esz);
   if (kind == kCollPosted) chunk = count;  // like LL: peers' buffers are never touched, nothing is staged per chunk
   if (kind == kCollPush) {
     const uint64_t W = is_all ? P : P - 1;
@@ -378,7 +391,17 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
         ll_set_layout(A, lay);
         continue;
       }
-      int64_t soff = c->heap_offset(send, bytes);
+      char* const key_stage = c->stage_work() + keyed_off(c);
+      int64_t soff = keyed ? (int64_t)(key_stage - c->my_heap()) : c->heap_offset(send, bytes);
+      if (keyed) {  // any readable device pointer will do: the switch reads the encoded copy, never the send buffer itself
+        B2R_REQUIRE(n == 1, "keyed NVLS needs a multicast mapping, which loopback groups do not have");
+        const uint64_t nunits = bytes / esz;
+        const int ethreads = 512;
+        const int ectas = (int)std::max<uint64_t>(1, std::min<uint64_t>((nunits * esz / 16 + ethreads * 4 - 1) / (ethreads * 4), (uint64_t)c->sm_count * 4));
+        if (esz == 4) encode_keys_kernel<4><<<ectas, ethreads, 0, rc[i].stream>>>(send, key_stage, nunits);
+        else encode_keys_kernel<8><<<ectas, ethreads, 0, rc[i].stream>>>(send, key_stage, nunits);
+        B2R_CUDA_CHECK(cudaGetLastError());
+      }
       int64_t roff = (gets_result && recv) ? c->heap_offset(recv, bytes) : -1;
       // in place is only safe zero-copy for two-shot / NVLS (a slice is read and written by its single owner)
       const bool inplace_hazard = (send == recv) && (kind == kCollOneshot || kind == kCollTree);
@@ -403,7 +426,7 @@ b2r_status_t run_collective(RankCall* rc, int n, int kind_call, uint64_t count, 
       c->epoch += 8;  // start + end + up to 4 tree rounds, rounded up; same increment on every rank
       if (kind == kCollPush || kind == kCollRing) A.seq = ++c->push_seq;
     }
-    const Shape shape = coll_shape(c0, kind, bytes, n, dtype == B2R_INT32 ? 4 : (dtype == B2R_FLOAT64 ? 8 : 16));
+    const Shape shape = coll_shape(c0, kind, bytes, n, (dtype == B2R_INT32 || (keyed && dtype == B2R_FLOAT32)) ? 4 : (dtype == B2R_FLOAT64 ? 8 : 16));
     int ctas = shape.ctas;
     int threads = shape.threads;
     if (kind == kCollLL) {

@@ -515,6 +515,87 @@ struct Nvls {
   __device__ static void ld_reduce(const char*, uint32_t*) {}
   __device__ static void st(char*, const uint32_t*) {}
 };
+// fp32 / fp64 min and max have no multimem form, but signed-integer min / max do, and IEEE values order like the integers
+// k = b ^ ((b >> 31) & 0x7fff...) (the map is its own inverse; -0 orders below +0, a NaN beyond the infinity of its sign). The host
+// stages the send buffer as keys (encode_keys_kernel, a local copy into the work region), the switch reduces the keys, and the
+// value is decoded before it is stored — so these specialisations read KEYS and write VALUES.
+template <int D, int O>
+struct NvlsKeyed {
+  static constexpr bool value = (D == B2R_FLOAT32 || D == B2R_FLOAT64) && O != B2R_SUM;
+};
+__device__ __forceinline__ uint32_t key32(uint32_t b) { return b ^ ((uint32_t)((int32_t)b >> 31) & 0x7fffffffu); }
+__device__ __forceinline__ void key64(uint32_t& lo, uint32_t& hi) {
+  const uint32_t m = (uint32_t)((int32_t)hi >> 31);
+  lo ^= m;
+  hi ^= m & 0x7fffffffu;
+}
+#define B2R_NVLS_KEY32(OP, PTXOP)                                                                                           \
+  template <>                                                                                                               \
+  struct Nvls<B2R_FLOAT32, OP> {                                                                                            \
+    static constexpr bool kSupported = true;                                                                                \
+    static constexpr int kBytes = 4;                                                                                        \
+    __device__ __forceinline__ static void ld_reduce(const char* p, uint32_t* w) {                                          \
+      asm volatile("multimem.ld_reduce.relaxed.sys.global." PTXOP " %0, [%1];" : "=r"(w[0]) : "l"(p) : "memory");           \
+      w[0] = key32(w[0]);                                                                                                   \
+    }                                                                                                                       \
+    __device__ __forceinline__ static void st(char* p, const uint32_t* w) {                                                 \
+      asm volatile("multimem.st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(w[0]) : "memory");                          \
+    }                                                                                                                       \
+  };
+B2R_NVLS_KEY32(B2R_MIN, "min.s32")
+B2R_NVLS_KEY32(B2R_MAX, "max.s32")
+#undef B2R_NVLS_KEY32
+#define B2R_NVLS_KEY64(OP, PTXOP)                                                                                           \
+  template <>                                                                                                               \
+  struct Nvls<B2R_FLOAT64, OP> {                                                                                            \
+    static constexpr bool kSupported = true;                                                                                \
+    static constexpr int kBytes = 8;                                                                                        \
+    __device__ __forceinline__ static void ld_reduce(const char* p, uint32_t* w) {                                          \
+      unsigned long long d;                                                                                                 \
+      asm volatile("multimem.ld_reduce.relaxed.sys.global." PTXOP " %0, [%1];" : "=l"(d) : "l"(p) : "memory");              \
+      w[0] = (uint32_t)(d & 0xffffffffull);                                                                                 \
+      w[1] = (uint32_t)(d >> 32);                                                                                           \
+      key64(w[0], w[1]);                                                                                                    \
+    }                                                                                                                       \
+    __device__ __forceinline__ static void st(char* p, const uint32_t* w) {                                                 \
+      const unsigned long long d = (unsigned long long)w[0] | ((unsigned long long)w[1] << 32);                             \
+      asm volatile("multimem.st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(d) : "memory");                             \
+    }                                                                                                                       \
+  };
+B2R_NVLS_KEY64(B2R_MIN, "min.s64")
+B2R_NVLS_KEY64(B2R_MAX, "max.s64")
+#undef B2R_NVLS_KEY64
+
+// The staging pass of the keyed forms: dst[i] = key(src[i]) over `nunits` units of W bytes (4 or 8); 16-byte vectors when both
+// pointers allow it. Purely local.
+template <int W>
+__global__ void __launch_bounds__(512) encode_keys_kernel(const char* __restrict__ src, char* __restrict__ dst, unsigned long long nunits) {
+  const unsigned long long tid = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x, nthreads = (unsigned long long)gridDim.x * blockDim.x;
+  unsigned long long done = 0;
+  if ((((unsigned long long)src | (unsigned long long)dst) & 15ull) == 0) {
+    const unsigned long long nvec = nunits * W / 16;
+    for (unsigned long long v = tid; v < nvec; v += nthreads) {
+      uint4 x = *reinterpret_cast<const uint4*>(src + v * 16);
+      if (W == 4) {
+        x.x = key32(x.x); x.y = key32(x.y); x.z = key32(x.z); x.w = key32(x.w);
+      } else {
+        key64(x.x, x.y);
+        key64(x.z, x.w);
+      }
+      *reinterpret_cast<uint4*>(dst + v * 16) = x;
+    }
+    done = nvec * (16 / W);
+  }
+  for (unsigned long long i = done + tid; i < nunits; i += nthreads) {
+    if (W == 4) {
+      *reinterpret_cast<uint32_t*>(dst + i * 4) = key32(*reinterpret_cast<const uint32_t*>(src + i * 4));
+    } else {
+      uint2 x = *reinterpret_cast<const uint2*>(src + i * 8);
+      key64(x.x, x.y);
+      *reinterpret_cast<uint2*>(dst + i * 8) = x;
+    }
+  }
+}
 template <>
 struct Nvls<B2R_FLOAT32, B2R_SUM> {
   static constexpr bool kSupported = true;
