@@ -186,6 +186,7 @@ constexpr int kAutoLLAllreduceBytes = 65536, kAutoLLReduceBytes = 262144;
 // 35-36); against two-shot by peer loads (fp32 / fp64 min and max, which travel as 32- / 64-bit integer keys) up to 32 MiB
 // (fp32: 16 MiB 60 vs 63 us) and 8 MiB (fp64: 38 vs 46; 16 MiB 68 vs 64).
 constexpr int kAutoNvlsKeys = 0;
+constexpr int kAutoPosted2GpuMaxBytes = 2 << 20;
 constexpr int kAutoPostedMaxBytes = 8 << 20, kAutoPostedKey4MaxBytes = 32 << 20, kAutoPostedKey8MaxBytes = 8 << 20;
 
 b2r_algo_t select_algo_cached(int is_allreduce, uint64_t bytes, b2r_dtype_t dtype, b2r_op_t op, int nranks, int has_multicast, uint64_t ll_max,
@@ -233,7 +234,15 @@ b2r_algo_t select_algo_cached(int is_allreduce, uint64_t bytes, b2r_dtype_t dtyp
   // 256 MiB is on par: 4-byte multimem loads AND 4-byte stores to the root); the store-forwarding ring is steady there (2.04 ms)
   if (nvls_ok && !is_allreduce && dtype == B2R_INT32 && bytes >= (512ull << 20)) return B2R_ALGO_RING;
   if (nvls_ok || keyed_ok) return B2R_ALGO_NVLS;
-  if (!is_allreduce && nranks == 2) return B2R_ALGO_ONESHOT;
+  if (!is_allreduce && nranks == 2) {
+    // Two GPUs: the root pulls (one-shot: 630 GB/s at 64 MiB, parity with NCCL from 4 MiB), but between the LL range and ~2 MiB its two
+    // barriers make it 18.5-19.3 us at 1 MiB against NCCL's 10.8-12.3 (profiles/collectives_2_4gpu.md). The posted reduce has no
+    // barrier: 11.4-12.9 us per call at 1 MiB on 4 and 8 GPUs whatever the type. Verified on 2 GPUs (tests/dist_worker.py), its timing
+    // there is inferred from those floors, not measured: B2R_AUTO_POSTED_2GPU_MAX_BYTES=0 restores the one-shot.
+    const uint64_t cut2 = (uint64_t)std::max(0, B2R_ENV_INT("B2R_AUTO_POSTED_2GPU_MAX_BYTES", kAutoPosted2GpuMaxBytes));
+    if (has_multicast && !B2R_ENV_INT("B2R_DISABLE_NVLS", 0) && bytes <= std::min(cut2, posted_max)) return B2R_ALGO_POSTED;
+    return B2R_ALGO_ONESHOT;
+  }
   // One-shot reads the WHOLE message from every peer: fine for two GPUs or tiny messages, hopeless beyond.
   const uint64_t oneshot_max = (uint64_t)std::max(0, B2R_ENV_INT("B2R_ONESHOT_MAX_KB", nranks <= 2 ? 512 : 16)) << 10;
   if (bytes <= oneshot_max) return B2R_ALGO_ONESHOT;

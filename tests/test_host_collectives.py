@@ -66,7 +66,7 @@ def test_int_sum_wraps_across_ranks():
     assert (got == want).all()
 
 
-POSTED_KNOBS = ("B2R_AUTO_POSTED_MAX_BYTES", "B2R_AUTO_POSTED_KEY_MAX_BYTES_8", "B2R_AUTO_POSTED_KEY_MAX_BYTES_4")
+POSTED_KNOBS = ("B2R_AUTO_POSTED_MAX_BYTES", "B2R_AUTO_POSTED_KEY_MAX_BYTES_8", "B2R_AUTO_POSTED_KEY_MAX_BYTES_4", "B2R_AUTO_POSTED_2GPU_MAX_BYTES")
 
 
 def test_algo_selection_is_pure_and_sensible():
@@ -87,7 +87,9 @@ def test_algo_selection_is_pure_and_sensible():
     assert sel(0, 32 << 20, _lib.FLOAT32, _lib.MAX, 4, 1) == _lib.ALGO_POSTED and sel(0, (32 << 20) + 4, _lib.FLOAT32, _lib.MAX, 4, 1) == _lib.ALGO_TWOSHOT
     assert sel(0, 8 << 20, _lib.FLOAT64, _lib.MIN, 8, 1) == _lib.ALGO_POSTED and sel(0, 16 << 20, _lib.FLOAT64, _lib.MIN, 8, 1) == _lib.ALGO_TWOSHOT
     assert sel(0, 1 << 20, _lib.FLOAT32, _lib.MIN, 8, 0) == _lib.ALGO_TWOSHOT  # no switch, no posted
-    assert sel(0, 1 << 20, _lib.FLOAT32, _lib.SUM, 2, 1) == _lib.ALGO_ONESHOT
+    assert sel(0, 1 << 20, _lib.FLOAT32, _lib.SUM, 2, 1) == _lib.ALGO_POSTED   # two GPUs: between the LL range and 2 MiB (the one-shot's barriers cost more than its pull saves)
+    assert sel(0, 1 << 20, _lib.FLOAT64, _lib.MIN, 2, 1) == _lib.ALGO_POSTED
+    assert sel(0, (2 << 20) + 4, _lib.FLOAT32, _lib.SUM, 2, 1) == _lib.ALGO_ONESHOT and sel(0, 1 << 20, _lib.FLOAT32, _lib.SUM, 2, 0) == _lib.ALGO_ONESHOT
     assert sel(1, 1 << 20, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS     # reduce-to-root only
     assert sel(0, 1 << 28, _lib.FLOAT32, _lib.SUM, 8, 1) == _lib.ALGO_NVLS
     assert sel(0, 1 << 30, _lib.FLOAT32, _lib.MIN, 8, 1) == _lib.ALGO_TWOSHOT
