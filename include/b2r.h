@@ -247,7 +247,11 @@ b2r_status_t b2r_comm_check(b2r_comm_t comm, void* stream);
  * NULL elsewhere). sendbuf is not modified unless sendbuf == recvbuf (in place). All ranks call in the same
  * order with the same count/dtype/op/root/algo. fp sums are deterministic on the P2P paths (bit-reproducible run to run):
  * ascending rank order for one-shot / two-shot / push / LL, chain order (farthest rank first) for the ring, pairwise order
- * rotated by the root for the tree; the NVLS path's order is defined by the switch. */
+ * rotated by the root for the tree; the NVLS and posted paths' order is defined by the switch (integers and min / max are exact
+ * on every path).
+ * Stream capture: the element-wise collectives number their calls on the HOST (barrier epochs, LL / posted call numbers are kernel
+ * arguments), so a captured graph that contains one must not be replayed — the replay would reuse call numbers its peers have
+ * already seen. Only b2r_reduce_scalar_sharded keeps its call number on the device and replays correctly. */
 b2r_status_t b2r_reduce(const void* sendbuf, void* recvbuf, uint64_t count, b2r_dtype_t dtype, b2r_op_t op, int root,
                         b2r_comm_t comm, void* stream);
 b2r_status_t b2r_allreduce(const void* sendbuf, void* recvbuf, uint64_t count, b2r_dtype_t dtype, b2r_op_t op,
