@@ -130,7 +130,7 @@ def read_result_file(path: str):
 
 
 def write_svg(series: dict, out_path: str, title: str, xlabel: str = "GPUs (ranks)", ylabel: str = "bandwidth of the whole problem [GiB/s]",
-              hlines: dict | None = None, logy: bool = True, width: int = 900, height: int = 560) -> str:
+              hlines: dict | None = None, logy: bool = True, width: int = 900, height: int = 560, xlabels: dict | None = None) -> str:
     """The reference's figures (mpi/makePlots.gp:21-39 -> int.eps / double.eps) rendered without gnuplot or matplotlib, neither
     of which is on the image: a self-contained SVG line chart. `series` = {label: [(x, y), ...]} drawn as lines with markers
     over a categorical x axis (the distinct x values, like the reference's 64 / 256 / 1024 ranks); `hlines` = {label: y} drawn
@@ -167,7 +167,7 @@ def write_svg(series: dict, out_path: str, title: str, xlabel: str = "GPUs (rank
         o.append(f'<line x1="{ml}" y1="{y:.1f}" x2="{ml + pw}" y2="{y:.1f}" stroke="#ddd"/>')
         o.append(f'<text x="{ml - 8}" y="{y + 4:.1f}" text-anchor="end">{t:g}</text>')
     for x in xs:
-        o.append(f'<text x="{fx(x):.1f}" y="{mt + ph + 20}" text-anchor="middle">{esc(x)}</text>')
+        o.append(f'<text x="{fx(x):.1f}" y="{mt + ph + 20}" text-anchor="middle">{esc((xlabels or {}).get(x, x))}</text>')
     o.append(f'<text x="{ml + pw / 2}" y="{height - 14}" text-anchor="middle">{esc(xlabel)}</text>')
     o.append(f'<text transform="translate(18,{mt + ph / 2}) rotate(-90)" text-anchor="middle">{esc(ylabel)}</text>')
     ly = mt + 10
@@ -217,6 +217,62 @@ def write_figures(results_dir: str, single_gpu: dict | None = None, dtypes=("INT
     return written
 
 
+def _human_bytes(b: int) -> str:
+    for unit, sh in (("GiB", 30), ("MiB", 20), ("KiB", 10)):
+        if b >= 1 << sh and b % (1 << sh) == 0:
+            return f"{b >> sh} {unit}"
+    return f"{b} B"
+
+
+def read_sweep_csv(paths, overrides=()) -> dict:
+    """Rows of `bench_collective --sweep --csv=` / `nccl_bench --sweep --csv=` (impl, coll, dtype, op, algo, gpus, bytes, us,
+    algbw, busbw[, label, knobs]) -> {(gpus, coll, impl, dtype, op): {bytes: (us, busbw)}}. Later files win over earlier
+    ones; `overrides` are (path, label[, max_bytes]) tuples of `--plan` CSVs whose rows with that label (up to max_bytes) replace
+    the b2r row of the same (coll, dtype, op, gpus, bytes) — how re-measured rows enter a figure."""
+    import csv
+
+    out: dict = {}
+
+    def put(r, impl):
+        key = (int(r[5]), r[1], impl, r[2], r[3])
+        out.setdefault(key, {})[int(r[6])] = (float(r[7]), float(r[9]))
+
+    for path in paths:
+        with open(path) as f:
+            for r in csv.reader(f):
+                if len(r) >= 10 and r[0] in ("b2r", "nccl"):
+                    put(r, r[0])
+    for ov in overrides:
+        path, label = ov[0], ov[1]
+        max_bytes = int(ov[2]) if len(ov) > 2 else None  # e.g. up to where AUTO picks the algorithm the plan rows forced
+        with open(path) as f:
+            for r in csv.reader(f):
+                if len(r) >= 11 and r[0] == "b2r" and r[10] == label and (int(r[5]), r[1], "b2r", r[2], r[3]) in out:
+                    if max_bytes is None or int(r[6]) <= max_bytes:
+                        put(r, "b2r")
+    return out
+
+
+def write_sweep_figures(rows: dict, out_dir: str, prefix: str = "sweep") -> list:
+    """One SVG per (GPU count, collective): bus bandwidth over message size, this library and NCCL, one pair of lines per
+    (dtype, op). The figure BASELINE config 5 asks for; the reference has no counterpart (its sweep is over ranks only)."""
+    os.makedirs(out_dir, exist_ok=True)
+    written = []
+    for gpus, coll in sorted({(k[0], k[1]) for k in rows}):
+        series = {}
+        for (g, c, impl, dt, op), pts in sorted(rows.items()):
+            if g != gpus or c != coll:
+                continue
+            name = ("b2r " if impl == "b2r" else "NCCL ") + f"{dt} {op}"
+            series[name] = [(b, bw) for b, (_, bw) in sorted(pts.items())]
+        sizes = sorted({b for pts in series.values() for b, _ in pts})
+        path = os.path.join(out_dir, f"{prefix}_{coll}_{gpus}gpu.svg")
+        written.append(write_svg(series, path, f"{coll} on {gpus} GPUs: bus bandwidth over message size (b2r AUTO vs NCCL)",
+                                 xlabel="message size per rank", ylabel="bus bandwidth [GB/s]", width=1200, height=620,
+                                 xlabels={b: _human_bytes(b) for b in sizes}))
+    return written
+
+
 def main(argv=None):
     ap = argparse.ArgumentParser(description=__doc__, formatter_class=argparse.RawDescriptionHelpFormatter)
     sub = ap.add_subparsers(dest="cmd", required=True)
@@ -230,10 +286,18 @@ def main(argv=None):
     g = sub.add_parser("figures", help="int.svg / double.svg rendered in pure Python (no gnuplot needed)")
     g.add_argument("--results", default="results")
     g.add_argument("--single-gpu", default=None)
+    w = sub.add_parser("sweeps", help="bus bandwidth over message size, b2r vs NCCL, one SVG per GPU count and collective")
+    w.add_argument("csv", nargs="+", help="sweep CSVs of bench_collective / nccl_bench")
+    w.add_argument("--override", action="append", default=[], metavar="PLAN_CSV:LABEL[:MAX_BYTES]", help="rows of a --plan CSV that replace re-measured b2r rows")
+    w.add_argument("--out", default="results/sweeps")
     args = ap.parse_args(argv)
     if args.cmd == "aggregate":
         for (dt, op), path in aggregate(args.collected, args.out).items():
             print(f"{dt} {op} -> {path}")
+    elif args.cmd == "sweeps":
+        ov = [tuple(o.split(":")) for o in args.override]
+        for path in write_sweep_figures(read_sweep_csv(args.csv, ov), args.out):
+            print(path)
     elif args.cmd == "figures":
         sg = single_gpu_lines(args.single_gpu) if args.single_gpu else {}
         for path in write_figures(args.results, sg):

@@ -124,6 +124,40 @@ def test_svg_figures_are_written_without_gnuplot(tmp_path):
         R.write_svg({}, str(tmp_path / "empty.svg"), "nothing")
 
 
+def test_sweep_figures_from_harness_csv(tmp_path):
+    """BASELINE config 5 as figures: rows of `bench_collective --sweep --csv` / `nccl_bench --sweep --csv` -> one SVG per (GPU count,
+    collective) with a b2r and an NCCL line per (dtype, op); re-measured plan rows replace b2r rows up to a size limit."""
+    import xml.dom.minidom
+
+    from cuda_mpi_reductions_b200.utils import results as R
+
+    sizes = [1 << 10, 1 << 20, 1 << 30]
+    base = tmp_path / "sweep.csv"
+    with open(base, "w") as f:
+        for impl, scale in (("b2r", 2.0), ("nccl", 1.0)):
+            for coll in ("reduce", "allreduce"):
+                for dt in ("INT", "BF16"):
+                    for b in sizes:
+                        us = b / 1e3 / scale + 10
+                        f.write(f"{impl},{coll},{dt},SUM,{'auto' if impl == 'b2r' else 'nccl'},8,{b},{us:.3f},{b / us * 1e-3:.3f},{b / us * 1e-3:.3f}\n")
+    plan = tmp_path / "plan.csv"
+    plan.write_text(f"b2r,reduce,INT,SUM,posted,8,{1 << 20},5.000,209.715,209.715,R.posted,\n"
+                    f"b2r,reduce,INT,SUM,posted,8,{1 << 30},5.000,1.000,1.000,R.posted,\n"      # beyond the limit: ignored
+                    f"b2r,reduce,FLOAT,MIN,posted,8,{1 << 20},5.000,1.000,1.000,R.posted,\n"     # no such series in the sweep: ignored
+                    f"b2r,reduce,INT,SUM,nvls,8,{1 << 20},9.000,1.000,1.000,Q.base,\n")          # another label: ignored
+    rows = R.read_sweep_csv([str(base)], [(str(plan), "R.posted", str(8 << 20))])
+    assert rows[(8, "reduce", "b2r", "INT", "SUM")][1 << 20] == (5.0, 209.715)
+    assert rows[(8, "reduce", "b2r", "INT", "SUM")][1 << 30][0] != 5.0
+    assert (8, "reduce", "b2r", "FLOAT", "MIN") not in rows
+    written = R.write_sweep_figures(rows, str(tmp_path / "figs"))
+    assert sorted(os.path.basename(w) for w in written) == ["sweep_allreduce_8gpu.svg", "sweep_reduce_8gpu.svg"]
+    for w in written:
+        doc = xml.dom.minidom.parse(w)
+        assert len(doc.getElementsByTagName("path")) == 4  # b2r + NCCL for two dtypes
+        text = open(w).read()
+        assert ">1 KiB<" in text and ">1 MiB<" in text and ">1 GiB<" in text and "NCCL BF16 SUM" in text
+
+
 def test_native_harness_defaults_are_the_reference_workloads():
     """models/workloads.py is the single table of the reference's workload constants; the C++ harnesses cannot import it, so
     their flag defaults are checked against it here (and bench.py loads it by path)."""
