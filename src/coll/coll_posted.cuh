@@ -64,7 +64,7 @@ struct PostedKey32 {
   __device__ __forceinline__ static V16 code(const V16& v) {
     V16 k;
 #pragma unroll
-    for (int j = 0; j < 4; ++j) k.w[j] = v.w[j] ^ ((uint32_t)((int32_t)v.w[j] >> 31) & 0x7fffffffu);
+    for (int j = 0; j < 4; ++j) k.w[j] = key32(v.w[j]);
     return k;
   }
 };
@@ -74,13 +74,9 @@ struct PostedKey64 {
   static constexpr int kBytes = 8;
   __device__ __forceinline__ static void ld_reduce(const char* p, uint32_t* w) { NvlsS64<O>::ld_reduce(p, w); }
   __device__ __forceinline__ static V16 code(const V16& v) {  // little endian: w[1], w[3] hold the sign and the high bits
-    V16 k;
-#pragma unroll
-    for (int j = 0; j < 4; j += 2) {
-      const uint32_t m = (uint32_t)((int32_t)v.w[j + 1] >> 31);
-      k.w[j] = v.w[j] ^ m;
-      k.w[j + 1] = v.w[j + 1] ^ (m & 0x7fffffffu);
-    }
+    V16 k = v;
+    key64(k.w[0], k.w[1]);
+    key64(k.w[2], k.w[3]);
     return k;
   }
 };
