@@ -57,7 +57,8 @@ def collectives_section(comm, dist, dev, rank: int, world: int, sizes=(64 << 20,
     nccl_recv = torch.empty(big // 4, dtype=torch.float32, device=dev)
     cases = [("reduce", torch.float32, s) for s in sizes] + [("allreduce", torch.float32, s) for s in sizes]
     cases += [("reduce", torch.int32, sizes[0]), ("allreduce", torch.int32, sizes[0])]
-    for coll, dtype, nbytes in cases:
+
+    def measure(coll, dtype, nbytes):
         n = nbytes // 4
         x, y = send[:n].view(dtype), recv[:n].view(dtype)
         nx, ny = nccl_send[:n].view(dtype), nccl_recv[:n].view(dtype)
@@ -93,19 +94,34 @@ def collectives_section(comm, dist, dev, rank: int, world: int, sizes=(64 << 20,
         # ---- timing (NCCL in place on ny: its values grow, which does not change what it moves)
         ms_b2r = _max_over_ranks(dist, _timed(ours, iters, 3, comm.barrier), dev)
         ms_nccl = _max_over_ranks(dist, _timed(theirs, iters, 3, comm.barrier), dev)
-        launches += iters
         factor = 2.0 * (world - 1) / world if coll == "allreduce" else 1.0  # nccl-tests bus-bandwidth convention
         bus_b2r = nbytes / (ms_b2r * 1e-3) * 1e-9 * factor
         bus_nccl = nbytes / (ms_nccl * 1e-3) * 1e-9 * factor
-        rows.append({"coll": coll, "dtype": str(dtype).replace("torch.", ""), "op": "sum", "bytes": nbytes, "iters": iters,
-                     "algo": comm.select_algo(nbytes, dtype, "sum", allreduce=(coll == "allreduce")),
-                     "b2r_us": ms_b2r * 1e3, "nccl_us": ms_nccl * 1e3, "b2r_busbw_gbs": bus_b2r, "nccl_busbw_gbs": bus_nccl,
-                     "ratio": bus_b2r / bus_nccl if bus_nccl > 0 else None,
-                     "b2r_check": "PASSED" if flags[0].item() else "FAILED", "nccl_check": "PASSED" if flags[1].item() else "FAILED"})
-    return {"rows": rows, "timed_launches_per_gpu": launches,
+        return iters, {"coll": coll, "dtype": str(dtype).replace("torch.", ""), "op": "sum", "bytes": nbytes, "iters": iters,
+                       "algo": comm.select_algo(nbytes, dtype, "sum", allreduce=(coll == "allreduce")),
+                       "b2r_us": ms_b2r * 1e3, "nccl_us": ms_nccl * 1e3, "b2r_busbw_gbs": bus_b2r, "nccl_busbw_gbs": bus_nccl,
+                       "ratio": bus_b2r / bus_nccl if bus_nccl > 0 else None,
+                       "b2r_check": "PASSED" if flags[0].item() else "FAILED", "nccl_check": "PASSED" if flags[1].item() else "FAILED"}
+
+    for coll, dtype, nbytes in cases:
+        iters, row = measure(coll, dtype, nbytes)
+        launches += iters
+        rows.append(row)
+    # One mid-size row after the ones above (a failure here leaves them standing): reduce-to-root of 4 MiB, where AUTO takes the
+    # posted reduce from 4 GPUs up. Both arms work out of L2 at this size (send + recv = 8 MiB), and each call is long enough
+    # (~20 us) for the host side of either library to stay ahead of the GPU.
+    mid_error = None
+    try:
+        iters, row = measure("reduce", torch.float32, min(4 << 20, big))
+        row["l2_resident"] = True
+        launches += iters
+        rows.append(row)
+    except Exception as e:  # noqa: BLE001
+        mid_error = f"{type(e).__name__}: {e}"
+    return {"rows": rows, "timed_launches_per_gpu": launches, "mid_size_row_error": mid_error,
             "buffers": "b2r: symmetric-heap tensors (zero copy); NCCL: ordinary torch tensors, in place",
             "busbw": "allreduce: algbw x 2(P-1)/P; reduce: algbw (nccl-tests convention)",
-            "timing": "CUDA events after a device-side barrier, 3 warm-up calls, max over ranks; messages >= 64 MiB per rank (> L2 with send+recv)"}
+            "timing": "CUDA events after a device-side barrier, 3 warm-up calls, max over ranks; messages >= 64 MiB per rank (> L2 with send+recv), except the row marked l2_resident"}
 
 
 def config4_section(comm, dist, dev, rank: int, world: int, total_elems: int = 1 << 27, steps: int = 20) -> dict:
